@@ -1,0 +1,183 @@
+"""Pins the oracle: against the reference's own run (tests/golden/ref_*.npz), against the ATen
+known-answer vectors (tests/golden/aten_*.npz) and against the installed torch CPU ops live."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+from oracle import c_oracle
+from oracle import mercury_oracle as orc
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+class ReplayNet(nn.Module):
+    """Returns the logits the reference's model produced, batch by batch."""
+
+    def __init__(self, logits, batch=32):
+        super().__init__()
+        self.logits = torch.from_numpy(np.asarray(logits))
+        self.batch = batch
+        self.pos = 0
+
+    def forward(self, x):
+        out = self.logits[self.pos:self.pos + x.shape[0]]
+        self.pos += x.shape[0]
+        return out
+
+
+def _pool_batches(g):
+    """The loader of make_golden.synthetic_pool, rebuilt from its seed."""
+    gen = torch.Generator().manual_seed(int(g["pool_seed"]))
+    batches = []
+    for b in range(10):
+        data = torch.rand(32, 3, 32, 32, generator=gen)
+        label = torch.randint(0, 10, (32,), generator=gen)
+        idx = torch.arange(b * 32, (b + 1) * 32) + 1000
+        batches.append((idx, data, label))
+    return batches
+
+
+@pytest.mark.parametrize("name", ["ref_update_samples_linear.npz", "ref_update_samples_resnet18.npz"])
+def test_faithful_restatement_matches_reference_run(golden_dir, name):
+    g = _load(golden_dir, name)
+    batches = _pool_batches(g)
+    assert np.array_equal(torch.cat([b[2] for b in batches]).numpy(), g["pool_labels"])
+    ema = orc.EMAverage()
+    torch.manual_seed(int(g["rng_seed"]))
+    for call in range(2):
+        net = ReplayNet(g[f"call{call}_logits"])
+        probs, data, label, index, avg = orc.update_samples_faithful(net, iter(batches), int(g["draw_batch"]), ema)
+        assert np.array_equal(index.numpy(), g[f"call{call}_index"])
+        assert np.array_equal(label.numpy(), g[f"call{call}_label"])
+        np.testing.assert_allclose(probs.numpy(), g[f"call{call}_probs"], rtol=1e-6)
+        np.testing.assert_allclose(data.double().sum(dim=(1, 2, 3)).numpy(), g[f"call{call}_data_rowsum"], rtol=1e-12)
+        np.testing.assert_allclose(float(avg), g[f"call{call}_avg"], rtol=1e-6)
+        np.testing.assert_allclose(float(ema.value), g[f"call{call}_ema"], rtol=1e-6)
+
+
+def test_explicit_uniform_draw_matches_reference_run(golden_dir):
+    """The last of the 10 draws of each call, re-made from explicit uniforms."""
+    g = _load(golden_dir, "ref_update_samples_resnet18.npz")
+    B = int(g["draw_batch"])
+    torch.manual_seed(int(g["rng_seed"]))
+    u_all = torch.rand(20 * B, dtype=torch.float64).numpy()
+    labels = torch.from_numpy(g["pool_labels"])
+    ema = orc.EMAverage()
+    for call in range(2):
+        logits = torch.from_numpy(g[f"call{call}_logits"])
+        for k in range(1, 11):  # growing pools, EMA updated each time (pytorch_collab.py:95-112)
+            losses = orc.score(logits[:32 * k], labels[:32 * k])
+            _, _, p = orc.pool_stats(losses, ema)
+        u = u_all[(call * 10 + 9) * B:(call * 10 + 10) * B]
+        idx = orc.draw_with_replacement(p.numpy(), u)
+        assert np.array_equal(g["pool_index"][idx], g[f"call{call}_index"])
+        nprob = orc.gather_reweight(p, torch.from_numpy(idx))[0]
+        np.testing.assert_allclose(nprob.numpy(), g[f"call{call}_probs"], rtol=1e-6)
+
+
+def test_groupwise_restatement_matches_reference_run(golden_dir):
+    g = _load(golden_dir, "ref_groupwise.npz")
+    for tag in ("repl", "norepl"):
+        imp, ind, gi = g[f"{tag}_importance"], g[f"{tag}_group_indicator"], int(g[f"{tag}_group_index"])
+        member = ind == gi
+        loc = member.nonzero()[0]
+        n_group = int(member.sum())
+        torch.manual_seed(int(g["rng_seed"]))
+        ys = []
+        for _ in range(len(g[f"{tag}_yield"])):
+            u = torch.rand(n_group, dtype=torch.float64).numpy()
+            ys.append(int(loc[orc.groupwise_draw(imp[member], u)]))
+        assert ys == list(g[f"{tag}_yield"])
+    # the importance array holds the reference's CE losses of its three slices
+    losses = orc.score(torch.from_numpy(g["logits"][:192]), torch.from_numpy(g["labels"]))
+    np.testing.assert_allclose(g["repl_importance"], losses.numpy().astype(np.float64), rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("n", [17, 320, 5000, 50000])
+def test_draws_match_aten_golden(golden_dir, n):
+    g = _load(golden_dir, "aten_multinomial.npz")
+    p, seed = g[f"n{n}_p"], int(g[f"n{n}_seed"])
+    k = len(g[f"n{n}_with"])
+    u = torch.rand(k, dtype=torch.float64, generator=torch.Generator().manual_seed(seed)).numpy()
+    assert np.array_equal(orc.draw_with_replacement(p, u), g[f"n{n}_with"])
+    st, chain, cdf = c_oracle.serial_cdf(p)
+    assert st == 0 and np.array_equal(cdf, orc.serial_cdf_f32(p))
+    assert np.array_equal(c_oracle.lower_bound(cdf, u), g[f"n{n}_with"])
+    k2 = len(g[f"n{n}_without"])
+    u2 = torch.rand(n, dtype=torch.float64, generator=torch.Generator().manual_seed(seed)).numpy()
+    assert np.array_equal(orc.draw_without_replacement(p, u2, k2), g[f"n{n}_without"])
+    if n <= 5000:
+        keys, idx = c_oracle.exp_race_topk(p, u2, k2)
+        assert np.array_equal(keys, orc.exp_race_keys(p, u2).numpy())
+        assert np.array_equal(idx, g[f"n{n}_without"])
+
+
+@pytest.mark.parametrize("n,k", [(1000, 64), (200000, 256)])
+def test_draws_match_torch_live(n, k):
+    w = torch.exp(torch.randn(n, generator=torch.Generator().manual_seed(5)) * 1.5)
+    p = w / w.sum()
+    g1, g2 = torch.Generator().manual_seed(77), torch.Generator().manual_seed(77)
+    ref = torch.multinomial(p, k, True, generator=g1)
+    u = orc.uniforms_like_multinomial(k, g2)
+    assert np.array_equal(orc.draw_with_replacement(p.numpy(), u.numpy()), ref.numpy())
+    assert torch.equal(g1.get_state(), g2.get_state())
+    g1, g2 = torch.Generator().manual_seed(78), torch.Generator().manual_seed(78)
+    ref = torch.multinomial(p, k, False, generator=g1)
+    u = orc.uniforms_like_multinomial(n, g2)
+    assert np.array_equal(orc.draw_without_replacement(p.numpy(), u.numpy(), k), ref.numpy())
+
+
+@pytest.mark.parametrize("name,tol", [("c10_f32", 1e-5), ("c10_f32_wide", 1e-5), ("c1000_bf16", 1e-5),
+                                      ("c1000_f32", 1e-5), ("c32768_bf16", 1e-5), ("c33_f32", 1e-5)])
+def test_score_matches_aten_golden(golden_dir, name, tol):
+    g = _load(golden_dir, "aten_cross_entropy.npz")
+    raw, y, loss = g[f"{name}_logits"], g[f"{name}_labels"], g[f"{name}_loss"]
+    bf16 = raw.dtype == np.int16
+    x = torch.from_numpy(raw).view(torch.bfloat16) if bf16 else torch.from_numpy(raw)
+    got = orc.score(x, torch.from_numpy(y)).numpy()
+    np.testing.assert_allclose(got, loss, rtol=1e-6, atol=1e-6)
+    assert got[0] == 0.0  # ignore_index row
+    st, c_loss = c_oracle.score(raw, y, bf16=bf16)
+    assert st == 0
+    # tiny losses lose relative accuracy in fp32: relative on loss, absolute floor 1e-5
+    np.testing.assert_allclose(c_loss, g[f"{name}_loss64"], rtol=tol, atol=1e-5)
+
+
+def test_distribution_checks_have_aten_messages():
+    for bad, msg in [([0.5, -0.1], "< 0"), ([0.5, float("inf")], "infinity or NaN"), ([0.0, 0.0], "<= 0")]:
+        with pytest.raises(RuntimeError) as a:
+            torch.multinomial(torch.tensor(bad), 1, True)
+        with pytest.raises(RuntimeError) as b:
+            orc.draw_with_replacement(np.asarray(bad, dtype=np.float32), np.asarray([0.3]))
+        assert msg in str(b.value)
+        assert msg in str(a.value) or "inf, nan or element < 0" in str(a.value)
+    assert c_oracle.serial_cdf(np.asarray([0.5, -0.1], dtype=np.float32))[0] == 1
+    assert c_oracle.serial_cdf(np.asarray([0.5, np.nan], dtype=np.float32))[0] == 1  # NaN: `val >= 0` fails first
+    assert c_oracle.serial_cdf(np.asarray([0.5, np.inf], dtype=np.float32))[0] == 2
+    assert c_oracle.serial_cdf(np.asarray([0.0, 0.0], dtype=np.float32))[0] == 3
+
+
+def test_reweight_seed():
+    g = torch.Generator().manual_seed(3)
+    losses = torch.rand(64, generator=g) * 3
+    nprob = torch.rand(64, generator=g) + 0.5
+    loss, seed = orc.reweighted_loss(losses, nprob)
+    np.testing.assert_allclose(seed.numpy(), (1.0 / (64 * nprob)).numpy(), rtol=1e-6)
+    np.testing.assert_allclose(float(loss), float((losses / nprob).mean()), rtol=1e-6)
+    p = (nprob / nprob.sum()).numpy()
+    idx = np.arange(64, dtype=np.int64)
+    np_, sd = c_oracle.gather_weights(p, idx)
+    np.testing.assert_allclose(sd, 1.0 / (64 * p * 64), rtol=1e-6)
+
+
+def test_ema_matches_reference_definition():
+    e = orc.EMAverage()
+    e.update(torch.tensor(2.0))
+    assert float(e.value) == 2.0
+    e.update(torch.tensor(4.0))
+    np.testing.assert_allclose(float(e.value), 0.9 * 2.0 + 0.1 * 4.0, rtol=1e-6)
