@@ -151,11 +151,11 @@ def test_score_matches_aten_golden(golden_dir, name, tol):
 def test_distribution_checks_have_aten_messages():
     for bad, msg in [([0.5, -0.1], "< 0"), ([0.5, float("inf")], "infinity or NaN"), ([0.0, 0.0], "<= 0")]:
         with pytest.raises(RuntimeError) as a:
-            torch.multinomial(torch.tensor(bad), 1, True)
+            torch.multinomial(torch.tensor(bad), 2, True)
         with pytest.raises(RuntimeError) as b:
             orc.draw_with_replacement(np.asarray(bad, dtype=np.float32), np.asarray([0.3]))
         assert msg in str(b.value)
-        assert msg in str(a.value) or "inf, nan or element < 0" in str(a.value)
+        assert msg in str(a.value)
     assert c_oracle.serial_cdf(np.asarray([0.5, -0.1], dtype=np.float32))[0] == 1
     assert c_oracle.serial_cdf(np.asarray([0.5, np.nan], dtype=np.float32))[0] == 1  # NaN: `val >= 0` fails first
     assert c_oracle.serial_cdf(np.asarray([0.5, np.inf], dtype=np.float32))[0] == 2
