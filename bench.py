@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""Benchmark of the importance-sampling hot path (BASELINE.json metric: importance-scored +
+sampled candidates/sec and % of the HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2|cfg3|cfg1|cfg5] [--impl reference]
+
+A "step" is one pass of the hot path over one pool: score -> pool statistics -> exact CDF ->
+B draws from caller-supplied uniforms -> gather + N*p weights + backward seed.  Prints ONE JSON
+line (rank 0).  See DESIGN.md "Measurement" for what each field means.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: candidates per GPU, classes, dtype, draws, payload shape per candidate (fp32)
+    "cfg1": dict(n=50_000, c=10, dtype="f32", b=128, payload=(3, 32, 32), note="BASELINE configs[0] shape (pool 50k)"),
+    "cfg2": dict(n=1_000_000, c=10, dtype="f32", b=128, payload=(3, 32, 32), note="BASELINE configs[1]: 1M x 10 fp32"),
+    "cfg3": dict(n=1_280_000, c=1000, dtype="bf16", b=256, payload=None, note="BASELINE configs[2]: 1.28M x 1000 bf16"),
+    "cfg5": dict(n=131_072, c=32768, dtype="bf16", b=256, payload=None,
+                 note="BASELINE configs[4] row shape (32k-class bf16), 128k-candidate resident slice per GPU"),
+}
+FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md
+
+
+def algorithmic_bytes(n, c, s, b, row_bytes):
+    """logits + int64 label read once, fp32 score written once; per draw the payload
+    row read+written, label and index read+written, nprob + seed + idx written."""
+    return n * (c * s + 8 + 4) + b * (2 * row_bytes + 2 * 8 + 2 * 8 + 4 + 4 + 8)
+
+
+def peak_hbm():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for name, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                continue
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_pool(wl, dev, seed, with_payload=True):
+    """Synthetic pool of BASELINE.md's distributions: logits randn*2, labels randint, payload rand."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    n, c = wl["n"], wl["c"]
+    dt = torch.float32 if wl["dtype"] == "f32" else torch.bfloat16
+    logits = torch.empty(n, c, dtype=dt, device=dev)
+    step = max(1, (1 << 27) // c)  # generate in slices to bound temporary memory
+    for i in range(0, n, step):
+        logits[i:i + step] = (torch.randn(min(step, n - i), c, generator=g, device=dev) * 2).to(dt)
+    labels = torch.randint(0, c, (n,), generator=g, device=dev)
+    return logits, labels
+
+
+def cpu_baseline(wl, budget_s=12.0, max_rows=None):
+    """The reference's own CPU arithmetic (oracle restatement on torch CPU ops), all host threads."""
+    from oracle import mercury_oracle as orc
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    n, c, b = wl["n"], wl["c"], wl["b"]
+    rows = n
+    if max_rows:
+        rows = min(n, max_rows)
+    # bound the sample so that one pass stays within a few seconds
+    while rows * c > 64_000_000 and rows > 4096:
+        rows //= 2
+    g = torch.Generator().manual_seed(0)
+    dt = torch.float32 if wl["dtype"] == "f32" else torch.bfloat16
+    x = (torch.randn(rows, c, generator=g) * 2).to(dt)
+    y = torch.randint(0, c, (rows,), generator=g)
+    gen = torch.Generator().manual_seed(3)
+    t0 = time.perf_counter()
+    reps = 0
+    while True:
+        ema = orc.EMAverage()
+        r = orc.update_samples_flat(x, y, b, ema, generator=gen)
+        _ = orc.reweighted_loss(torch.ones(b), r["nprob"])
+        reps += 1
+        el = time.perf_counter() - t0
+        if el > budget_s or reps >= 200:
+            break
+    return {"value": rows * reps / el, "unit": "candidates/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{reps} passes over {rows} x {c} {wl['dtype']} candidates, B={b} "
+                      f"({'full pool' if rows == n else 'row slice of the pool, rate per candidate'}), {el:.1f} s"}
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warm = args.steps, args.warmup
+    base = cpu_baseline(wl, budget_s=max(5.0, min(60.0, 2.0 * steps)))
+    line = {
+        "impl": "reference", "metric": "importance-scored+sampled candidates/sec", "value": base["value"], "unit": "candidates/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": 1e3 * wl["n"] / base["value"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
+        "config": {"workload": args.workload, "note": wl["note"], "candidates": wl["n"], "classes": wl["c"], "draws": wl["b"]},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pools", type=int, default=0, help="distinct pools rotated to defeat L2 (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = dict(WORKLOADS[args.workload])
+
+    if args.impl == "reference":
+        run_reference(args, wl)
+        return
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (there is no CPU path); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+
+    from mercury_b200 import ops
+
+    n, c, b = wl["n"], wl["c"], wl["b"]
+    s = 4 if wl["dtype"] == "f32" else 2
+    row_bytes = 0
+    payload = None
+    if wl["payload"]:
+        payload = torch.rand((n,) + wl["payload"], device=dev, generator=torch.Generator(device=dev).manual_seed(2))
+        row_bytes = payload[0].numel() * 4
+    index = torch.arange(n, device=dev) + rank * n
+    pool_bytes = n * (c * s + 8)
+    npools = args.pools or max(2, min(8, -(-(300 << 20) // pool_bytes)))  # >= 300 MB in rotation (> 126 MB L2)
+    pools = [make_pool(wl, dev, seed=100 * rank + i) for i in range(npools)]
+    gen = torch.Generator().manual_seed(3)
+    u_host = torch.rand(b, dtype=torch.float64, generator=gen).pin_memory()
+    u = u_host.to(dev)
+    ema = torch.zeros(1, device=dev)
+    out = {}  # result buffers reused across steps: no allocation inside the timed region
+
+    if world > 1:
+        from mercury_b200.sharded import ShardedPool
+
+        sp = ShardedPool(n_local=n, device=dev)
+
+    def step(i, first=False):
+        lg, lb = pools[i % npools]
+        if world > 1:
+            return sp.update_samples(lg, lb, u, data=payload, index=index, out=out)
+        r = ops.update_samples(lg, lb, u, ema, first, data=payload, index=index, out=out)
+        out.update({k: v for k, v in r.items() if k in ("scores", "stats", "idx", "nprob", "seed", "data", "labels", "index")})
+        return r
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(3, args.warmup)):
+        step(i, first=(i == 0))
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            r = step(i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1) / args.steps
+        # keep the clocks sampled over a region long enough for nvidia-smi to see it
+        t_end = time.time() + 0.6
+        i = 0
+        while time.time() < t_end:
+            step(i)
+            i += 1
+        torch.cuda.synchronize()
+    ops.check_status(r["status"])
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+    total_candidates = n * world
+    value = total_candidates / (ms * 1e-3)
+
+    # ---- dominant kernel (K1 score) timed alone, on the launching stream
+    sc = torch.empty(n, dtype=torch.float32, device=dev)
+    st = ops.new_status(dev)
+    for i in range(3):
+        ops.score(*pools[i % npools], status=st, out=sc)
+    torch.cuda.synchronize()
+    evs = []
+    for i in range(max(args.steps, 10)):
+        a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        ops.score(*pools[i % npools], status=st, out=sc)
+        z.record()
+        evs.append((a, z))
+    torch.cuda.synchronize()
+    k1_ms = sum(a.elapsed_time(z) for a, z in evs) / len(evs)
+    peak, peak_src = peak_hbm()
+    k1_bytes = n * (c * s + 8 + 4)
+    k1_gbs = k1_bytes / (k1_ms * 1e-3) / 1e9
+    step_bytes = algorithmic_bytes(n, c, s, b, row_bytes)
+
+    # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
+    lg0, lb0 = pools[0]
+    h_logits = torch.empty(lg0.shape, dtype=lg0.dtype).pin_memory()
+    h_labels = torch.empty(lb0.shape, dtype=lb0.dtype).pin_memory()
+    h_logits.copy_(lg0)
+    h_labels.copy_(lb0)
+    d_logits, d_labels, d_u = torch.empty_like(lg0), torch.empty_like(lb0), torch.empty_like(u)
+    h_idx = torch.empty(b, dtype=torch.int64).pin_memory()
+    h_np = torch.empty(b, dtype=torch.float32).pin_memory()
+    h_seed = torch.empty(b, dtype=torch.float32).pin_memory()
+    h_stats = torch.empty(8, dtype=torch.float32).pin_memory()
+    ema2 = torch.zeros(1, device=dev)
+
+    def e2e_step(first=False):
+        d_logits.copy_(h_logits, non_blocking=True)
+        d_labels.copy_(h_labels, non_blocking=True)
+        d_u.copy_(u_host, non_blocking=True)
+        if world > 1:
+            rr = sp.update_samples(d_logits, d_labels, d_u, data=payload, index=index, out=out)
+        else:
+            rr = ops.update_samples(d_logits, d_labels, d_u, ema2, first, data=payload, index=index, out=out)
+        h_idx.copy_(rr["idx"], non_blocking=True)
+        h_np.copy_(rr["nprob"], non_blocking=True)
+        h_seed.copy_(rr["seed"], non_blocking=True)
+        h_stats.copy_(rr["stats"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller reads the result every step
+
+    for i in range(3):
+        e2e_step(first=(i == 0))
+    barrier()
+    e2e_steps = max(5, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    if dist is not None:
+        t = torch.tensor([e2e_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t)
+    h2d = n * (c * s + 8) + b * 8
+    d2h = b * (8 + 4 + 4) + 32
+
+    if rank == 0:
+        launches_per_step = 6 + (0 if world == 1 else 0)
+        line = {
+            "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
+            "config": {"workload": args.workload, "note": wl["note"], "candidates_per_gpu": n, "classes": c, "draws": b,
+                       "payload_row_bytes": row_bytes, "l2": f"{npools} distinct pools rotated ({npools * pool_bytes >> 20} MiB > 126 MiB L2)",
+                       "cdf": "exact serial-fp32 (bit-identical to torch.multinomial on CPU)",
+                       "multi_gpu": None if world == 1 else "pool sharded by rank; NCCL all-gather of scores; replicated exact CDF; local draw"},
+            "step_roofline": {"algorithmic_bytes": step_bytes, "achieved_gbs": step_bytes / (ms * 1e-3) / 1e9,
+                              "frac": step_bytes / (ms * 1e-3) / 1e9 / peak},
+            "roofline": {"kernel": "K1 score (mercury_score)", "bound": "hbm", "achieved": k1_gbs, "peak": peak, "unit": "GB/s",
+                         "frac": k1_gbs / peak, "traffic": None, "peak_source": peak_src, "ms_per_launch": k1_ms,
+                         "algorithmic_bytes_per_launch": k1_bytes},
+            "e2e": {"value": total_candidates / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps},
+            "gpu_launches": launches_per_step * args.steps,
+            "clocks": clocks.summary(),
+        }
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl)
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,151 @@
+/* mercury_b200 -- C ABI of the B200-native importance-sampling hot path.
+ *
+ * Drop-in boundary.  The reference (AIoT-MLSys-Lab/Mercury) has no FFI of its own: its hot path
+ * is the Python method Trainer.update_samples (pytorch_collab.py:89-117) plus three lines of
+ * Trainer.train (:137,:145,:148) and the alternative Groupwise_Sampler (util.py:94-160), and all
+ * arithmetic is delegated to PyTorch calls.  Each entry point below replaces one of those call
+ * sites; the citation after "replaces" names it.  mercury_b200/ops.py binds them with ctypes and
+ * INTEGRATION.md shows the stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless its name starts with h_;
+ *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*), performs no
+ *    allocation, no host synchronisation and keeps no global state;
+ *  - scratch memory is supplied by the caller (`ws`, sized by the matching *_workspace_bytes);
+ *    workspaces must be 256-byte aligned; a workspace may be reused by the next call on the
+ *    same stream without clearing it;
+ *  - return value: 0 on success, a negative MERCURY_ERR_* otherwise (mercury_last_error() gives
+ *    the text for the calling thread);
+ *  - data errors that torch reports by raising (bad label, negative / non-finite probability,
+ *    zero total) are reported through a device status word (bit set MERCURY_ST_*), which the
+ *    caller may read whenever it next synchronises.
+ */
+#ifndef MERCURY_B200_H
+#define MERCURY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MERCURY_ABI_VERSION 1
+
+enum { MERCURY_OK = 0, MERCURY_ERR_ARG = -1, MERCURY_ERR_CUDA = -2, MERCURY_ERR_WORKSPACE = -3 };
+
+enum { MERCURY_F32 = 0, MERCURY_BF16 = 1 };
+
+/* how the cumulative distribution is accumulated */
+enum {
+    MERCURY_CDF_EXACT_SERIAL_F32 = 0, /* bit-identical to ATen's serial `sum += val` in fp32 */
+    MERCURY_CDF_F64 = 1               /* deterministic fp64 reduce-then-scan (not bit-identical) */
+};
+
+/* device status word bits */
+enum {
+    MERCURY_ST_BAD_LABEL = 1,  /* F.cross_entropy: "Target out of bounds"                          */
+    MERCURY_ST_NEGATIVE = 2,   /* multinomial: "encountering probability entry < 0" (NaN included) */
+    MERCURY_ST_NONFINITE = 4,  /* multinomial: "probability entry = infinity or NaN"               */
+    MERCURY_ST_ZERO_SUM = 8,   /* multinomial: "sum of probabilities <= 0"                         */
+    MERCURY_ST_TOPK_TIES = 16  /* exponential race: more exact ties at the k-th key than buffered  */
+};
+
+/* layout of the 8-float statistics block written by mercury_pool_stats */
+enum {
+    MERCURY_STAT_MEAN = 0,     /* mean(scores)              pytorch_collab.py:109 */
+    MERCURY_STAT_EMA = 1,      /* EMAverage.value afterwards util.py:207-213      */
+    MERCURY_STAT_SHIFT = 2,    /* alpha * ema                pytorch_collab.py:111 */
+    MERCURY_STAT_TOTAL = 3,    /* sum(scores + shift)        pytorch_collab.py:112 */
+    MERCURY_STAT_COUNT = 8
+};
+
+int mercury_abi_version(void);
+const char* mercury_last_error(void);
+
+/* ---- K1: per-candidate importance score -----------------------------------------------------
+ * replaces F.cross_entropy(output, label, reduction='none') at pytorch_collab.py:102 and
+ * util.py:129.  logits [n, c] with `row_stride` elements between rows, dtype MERCURY_F32 or
+ * MERCURY_BF16 (upcast in registers); labels int64 [n]; label == ignore_index scores 0; a label
+ * outside [0, c) sets MERCURY_ST_BAD_LABEL and scores 0.  scores fp32 [n].  The logits are read
+ * exactly once. */
+int mercury_score(const void* logits, int dtype, const int64_t* labels, int64_t n, int64_t c,
+                  int64_t row_stride, int64_t ignore_index, float* scores, int32_t* status,
+                  void* stream);
+
+/* ---- pool statistics, smoothing shift, normaliser --------------------------------------------
+ * replaces torch.mean (:109), EMAverage.update (:110, util.py:207-213), `+ alpha*ema` (:111) and
+ * torch.sum (:112).  `ema_state` is one device float holding EMAverage.value; `ema_first` != 0
+ * means "first update copies".  With n_bounds > 0, `h_bounds` (HOST int64, ascending, last == n)
+ * lists growing pool sizes and the EMA is updated once per prefix mean, reproducing the
+ * reference's 10 updates per call (:95-110); with n_bounds == 0 there is one update on the
+ * whole pool.  Writes stats[MERCURY_STAT_COUNT] (see enum) and updates *ema_state. */
+size_t mercury_pool_stats_workspace_bytes(int64_t n);
+int mercury_pool_stats(const float* scores, int64_t n, const int64_t* h_bounds, int n_bounds,
+                       float* ema_state, int ema_first, double ema_alpha, double smooth_alpha,
+                       float* stats, void* ws, size_t ws_bytes, void* stream);
+
+/* p_i = (score_i + shift) / total, the vector the reference hands to torch.multinomial
+ * (pytorch_collab.py:111-112), materialised. */
+int mercury_normalize(const float* scores, int64_t n, const float* stats, float* p, void* stream);
+
+/* ---- K2: cumulative distribution --------------------------------------------------------------
+ * replaces the first half of torch.multinomial(p, B, replacement=True) at pytorch_collab.py:114
+ * (ATen multinomial_with_replacement: cum_dist).  weights fp32 [n] (>= 0, any scale);
+ * cdf fp32 [n] = running sum / total; *total = the running sum's last value.  n <= 2^24. */
+size_t mercury_cdf_workspace_bytes(int64_t n);
+int mercury_cdf(const float* weights, int64_t n, int mode, float* cdf, float* total,
+                int32_t* status, void* ws, size_t ws_bytes, void* stream);
+
+/* replaces the second half of torch.multinomial(..., replacement=True) (:114): for each fp64
+ * uniform u_j the first slot with (double)cdf[slot] >= u_j.  idx int64 [b]. */
+int mercury_sample_with_replacement(const float* cdf, int64_t n, const double* uniforms, int64_t b,
+                                    int64_t* idx, void* stream);
+
+/* ---- K2': exponential race (Gumbel top-k), draws without replacement --------------------------
+ * replaces torch.multinomial(p, k, replacement=False) and every n_sample == 1 draw (util.py:150):
+ * keys_i = weights_i / float(-log1p(-u_i)), idx = the k largest keys in descending order.
+ * uniforms fp64 [n].  k <= 2048. */
+size_t mercury_sample_topk_workspace_bytes(int64_t n, int64_t k);
+int mercury_sample_topk(const float* weights, int64_t n, const double* uniforms, int64_t k,
+                        int64_t* idx, int32_t* status, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- K3: gather the drawn candidates + importance weights + backward seed ----------------------
+ * replaces losses_pros[idx] * N, cat(datas)[idx], cat(labels)[idx], cat(index)[idx]
+ * (pytorch_collab.py:116-117) and the gradient that torch.div / torch.mean / backward
+ * (:137,:145,:148) send to the per-sample losses: seed_j = (1/b) / nprob_j.
+ * p fp32 [n]; data [n, row_bytes] bytes (may be NULL, then out_data is ignored); labels / index
+ * int64 [n] (may be NULL).  nprob, seed fp32 [b]. */
+int mercury_gather_reweight(const float* p, const int64_t* idx, int64_t b, int64_t n,
+                            const void* data, int64_t row_bytes, const int64_t* labels,
+                            const int64_t* index, void* out_data, int64_t* out_labels,
+                            int64_t* out_index, float* nprob, float* seed, void* stream);
+
+/* ---- the whole step ---------------------------------------------------------------------------
+ * replaces Trainer.update_samples' arithmetic (pytorch_collab.py:102-117) on an assembled pool:
+ * score -> stats -> exact CDF -> b draws from caller-supplied uniforms -> gather + weights + seed.
+ * Never materialises p or the CDF: only the chunks a draw lands in are rebuilt.  If `scores_in`
+ * is non-NULL the scoring step is skipped and those scores are used (logits may then be NULL);
+ * the sharded mode uses this after the all-gather.  Optional outputs may be NULL. */
+typedef struct mercury_update_args {
+    const void* logits; int dtype; const int64_t* labels; int64_t n, c, row_stride, ignore_index;
+    const float* scores_in;           /* optional: precomputed scores [n]                        */
+    const int64_t* h_bounds; int n_bounds;  /* see mercury_pool_stats                             */
+    float* ema_state; int ema_first; double ema_alpha, smooth_alpha;
+    const double* uniforms; int64_t b;      /* fp64 uniforms [b]                                  */
+    const void* data; int64_t row_bytes; const int64_t* index;   /* payload [n,row_bytes], ids [n] */
+    float* scores;                    /* out fp32 [n] (required unless scores_in given)          */
+    float* stats;                     /* out fp32 [MERCURY_STAT_COUNT]                           */
+    int64_t* idx;                     /* out int64 [b] pool positions                             */
+    float* nprob; float* seed;        /* out fp32 [b]                                            */
+    void* out_data; int64_t* out_labels; int64_t* out_index;    /* out, gathered rows             */
+    int32_t* status;                  /* in/out device status word                               */
+} mercury_update_args;
+
+size_t mercury_update_samples_workspace_bytes(int64_t n, int64_t b);
+int mercury_update_samples(const mercury_update_args* args, void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MERCURY_B200_H */

@@ -1,0 +1,69 @@
+// ABI housekeeping: version, per-thread error text, and the whole-step entry point that chains
+// K1 -> stats -> exact CDF boundaries -> fused draw/gather (reference pytorch_collab.py:102-117).
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "common.cuh"
+#include "internal.cuh"
+
+namespace mercury {
+
+static thread_local char g_err[512] = "";
+
+void set_last_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_last_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));
+    return MERCURY_ERR_CUDA;
+}
+
+}  // namespace mercury
+
+using namespace mercury;
+
+extern "C" int mercury_abi_version(void) { return MERCURY_ABI_VERSION; }
+extern "C" const char* mercury_last_error(void) { return g_err; }
+
+extern "C" size_t mercury_update_samples_workspace_bytes(int64_t n, int64_t b) {
+    (void)b;
+    return cdf_ws_bytes(n);
+}
+
+extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, size_t ws_bytes, void* stream) {
+    MB_CHECK_ARG(a != nullptr, "mercury_update_samples: null argument block");
+    MB_CHECK_ARG(a->n >= 1, "mercury_update_samples: empty pool");
+    MB_CHECK_ARG(a->n <= ((int64_t)1 << 24), "number of categories cannot exceed 2^24");
+    MB_CHECK_ARG(a->b >= 0, "mercury_update_samples: negative draw count");
+    MB_CHECK_ARG(a->stats && a->ema_state && a->status, "mercury_update_samples: stats / ema_state / status are required");
+    MB_CHECK_ARG(a->b == 0 || (a->uniforms && a->idx && a->nprob && a->seed),
+                 "mercury_update_samples: uniforms / idx / nprob / seed are required when b > 0");
+    const float* scores = a->scores_in;
+    if (!scores) {
+        MB_CHECK_ARG(a->logits && a->labels && a->scores, "mercury_update_samples: logits / labels / scores are required");
+        MB_CHECK_ARG(a->c >= 1 && a->row_stride >= a->c, "mercury_update_samples: bad class count or row stride");
+        MB_CHECK_ARG(a->dtype == MERCURY_F32 || a->dtype == MERCURY_BF16, "mercury_update_samples: bad dtype");
+    }
+    MB_CHECK_ARG(a->n_bounds >= 0 && a->n_bounds <= 64, "mercury_update_samples: at most 64 pool sizes");
+    for (int i = 0; i < a->n_bounds; ++i) {
+        MB_CHECK_ARG(a->h_bounds[i] >= 1 && a->h_bounds[i] <= a->n && (i == 0 || a->h_bounds[i] > a->h_bounds[i - 1]),
+                     "mercury_update_samples: pool sizes must be ascending in [1, n]");
+    }
+    MB_CHECK_ARG(a->n_bounds == 0 || a->h_bounds[a->n_bounds - 1] == a->n, "mercury_update_samples: last pool size must equal n");
+    int rc = check_ws(ws, ws_bytes, cdf_ws_bytes(a->n), "mercury_update_samples");
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (!scores) {
+        rc = score_dispatch(a->logits, a->dtype, a->labels, a->n, a->c, a->row_stride, a->ignore_index, a->scores, a->status, st);
+        if (rc) return rc;
+        scores = a->scores;
+    }
+    rc = pool_stats_launch(scores, a->n, a->h_bounds, a->n_bounds, a->ema_state, a->ema_first, a->ema_alpha, a->smooth_alpha,
+                           a->stats, ws, st);
+    if (rc) return rc;
+    return update_draw_launch(*a, scores, ws, st);
+}

@@ -1,0 +1,442 @@
+// K1 -- fused per-candidate importance score (row-wise log-softmax + NLL, reduction='none').
+// Replaces F.cross_entropy at reference pytorch_collab.py:102 / util.py:129.
+//
+// The logits are read from HBM exactly once; everything else happens in registers / shared
+// memory.  Three layouts, chosen by row size (DESIGN.md "K1"):
+//   small rows (<= 256 B, e.g. 10 classes)   : tiles of rows staged by 1-D bulk (TMA) copies into
+//                                              a shared-memory ring, one thread per row;
+//   medium rows (<= 8 KB, e.g. 1000 x bf16)  : one warp per row, 128-bit streaming loads, the row
+//                                              lives in registers, warp-shuffle max / sum;
+//   wide rows (e.g. 32768 x bf16 = 64 KB)    : one CTA per row, the row streams through a
+//                                              bulk-copy ring in 16 KB chunks, online softmax.
+// A scalar warp-per-row kernel covers everything unaligned or strided.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace mercury {
+
+namespace {
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kProducerThreads = 32;
+
+template <typename T> struct Elem;
+template <> struct Elem<float> {
+    static __device__ __forceinline__ float ld(const float* p) { return *p; }
+    static constexpr uint32_t kNegInfWord = 0xff800000u;
+};
+template <> struct Elem<__nv_bfloat16> {
+    static __device__ __forceinline__ float ld(const __nv_bfloat16* p) {
+        return __uint_as_float(static_cast<uint32_t>(*reinterpret_cast<const unsigned short*>(p)) << 16);
+    }
+    static constexpr uint32_t kNegInfWord = 0xff80ff80u;
+};
+
+// label handling shared by all layouts: returns true if the row contributes a loss.
+// Call it from ONE thread per row (it raises the status bit with an atomic).
+__device__ __forceinline__ bool label_ok(int64_t y, int64_t c, int64_t ignore_index, int32_t* status) {
+    if (y == ignore_index) return false;
+    if (y < 0 || y >= c) {
+        atomicOr(status, MERCURY_ST_BAD_LABEL);
+        return false;
+    }
+    return true;
+}
+__device__ __forceinline__ bool label_in_range(int64_t y, int64_t c, int64_t ignore_index) {
+    return y != ignore_index && y >= 0 && y < c;
+}
+
+// ------------------------------------------------------------------------------------------------
+// generic: one warp per row, scalar loads, two passes (second pass served by L1/L2)
+template <typename T>
+__global__ void __launch_bounds__(256) score_generic_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels,
+                                                            int64_t n, int64_t c, int64_t row_stride, int64_t ignore_index,
+                                                            float* __restrict__ scores, int32_t* status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < n; row += nwarps) {
+        const T* rp = logits + row * row_stride;
+        float m = -INFINITY;
+        for (int64_t j = lane; j < c; j += 32) m = fmaxf(m, Elem<T>::ld(rp + j));
+        m = warp_max(m);
+        float l = 0.f;
+        for (int64_t j = lane; j < c; j += 32) l += ex2_approx((Elem<T>::ld(rp + j) - m) * kLog2e);
+        l = warp_sum(l);
+        if (lane == 0) {
+            const int64_t y = labels[row];
+            float out = 0.f;
+            if (label_ok(y, c, ignore_index, status)) out = logf(l) - (Elem<T>::ld(rp + y) - m);
+            scores[row] = out;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// medium rows: one warp per row, the row held in registers as VPL 128-bit vectors per lane
+template <typename T, int VPL>
+__global__ void __launch_bounds__(256) score_warp_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels,
+                                                         int64_t n, int64_t c, int64_t row_stride, int64_t ignore_index,
+                                                         float* __restrict__ scores, int32_t* status) {
+    const int lane = threadIdx.x & 31;
+    const int nvec = (int)((c * (int64_t)sizeof(T)) >> 4);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < n; row += nwarps) {
+        const T* rp = logits + row * row_stride;
+        uint4 v[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int k = lane + 32 * i;
+            if (k < nvec) {
+                v[i] = ldg_stream(reinterpret_cast<const uint4*>(rp) + k);
+            } else {
+                v[i] = make_uint4(Elem<T>::kNegInfWord, Elem<T>::kNegInfWord, Elem<T>::kNegInfWord, Elem<T>::kNegInfWord);
+            }
+        }
+        const int64_t y = labels[row];
+        const bool ok = label_in_range(y, c, ignore_index);
+        if (!ok && lane == 0) label_ok(y, c, ignore_index, status);
+        const float xy = ok ? Elem<T>::ld(rp + y) : 0.f;
+
+        float m = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (sizeof(T) == 4) {
+                    m = fmaxf(m, __uint_as_float(w[q]));
+                } else {
+                    m = fmaxf(m, fmaxf(bf16_lo(w[q]), bf16_hi(w[q])));
+                }
+            }
+        }
+        m = warp_max(m);
+        float l = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (sizeof(T) == 4) {
+                    l += ex2_approx((__uint_as_float(w[q]) - m) * kLog2e);
+                } else {
+                    l += ex2_approx((bf16_lo(w[q]) - m) * kLog2e);
+                    l += ex2_approx((bf16_hi(w[q]) - m) * kLog2e);
+                }
+            }
+        }
+        l = warp_sum(l);
+        if (lane == 0) scores[row] = ok ? logf(l) - (xy - m) : 0.f;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// bulk-copy ring shared by the small-row and wide-row kernels
+template <int STAGES> struct Ring {
+    uint64_t full[STAGES];
+    uint64_t empty[STAGES];
+};
+
+template <int STAGES>
+__device__ __forceinline__ void ring_init(Ring<STAGES>* ring, int consumer_warps) {
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&ring->full[s], 1);
+            mbar_init(&ring->empty[s], consumer_warps);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+}
+
+// small rows: tile = TR rows of logits + their labels per stage; consumers own rows.
+// CT > 0: compile-time class count (rows cached in registers); CT == 0: run-time class count.
+template <typename T, int CT, int STAGES, int CONSUMERS>
+__global__ void __launch_bounds__(CONSUMERS + kProducerThreads, 1)
+score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels, int64_t n, int c_rt, int tile_rows,
+                   int64_t ignore_index, float* __restrict__ scores, int32_t* status) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int c = CT > 0 ? CT : c_rt;
+    Ring<STAGES>* ring = reinterpret_cast<Ring<STAGES>*>(smem);
+    const uint32_t logit_bytes = (uint32_t)tile_rows * c * sizeof(T);
+    const uint32_t logit_slot = (logit_bytes + 127u) & ~127u;
+    const uint32_t stage_bytes = logit_slot + (uint32_t)tile_rows * 8u;
+    unsigned char* stage0 = smem + 128;
+    static_assert(sizeof(Ring<STAGES>) <= 128, "ring header");
+    ring_init(ring, CONSUMERS / 32);
+
+    const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0) {
+        // ---- producer warp
+        int it = 0;
+        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+            const int s = it % STAGES, round = it / STAGES;
+            if (round > 0) mbar_wait(&ring->empty[s], (round - 1) & 1);
+            const int64_t row0 = tile * tile_rows;
+            const int rows = (int)min((int64_t)tile_rows, n - row0);
+            unsigned char* dst = stage0 + (size_t)s * stage_bytes;
+            const uint32_t lb = (uint32_t)rows * c * sizeof(T), yb = (uint32_t)rows * 8u;
+            if (((lb | yb) & 15u) == 0) {
+                if (lane == 0) {
+                    mbar_arrive_expect_tx(&ring->full[s], lb + yb);
+                    bulk_g2s(dst, logits + row0 * c, lb, &ring->full[s]);
+                    bulk_g2s(dst + logit_slot, labels + row0, yb, &ring->full[s]);
+                }
+            } else {  // ragged last tile: plain loads by the producer warp
+                const T* src = logits + row0 * c;
+                T* d = reinterpret_cast<T*>(dst);
+                for (int k = lane; k < rows * c; k += 32) d[k] = src[k];
+                int64_t* dy = reinterpret_cast<int64_t*>(dst + logit_slot);
+                for (int k = lane; k < rows; k += 32) dy[k] = labels[row0 + k];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ring->full[s]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ---- consumers
+        const int t = threadIdx.x - kProducerThreads;
+        int it = 0;
+        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+            const int s = it % STAGES, round = it / STAGES;
+            mbar_wait(&ring->full[s], round & 1);
+            const int64_t row0 = tile * tile_rows;
+            const int rows = (int)min((int64_t)tile_rows, n - row0);
+            const unsigned char* base = stage0 + (size_t)s * stage_bytes;
+            const T* tl = reinterpret_cast<const T*>(base);
+            const int64_t* ty = reinterpret_cast<const int64_t*>(base + logit_slot);
+            for (int r = t; r < rows; r += CONSUMERS) {
+                const T* rp = tl + (size_t)r * c;
+                const int64_t y = ty[r];
+                float m = -INFINITY, l = 0.f;
+                if constexpr (CT > 0) {
+                    float x[CT > 0 ? CT : 1];
+                    if constexpr (sizeof(T) == 4 && (CT % 2) == 0) {
+#pragma unroll
+                        for (int j = 0; j < CT / 2; ++j) {
+                            const float2 p2 = reinterpret_cast<const float2*>(rp)[j];
+                            x[2 * j] = p2.x;
+                            x[2 * j + 1] = p2.y;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < CT; ++j) x[j] = Elem<T>::ld(rp + j);
+                    }
+#pragma unroll
+                    for (int j = 0; j < CT; ++j) m = fmaxf(m, x[j]);
+#pragma unroll
+                    for (int j = 0; j < CT; ++j) l += ex2_approx((x[j] - m) * kLog2e);
+                } else {
+                    // rotate the start column by the row so that lanes hit different banks
+                    int j0 = r % c;
+                    int j = j0;
+                    for (int k = 0; k < c; ++k) {
+                        m = fmaxf(m, Elem<T>::ld(rp + j));
+                        if (++j == c) j = 0;
+                    }
+                    j = j0;
+                    for (int k = 0; k < c; ++k) {
+                        l += ex2_approx((Elem<T>::ld(rp + j) - m) * kLog2e);
+                        if (++j == c) j = 0;
+                    }
+                }
+                float out = 0.f;
+                if (label_ok(y, c, ignore_index, status)) out = logf(l) - (Elem<T>::ld(rp + y) - m);
+                scores[row0 + r] = out;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ring->empty[s]);
+        }
+    }
+}
+
+// wide rows: one CTA per row, CHUNK-byte pieces through the ring, per-thread online softmax
+template <typename T, int STAGES, int CHUNK, int CONSUMERS>
+__global__ void __launch_bounds__(CONSUMERS + kProducerThreads)
+score_wide_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels, int64_t n, int64_t c, int64_t row_stride,
+                  int64_t ignore_index, float* __restrict__ scores, int32_t* status) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    Ring<STAGES>* ring = reinterpret_cast<Ring<STAGES>*>(smem);
+    float* red = reinterpret_cast<float*>(smem + 128);  // [2][CONSUMERS/32] max, sum
+    unsigned char* stage0 = smem + 256;
+    ring_init(ring, CONSUMERS / 32);
+    constexpr int VPT = CHUNK / 16 / CONSUMERS;  // vectors per thread per chunk
+    static_assert(VPT >= 1 && VPT * 16 * CONSUMERS == CHUNK, "chunk/consumer geometry");
+    constexpr int NW = CONSUMERS / 32;
+
+    const uint32_t row_bytes = (uint32_t)(c * sizeof(T));
+    const int chunks = (int)((row_bytes + CHUNK - 1) / CHUNK);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int it = 0;
+            for (int64_t row = blockIdx.x; row < n; row += gridDim.x) {
+                const unsigned char* src = reinterpret_cast<const unsigned char*>(logits + row * row_stride);
+                for (int k = 0; k < chunks; ++k, ++it) {
+                    const int s = it % STAGES, round = it / STAGES;
+                    if (round > 0) mbar_wait(&ring->empty[s], (round - 1) & 1);
+                    const uint32_t bytes = min((uint32_t)CHUNK, row_bytes - (uint32_t)k * CHUNK);
+                    mbar_arrive_expect_tx(&ring->full[s], bytes);
+                    bulk_g2s(stage0 + (size_t)s * CHUNK, src + (size_t)k * CHUNK, bytes, &ring->full[s]);
+                }
+            }
+        }
+    } else {
+        const int t = threadIdx.x - kProducerThreads;
+        const int cw = t >> 5;
+        int it = 0;
+        for (int64_t row = blockIdx.x; row < n; row += gridDim.x) {
+            const int64_t y = labels[row];
+            const bool ok = (t == 0) ? label_ok(y, c, ignore_index, status) : false;
+            const float xy = ok ? Elem<T>::ld(logits + row * row_stride + y) : 0.f;
+            float m = -INFINITY, l = 0.f;
+            for (int k = 0; k < chunks; ++k, ++it) {
+                const int s = it % STAGES, round = it / STAGES;
+                mbar_wait(&ring->full[s], round & 1);
+                const uint32_t bytes = min((uint32_t)CHUNK, row_bytes - (uint32_t)k * CHUNK);
+                const int nv = (int)(bytes >> 4);
+                const uint4* sv = reinterpret_cast<const uint4*>(stage0 + (size_t)s * CHUNK);
+                uint4 v[VPT];
+#pragma unroll
+                for (int i = 0; i < VPT; ++i) {
+                    const int q = t + i * CONSUMERS;
+                    v[i] = q < nv ? sv[q]
+                                  : make_uint4(Elem<T>::kNegInfWord, Elem<T>::kNegInfWord, Elem<T>::kNegInfWord, Elem<T>::kNegInfWord);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ring->empty[s]);  // the chunk now lives in registers
+                float cm = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < VPT; ++i) {
+                    const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (sizeof(T) == 4) cm = fmaxf(cm, __uint_as_float(w[q]));
+                        else cm = fmaxf(cm, fmaxf(bf16_lo(w[q]), bf16_hi(w[q])));
+                    }
+                }
+                if (cm > -INFINITY) {
+                    const float mn = fmaxf(m, cm);
+                    l *= ex2_approx((m - mn) * kLog2e);  // m == -inf -> factor 0 (l is 0 anyway)
+                    m = mn;
+#pragma unroll
+                    for (int i = 0; i < VPT; ++i) {
+                        const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            if (sizeof(T) == 4) {
+                                l += ex2_approx((__uint_as_float(w[q]) - m) * kLog2e);
+                            } else {
+                                l += ex2_approx((bf16_lo(w[q]) - m) * kLog2e);
+                                l += ex2_approx((bf16_hi(w[q]) - m) * kLog2e);
+                            }
+                        }
+                    }
+                }
+            }
+            // combine the CONSUMERS partial (m, l) pairs: consumers-only named barrier (id 1)
+            const float wm = warp_max(m);
+            if (lane == 0) red[cw] = wm;
+            asm volatile("bar.sync 1, %0;" ::"n"(CONSUMERS) : "memory");
+            float M = red[0];
+#pragma unroll
+            for (int i = 1; i < NW; ++i) M = fmaxf(M, red[i]);
+            const float part = (m > -INFINITY) ? l * ex2_approx((m - M) * kLog2e) : 0.f;
+            const float ws = warp_sum(part);
+            if (lane == 0) red[NW + cw] = ws;
+            asm volatile("bar.sync 1, %0;" ::"n"(CONSUMERS) : "memory");
+            if (t == 0) {
+                float L = 0.f;
+#pragma unroll
+                for (int i = 0; i < NW; ++i) L += red[NW + i];
+                scores[row] = ok ? logf(L) - (xy - M) : 0.f;
+            }
+            // red[] is rewritten only after the next row's first barrier, which every consumer
+            // reaches after reading it here
+            asm volatile("bar.sync 1, %0;" ::"n"(CONSUMERS) : "memory");
+        }
+    }
+}
+
+template <typename T>
+int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride, int64_t ignore_index,
+                 float* scores, int32_t* status, cudaStream_t st) {
+    const int64_t row_bytes = c * (int64_t)sizeof(T);
+    const bool base16 = (reinterpret_cast<uintptr_t>(logits) & 15) == 0;
+    const bool stride16 = ((row_stride * (int64_t)sizeof(T)) & 15) == 0;
+    const bool lab16 = (reinterpret_cast<uintptr_t>(labels) & 15) == 0;
+
+    if (row_stride == c && base16 && lab16 && row_bytes <= 256) {
+        constexpr int STAGES = 3, CONSUMERS = 512;
+        int tile_rows = row_bytes <= 40 ? 1024 : row_bytes <= 88 ? 512 : row_bytes <= 184 ? 256 : 128;
+        const size_t logit_slot = ((size_t)tile_rows * row_bytes + 127) & ~(size_t)127;
+        const size_t smem = 128 + STAGES * (logit_slot + (size_t)tile_rows * 8);
+        const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
+        const int grid = (int)min_i64(ntiles, kSMs);
+        auto go = [&](auto kern) -> int {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return cuda_fail(e, "score_small smem attribute");
+            kern<<<grid, CONSUMERS + kProducerThreads, smem, st>>>(logits, labels, n, (int)c, tile_rows, ignore_index, scores, status);
+            MB_CHECK_LAUNCH("score_small_kernel");
+            return MERCURY_OK;
+        };
+        if (c == 10) return go(score_small_kernel<T, 10, STAGES, CONSUMERS>);
+        return go(score_small_kernel<T, 0, STAGES, CONSUMERS>);
+    }
+    if (base16 && stride16 && (row_bytes & 15) == 0 && row_bytes <= 8192) {
+        const int nvec = (int)(row_bytes >> 4);
+        const int64_t warps_needed = n;
+        const int grid = (int)min_i64((warps_needed + 7) / 8, (int64_t)kSMs * 8);
+#define MB_LAUNCH_WARP(VPL)                                                                                         \
+    score_warp_kernel<T, VPL><<<grid, 256, 0, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status)
+        if (nvec <= 32) MB_LAUNCH_WARP(1);
+        else if (nvec <= 64) MB_LAUNCH_WARP(2);
+        else if (nvec <= 128) MB_LAUNCH_WARP(4);
+        else if (nvec <= 256) MB_LAUNCH_WARP(8);
+        else MB_LAUNCH_WARP(16);
+#undef MB_LAUNCH_WARP
+        MB_CHECK_LAUNCH("score_warp_kernel");
+        return MERCURY_OK;
+    }
+    if (base16 && stride16 && (row_bytes & 15) == 0) {
+        constexpr int STAGES = 4, CHUNK = 16384, CONSUMERS = 256;
+        const size_t smem = 256 + (size_t)STAGES * CHUNK;
+        auto kern = score_wide_kernel<T, STAGES, CHUNK, CONSUMERS>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return cuda_fail(e, "score_wide smem attribute");
+        const int grid = (int)min_i64(n, (int64_t)kSMs * 3);
+        kern<<<grid, CONSUMERS + kProducerThreads, smem, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
+        MB_CHECK_LAUNCH("score_wide_kernel");
+        return MERCURY_OK;
+    }
+    const int grid = (int)min_i64((n + 7) / 8, (int64_t)kSMs * 8);
+    score_generic_kernel<T><<<grid, 256, 0, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
+    MB_CHECK_LAUNCH("score_generic_kernel");
+    return MERCURY_OK;
+}
+
+}  // namespace
+
+int score_dispatch(const void* logits, int dtype, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride,
+                   int64_t ignore_index, float* scores, int32_t* status, cudaStream_t st) {
+    if (n == 0) return MERCURY_OK;
+    if (dtype == MERCURY_F32)
+        return launch_score(static_cast<const float*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st);
+    return launch_score(static_cast<const __nv_bfloat16*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st);
+}
+
+}  // namespace mercury
+
+extern "C" int mercury_score(const void* logits, int dtype, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride,
+                             int64_t ignore_index, float* scores, int32_t* status, void* stream) {
+    using namespace mercury;
+    MB_CHECK_ARG(n >= 0 && c >= 1, "mercury_score: need n >= 0 and c >= 1 (n=%lld c=%lld)", (long long)n, (long long)c);
+    MB_CHECK_ARG(dtype == MERCURY_F32 || dtype == MERCURY_BF16, "mercury_score: dtype must be MERCURY_F32 or MERCURY_BF16");
+    MB_CHECK_ARG(row_stride >= c, "mercury_score: row_stride (%lld) < c (%lld)", (long long)row_stride, (long long)c);
+    MB_CHECK_ARG(n == 0 || (logits && labels && scores && status), "mercury_score: null pointer");
+    return score_dispatch(logits, dtype, labels, n, c, row_stride, ignore_index, scores, status, static_cast<cudaStream_t>(stream));
+}
