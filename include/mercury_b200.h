@@ -97,6 +97,18 @@ size_t mercury_cdf_workspace_bytes(int64_t n);
 int mercury_cdf(const float* weights, int64_t n, int mode, float* cdf, float* total,
                 int32_t* status, void* ws, size_t ws_bytes, void* stream);
 
+/* No counterpart in the reference.  mercury_cdf for hosts that cannot allocate device memory
+ * (a plugin inside a runtime that owns the whole GPU, a small C/Go/Java binding with no
+ * allocator of its own): same inputs, outputs and result as mercury_cdf, but the scratch is a
+ * 112 KiB array built into the library (held on every GPU that loads it), so nothing is
+ * allocated or freed, ever.  n <= MERCURY_STATIC_MAX_N, larger pools are refused with
+ * MERCURY_ERR_ARG.  The first call on each device looks the array's address up; make that call
+ * outside stream capture.  All calls on a device share the array: calls that overlap on the GPU
+ * race, so keep them on one stream.  Nothing in the array needs clearing between calls. */
+#define MERCURY_STATIC_MAX_N (1 << 22)
+int mercury_cdf_static(const float* weights, int64_t n, int mode, float* cdf, float* total,
+                       int32_t* status, void* stream);
+
 /* replaces the second half of torch.multinomial(..., replacement=True) (:114): for each fp64
  * uniform u_j the first slot with (double)cdf[slot] >= u_j.  idx int64 [b]. */
 int mercury_sample_with_replacement(const float* cdf, int64_t n, const double* uniforms, int64_t b,

@@ -17,6 +17,7 @@ F32, BF16 = 0, 1
 CDF_EXACT_SERIAL_F32, CDF_F64 = 0, 1
 ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES = 1, 2, 4, 8, 16
 STAT_MEAN, STAT_EMA, STAT_SHIFT, STAT_TOTAL, STAT_COUNT = 0, 1, 2, 3, 8
+STATIC_MAX_N = 1 << 22
 
 c_i64, c_f64, c_int, c_vp, c_sz = ctypes.c_int64, ctypes.c_double, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
 
@@ -48,6 +49,7 @@ SIGNATURES = {
     "mercury_normalize": (c_int, [c_vp, c_i64, c_vp, c_vp, c_vp]),
     "mercury_cdf_workspace_bytes": (c_sz, [c_i64]),
     "mercury_cdf": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "mercury_cdf_static": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
     "mercury_sample_with_replacement": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp]),
     "mercury_sample_topk_workspace_bytes": (c_sz, [c_i64, c_i64]),
     "mercury_sample_topk": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_sz, c_vp]),

@@ -18,6 +18,8 @@
 // A wrong guess costs time, never correctness.
 #include <math.h>
 
+#include <mutex>
+
 #include "chain.cuh"
 #include "common.cuh"
 #include "internal.cuh"
@@ -743,4 +745,73 @@ extern "C" int mercury_sample_with_replacement(const float* cdf, int64_t n, cons
     search_kernel<<<(unsigned)((b + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(cdf, n, uniforms, b, idx);
     MB_CHECK_LAUNCH("search_kernel");
     return MERCURY_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// mercury_cdf_static: the same cumulative distribution, for callers that cannot hand us scratch.
+//
+// Who needs this: a host that has no device allocator to call on -- a plugin running inside
+// another runtime that reserved the whole GPU for its own pool at start-up (a cudaMalloc there
+// fails or fragments that pool), or a small C/Go/Java host binding this ABI that would otherwise
+// have to size a workspace, keep it alive and free it around every call.  They pass only the
+// input and the outputs; the scratch lives in the array below, inside the library image, so
+// every GPU that loads the library carries these 112 KiB until the process exits.
+//
+// The name `g_static_scratch` is only a stand-in on the host side: its device address has to be
+// asked for (cudaGetSymbolAddress) with the right device current, once per device.  The first
+// call on a device does that, so make that first call outside any stream capture.
+//
+// Limits and sharing: n <= MERCURY_STATIC_MAX_N (1 << 22); every call on a device uses the same
+// array, so two calls whose kernels overlap on the GPU (different streams, different host
+// threads) race on it -- keep them on one stream or order them with events.  The array keeps
+// whatever the previous call left there; that is harmless because each stage writes a field
+// before any later stage reads it, so nothing in it has to start at zero and nothing is cleared.
+constexpr int64_t kStaticMaxN = (int64_t)MERCURY_STATIC_MAX_N;
+constexpr size_t kStaticScratchBytes = 112 * 1024;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxDevices] = {};
+
+int static_scratch_for_current_device(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "mercury_cdf_static: cudaGetDevice");
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_last_error("mercury_cdf_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+        return MERCURY_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);  // device `dev` is current here
+        if (e != cudaSuccess) return cuda_fail(e, "mercury_cdf_static: cudaGetSymbolAddress");
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255)) {
+            set_last_error("mercury_cdf_static: scratch symbol resolved to a bad address");
+            return MERCURY_ERR_CUDA;
+        }
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return MERCURY_OK;
+}
+}  // namespace
+
+extern "C" int mercury_cdf_static(const float* weights, int64_t n, int mode, float* cdf, float* total, int32_t* status,
+                                  void* stream) {
+    MB_CHECK_ARG(n >= 1, "mercury_cdf_static: empty distribution");
+    MB_CHECK_ARG(n <= kStaticMaxN,
+                 "mercury_cdf_static: n = %lld exceeds the built-in scratch (at most %lld candidates); "
+                 "use mercury_cdf with a caller-provided workspace",
+                 (long long)n, (long long)kStaticMaxN);
+    if (cdf_ws_bytes(n) > kStaticScratchBytes) {  // cannot happen for n <= kStaticMaxN; kept as a guard
+        set_last_error("mercury_cdf_static: internal scratch too small for n = %lld", (long long)n);
+        return MERCURY_ERR_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    const int rc = static_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    return mercury_cdf(weights, n, mode, cdf, total, status, scratch, kStaticScratchBytes, stream);
 }
