@@ -133,6 +133,16 @@ int mercury_gather_reweight(const float* p, const int64_t* idx, int64_t b, int64
                             const int64_t* index, void* out_data, int64_t* out_labels,
                             int64_t* out_index, float* nprob, float* seed, void* stream);
 
+/* Sharded pools (one process per GPU, pytorch_collab.py:282-287 gives each worker its own
+ * presample shard): `idx` are GLOBAL pool positions, this rank owns [shard_lo, shard_lo+shard_n).
+ * Rows of owned draws are gathered from the local shard, all other output rows are zero-filled
+ * (labels / index 0, owned[j] = 0), so a SUM all-reduce across ranks assembles the batch that
+ * pytorch_collab.py:116-117 gathers from a single pool.  owned int32 [b] may be NULL. */
+int mercury_gather_owned(const int64_t* idx, int64_t b, int64_t shard_lo, int64_t shard_n,
+                         const void* data, int64_t row_bytes, const int64_t* labels,
+                         const int64_t* index, void* out_data, int64_t* out_labels,
+                         int64_t* out_index, int32_t* owned, void* stream);
+
 /* ---- the whole step ---------------------------------------------------------------------------
  * replaces Trainer.update_samples' arithmetic (pytorch_collab.py:102-117) on an assembled pool:
  * score -> stats -> exact CDF -> b draws from caller-supplied uniforms -> gather + weights + seed.

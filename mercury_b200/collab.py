@@ -1,0 +1,149 @@
+"""Drop-in ``Trainer`` exposing the reference's hot-path surface (pytorch_collab.py:36-249).
+
+Only the importance-sampling path is re-implemented: ``update_samples`` (pytorch_collab.py:89-117)
+and the reweighted loss of ``train`` (:133-148) run on the CUDA ops; the model forward/backward,
+the optimiser and the evaluation stay stock PyTorch and are kept deliberately thin (the trainer
+loop, logging and TensorBoard output of the reference are out of scope).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from . import _lib, ops
+from .sampler import EMAverage, reweighted_mean
+
+
+class Trainer(object):
+    POOL_BATCHES = 10  # pytorch_collab.py:95
+
+    def __init__(self, net, optimizer, train_loader, presam_loader, test_loader, device):
+        self.net = net
+        self.optimizer = optimizer
+        self.train_loader = train_loader
+        self.presam_loader = presam_loader
+        self.test_loader = test_loader
+        self.device = torch.device(device)
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.world_size = dist.get_world_size() if dist.is_initialized() else 1
+        self.epoch = 0
+        self.step = 1
+        self.next_batch_iter = None
+        self.should_compute_importance = True
+        self.last = None       # full result of the last update_samples (scores, seed, idx, ...)
+        self._pool = None      # preallocated pool buffers: no torch.cat (pytorch_collab.py:108,116-117)
+        self._grad_bucket = None
+
+    # ---- pool feeder (pytorch_collab.py:74-82, with next(it) for Python 3)
+    def get_next(self):
+        if self.next_batch_iter is None:
+            self.next_batch_iter = iter(self.presam_loader)
+        try:
+            b = next(self.next_batch_iter)
+        except StopIteration:
+            self.next_batch_iter = iter(self.presam_loader)
+            b = next(self.next_batch_iter)
+        return b
+
+    def average_model(self):  # pytorch_collab.py:84-87
+        if self.world_size > 1:
+            for p in self.net.parameters():
+                dist.all_reduce(p.data, op=dist.ReduceOp.SUM)
+                p.data /= float(self.world_size)
+
+    def _buffers(self, n, data, out):
+        if self._pool is None or self._pool["logits"].shape != (n, out.shape[1]) or self._pool["data"].shape[1:] != data.shape[1:]:
+            self._pool = dict(logits=torch.empty(n, out.shape[1], dtype=out.dtype, device=self.device),
+                              data=torch.empty((n,) + tuple(data.shape[1:]), dtype=data.dtype, device=self.device),
+                              labels=torch.empty(n, dtype=torch.int64, device=self.device),
+                              index=torch.empty(n, dtype=torch.int64, device=self.device))
+        return self._pool
+
+    def update_samples(self, ema_loss: EMAverage, alpha=0.5):
+        """pytorch_collab.py:89-117: same 5-tuple ``(N*p_i, data, label, index, pool_mean_loss)``.
+
+        The ten presample batches are scored by the model (stock PyTorch, no_grad) straight into a
+        preallocated pool; one fused call then does what :102-117 do, including the ten EMA updates
+        on the growing pools and the generator advancing by ten draws (the last draw is returned).
+        """
+        B = self.train_loader.batch_size
+        bounds, pos, pool = [], 0, None
+        for _ in range(self.POOL_BATCHES if self.should_compute_importance else 0):
+            with torch.no_grad():
+                idx, data, label = self.get_next()
+                data = data.to(self.device, non_blocking=True)
+                label = label.to(self.device, non_blocking=True)
+                output = self.net(data)
+                if pool is None:
+                    pool = self._buffers(self.POOL_BATCHES * data.shape[0], data, output)
+                m = data.shape[0]
+                pool["logits"][pos:pos + m] = output
+                pool["data"][pos:pos + m] = data
+                pool["labels"][pos:pos + m] = label
+                pool["index"][pos:pos + m] = torch.as_tensor(idx).to(self.device, non_blocking=True)
+                pos += m
+                bounds.append(pos)
+        u = torch.rand(len(bounds) * B, dtype=torch.float64)[(len(bounds) - 1) * B:].to(self.device, non_blocking=True)
+        r = ops.update_samples(pool["logits"][:pos], pool["labels"][:pos], u, ema_loss.state, ema_loss.first_update,
+                               ema_alpha=ema_loss.alpha, smooth_alpha=alpha, data=pool["data"][:pos],
+                               index=pool["index"][:pos], bounds=bounds)
+        ema_loss.first_update = False
+        self.last = r
+        return r.nprob, r.data, r.labels, r.index, r.stats[_lib.STAT_MEAN]
+
+    def train(self, max_steps=None):
+        """One epoch of pytorch_collab.py:119-199 (timers, printing and periodic evaluation dropped)."""
+        presam_ema_loss = EMAverage(device=self.device)  # re-created every epoch, :121
+        probs, i_data, i_label, _, _ = self.update_samples(presam_ema_loss)
+        seed = self.last.seed
+        losses_seen = []
+        for n_step, _batch in enumerate(self.train_loader):  # the loader only counts steps (:127)
+            output = self.net(i_data)
+            losses = F.cross_entropy(output, i_label, reduction="none")      # :133 training side, stock
+            loss = reweighted_mean(losses, seed)                             # :137,:145
+            self.optimizer.zero_grad()
+            loss.backward()                                                  # :148
+            self.should_compute_importance = True
+            probs, i_data, i_label, _, _ = self.update_samples(presam_ema_loss)   # :159 next batch, pre-step weights
+            seed = self.last.seed
+            self.average_gradients()                                         # :160
+            self.optimizer.step()                                            # :164
+            losses_seen.append(loss.detach())
+            self.step += 1
+            if max_steps is not None and n_step + 1 >= max_steps:
+                break
+        return torch.stack(losses_seen).mean() if losses_seen else None, None, presam_ema_loss
+
+    def fit(self, epochs, max_steps=None):
+        self.average_model()
+        for epoch in range(1, epochs + 1):
+            self.epoch = epoch
+            self.train(max_steps=max_steps)
+
+    def average_gradients(self):
+        """pytorch_collab.py:236-249: one all-reduce of a persistent flat bucket, then divide."""
+        if self.world_size == 1:
+            return
+        grads = [p.grad for p in self.net.parameters() if p.grad is not None]
+        total = sum(g.numel() for g in grads)
+        if self._grad_bucket is None or self._grad_bucket.numel() != total:
+            self._grad_bucket = torch.empty(total, dtype=grads[0].dtype, device=grads[0].device)
+        torch._foreach_copy_(list(self._grad_bucket.split([g.numel() for g in grads])), [g.reshape(-1) for g in grads])
+        dist.all_reduce(self._grad_bucket, op=dist.ReduceOp.SUM)
+        self._grad_bucket /= self.world_size
+        torch._foreach_copy_([g.reshape(-1) for g in grads], list(self._grad_bucket.split([g.numel() for g in grads])))
+
+    def evaluate(self):
+        """pytorch_collab.py:201-234 reduced to the test split: (mean loss, accuracy)."""
+        self.net.eval()
+        tot, correct, cnt = 0.0, 0, 0
+        with torch.no_grad():
+            for idx, data, label in self.test_loader:
+                data, label = data.to(self.device), label.to(self.device)
+                output = self.net(data)
+                tot += float(F.cross_entropy(output, label, reduction="sum"))
+                correct += int((output.argmax(1) == label).sum())
+                cnt += data.shape[0]
+        self.net.train()
+        return tot / max(cnt, 1), correct / max(cnt, 1)

@@ -255,6 +255,37 @@ def gather_reweight(p: torch.Tensor, idx: torch.Tensor, data: Optional[torch.Ten
     return nprob, seed, out_data, out_labels, out_index
 
 
+def gather_owned(idx: torch.Tensor, shard_lo: int, shard_n: int, data: Optional[torch.Tensor] = None,
+                 labels: Optional[torch.Tensor] = None, index: Optional[torch.Tensor] = None, out: Optional[dict] = None):
+    """Rows of the draws this rank owns (global positions ``idx``), zero rows elsewhere; returns
+    (data, labels, index, owned mask int32).  A SUM all-reduce over ranks then assembles the batch."""
+    _cuda(idx, "idx", torch.int64)
+    b, dev = idx.numel(), idx.device
+    out = out or {}
+
+    def buf(key, shape, dtype):
+        t = out.get(key)
+        return t if t is not None else torch.empty(shape, dtype=dtype, device=dev)
+
+    out_data = out_labels = out_index = None
+    row_bytes = 0
+    if data is not None:
+        data = _cuda(data, "data").contiguous()
+        row_bytes = _row_bytes(data)
+        out_data = buf("data", (b,) + tuple(data.shape[1:]), data.dtype)
+    if labels is not None:
+        labels = _cuda(labels, "labels", torch.int64).contiguous()
+        out_labels = buf("labels", (b,), torch.int64)
+    if index is not None:
+        index = _cuda(index, "index", torch.int64).contiguous()
+        out_index = buf("index", (b,), torch.int64)
+    owned = buf("owned", (b,), torch.int32)
+    _lib.check(_lib.load().mercury_gather_owned(idx.data_ptr(), b, shard_lo, shard_n, _ptr(data), row_bytes, _ptr(labels),
+                                                _ptr(index), _ptr(out_data), _ptr(out_labels), _ptr(out_index),
+                                                owned.data_ptr(), _stream()))
+    return out_data, out_labels, out_index, owned
+
+
 # ------------------------------------------------------------------------------ the whole step
 class UpdateResult(dict):
     """scores, stats, idx, nprob, seed, data, labels, index, status (all CUDA tensors)."""

@@ -1,0 +1,110 @@
+"""Candidate pool sharded over the GPUs of one box (one process per GPU, torch.distributed/NCCL).
+
+Reference behaviour: pytorch_collab.py:282-287 hands every worker its own presample shard and
+``update_samples`` never communicates (each rank draws from its local pool only).  The
+north-star mode implemented here makes the draw GLOBAL:
+
+  1. every rank scores its contiguous shard with K1 straight into its slice of a pool-sized
+     score vector (no communication);
+  2. ``all_gather_into_tensor`` (NCCL over NVLink/NVSwitch) fills the other slices in place:
+     N*4 bytes in total (4 MB at 1 M candidates);
+  3. every rank runs the identical statistics + exact CDF + draw on the full vector with the
+     same uniforms, so all ranks hold the same global indices / N*p weights / seeds, bit-equal
+     to the single-process result on the concatenated pool, with no host round trip;
+  4. rows are gathered by their owner (zero elsewhere); ``assemble=True`` SUM-all-reduces the
+     B gathered rows so that every rank ends up with the whole batch.
+
+The compute steps go through a small backend object so that the host-side logic (shard
+arithmetic, collectives, ownership) can be exercised on CPU with gloo in the tests; the default
+backend is the CUDA ops and has no CPU path.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+class CudaBackend:
+    """The product path: hand-written kernels through the C ABI."""
+
+    def __init__(self):
+        from . import ops
+
+        self.ops = ops
+
+    def score(self, logits, labels, out):
+        self.ops.score(logits, labels, out=out)
+
+    def draw(self, scores_all, uniforms, ema_state, ema_first, ema_alpha, smooth_alpha, out):
+        r = self.ops.update_samples(None, None, uniforms, ema_state, ema_first, ema_alpha=ema_alpha,
+                                    smooth_alpha=smooth_alpha, scores_in=scores_all, out=out)
+        return r.idx, r.nprob, r.seed, r.stats, r.status
+
+    def gather_owned(self, idx, lo, n, data, labels, index, out):
+        return self.ops.gather_owned(idx, lo, n, data, labels, index, out=out)
+
+
+def shard_bounds(n_global: int, world: int, rank: int):
+    """Contiguous equal shards in rank order: shard g = [g*N/G, (g+1)*N/G)."""
+    if n_global % world:
+        raise ValueError("the pool must divide evenly across ranks (all_gather needs equal shards)")
+    n_local = n_global // world
+    return rank * n_local, n_local
+
+
+class ShardedPool:
+    def __init__(self, n_local: int, device, group=None, ema_alpha: float = 0.9, smooth_alpha: float = 0.5, backend=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.n_local = n_local
+        self.n_global = n_local * self.world
+        if self.n_global > (1 << 24):
+            raise RuntimeError("number of categories cannot exceed 2^24")
+        self.lo, _ = shard_bounds(self.n_global, self.world, self.rank)
+        self.device = torch.device(device)
+        self.backend = backend if backend is not None else CudaBackend()
+        self.scores_all = torch.empty(self.n_global, dtype=torch.float32, device=self.device)
+        self.ema_state = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self.ema_first = True
+        self.ema_alpha, self.smooth_alpha = ema_alpha, smooth_alpha
+        self._draw_out: dict = {}
+        self._gather_out: dict = {}
+
+    @property
+    def local_scores(self) -> torch.Tensor:
+        return self.scores_all[self.lo:self.lo + self.n_local]
+
+    def _all_gather_scores(self):
+        if self.world == 1:
+            return
+        try:
+            dist.all_gather_into_tensor(self.scores_all, self.local_scores, group=self.group)
+        except (RuntimeError, NotImplementedError):  # backends without the flat variant
+            parts = list(self.scores_all.split(self.n_local))
+            dist.all_gather(parts, self.local_scores.clone(), group=self.group)
+
+    def update_samples(self, logits_local, labels_local, uniforms, data=None, index=None, assemble: bool = False,
+                       out: Optional[dict] = None):
+        """One global importance-sampling step.  Returns a dict with the replicated ``idx`` (global
+        positions), ``nprob``, ``seed``, ``stats``, ``status`` and this rank's ``data`` / ``labels`` /
+        ``index`` rows (zero where another rank owns the draw) plus the ``owned`` mask."""
+        b = self.backend
+        b.score(logits_local, labels_local, self.local_scores)
+        self._all_gather_scores()
+        idx, nprob, seed, stats, status = b.draw(self.scores_all, uniforms, self.ema_state, self.ema_first, self.ema_alpha,
+                                                 self.smooth_alpha, self._draw_out)
+        self.ema_first = False
+        self._draw_out.update(idx=idx, nprob=nprob, seed=seed, stats=stats)
+        d, l, ix, owned = b.gather_owned(idx, self.lo, self.n_local, data, labels_local, index, self._gather_out)
+        self._gather_out.update({k: v for k, v in (("data", d), ("labels", l), ("index", ix), ("owned", owned)) if v is not None})
+        if assemble and self.world > 1:
+            for t in (d, l, ix):
+                if t is not None:
+                    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return dict(idx=idx, nprob=nprob, seed=seed, stats=stats, status=status, data=d, labels=l, index=ix, owned=owned,
+                    scores=self.scores_all)

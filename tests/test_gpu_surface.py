@@ -1,0 +1,185 @@
+"""GPU tests of the reference-shaped Python surface (Trainer.update_samples, EMAverage,
+Groupwise_Sampler, reweighted loss, ShardedPool) against the reference's own recorded run
+(tests/golden/ref_*.npz) and the oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from oracle import mercury_oracle as orc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+class ReplayNet(nn.Module):
+    """Plays back the logits the reference's ResNet18 produced, batch by batch (the model is outside the path)."""
+
+    def __init__(self, logits):
+        super().__init__()
+        self.logits = torch.from_numpy(np.asarray(logits)).to(DEV)
+        self.pos = 0
+
+    def forward(self, x):
+        out = self.logits[self.pos:self.pos + x.shape[0]]
+        self.pos += x.shape[0]
+        return out
+
+
+class _Loader:
+    def __init__(self, batches, batch_size):
+        self.batches, self.batch_size = batches, batch_size
+
+    def __iter__(self):
+        return iter(self.batches)
+
+
+def _pool_batches(seed):
+    gen = torch.Generator().manual_seed(seed)
+    out = []
+    for b in range(10):
+        data = torch.rand(32, 3, 32, 32, generator=gen)
+        label = torch.randint(0, 10, (32,), generator=gen)
+        out.append((torch.arange(b * 32, (b + 1) * 32) + 1000, data, label))
+    return out
+
+
+@pytest.mark.parametrize("name", ["ref_update_samples_linear.npz", "ref_update_samples_resnet18.npz"])
+def test_trainer_update_samples_equals_the_reference_run(golden_dir, name):
+    from mercury_b200.collab import Trainer
+    from mercury_b200.sampler import EMAverage
+
+    g = np.load(os.path.join(golden_dir, name))
+    batches = _pool_batches(int(g["pool_seed"]))
+    net = ReplayNet(np.concatenate([g["call0_logits"], g["call1_logits"]]))
+    tr = Trainer(net, None, _Loader([], int(g["draw_batch"])), _Loader(batches, 32), None, DEV)
+    ema = EMAverage(device=DEV)
+    torch.manual_seed(int(g["rng_seed"]))  # the generator torch.multinomial drew from in the reference run
+    for call in range(2):
+        probs, data, label, index, avg = tr.update_samples(ema)
+        assert np.array_equal(index.cpu().numpy(), g[f"call{call}_index"])
+        assert np.array_equal(label.cpu().numpy(), g[f"call{call}_label"])
+        np.testing.assert_allclose(probs.cpu().numpy(), g[f"call{call}_probs"], rtol=1e-5)
+        np.testing.assert_allclose(data.double().sum(dim=(1, 2, 3)).cpu().numpy(), g[f"call{call}_data_rowsum"], rtol=1e-12)
+        np.testing.assert_allclose(float(avg), g[f"call{call}_avg"], rtol=1e-5)
+        np.testing.assert_allclose(float(ema.value), g[f"call{call}_ema"], rtol=1e-5)
+
+
+def test_emaverage_follows_util_py():
+    from mercury_b200.sampler import EMAverage
+
+    e, ref = EMAverage(device=DEV), orc.EMAverage()
+    for v in [2.0, 4.0, 0.5, 7.25]:
+        e.update(v)
+        ref.update(torch.tensor(v))
+        np.testing.assert_allclose(float(e.value), float(ref.value), rtol=1e-6)
+    assert not e.first_update and "{:.6f}".format(float(ref.value)) == str(e)
+
+
+def test_groupwise_sampler_equals_the_reference_run(golden_dir):
+    from mercury_b200.sampler import Groupwise_Sampler
+
+    g = np.load(os.path.join(golden_dir, "ref_groupwise.npz"))
+
+    class DS:
+        def __init__(self):
+            gen = torch.Generator().manual_seed(701)
+            self.data = torch.rand(192, 3, 32, 32, generator=gen)
+            self.targets = torch.randint(0, 10, (192,), generator=gen)
+
+        def __len__(self):
+            return 192
+
+        def get_slice(self, s, e):
+            return self.data[s:e], self.targets[s:e]
+
+    ds = DS()
+    assert np.array_equal(ds.targets.numpy(), g["labels"])
+    for tag, repl in (("repl", True), ("norepl", False)):
+        net = ReplayNet(g["logits"][:192])
+        s = Groupwise_Sampler(ds, replacement=repl, device=DEV)
+        s.update_importance(0, 64, net)
+        s.update_importance(0, 64, net)
+        s.update_importance(1, 64, net)
+        np.testing.assert_allclose(s.importance.cpu().numpy(), g[f"{tag}_importance"], rtol=1e-5, atol=1e-6)
+        assert np.array_equal(s.group_indicator.cpu().numpy(), g[f"{tag}_group_indicator"].astype(np.int32))
+        assert s.group_index == int(g[f"{tag}_group_index"])
+        torch.manual_seed(int(g["rng_seed"]))
+        it = iter(s)
+        ys = [int(next(it)) for _ in range(len(g[f"{tag}_yield"]))]
+        assert ys == list(g[f"{tag}_yield"])
+    few = s.draw(8).cpu().numpy()
+    assert len(set(few.tolist())) == 8 and few.min() >= 128  # one race, no replacement, current group only
+
+
+def test_reweighted_mean_matches_autograd():
+    from mercury_b200.sampler import reweighted_mean
+
+    gen = torch.Generator().manual_seed(1)
+    losses = (torch.rand(64, generator=gen) * 3).to(DEV).requires_grad_(True)
+    nprob = (torch.rand(64, generator=gen) + 0.5).to(DEV)
+    seed = (1.0 / 64) / nprob
+    out = reweighted_mean(losses, seed)
+    (out * 2.0).backward()
+    ref_loss, ref_seed = orc.reweighted_loss(losses.detach().cpu(), nprob.cpu())
+    np.testing.assert_allclose(float(out), float(ref_loss), rtol=1e-5)
+    np.testing.assert_allclose(losses.grad.cpu().numpy(), 2.0 * ref_seed.numpy(), rtol=1e-5)
+
+
+def test_trainer_runs_a_few_importance_sampled_steps():
+    """cfg1-shaped smoke of the drop-in Trainer: synthetic CIFAR loaders, small CNN, 3 steps."""
+    from mercury_b200.collab import Trainer
+    from mercury_b200.exp_dataset import load_cifar10
+
+    torch.manual_seed(0)
+    train_loader, presam_loader, test_loader = load_cifar10(1, n_train=1280, n_test=64)
+    net = nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.ReLU(), nn.AdaptiveAvgPool2d(4), nn.Flatten(), nn.Linear(128, 10)).to(DEV)
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)
+    tr = Trainer(net, opt, train_loader, presam_loader, test_loader, DEV)
+    before = [p.detach().clone() for p in net.parameters()]
+    loss, _, ema = tr.train(max_steps=3)
+    assert torch.isfinite(loss) and tr.step == 4 and float(ema.value) > 0
+    assert any(not torch.equal(a, b) for a, b in zip(before, net.parameters()))
+    r = tr.last
+    assert r.idx.shape == (32,) and int(r.idx.max()) < 320 and r.data.shape == (32, 3, 32, 32)
+    tl, acc = tr.evaluate()
+    assert np.isfinite(tl) and 0.0 <= acc <= 1.0
+
+
+def test_sharded_pool_single_rank_equals_flat_path():
+    from mercury_b200 import ops
+    from mercury_b200.sharded import ShardedPool
+
+    gen = torch.Generator().manual_seed(5)
+    n, c, b = 30000, 10, 96
+    logits = (torch.randn(n, c, generator=gen) * 2).to(DEV)
+    labels = torch.randint(0, c, (n,), generator=gen).to(DEV)
+    data = torch.rand(n, 3, 8, 8, generator=gen).to(DEV)
+    index = torch.randperm(n, generator=gen).to(DEV)
+    u = torch.rand(b, dtype=torch.float64, generator=gen).to(DEV)
+    sp = ShardedPool(n, DEV)
+    flat_ema = torch.zeros(1, device=DEV)
+    for step in range(2):
+        r = sp.update_samples(logits, labels, u, data=data, index=index)
+        f = ops.update_samples(logits, labels, u, flat_ema, step == 0, data=data, index=index)
+        assert torch.equal(r["idx"], f.idx) and torch.equal(r["nprob"], f.nprob) and torch.equal(r["seed"], f.seed)
+        assert torch.equal(r["data"], f.data) and torch.equal(r["labels"], f.labels) and torch.equal(r["index"], f.index)
+        assert int(r["owned"].sum()) == b
+        logits = logits + 0.25
+
+
+def test_gather_owned_zero_fills_foreign_rows():
+    from mercury_b200 import ops
+
+    gen = torch.Generator().manual_seed(6)
+    data = torch.rand(100, 7, generator=gen).to(DEV)
+    labels = torch.randint(0, 10, (100,), generator=gen).to(DEV)
+    idx = torch.tensor([5, 250, 199, 200, 299, 300, 0], device=DEV)
+    d, l, ix, owned = ops.gather_owned(idx, 200, 100, data, labels, None)
+    assert owned.tolist() == [0, 1, 0, 1, 1, 0, 0]
+    assert torch.equal(d[1], data[50]) and torch.equal(d[3], data[0]) and torch.equal(d[4], data[99])
+    assert float(d[0].abs().sum() + d[2].abs().sum() + d[5].abs().sum() + d[6].abs().sum()) == 0.0
+    assert l.tolist() == [0, int(labels[50]), 0, int(labels[0]), int(labels[99]), 0, 0] and ix is None

@@ -1,0 +1,114 @@
+"""World-size-2 gloo test (CPU) of the sharded-pool host logic: shard arithmetic, the in-place
+all-gather of scores, replicated global draw, ownership and batch assembly.  The compute steps
+are injected from the oracle (tests may do that; the product backend is CUDA-only); the GPU
+version of the same check lives in test_gpu_surface.py."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import mercury_oracle as orc
+
+
+class OracleBackend:
+    """CPU stand-in with the CudaBackend interface of mercury_b200.sharded (tests only)."""
+
+    def score(self, logits, labels, out):
+        out.copy_(orc.score(logits, labels))
+
+    def draw(self, scores_all, uniforms, ema_state, ema_first, ema_alpha, smooth_alpha, out):
+        ema = orc.EMAverage(ema_alpha)
+        ema.first_update = bool(ema_first)
+        ema.value = ema_state[0].clone()
+        mean, w, p = orc.pool_stats(scores_all, ema, smooth_alpha)
+        ema_state[0] = ema.value
+        idx = torch.from_numpy(orc.draw_with_replacement(p.numpy(), uniforms.numpy()))
+        nprob = p[idx] * p.numel()
+        seed = (1.0 / idx.numel()) / nprob
+        stats = torch.tensor([float(mean), float(ema.value), smooth_alpha * float(ema.value), float(w.sum()), 0, 0, 0, 0])
+        return idx, nprob, seed, stats, torch.zeros(1, dtype=torch.int32)
+
+    def gather_owned(self, idx, lo, n, data, labels, index, out):
+        local = idx - lo
+        mine = (local >= 0) & (local < n)
+        safe = torch.where(mine, local, torch.zeros_like(local))
+
+        def take(t):
+            if t is None:
+                return None
+            rows = t[safe].clone()
+            rows[~mine] = 0
+            return rows
+
+        return take(data), take(labels), take(index), mine.to(torch.int32)
+
+
+def _pool(n, c, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    logits = torch.randn(n, c, generator=g) * 2
+    labels = torch.randint(0, c, (n,), generator=g)
+    data = torch.rand(n, 3, 4, 4, generator=g)
+    index = torch.randperm(n, generator=g)
+    u = torch.rand(48, dtype=torch.float64, generator=g)
+    return logits, labels, data, index, u
+
+
+def _worker(rank, world, port, n, c, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mercury_b200.sharded import ShardedPool, shard_bounds
+
+        logits, labels, data, index, u = _pool(n, c)
+        lo, nl = shard_bounds(n, world, rank)
+        sp = ShardedPool(nl, "cpu", backend=OracleBackend())
+        outs = []
+        for step in range(2):  # EMA carried across steps identically on every rank
+            r = sp.update_samples(logits[lo:lo + nl] + step, labels[lo:lo + nl], u, data=data[lo:lo + nl],
+                                  index=index[lo:lo + nl], assemble=True)
+            outs.append({k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in r.items()})
+        ret[rank] = outs
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_sharded_pool_world2_matches_single_process():
+    n, c, world = 4096, 10, 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), n, c, ret), nprocs=world, join=True)
+    logits, labels, data, index, u = _pool(n, c)
+    ema = orc.EMAverage()
+    for step in range(2):
+        ref = orc.update_samples_flat(logits + step, labels, len(u), ema, u=u.numpy(), data=data, index=index)
+        for rank in range(world):
+            got = ret[rank][step]
+            assert np.array_equal(got["idx"].numpy(), ref["idx"].numpy())          # same global draw on every rank
+            np.testing.assert_allclose(got["nprob"].numpy(), ref["nprob"].numpy(), rtol=1e-6)
+            assert torch.equal(got["scores"], ref["scores"])                      # all-gathered score vector
+            assert torch.equal(got["data"], ref["data"])                          # assembled batch
+            assert torch.equal(got["labels"], ref["labels"]) and torch.equal(got["index"], ref["index"])
+            lo = rank * (n // world)
+            mine = (ref["idx"] >= lo) & (ref["idx"] < lo + n // world)
+            assert torch.equal(got["owned"].bool(), mine)
+        assert int(ret[0][step]["owned"].sum() + ret[1][step]["owned"].sum()) == len(u)  # every draw has one owner
+
+
+def test_shard_bounds():
+    from mercury_b200.sharded import shard_bounds
+
+    assert shard_bounds(50000, 8, 3) == (18750, 6250)   # BASELINE cfg4: 8 shards of 6250
+    assert [shard_bounds(16, 4, r)[0] for r in range(4)] == [0, 4, 8, 12]
+    with pytest.raises(ValueError):
+        shard_bounds(10, 4, 0)
