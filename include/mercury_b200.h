@@ -100,7 +100,7 @@ int mercury_cdf(const float* weights, int64_t n, int mode, float* cdf, float* to
 /* No counterpart in the reference.  mercury_cdf for hosts that cannot allocate device memory
  * (a plugin inside a runtime that owns the whole GPU, a small C/Go/Java binding with no
  * allocator of its own): same inputs, outputs and result as mercury_cdf, but the scratch is a
- * 112 KiB array built into the library (held on every GPU that loads it), so nothing is
+ * 208 KiB array built into the library (held on every GPU that loads it), so nothing is
  * allocated or freed, ever.  n <= MERCURY_STATIC_MAX_N, larger pools are refused with
  * MERCURY_ERR_ARG.  The first call on each device looks the array's address up; make that call
  * outside stream capture.  All calls on a device share the array: calls that overlap on the GPU
@@ -142,6 +142,11 @@ int mercury_gather_owned(const int64_t* idx, int64_t b, int64_t shard_lo, int64_
                          const void* data, int64_t row_bytes, const int64_t* labels,
                          const int64_t* index, void* out_data, int64_t* out_labels,
                          int64_t* out_index, int32_t* owned, void* stream);
+
+/* Test hook, no counterpart in the reference: scales every phase guess of the exact CDF (1.0 =
+ * normal).  Guesses only choose which maps are precomputed, so any value must leave results
+ * unchanged; the tests use it to force the mis-guess paths.  Process-global; not for production. */
+void mercury_test_set_guess_bias(double bias);
 
 /* ---- the whole step ---------------------------------------------------------------------------
  * replaces Trainer.update_samples' arithmetic (pytorch_collab.py:102-117) on an assembled pool:

@@ -55,6 +55,7 @@ SIGNATURES = {
     "mercury_sample_topk": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "mercury_gather_reweight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mercury_gather_owned": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "mercury_test_set_guess_bias": (None, [c_f64]),
     "mercury_update_samples_workspace_bytes": (c_sz, [c_i64, c_i64]),
     "mercury_update_samples": (c_int, [ctypes.POINTER(UpdateArgs), c_vp, c_sz, c_vp]),
 }

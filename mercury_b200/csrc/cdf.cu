@@ -52,6 +52,69 @@ struct WeightSrc {
 };
 
 // ---------------------------------------------------------------------------------------------
+// phase guesses (used only to choose which maps to precompute; a wrong guess costs time, not bits)
+constexpr uint32_t kAnyPhase = 0x3ffu;   // all addends zero: the identity map in every phase
+constexpr uint32_t kFlag = 0x80000000u;  // chunk: sub-summaries present; sub-chunk: phase change expected
+constexpr int kSub = 64, kSubsPerChunk = kChunk / kSub;
+constexpr int kSubSlots = 128;           // flagged chunks that get sub-chunk summaries
+constexpr double kGuessMargin = 1.0 / 1024.0;
+static_assert(kSubsPerChunk == 32, "one sub-chunk per lane of the walking warp");
+
+// Guess the phase of the running sum over a span from its approximate value at both ends, with
+// a margin for the drift of the fp32 chain: returns the low guess, and whether the span may
+// change phase.
+__device__ __forceinline__ bool guess_span(double a_lo, double a_hi, double bias, uint32_t* e_lo) {
+    const uint32_t lo = phase_of(f2b((float)(a_lo * bias * (1.0 - kGuessMargin))));
+    const uint32_t hi = phase_of(f2b((float)(a_hi * bias * (1.0 + kGuessMargin))));
+    *e_lo = lo;
+    return lo != hi;
+}
+
+// Exclusive scan (fp64) of one value per chunk over a 1024-thread CTA -> approx[0..nchunks], and
+// a compact slot number for every chunk that may change phase -> slotid[c] (-1: none).
+template <typename F>
+__device__ __forceinline__ void scan_chunks(F value_of, int nchunks, double bias, double* __restrict__ approx,
+                                            int* __restrict__ slotid, double* red, int* redi) {
+    __shared__ double carry;
+    __shared__ int carry_slots;
+    if (threadIdx.x == 0) { carry = 0.0; carry_slots = 0; }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int c0 = 0; c0 < nchunks; c0 += 1024) {
+        const int c = c0 + threadIdx.x;
+        const double v = c < nchunks ? value_of(c) : 0.0;
+        double inc = v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const double o = __shfl_up_sync(0xffffffffu, inc, off);
+            if (lane >= off) inc += o;
+        }
+        __syncthreads();
+        if (lane == 31) red[warp] = inc;
+        __syncthreads();
+        double pre = carry;
+        for (int i = 0; i < warp; ++i) pre += red[i];
+        const double a_lo = pre + inc - v, a_hi = pre + inc;
+        uint32_t e;
+        const bool flagged = c < nchunks && guess_span(a_lo, a_hi, bias, &e);
+        const unsigned bal = __ballot_sync(0xffffffffu, flagged);
+        if (lane == 0) redi[warp] = __popc(bal);
+        __syncthreads();
+        int before = carry_slots;
+        for (int i = 0; i < warp; ++i) before += redi[i];
+        before += __popc(bal & ((1u << lane) - 1u));
+        if (c < nchunks) {
+            approx[c] = a_lo;
+            slotid[c] = flagged && before < kSubSlots ? before : -1;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) { carry = a_hi; carry_slots = before + (flagged ? 1 : 0); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) approx[nchunks] = carry;
+}
+
+// ---------------------------------------------------------------------------------------------
 // block-wide helpers
 template <int NT>
 __device__ __forceinline__ double block_sum(double v, double* red) {
@@ -210,9 +273,9 @@ __global__ void __launch_bounds__(1024) stats_finalize_kernel(const float* __res
                                                               const double* __restrict__ sums, int nchunks, Bounds bounds,
                                                               float* ema_state, int ema_first, double ema_alpha,
                                                               double smooth_alpha, float* __restrict__ stats,
-                                                              double* __restrict__ approx) {
+                                                              double* __restrict__ approx, int* __restrict__ slotid, double bias) {
     __shared__ double red[32];
-    __shared__ double carry;
+    __shared__ int redi[32];
     float ema = *ema_state;
     float mean = 0.f;
     double pool_sum = 0.0;
@@ -239,66 +302,20 @@ __global__ void __launch_bounds__(1024) stats_finalize_kernel(const float* __res
         stats[MERCURY_STAT_TOTAL] = total;
         stats[4] = stats[5] = stats[6] = stats[7] = 0.f;
         *ema_state = ema;
-        carry = 0.0;
     }
-    __syncthreads();
     // exclusive scan of the per-chunk totals of p ~ (sum_scores + len*shift) / total
-    for (int c0 = 0; c0 < nchunks; c0 += 1024) {
-        const int c = c0 + threadIdx.x;
-        double v = 0.0;
-        if (c < nchunks) {
-            const int len = (int)min((int64_t)kChunk, n - (int64_t)c * kChunk);
-            v = (sums[c] + (double)len * (double)shift) / (double)total;
-        }
-        // inclusive warp scan, then across warps
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        double inc = v;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const double o = __shfl_up_sync(0xffffffffu, inc, off);
-            if (lane >= off) inc += o;
-        }
-        __syncthreads();
-        if (lane == 31) red[warp] = inc;
-        __syncthreads();
-        double pre = carry;
-        for (int i = 0; i < warp; ++i) pre += red[i];
-        if (c < nchunks) approx[c] = pre + inc - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = pre + inc;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) approx[nchunks] = carry;
+    scan_chunks([&](int c) {
+        const int len = (int)min((int64_t)kChunk, n - (int64_t)c * kChunk);
+        return (sums[c] + (double)len * (double)shift) / (double)total;
+    }, nchunks, bias, approx, slotid, red, redi);
 }
 
 // 2b. the same scan for raw weights
 __global__ void __launch_bounds__(1024) prefix_finalize_kernel(const double* __restrict__ sums, int nchunks,
-                                                               double* __restrict__ approx) {
+                                                               double* __restrict__ approx, int* __restrict__ slotid, double bias) {
     __shared__ double red[32];
-    __shared__ double carry;
-    if (threadIdx.x == 0) carry = 0.0;
-    __syncthreads();
-    for (int c0 = 0; c0 < nchunks; c0 += 1024) {
-        const int c = c0 + threadIdx.x;
-        const double v = c < nchunks ? sums[c] : 0.0;
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        double inc = v;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const double o = __shfl_up_sync(0xffffffffu, inc, off);
-            if (lane >= off) inc += o;
-        }
-        __syncthreads();
-        if (lane == 31) red[warp] = inc;
-        __syncthreads();
-        double pre = carry;
-        for (int i = 0; i < warp; ++i) pre += red[i];
-        if (c < nchunks) approx[c] = pre + inc - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = pre + inc;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) approx[nchunks] = carry;
+    __shared__ int redi[32];
+    scan_chunks([&](int c) { return sums[c]; }, nchunks, bias, approx, slotid, red, redi);
 }
 
 __global__ void __launch_bounds__(256) normalize_kernel(const float* __restrict__ scores, int64_t n,
@@ -309,35 +326,62 @@ __global__ void __launch_bounds__(256) normalize_kernel(const float* __restrict_
 }
 
 // ---------------------------------------------------------------------------------------------
-// 3. per-chunk maps for the guessed phase and the next one
+// 3. summaries: one map per chunk (for the guessed phase; and the next one where the running
+//    sum may change phase), plus, for those "flagged" chunks, one map per 64-candidate sub-chunk
 struct __align__(32) Summary { uint32_t e; Pair q[2]; uint32_t pad[3]; };
+struct __align__(128) SubSummary { uint32_t e[kSubsPerChunk]; Pair q0[kSubsPerChunk]; Pair q1[kSubsPerChunk]; };
+static_assert(sizeof(SubSummary) == 640, "SubSummary layout");
+
+__device__ __forceinline__ Pair pick_map(uint32_t E, uint32_t e, Pair q0, Pair q1) {
+    e &= ~kFlag;
+    if (e == kAnyPhase || E == e) return q0;
+    if (E == e + 1u) return q1;
+    return Pair{kSatCap, kSatCap};  // guessed wrong: looks like a phase change, gets resolved exactly
+}
+
+double g_guess_bias = 1.0;  // test hook (mercury_test_set_guess_bias): scales every guess
 
 constexpr int kSumNT = 256, kSumIPT = kChunk / kSumNT;
+static_assert(kSumIPT * 8 == kSub, "a sub-chunk is 8 consecutive threads");
 
 __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_t n, const double* __restrict__ approx,
-                                                           Summary* __restrict__ out, int32_t* status, int check) {
+                                                           const int* __restrict__ slotid, double bias,
+                                                           Summary* __restrict__ out, SubSummary* __restrict__ subs,
+                                                           int32_t* status, int check) {
     __shared__ Pair wt[2][kSumNT / 32];
+    __shared__ float wsum[kSumNT / 32];
+    __shared__ int wnz[kSumNT / 32];
     const int64_t start = (int64_t)blockIdx.x * kChunk;
     const int len = (int)min((int64_t)kChunk, n - start);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t pb[kSumIPT];
     load_chunk<kSumNT, kSumIPT>(src, start, len, pb);
-    // guess low: the walk tolerates "one phase too low", not "one too high"
-    const uint32_t e = phase_of(f2b((float)(approx[blockIdx.x] * (1.0 - 1e-4))));
+    // Guess the phase from the approximate running total at both ends of the chunk.  If both ends
+    // agree the chunk is expected to stay in one phase; otherwise it is flagged: it also gets the
+    // map for the next phase and (if a slot was assigned by the prefix scan) sub-chunk summaries.
+    const double a_lo = approx[blockIdx.x], a_hi = approx[blockIdx.x + 1];
+    uint32_t e;
+    const bool flagged = guess_span(a_lo, a_hi, bias, &e);  // block-uniform
+    const int slot = slotid[blockIdx.x];
     Pair a0 = identity_pair(), a1 = identity_pair();
     int bad = 0;
+    bool nz = false;
+    float tsum = 0.f;
 #pragma unroll
     for (int k = 0; k < kSumIPT; ++k) {
+        const float x = b2f(pb[k]);
         if (check) {
-            const float x = b2f(pb[k]);
             if (!(x >= 0.f)) bad |= MERCURY_ST_NEGATIVE;
             else if (isinf(x)) bad |= MERCURY_ST_NONFINITE;
         }
+        nz |= pb[k] != 0u;
+        tsum += x;
         a0 = compose(a0, addend_pair(pb[k], e));
-        a1 = compose(a1, addend_pair(pb[k], e + 1u));
+        if (flagged) a1 = compose(a1, addend_pair(pb[k], e + 1u));
     }
     if (bad) atomicOr(status, bad);
+    const unsigned nzmask = __ballot_sync(0xffffffffu, nz);
     // ordered reduction: lane 0 ends with the composition of the whole warp
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int off = 1; off < 32; off <<= 1) {
         Pair o0, o1;
@@ -345,68 +389,246 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         o1.d0 = __shfl_down_sync(0xffffffffu, a1.d0, off); o1.d1 = __shfl_down_sync(0xffffffffu, a1.d1, off);
         if (lane + off < 32) { a0 = compose(a0, o0); a1 = compose(a1, o1); }
     }
-    if (lane == 0) { wt[0][warp] = a0; wt[1][warp] = a1; }
+    float inc = tsum;  // inclusive scan of the thread sums (approximate, only feeds guesses)
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const float o = __shfl_up_sync(0xffffffffu, inc, off);
+        if (lane >= off) inc += o;
+    }
+    if (lane == 0) { wt[0][warp] = a0; wt[1][warp] = a1; wnz[warp] = nzmask != 0u; }
+    if (lane == 31) wsum[warp] = inc;
     __syncthreads();
     if (threadIdx.x == 0) {
         Pair t0 = identity_pair(), t1 = identity_pair();
+        int any = 0;
 #pragma unroll
-        for (int i = 0; i < kSumNT / 32; ++i) { t0 = compose(t0, wt[0][i]); t1 = compose(t1, wt[1][i]); }
+        for (int i = 0; i < kSumNT / 32; ++i) { t0 = compose(t0, wt[0][i]); t1 = compose(t1, wt[1][i]); any |= wnz[i]; }
         Summary s;
-        s.e = e; s.q[0] = t0; s.q[1] = t1; s.pad[0] = s.pad[1] = s.pad[2] = 0;
+        s.e = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u);
+        s.q[0] = t0;
+        s.q[1] = flagged ? t1 : Pair{kSatCap, kSatCap};
+        s.pad[0] = (uint32_t)slot; s.pad[1] = s.pad[2] = 0;
         out[blockIdx.x] = s;
+    }
+    if (slot < 0) return;
+    // ---- per sub-chunk (8 consecutive threads = 64 candidates)
+    float pre = 0.f;
+    for (int i = 0; i < warp; ++i) pre += wsum[i];
+    const float t_lo = pre + inc - tsum, t_hi = pre + inc;          // running total at this thread's ends
+    const int lead = lane & ~7;
+    const float s_lo = __shfl_sync(0xffffffffu, t_lo, lead), s_hi = __shfl_sync(0xffffffffu, t_hi, lead + 7);
+    uint32_t es;
+    const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, bias, &es);
+    Pair m0 = identity_pair(), m1 = identity_pair();
+#pragma unroll
+    for (int k = 0; k < kSumIPT; ++k) {
+        m0 = compose(m0, addend_pair(pb[k], es));
+        m1 = compose(m1, addend_pair(pb[k], es + 1u));
+    }
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) {
+        Pair o0, o1;
+        o0.d0 = __shfl_down_sync(0xffffffffu, m0.d0, off, 8); o0.d1 = __shfl_down_sync(0xffffffffu, m0.d1, off, 8);
+        o1.d0 = __shfl_down_sync(0xffffffffu, m1.d0, off, 8); o1.d1 = __shfl_down_sync(0xffffffffu, m1.d1, off, 8);
+        if ((lane & 7) + off < 8) { m0 = compose(m0, o0); m1 = compose(m1, o1); }
+    }
+    if ((lane & 7) == 0) {
+        const int k = threadIdx.x >> 3;
+        const bool sub_nz = ((nzmask >> lead) & 0xffu) != 0u;
+        SubSummary* ss = subs + slot;
+        ss->e[k] = (sub_nz ? es : kAnyPhase) | (sub_flagged ? kFlag : 0u);
+        ss->q0[k] = m0;
+        ss->q1[k] = m1;
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// 4. the spine: exact running sum at every chunk boundary
-constexpr int kSpineNT = 512, kSpineIPT = kChunk / kSpineNT;
+// 4. the spine: exact running sum at every chunk boundary.  One warp walks the chunk maps 32 at
+//    a time (no block barriers on the serial path); the rest of the CTA only prefetches the
+//    summaries -- and, for flagged chunks, the sub-chunk maps and the raw candidates of the
+//    sub-chunks expected to change phase -- into shared memory before the walk starts.
+constexpr int kSpineNT = 512;
+constexpr int kMaxSlots = 24, kRawPerSlot = 4;
 
-__global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks,
-                                                         const Summary* __restrict__ sums, uint32_t* __restrict__ start_bits,
+struct SlotData {
+    SubSummary sub;
+    uint32_t raw[kRawPerSlot][kSub];
+    uint8_t rawsub[kRawPerSlot];
+    uint8_t pad[12];
+};
+
+__host__ __device__ inline size_t spine_smem_bytes(int nchunks) {
+    size_t b = (size_t)nchunks * 21;                 // 5 words + 1 slot byte per chunk
+    b = (b + 127) & ~(size_t)127;
+    return b + (size_t)kMaxSlots * sizeof(SlotData) + (size_t)kChunk * 4;
+}
+
+__device__ __forceinline__ Pair warp_scan_pair(Pair x, int lane) {
+    // Without exact ties every map is a plain integer increment (d0 == d1): the scan is then an
+    // integer prefix sum (32 * 2^25 fits in 32 bits), half the shuffles and no selects.
+    if (__ballot_sync(0xffffffffu, x.d0 != x.d1) == 0u) {
+        uint32_t v = x.d0;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, v, off);
+            if (lane >= off) v += o;
+        }
+        v = sat(v);
+        return Pair{v, v};
+    }
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        Pair o = shfl_up_pair(x, off);
+        if (lane >= off) x = compose(o, x);
+    }
+    return x;
+}
+
+// exact pass over `count` consecutive candidates held in shared memory, from state b: this is
+// the reference's own loop (`sum += val` in fp32), run redundantly by every lane of the warp.
+__device__ __forceinline__ uint32_t serial_chain(uint32_t b, const uint32_t* __restrict__ v, int count) {
+    float s = b2f(b);
+    const uint4* v4 = reinterpret_cast<const uint4*>(v);
+#pragma unroll 4
+    for (int i = 0; i < count / 4; ++i) {
+        const uint4 q = v4[i];
+        s = __fadd_rn(s, b2f(q.x));
+        s = __fadd_rn(s, b2f(q.y));
+        s = __fadd_rn(s, b2f(q.z));
+        s = __fadd_rn(s, b2f(q.w));
+    }
+    return f2b(s);
+}
+
+__global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
+                                                         const SubSummary* __restrict__ subs, uint32_t* __restrict__ start_bits,
                                                          float* __restrict__ total_out, int32_t* status) {
-    __shared__ ResolveSmem rs;
-    __shared__ int first_bad;
+    extern __shared__ __align__(128) unsigned char sm[];
+    __shared__ int nslots_s;
+    __shared__ int slot_chunk[kMaxSlots];   // chunk held by each shared-memory slot
+    __shared__ int slot_global[kMaxSlots];  // ... and where its sub-summaries live in `subs`
+    uint32_t* ce = reinterpret_cast<uint32_t*>(sm);
+    uint32_t* qa0 = ce + nchunks; uint32_t* qa1 = qa0 + nchunks; uint32_t* qb0 = qa1 + nchunks; uint32_t* qb1 = qb0 + nchunks;
+    uint8_t* slot_of = reinterpret_cast<uint8_t*>(qb1 + nchunks);
+    const size_t off = (((size_t)nchunks * 21) + 127) & ~(size_t)127;
+    SlotData* slots = reinterpret_cast<SlotData*>(sm + off);
+    uint32_t* stage = reinterpret_cast<uint32_t*>(sm + off + (size_t)kMaxSlots * sizeof(SlotData));  // kChunk words
+    const int tid = threadIdx.x, lane = tid & 31;
+    float shift, totalw;
+    src.prepare(shift, totalw);
+
+    // ---- prefetch (whole CTA)
+    if (tid == 0) nslots_s = 0;
+    __syncthreads();
+    for (int c = tid; c < nchunks; c += kSpineNT) {
+        const Summary s = sums[c];
+        ce[c] = s.e; qa0[c] = s.q[0].d0; qa1[c] = s.q[0].d1; qb0[c] = s.q[1].d0; qb1[c] = s.q[1].d1;
+        uint8_t so = 0;
+        if (s.e & kFlag) {
+            const int sl = atomicAdd(&nslots_s, 1);
+            if (sl < kMaxSlots) { so = (uint8_t)(sl + 1); slot_chunk[sl] = c; slot_global[sl] = (int)s.pad[0]; }
+        }
+        slot_of[c] = so;
+    }
+    __syncthreads();
+    const int nsl = min(nslots_s, kMaxSlots);
+    constexpr int kSubWords = (int)(sizeof(SubSummary) / 4);
+    for (int i = tid; i < nsl * kSubWords; i += kSpineNT) {
+        const int sl = i / kSubWords, w = i % kSubWords;
+        reinterpret_cast<uint32_t*>(&slots[sl].sub)[w] = reinterpret_cast<const uint32_t*>(subs + slot_global[sl])[w];
+    }
+    __syncthreads();
+    if (tid < nsl) {
+        int cnt = 0;
+        for (int k = 0; k < kSubsPerChunk; ++k)
+            if ((slots[tid].sub.e[k] & kFlag) && cnt < kRawPerSlot) slots[tid].rawsub[cnt++] = (uint8_t)k;
+        for (; cnt < kRawPerSlot; ++cnt) slots[tid].rawsub[cnt] = 0xff;
+    }
+    __syncthreads();
+    for (int i = tid; i < nsl * kRawPerSlot * kSub; i += kSpineNT) {
+        const int sl = i / (kRawPerSlot * kSub), r = (i / kSub) % kRawPerSlot, j = i % kSub;
+        const int k = slots[sl].rawsub[r];
+        if (k != 0xff) {
+            const int64_t idx = (int64_t)slot_chunk[sl] * kChunk + k * kSub + j;
+            slots[sl].raw[r][j] = idx < n ? f2b(src.get(idx, shift, totalw)) : 0u;
+        }
+    }
+    __syncthreads();
+    if (tid >= 32) return;
+
+    // ---- the walk (one warp)
     uint32_t bits = 0u;  // the running sum starts at +0
     int c = 0;
     while (c < nchunks) {
         const uint32_t E = phase_of(bits), S = bits - (E << 23);
-        const int W = min(nchunks - c, kSpineNT);
-        Pair mine = identity_pair();
-        if ((int)threadIdx.x < W) {
-            const Summary s = sums[c + threadIdx.x];
-            if (E == s.e) mine = s.q[0];
-            else if (E == s.e + 1u) mine = s.q[1];
-            else mine = Pair{kSatCap, kSatCap};  // wrong guess: force a resolve
-        }
-        if (threadIdx.x == 0) first_bad = INT_MAX;
-        Pair all;
-        const Pair ex = block_exclusive_scan<kSpineNT>(mine, rs.tot, &all);
-        const uint32_t s_in = apply(ex, S);
-        const uint32_t s_out = s_in + ((s_in & 1u) ? mine.d1 : mine.d0);
-        const bool in_win = (int)threadIdx.x < W;
-        if (in_win && s_in < kPhaseLimit && s_out >= kPhaseLimit) atomicMin(&first_bad, (int)threadIdx.x);
-        __syncthreads();
-        const int f = first_bad;
-        if (in_win && (int)threadIdx.x <= min(f, W - 1)) start_bits[c + threadIdx.x] = bits_of(E, s_in);
-        if (f == INT_MAX) {
-            bits = bits_of(E, apply(all, S));
-            c += W;
-            __syncthreads();
+        const int cc = c + lane;
+        const bool valid = cc < nchunks;
+        const Pair m = valid ? pick_map(E, ce[cc], Pair{qa0[cc], qa1[cc]}, Pair{qb0[cc], qb1[cc]}) : identity_pair();
+        const Pair inc = warp_scan_pair(m, lane);
+        Pair ex = shfl_up_pair(inc, 1);
+        if (lane == 0) ex = identity_pair();
+        const uint32_t s_in = apply(ex, S), s_out = apply(inc, S);
+        const unsigned mask = __ballot_sync(0xffffffffu, valid && s_out >= kPhaseLimit);
+        const int f = mask ? __ffs(mask) - 1 : 32;
+        if (valid && lane <= f) start_bits[cc] = bits_of(E, s_in);
+        if (f == 32) {
+            bits = bits_of(E, __shfl_sync(0xffffffffu, s_out, min(31, nchunks - 1 - c)));
+            c += 32;
             continue;
         }
-        // chunk c+f leaves the phase (or was guessed wrong): resolve it exactly
-        if ((int)threadIdx.x == f) rs.next_bits = bits_of(E, s_in);
-        __syncthreads();
-        const uint32_t start = rs.next_bits;
-        __syncthreads();
-        const int64_t e0 = (int64_t)(c + f) * kChunk;
-        const int len = (int)min((int64_t)kChunk, n - e0);
-        uint32_t pb[kSpineIPT];
-        load_chunk<kSpineNT, kSpineIPT>(src, e0, len, pb);
-        bits = resolve_chunk<kSpineNT, kSpineIPT>(pb, len, start, nullptr, 1.f, &rs);
-        c += f + 1;
+        // chunk d changes phase (or was guessed wrong): resolve it exactly, inside the warp
+        const int d = c + f;
+        uint32_t b = bits_of(E, __shfl_sync(0xffffffffu, s_in, f));
+        const bool have_sub = (ce[d] & kFlag) != 0u;
+        const int slot = (int)slot_of[d] - 1;
+        if (have_sub) {
+            uint32_t se; Pair m0, m1;
+            if (slot >= 0) { se = slots[slot].sub.e[lane]; m0 = slots[slot].sub.q0[lane]; m1 = slots[slot].sub.q1[lane]; }
+            else { const SubSummary* g = subs + sums[d].pad[0]; se = g->e[lane]; m0 = g->q0[lane]; m1 = g->q1[lane]; }
+            int first = 0;
+            while (first < kSubsPerChunk) {
+                const uint32_t E2 = phase_of(b), S2 = b - (E2 << 23);
+                const Pair mm = lane >= first ? pick_map(E2, se, m0, m1) : identity_pair();
+                const Pair inc2 = warp_scan_pair(mm, lane);
+                Pair ex2 = shfl_up_pair(inc2, 1);
+                if (lane == 0) ex2 = identity_pair();
+                const uint32_t si = apply(ex2, S2), so = apply(inc2, S2);
+                const unsigned m2 = __ballot_sync(0xffffffffu, lane >= first && so >= kPhaseLimit);
+                if (!m2) { b = bits_of(E2, __shfl_sync(0xffffffffu, so, 31)); break; }
+                const int f2 = __ffs(m2) - 1;
+                const uint32_t sb = bits_of(E2, __shfl_sync(0xffffffffu, si, f2));
+                // the 64 raw candidates of sub-chunk f2: prefetched, or staged now
+                int r = -1;
+                if (slot >= 0) {
+#pragma unroll
+                    for (int q = 0; q < kRawPerSlot; ++q) if (slots[slot].rawsub[q] == f2) r = q;
+                }
+                const uint32_t* raw;
+                if (r >= 0) raw = slots[slot].raw[r];
+                else {
+                    const int64_t i0 = (int64_t)d * kChunk + f2 * kSub + 2 * lane;
+                    stage[2 * lane] = i0 < n ? f2b(src.get(i0, shift, totalw)) : 0u;
+                    stage[2 * lane + 1] = i0 + 1 < n ? f2b(src.get(i0 + 1, shift, totalw)) : 0u;
+                    __syncwarp();
+                    raw = stage;
+                }
+                b = serial_chain(sb, raw, kSub);
+                __syncwarp();
+                first = f2 + 1;
+            }
+        } else {
+            // no sub-summaries (the chunk was not expected to change phase): stage it and go
+            // through it sub-chunk by sub-chunk.  Slow, rare, exact.
+            const int64_t e0 = (int64_t)d * kChunk;
+            for (int i = lane; i < kChunk; i += 32) stage[i] = e0 + i < n ? f2b(src.get(e0 + i, shift, totalw)) : 0u;
+            __syncwarp();
+            b = serial_chain(b, stage, kChunk);
+            __syncwarp();
+        }
+        bits = b;
+        c = d + 1;
     }
-    if (threadIdx.x == 0) {
+    if (lane == 0) {
         start_bits[nchunks] = bits;
         const float total = b2f(bits);
         *total_out = total;
@@ -589,7 +811,8 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
 
 // workspace carving (all offsets 256-byte aligned)
 struct CdfWs {
-    double* sums; double* approx; Summary* summaries; uint32_t* start_bits; float* total; size_t bytes;
+    double* sums; double* approx; int* slotid; Summary* summaries; SubSummary* subs; uint32_t* start_bits; float* total;
+    size_t bytes;
 };
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 inline CdfWs carve(void* ws, int64_t n) {
@@ -600,6 +823,8 @@ inline CdfWs carve(void* ws, int64_t n) {
     w.sums = reinterpret_cast<double*>(p + off); off += align256(nchunks * 8);
     w.approx = reinterpret_cast<double*>(p + off); off += align256((nchunks + 1) * 8);
     w.summaries = reinterpret_cast<Summary*>(p + off); off += align256(nchunks * sizeof(Summary));
+    w.subs = reinterpret_cast<SubSummary*>(p + off); off += align256((size_t)kSubSlots * sizeof(SubSummary));
+    w.slotid = reinterpret_cast<int*>(p + off); off += align256(nchunks * 4);
     w.start_bits = reinterpret_cast<uint32_t*>(p + off); off += align256((nchunks + 1) * 4);
     w.total = reinterpret_cast<float*>(p + off); off += 256;
     w.bytes = off;
@@ -622,9 +847,16 @@ namespace {
 // exact boundaries of the chain over `src` (weights or scores+stats); approx must be filled
 int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_t* status, int check, cudaStream_t st) {
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
-    summarize_kernel<<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.summaries, status, check);
+    summarize_kernel<<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status, check);
     MB_CHECK_LAUNCH("summarize_kernel");
-    spine_kernel<<<1, kSpineNT, 0, st>>>(src, n, nchunks, w.summaries, w.start_bits, w.total, status);
+    const size_t smem = spine_smem_bytes(nchunks);
+    static bool attr_set = false;  // per process; the attribute is sticky per device function
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(spine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spine_smem_bytes(8192));
+        if (e != cudaSuccess) return cuda_fail(e, "spine_kernel smem attribute");
+        attr_set = true;
+    }
+    spine_kernel<<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status);
     MB_CHECK_LAUNCH("spine_kernel");
     return MERCURY_OK;
 }
@@ -648,7 +880,7 @@ int pool_stats_launch(const float* scores, int64_t n, const int64_t* h_bounds, i
     chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, n, w.sums, nullptr, 0);
     MB_CHECK_LAUNCH("chunk_sums_kernel");
     stats_finalize_kernel<<<1, 1024, 0, st>>>(scores, n, w.sums, nchunks, bd, ema_state, ema_first, ema_alpha, smooth_alpha,
-                                              stats, w.approx);
+                                              stats, w.approx, w.slotid, g_guess_bias);
     MB_CHECK_LAUNCH("stats_finalize_kernel");
     return MERCURY_OK;
 }
@@ -675,6 +907,8 @@ int update_draw_launch(const mercury_update_args& a, const float* scores, void* 
 }  // namespace mercury
 
 using namespace mercury;
+
+extern "C" void mercury_test_set_guess_bias(double bias) { g_guess_bias = bias; }
 
 extern "C" size_t mercury_pool_stats_workspace_bytes(int64_t n) { return cdf_ws_bytes(n); }
 
@@ -720,7 +954,7 @@ extern "C" int mercury_cdf(const float* weights, int64_t n, int mode, float* cdf
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
     chunk_sums_kernel<<<nchunks, 256, 0, st>>>(weights, n, w.sums, status, 1);
     MB_CHECK_LAUNCH("chunk_sums_kernel");
-    prefix_finalize_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, w.approx);
+    prefix_finalize_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, w.approx, w.slotid, g_guess_bias);
     MB_CHECK_LAUNCH("prefix_finalize_kernel");
     if (mode == MERCURY_CDF_F64) {
         materialize_f64_kernel<<<nchunks, 256, 0, st>>>(weights, n, w.approx, nchunks, cdf, total, status);
@@ -755,7 +989,7 @@ extern "C" int mercury_sample_with_replacement(const float* cdf, int64_t n, cons
 // fails or fragments that pool), or a small C/Go/Java host binding this ABI that would otherwise
 // have to size a workspace, keep it alive and free it around every call.  They pass only the
 // input and the outputs; the scratch lives in the array below, inside the library image, so
-// every GPU that loads the library carries these 112 KiB until the process exits.
+// every GPU that loads the library carries these 208 KiB until the process exits.
 //
 // The name `g_static_scratch` is only a stand-in on the host side: its device address has to be
 // asked for (cudaGetSymbolAddress) with the right device current, once per device.  The first
@@ -767,7 +1001,7 @@ extern "C" int mercury_sample_with_replacement(const float* cdf, int64_t n, cons
 // whatever the previous call left there; that is harmless because each stage writes a field
 // before any later stage reads it, so nothing in it has to start at zero and nothing is cleared.
 constexpr int64_t kStaticMaxN = (int64_t)MERCURY_STATIC_MAX_N;
-constexpr size_t kStaticScratchBytes = 112 * 1024;
+constexpr size_t kStaticScratchBytes = 208 * 1024;
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
 namespace {

@@ -328,3 +328,23 @@ def test_update_samples_from_precomputed_scores(ops):
     a = ops.update_samples(x.to(DEV), y.to(DEV), u, torch.zeros(1, device=DEV), True)
     b = ops.update_samples(None, y.to(DEV), u, torch.zeros(1, device=DEV), True, scores_in=a.scores)
     assert torch.equal(a.idx, b.idx) and torch.equal(a.nprob, b.nprob) and torch.equal(a.labels, b.labels)
+
+
+@pytest.mark.parametrize("bias", [0.0, 0.5, 0.997, 1.002, 4.0])
+@pytest.mark.parametrize("kind,n", [("uniform", 1000000), ("lognormal_raw", 300000), ("constant", 1 << 21), ("zeros_mixed", 50000)])
+def test_exact_cdf_is_exact_whatever_the_phase_guesses(ops, kind, n, bias):
+    """Guesses only select which maps are precomputed: forcing them wrong must not change a bit."""
+    from mercury_b200 import _lib
+
+    w = _weights(kind, n, seed=11)
+    chain = orc.serial_chain_f32(w.numpy())
+    ref = (chain / chain[-1]).astype(np.float32)
+    lib = _lib.load()
+    lib.mercury_test_set_guess_bias(bias)
+    try:
+        cdf, total = ops.cdf(w.to(DEV), "exact")
+        got = cdf.cpu().numpy()
+    finally:
+        lib.mercury_test_set_guess_bias(1.0)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+    assert total.cpu().numpy().view(np.uint32)[0] == chain[-1:].view(np.uint32)[0]
