@@ -33,6 +33,25 @@ template <> struct Elem<__nv_bfloat16> {
     static constexpr uint32_t kNegInfWord = 0xff80ff80u;
 };
 
+constexpr float kLn2 = 0.6931471805599453f;
+
+// packed bf16x2 max (one ALU op per two logits): NaN-free operand wins, like fmaxf
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+
+// exp(x - m) summed as 2^(x*k - hi) with hi = fl(m*k): one FFMA + one MUFU per logit.  Every
+// term is off by the same factor 2^lo, lo = m*k - hi (exact, from an FMA); `log_fix` removes it
+// from log(sum) afterwards, so nothing is lost against computing (x - m) first.
+struct ExpScale {
+    float hi, lo;
+    __device__ __forceinline__ explicit ExpScale(float m) { hi = m * kLog2e; lo = fmaf(m, kLog2e, -hi); }
+    __device__ __forceinline__ float term(float x) const { return ex2_approx(fmaf(x, kLog2e, -hi)); }
+    __device__ __forceinline__ float log_fix() const { return lo * kLn2; }  // log(sum_true) = log(sum) - log_fix
+};
+
 // label handling shared by all layouts: returns true if the row contributes a loss.
 // Call it from ONE thread per row (it raises the status bit with an atomic).
 __device__ __forceinline__ bool label_ok(int64_t y, int64_t c, int64_t ignore_index, int32_t* status) {
@@ -98,36 +117,39 @@ __global__ void __launch_bounds__(256) score_warp_kernel(const T* __restrict__ l
         if (!ok && lane == 0) label_ok(y, c, ignore_index, status);
         const float xy = ok ? Elem<T>::ld(rp + y) : 0.f;
 
-        float m = -INFINITY;
+        float m;
+        if constexpr (sizeof(T) == 4) {
+            m = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) {
-            const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (sizeof(T) == 4) {
-                    m = fmaxf(m, __uint_as_float(w[q]));
-                } else {
-                    m = fmaxf(m, fmaxf(bf16_lo(w[q]), bf16_hi(w[q])));
-                }
+            for (int i = 0; i < VPL; ++i) {
+                m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(v[i].x), __uint_as_float(v[i].y)),
+                                   fmaxf(__uint_as_float(v[i].z), __uint_as_float(v[i].w))));
             }
+        } else {
+            uint32_t mx = Elem<T>::kNegInfWord;
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) mx = bf16x2_max(bf16x2_max(mx, bf16x2_max(v[i].x, v[i].y)), bf16x2_max(v[i].z, v[i].w));
+            m = fmaxf(bf16_lo(mx), bf16_hi(mx));
         }
         m = warp_max(m);
-        float l = 0.f;
+        const ExpScale es(m);
+        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;  // independent partial sums (ILP)
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
-            const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (sizeof(T) == 4) {
-                    l += ex2_approx((__uint_as_float(w[q]) - m) * kLog2e);
-                } else {
-                    l += ex2_approx((bf16_lo(w[q]) - m) * kLog2e);
-                    l += ex2_approx((bf16_hi(w[q]) - m) * kLog2e);
-                }
+            if constexpr (sizeof(T) == 4) {
+                l0 += es.term(__uint_as_float(v[i].x));
+                l1 += es.term(__uint_as_float(v[i].y));
+                l2 += es.term(__uint_as_float(v[i].z));
+                l3 += es.term(__uint_as_float(v[i].w));
+            } else {
+                l0 += es.term(bf16_lo(v[i].x)); l1 += es.term(bf16_hi(v[i].x));
+                l2 += es.term(bf16_lo(v[i].y)); l3 += es.term(bf16_hi(v[i].y));
+                l0 += es.term(bf16_lo(v[i].z)); l1 += es.term(bf16_hi(v[i].z));
+                l2 += es.term(bf16_lo(v[i].w)); l3 += es.term(bf16_hi(v[i].w));
             }
         }
-        l = warp_sum(l);
-        if (lane == 0) scores[row] = ok ? logf(l) - (xy - m) : 0.f;
+        const float l = warp_sum((l0 + l1) + (l2 + l3));
+        if (lane == 0) scores[row] = ok ? (logf(l) - es.log_fix()) - (xy - m) : 0.f;
     }
 }
 
@@ -309,33 +331,42 @@ score_wide_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labe
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ring->empty[s]);  // the chunk now lives in registers
-                float cm = -INFINITY;
+                float cm;
+                if constexpr (sizeof(T) == 4) {
+                    cm = -INFINITY;
 #pragma unroll
-                for (int i = 0; i < VPT; ++i) {
-                    const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+                    for (int i = 0; i < VPT; ++i)
+                        cm = fmaxf(cm, fmaxf(fmaxf(__uint_as_float(v[i].x), __uint_as_float(v[i].y)),
+                                             fmaxf(__uint_as_float(v[i].z), __uint_as_float(v[i].w))));
+                } else {
+                    uint32_t mx = Elem<T>::kNegInfWord;
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        if (sizeof(T) == 4) cm = fmaxf(cm, __uint_as_float(w[q]));
-                        else cm = fmaxf(cm, fmaxf(bf16_lo(w[q]), bf16_hi(w[q])));
-                    }
+                    for (int i = 0; i < VPT; ++i) mx = bf16x2_max(bf16x2_max(mx, bf16x2_max(v[i].x, v[i].y)), bf16x2_max(v[i].z, v[i].w));
+                    cm = fmaxf(bf16_lo(mx), bf16_hi(mx));
                 }
                 if (cm > -INFINITY) {
                     const float mn = fmaxf(m, cm);
-                    l *= ex2_approx((m - mn) * kLog2e);  // m == -inf -> factor 0 (l is 0 anyway)
-                    m = mn;
+                    const ExpScale es(mn);
+                    float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
 #pragma unroll
                     for (int i = 0; i < VPT; ++i) {
-                        const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            if (sizeof(T) == 4) {
-                                l += ex2_approx((__uint_as_float(w[q]) - m) * kLog2e);
-                            } else {
-                                l += ex2_approx((bf16_lo(w[q]) - m) * kLog2e);
-                                l += ex2_approx((bf16_hi(w[q]) - m) * kLog2e);
-                            }
+                        if constexpr (sizeof(T) == 4) {
+                            p0 += es.term(__uint_as_float(v[i].x));
+                            p1 += es.term(__uint_as_float(v[i].y));
+                            p2 += es.term(__uint_as_float(v[i].z));
+                            p3 += es.term(__uint_as_float(v[i].w));
+                        } else {
+                            p0 += es.term(bf16_lo(v[i].x)); p1 += es.term(bf16_hi(v[i].x));
+                            p2 += es.term(bf16_lo(v[i].y)); p3 += es.term(bf16_hi(v[i].y));
+                            p0 += es.term(bf16_lo(v[i].z)); p1 += es.term(bf16_hi(v[i].z));
+                            p2 += es.term(bf16_lo(v[i].w)); p3 += es.term(bf16_hi(v[i].w));
                         }
                     }
+                    const float ps = (p0 + p1) + (p2 + p3);
+                    // rescale the running sum to the new max (m == -inf -> factor 0, l is 0 anyway) and
+                    // take the common 2^lo factor out of this chunk's terms (|lo*ln2| ~ 1e-6: first order)
+                    l = fmaf(l, ex2_approx((m - mn) * kLog2e), fmaf(ps, -es.log_fix(), ps));
+                    m = mn;
                 }
             }
             // combine the CONSUMERS partial (m, l) pairs: consumers-only named barrier (id 1)
