@@ -31,7 +31,7 @@ extern "C" const char* mercury_last_error(void) { return g_err; }
 
 extern "C" size_t mercury_update_samples_workspace_bytes(int64_t n, int64_t b) {
     (void)b;
-    return cdf_ws_bytes(n);
+    return update_ws_bytes(n);
 }
 
 extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, size_t ws_bytes, void* stream) {
@@ -54,16 +54,18 @@ extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, si
                      "mercury_update_samples: pool sizes must be ascending in [1, n]");
     }
     MB_CHECK_ARG(a->n_bounds == 0 || a->h_bounds[a->n_bounds - 1] == a->n, "mercury_update_samples: last pool size must equal n");
-    int rc = check_ws(ws, ws_bytes, cdf_ws_bytes(a->n), "mercury_update_samples");
+    int rc = check_ws(ws, ws_bytes, update_ws_bytes(a->n), "mercury_update_samples");
     if (rc) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const double* part = nullptr;
+    int per = 0;
     if (!scores) {
-        rc = score_dispatch(a->logits, a->dtype, a->labels, a->n, a->c, a->row_stride, a->ignore_index, a->scores, a->status, st);
+        double* part_buf = update_ws_part_sums(ws, a->n);
+        rc = score_dispatch(a->logits, a->dtype, a->labels, a->n, a->c, a->row_stride, a->ignore_index, a->scores, a->status, st,
+                            part_buf, &per);
         if (rc) return rc;
         scores = a->scores;
+        part = part_buf;
     }
-    rc = pool_stats_launch(scores, a->n, a->h_bounds, a->n_bounds, a->ema_state, a->ema_first, a->ema_alpha, a->smooth_alpha,
-                           a->stats, ws, st);
-    if (rc) return rc;
-    return update_draw_launch(*a, scores, ws, st);
+    return update_tail_launch(*a, scores, part, per, ws, st);
 }

@@ -185,7 +185,7 @@ __device__ uint32_t resolve_chunk(const uint32_t (&pb)[IPT], int len, uint32_t b
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
             const int i = base + k;
-            if (i >= pos && i < len) loc = compose(loc, addend_pair(pb[k], E));
+            if (i >= pos && i < len) loc = compose(loc, addend_pair_fast(pb[k], E));
         }
         if (threadIdx.x == 0) sm->cross = INT_MAX;
         const Pair ex = block_exclusive_scan<NT>(loc, sm->tot, nullptr);  // (its barriers publish cross)
@@ -197,7 +197,7 @@ __device__ uint32_t resolve_chunk(const uint32_t (&pb)[IPT], int len, uint32_t b
         for (int k = 0; k < IPT; ++k) {
             const int i = base + k;
             if (i >= pos && i < len && my_cross == INT_MAX) {
-                const Pair d = addend_pair(pb[k], E);
+                const Pair d = addend_pair_fast(pb[k], E);
                 const uint32_t sn = s + ((s & 1u) ? d.d1 : d.d0);
                 if (sn >= kPhaseLimit) {
                     my_cross = i; s_before = s; k_cross = k;
@@ -234,15 +234,20 @@ __device__ uint32_t resolve_chunk(const uint32_t (&pb)[IPT], int len, uint32_t b
 }
 
 template <int NT, int IPT>
-__device__ __forceinline__ void load_chunk(const WeightSrc& src, int64_t start, int len, uint32_t (&pb)[IPT]) {
-    float shift, total;
-    src.prepare(shift, total);
+__device__ __forceinline__ void load_chunk(const WeightSrc& src, int64_t start, int len, uint32_t (&pb)[IPT], float shift,
+                                           float total) {
     const int base = threadIdx.x * IPT;
 #pragma unroll
     for (int k = 0; k < IPT; ++k) {
         const int i = base + k;
         pb[k] = i < len ? f2b(src.get(start + i, shift, total)) : 0u;
     }
+}
+template <int NT, int IPT>
+__device__ __forceinline__ void load_chunk(const WeightSrc& src, int64_t start, int len, uint32_t (&pb)[IPT]) {
+    float shift, total;
+    src.prepare(shift, total);
+    load_chunk<NT, IPT>(src, start, len, pb, shift, total);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -344,25 +349,74 @@ double g_guess_bias = 1.0;  // test hook (mercury_test_set_guess_bias): scales e
 constexpr int kSumNT = 256, kSumIPT = kChunk / kSumNT;
 static_assert(kSumIPT * 8 == kSub, "a sub-chunk is 8 consecutive threads");
 
+// Statistics folded into the summaries (pools of up to kFusedMaxChunks chunks, one EMA update):
+// every CTA reduces the partial sums of the scores itself -- same data, same order, so all CTAs
+// agree to the bit on mean / EMA / shift / total -- which removes a single-CTA kernel from the
+// dependency chain.  CTA 0 publishes the statistics block; the spine stores the new EMA state.
+constexpr int kFusedMaxChunks = 2048;
+struct FusedStats {
+    const double* part;  // sums of `per` consecutive scores each (per divides kChunk)
+    int npart, per;
+    const float* ema_in; int ema_first; double ema_alpha, smooth_alpha;
+    float* stats;
+};
+
+template <bool FUSED>
 __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_t n, const double* __restrict__ approx,
                                                            const int* __restrict__ slotid, double bias,
                                                            Summary* __restrict__ out, SubSummary* __restrict__ subs,
-                                                           int32_t* status, int check) {
+                                                           int32_t* status, int check, FusedStats fs) {
     __shared__ Pair wt[2][kSumNT / 32];
     __shared__ float wsum[kSumNT / 32];
     __shared__ int wnz[kSumNT / 32];
+    __shared__ double dred[3][kSumNT / 32];
     const int64_t start = (int64_t)blockIdx.x * kChunk;
     const int len = (int)min((int64_t)kChunk, n - start);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t pb[kSumIPT];
-    load_chunk<kSumNT, kSumIPT>(src, start, len, pb);
+    double a_lo, a_hi;
+    int slot;
+    if constexpr (FUSED) {
+        const int first_part = (int)(start / fs.per), parts_per_chunk = kChunk / fs.per;
+        double tot = 0.0, pre = 0.0, own = 0.0;
+        for (int i = threadIdx.x; i < fs.npart; i += kSumNT) {
+            const double v = fs.part[i];
+            tot += v;
+            if (i < first_part) pre += v;
+            else if (i < first_part + parts_per_chunk) own += v;
+        }
+        tot = warp_sum(tot); pre = warp_sum(pre); own = warp_sum(own);
+        if (lane == 0) { dred[0][warp] = tot; dred[1][warp] = pre; dred[2][warp] = own; }
+        __syncthreads();
+        tot = pre = own = 0.0;
+#pragma unroll
+        for (int i = 0; i < kSumNT / 32; ++i) { tot += dred[0][i]; pre += dred[1][i]; own += dred[2][i]; }
+        // pytorch_collab.py:109-112 -- mean, EMA (util.py:207-213), shift = alpha*ema, total = sum(s + shift)
+        const float mean = (float)(tot / (double)n);
+        const float a = (float)fs.ema_alpha, one_minus_a = (float)(1.0 - fs.ema_alpha);
+        const float ema = fs.ema_first ? mean : __fadd_rn(__fmul_rn(a, *fs.ema_in), __fmul_rn(one_minus_a, mean));
+        const float shift = __fmul_rn((float)fs.smooth_alpha, ema);
+        const float total = (float)(tot + (double)n * (double)shift);
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            fs.stats[MERCURY_STAT_MEAN] = mean; fs.stats[MERCURY_STAT_EMA] = ema;
+            fs.stats[MERCURY_STAT_SHIFT] = shift; fs.stats[MERCURY_STAT_TOTAL] = total;
+            fs.stats[4] = fs.stats[5] = fs.stats[6] = fs.stats[7] = 0.f;
+        }
+        a_lo = (pre + (double)start * (double)shift) / (double)total;
+        a_hi = a_lo + (own + (double)len * (double)shift) / (double)total;
+        load_chunk<kSumNT, kSumIPT>(WeightSrc{src.w, fs.stats}, start, len, pb, shift, total);
+        slot = -2;  // decided below: flagged chunks index `subs` directly
+    } else {
+        a_lo = approx[blockIdx.x]; a_hi = approx[blockIdx.x + 1];
+        slot = slotid[blockIdx.x];
+        load_chunk<kSumNT, kSumIPT>(src, start, len, pb);
+    }
     // Guess the phase from the approximate running total at both ends of the chunk.  If both ends
     // agree the chunk is expected to stay in one phase; otherwise it is flagged: it also gets the
     // map for the next phase and (if a slot was assigned by the prefix scan) sub-chunk summaries.
-    const double a_lo = approx[blockIdx.x], a_hi = approx[blockIdx.x + 1];
     uint32_t e;
     const bool flagged = guess_span(a_lo, a_hi, bias, &e);  // block-uniform
-    const int slot = slotid[blockIdx.x];
+    if (FUSED) slot = flagged ? (int)blockIdx.x : -1;
     Pair a0 = identity_pair(), a1 = identity_pair();
     int bad = 0;
     bool nz = false;
@@ -376,24 +430,32 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         }
         nz |= pb[k] != 0u;
         tsum += x;
-        a0 = compose(a0, addend_pair(pb[k], e));
-        if (flagged) a1 = compose(a1, addend_pair(pb[k], e + 1u));
+        a0 = compose(a0, addend_pair_fast(pb[k], e));
+        if (flagged) a1 = compose(a1, addend_pair_fast(pb[k], e + 1u));
     }
     if (bad) atomicOr(status, bad);
     const unsigned nzmask = __ballot_sync(0xffffffffu, nz);
-    // ordered reduction: lane 0 ends with the composition of the whole warp
+    // ordered reduction: lane 0 ends with the composition of the whole warp.  Without exact ties
+    // every map is a plain increment and the composition is one integer warp reduction.
+    if (__ballot_sync(0xffffffffu, a0.d0 != a0.d1 || a1.d0 != a1.d1) == 0u) {
+        a0.d0 = a0.d1 = sat(__reduce_add_sync(0xffffffffu, a0.d0));
+        a1.d0 = a1.d1 = sat(__reduce_add_sync(0xffffffffu, a1.d0));
+    } else {
 #pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        Pair o0, o1;
-        o0.d0 = __shfl_down_sync(0xffffffffu, a0.d0, off); o0.d1 = __shfl_down_sync(0xffffffffu, a0.d1, off);
-        o1.d0 = __shfl_down_sync(0xffffffffu, a1.d0, off); o1.d1 = __shfl_down_sync(0xffffffffu, a1.d1, off);
-        if (lane + off < 32) { a0 = compose(a0, o0); a1 = compose(a1, o1); }
+        for (int off = 1; off < 32; off <<= 1) {
+            Pair o0, o1;
+            o0.d0 = __shfl_down_sync(0xffffffffu, a0.d0, off); o0.d1 = __shfl_down_sync(0xffffffffu, a0.d1, off);
+            o1.d0 = __shfl_down_sync(0xffffffffu, a1.d0, off); o1.d1 = __shfl_down_sync(0xffffffffu, a1.d1, off);
+            if (lane + off < 32) { a0 = compose(a0, o0); a1 = compose(a1, o1); }
+        }
     }
-    float inc = tsum;  // inclusive scan of the thread sums (approximate, only feeds guesses)
+    float inc = tsum;  // inclusive scan of the thread sums (approximate, only feeds sub-chunk guesses)
+    if (slot >= 0) {
 #pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        const float o = __shfl_up_sync(0xffffffffu, inc, off);
-        if (lane >= off) inc += o;
+        for (int off = 1; off < 32; off <<= 1) {
+            const float o = __shfl_up_sync(0xffffffffu, inc, off);
+            if (lane >= off) inc += o;
+        }
     }
     if (lane == 0) { wt[0][warp] = a0; wt[1][warp] = a1; wnz[warp] = nzmask != 0u; }
     if (lane == 31) wsum[warp] = inc;
@@ -422,8 +484,8 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
     Pair m0 = identity_pair(), m1 = identity_pair();
 #pragma unroll
     for (int k = 0; k < kSumIPT; ++k) {
-        m0 = compose(m0, addend_pair(pb[k], es));
-        m1 = compose(m1, addend_pair(pb[k], es + 1u));
+        m0 = compose(m0, addend_pair_fast(pb[k], es));
+        m1 = compose(m1, addend_pair_fast(pb[k], es + 1u));
     }
 #pragma unroll
     for (int off = 1; off < 8; off <<= 1) {
@@ -502,7 +564,7 @@ __device__ __forceinline__ uint32_t serial_chain(uint32_t b, const uint32_t* __r
 
 __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
                                                          const SubSummary* __restrict__ subs, uint32_t* __restrict__ start_bits,
-                                                         float* __restrict__ total_out, int32_t* status) {
+                                                         float* __restrict__ total_out, int32_t* status, float* ema_out) {
     extern __shared__ __align__(128) unsigned char sm[];
     __shared__ int nslots_s;
     __shared__ int slot_chunk[kMaxSlots];   // chunk held by each shared-memory slot
@@ -629,6 +691,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
         c = d + 1;
     }
     if (lane == 0) {
+        if (ema_out) *ema_out = src.stats[MERCURY_STAT_EMA];  // fused statistics: EMAverage.value for the next call
         start_bits[nchunks] = bits;
         const float total = b2f(bits);
         *total_out = total;
@@ -815,15 +878,18 @@ struct CdfWs {
     size_t bytes;
 };
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
-inline CdfWs carve(void* ws, int64_t n) {
+inline CdfWs carve(void* ws, int64_t n, bool direct_subs = false) {
     const size_t nchunks = (size_t)((n + kChunk - 1) / kChunk);
+    const size_t nsubs = direct_subs && nchunks <= (size_t)kFusedMaxChunks ? (nchunks > (size_t)kSubSlots ? nchunks : (size_t)kSubSlots)
+                                                                          : (size_t)kSubSlots;
+    const size_t nsums = direct_subs ? (size_t)(n / 128 + 2) : nchunks;
     unsigned char* p = static_cast<unsigned char*>(ws);
     CdfWs w;
     size_t off = 0;
-    w.sums = reinterpret_cast<double*>(p + off); off += align256(nchunks * 8);
+    w.sums = reinterpret_cast<double*>(p + off); off += align256(nsums * 8);
     w.approx = reinterpret_cast<double*>(p + off); off += align256((nchunks + 1) * 8);
     w.summaries = reinterpret_cast<Summary*>(p + off); off += align256(nchunks * sizeof(Summary));
-    w.subs = reinterpret_cast<SubSummary*>(p + off); off += align256((size_t)kSubSlots * sizeof(SubSummary));
+    w.subs = reinterpret_cast<SubSummary*>(p + off); off += align256(nsubs * sizeof(SubSummary));
     w.slotid = reinterpret_cast<int*>(p + off); off += align256(nchunks * 4);
     w.start_bits = reinterpret_cast<uint32_t*>(p + off); off += align256((nchunks + 1) * 4);
     w.total = reinterpret_cast<float*>(p + off); off += 256;
@@ -845,9 +911,16 @@ int check_ws(void* ws, size_t have, size_t need, const char* who) {
 namespace {
 
 // exact boundaries of the chain over `src` (weights or scores+stats); approx must be filled
-int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_t* status, int check, cudaStream_t st) {
+int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_t* status, int check, cudaStream_t st,
+                         const FusedStats* fused = nullptr, float* ema_out = nullptr) {
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
-    summarize_kernel<<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status, check);
+    if (fused) {
+        summarize_kernel<true><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status,
+                                                           check, *fused);
+    } else {
+        summarize_kernel<false><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status,
+                                                            check, FusedStats{});
+    }
     MB_CHECK_LAUNCH("summarize_kernel");
     const size_t smem = spine_smem_bytes(nchunks);
     static bool attr_set = false;  // per process; the attribute is sticky per device function
@@ -856,7 +929,7 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel smem attribute");
         attr_set = true;
     }
-    spine_kernel<<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status);
+    spine_kernel<<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out);
     MB_CHECK_LAUNCH("spine_kernel");
     return MERCURY_OK;
 }
@@ -864,10 +937,11 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
 }  // namespace
 
 size_t cdf_ws_bytes(int64_t n) { return carve(nullptr, n < 1 ? 1 : n).bytes; }
+size_t update_ws_bytes(int64_t n) { return carve(nullptr, n < 1 ? 1 : n, true).bytes; }
 
 int pool_stats_launch(const float* scores, int64_t n, const int64_t* h_bounds, int n_bounds, float* ema_state, int ema_first,
-                      double ema_alpha, double smooth_alpha, float* stats, void* ws, cudaStream_t st) {
-    const CdfWs w = carve(ws, n);
+                      double ema_alpha, double smooth_alpha, float* stats, void* ws, cudaStream_t st, bool update_layout) {
+    const CdfWs w = carve(ws, n, update_layout);
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
     Bounds bd;
     if (n_bounds > 0) {
@@ -885,11 +959,31 @@ int pool_stats_launch(const float* scores, int64_t n, const int64_t* h_bounds, i
     return MERCURY_OK;
 }
 
-int update_draw_launch(const mercury_update_args& a, const float* scores, void* ws, cudaStream_t st) {
-    const CdfWs w = carve(ws, a.n);
+// statistics + boundaries + draw for the whole-step entry point.  `part`/`per` are the partial
+// sums K1 produced on the way (per == 0: none, a chunk-sum pass runs instead).
+int update_tail_launch(const mercury_update_args& a, const float* scores, const double* part, int per, void* ws, cudaStream_t st) {
+    const CdfWs w = carve(ws, a.n, true);
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
     WeightSrc src{scores, a.stats};
-    int rc = run_exact_boundaries(src, a.n, w, a.status, 1, st);
+    int rc;
+    if (a.n_bounds == 0 && nchunks <= kFusedMaxChunks) {
+        if (per == 0) {
+            chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, a.n, w.sums, nullptr, 0);
+            MB_CHECK_LAUNCH("chunk_sums_kernel");
+            part = w.sums;
+            per = kChunk;
+        }
+        FusedStats fs;
+        fs.part = part; fs.per = per; fs.npart = (int)((a.n + per - 1) / per);
+        fs.ema_in = a.ema_state; fs.ema_first = a.ema_first; fs.ema_alpha = a.ema_alpha; fs.smooth_alpha = a.smooth_alpha;
+        fs.stats = a.stats;
+        rc = run_exact_boundaries(src, a.n, w, a.status, 1, st, &fs, a.ema_state);
+    } else {
+        rc = pool_stats_launch(scores, a.n, a.h_bounds, a.n_bounds, a.ema_state, a.ema_first, a.ema_alpha, a.smooth_alpha, a.stats,
+                               ws, st, true);
+        if (rc) return rc;
+        rc = run_exact_boundaries(src, a.n, w, a.status, 1, st);
+    }
     if (rc) return rc;
     if (a.b > 0) {
         DrawArgs d;
@@ -903,6 +997,8 @@ int update_draw_launch(const mercury_update_args& a, const float* scores, void* 
     }
     return MERCURY_OK;
 }
+
+double* update_ws_part_sums(void* ws, int64_t n) { return carve(ws, n, true).sums; }
 
 }  // namespace mercury
 
@@ -927,7 +1023,7 @@ extern "C" int mercury_pool_stats(const float* scores, int64_t n, const int64_t*
     int rc = check_ws(ws, ws_bytes, cdf_ws_bytes(n), "mercury_pool_stats");
     if (rc) return rc;
     return pool_stats_launch(scores, n, h_bounds, n_bounds, ema_state, ema_first, ema_alpha, smooth_alpha, stats, ws,
-                             static_cast<cudaStream_t>(stream));
+                             static_cast<cudaStream_t>(stream), false);
 }
 
 extern "C" int mercury_normalize(const float* scores, int64_t n, const float* stats, float* p, void* stream) {

@@ -13,6 +13,7 @@
 #include <math.h>
 
 #include "common.cuh"
+#include "internal.cuh"
 
 namespace mercury {
 
@@ -20,6 +21,7 @@ namespace {
 
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr int kProducerThreads = 32;
+constexpr int kSmallHeader = 512;  // ring barriers + per-warp partial sums in front of the stages
 
 template <typename T> struct Elem;
 template <> struct Elem<float> {
@@ -175,17 +177,18 @@ __device__ __forceinline__ void ring_init(Ring<STAGES>* ring, int consumer_warps
 // small rows: tile = TR rows of logits + their labels per stage; consumers own rows.
 // CT > 0: compile-time class count (rows cached in registers); CT == 0: run-time class count.
 template <typename T, int CT, int STAGES, int CONSUMERS>
-__global__ void __launch_bounds__(CONSUMERS + kProducerThreads, 1)
+__global__ void __launch_bounds__(CONSUMERS + kProducerThreads, 3)
 score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels, int64_t n, int c_rt, int tile_rows,
-                   int64_t ignore_index, float* __restrict__ scores, int32_t* status) {
+                   int64_t ignore_index, float* __restrict__ scores, int32_t* status, double* __restrict__ tile_sums) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int c = CT > 0 ? CT : c_rt;
     Ring<STAGES>* ring = reinterpret_cast<Ring<STAGES>*>(smem);
     const uint32_t logit_bytes = (uint32_t)tile_rows * c * sizeof(T);
     const uint32_t logit_slot = (logit_bytes + 127u) & ~127u;
     const uint32_t stage_bytes = logit_slot + (uint32_t)tile_rows * 8u;
-    unsigned char* stage0 = smem + 128;
-    static_assert(sizeof(Ring<STAGES>) <= 128, "ring header");
+    double* tred = reinterpret_cast<double*>(smem + 128);  // [2][CONSUMERS / 32] per-warp score sums
+    unsigned char* stage0 = smem + kSmallHeader;
+    static_assert(sizeof(Ring<STAGES>) <= 128 && 128 + 2 * (CONSUMERS / 32) * 8 <= kSmallHeader, "header layout");
     ring_init(ring, CONSUMERS / 32);
 
     const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
@@ -230,10 +233,11 @@ score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ lab
             const unsigned char* base = stage0 + (size_t)s * stage_bytes;
             const T* tl = reinterpret_cast<const T*>(base);
             const int64_t* ty = reinterpret_cast<const int64_t*>(base + logit_slot);
+            double tile_acc = 0.0;
             for (int r = t; r < rows; r += CONSUMERS) {
                 const T* rp = tl + (size_t)r * c;
                 const int64_t y = ty[r];
-                float m = -INFINITY, l = 0.f;
+                float m = -INFINITY, l = 0.f, fix = 0.f;
                 if constexpr (CT > 0) {
                     float x[CT > 0 ? CT : 1];
                     if constexpr (sizeof(T) == 4 && (CT % 2) == 0) {
@@ -249,8 +253,13 @@ score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ lab
                     }
 #pragma unroll
                     for (int j = 0; j < CT; ++j) m = fmaxf(m, x[j]);
+                    const ExpScale es(m);
+                    float la = 0.f, lb = 0.f;
 #pragma unroll
-                    for (int j = 0; j < CT; ++j) l += ex2_approx((x[j] - m) * kLog2e);
+                    for (int j = 0; j + 1 < CT; j += 2) { la += es.term(x[j]); lb += es.term(x[j + 1]); }
+                    if (CT & 1) la += es.term(x[CT - 1]);
+                    l = la + lb;
+                    fix = es.log_fix();
                 } else {
                     // rotate the start column by the row so that lanes hit different banks
                     int j0 = r % c;
@@ -266,11 +275,24 @@ score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ lab
                     }
                 }
                 float out = 0.f;
-                if (label_ok(y, c, ignore_index, status)) out = logf(l) - (Elem<T>::ld(rp + y) - m);
+                if (label_ok(y, c, ignore_index, status)) out = (logf(l) - fix) - (Elem<T>::ld(rp + y) - m);
                 scores[row0 + r] = out;
+                tile_acc += (double)out;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&ring->empty[s]);
+            if (tile_sums) {  // sum of this tile's scores, fixed order: feeds the pool statistics
+                tile_acc = warp_sum(tile_acc);
+                double* buf = tred + (it & 1) * (CONSUMERS / 32);
+                if (lane == 0) buf[(t >> 5)] = tile_acc;
+                asm volatile("bar.sync 2, %0;" ::"n"(CONSUMERS) : "memory");
+                if (t == 0) {
+                    double sum = 0.0;
+#pragma unroll
+                    for (int i = 0; i < CONSUMERS / 32; ++i) sum += buf[i];
+                    tile_sums[tile] = sum;
+                }
+            }
         }
     }
 }
@@ -395,24 +417,28 @@ score_wide_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labe
 
 template <typename T>
 int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride, int64_t ignore_index,
-                 float* scores, int32_t* status, cudaStream_t st) {
+                 float* scores, int32_t* status, cudaStream_t st, double* part_sums, int* per_out) {
+    if (per_out) *per_out = 0;
     const int64_t row_bytes = c * (int64_t)sizeof(T);
     const bool base16 = (reinterpret_cast<uintptr_t>(logits) & 15) == 0;
     const bool stride16 = ((row_stride * (int64_t)sizeof(T)) & 15) == 0;
     const bool lab16 = (reinterpret_cast<uintptr_t>(labels) & 15) == 0;
 
     if (row_stride == c && base16 && lab16 && row_bytes <= 256) {
-        constexpr int STAGES = 3, CONSUMERS = 512;
-        int tile_rows = row_bytes <= 40 ? 1024 : row_bytes <= 88 ? 512 : row_bytes <= 184 ? 256 : 128;
+        constexpr int STAGES = 3, CONSUMERS = 256;
+        // ~24 KB per stage: three CTAs (27 warps) share an SM and cover each other's stalls
+        int tile_rows = row_bytes <= 40 ? 512 : row_bytes <= 88 ? 256 : row_bytes <= 184 ? 128 : 64;
         const size_t logit_slot = ((size_t)tile_rows * row_bytes + 127) & ~(size_t)127;
-        const size_t smem = 128 + STAGES * (logit_slot + (size_t)tile_rows * 8);
+        const size_t smem = kSmallHeader + STAGES * (logit_slot + (size_t)tile_rows * 8);
         const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
-        const int grid = (int)min_i64(ntiles, kSMs);
+        const int grid = (int)min_i64(ntiles, 3 * kSMs);
         auto go = [&](auto kern) -> int {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (e != cudaSuccess) return cuda_fail(e, "score_small smem attribute");
-            kern<<<grid, CONSUMERS + kProducerThreads, smem, st>>>(logits, labels, n, (int)c, tile_rows, ignore_index, scores, status);
+            kern<<<grid, CONSUMERS + kProducerThreads, smem, st>>>(logits, labels, n, (int)c, tile_rows, ignore_index, scores, status,
+                                                                   part_sums);
             MB_CHECK_LAUNCH("score_small_kernel");
+            if (per_out && part_sums) *per_out = tile_rows;
             return MERCURY_OK;
         };
         if (c == 10) return go(score_small_kernel<T, 10, STAGES, CONSUMERS>);
@@ -453,11 +479,14 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
 }  // namespace
 
 int score_dispatch(const void* logits, int dtype, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride,
-                   int64_t ignore_index, float* scores, int32_t* status, cudaStream_t st) {
+                   int64_t ignore_index, float* scores, int32_t* status, cudaStream_t st, double* part_sums, int* per_out) {
+    if (per_out) *per_out = 0;
     if (n == 0) return MERCURY_OK;
     if (dtype == MERCURY_F32)
-        return launch_score(static_cast<const float*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st);
-    return launch_score(static_cast<const __nv_bfloat16*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st);
+        return launch_score(static_cast<const float*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st,
+                            part_sums, per_out);
+    return launch_score(static_cast<const __nv_bfloat16*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st,
+                        part_sums, per_out);
 }
 
 }  // namespace mercury

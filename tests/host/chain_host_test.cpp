@@ -34,7 +34,12 @@ static uint32_t resolve_chunk(const float* p, int len, uint32_t bits, uint32_t* 
         Pair acc = identity_pair();
         uint32_t prevS = S;
         for (int k = pos; k < len; ++k) {
-            acc = compose(acc, addend_pair(f2b(p[k]), E));
+            const Pair slow = addend_pair(f2b(p[k]), E), fast = addend_pair_fast(f2b(p[k]), E);
+            if (slow.d0 != fast.d0 || slow.d1 != fast.d1) {
+                printf("addend_pair_fast mismatch: p=%08x E=%u slow=(%u,%u) fast=(%u,%u)\n", f2b(p[k]), E, slow.d0, slow.d1, fast.d0, fast.d1);
+                exit(2);
+            }
+            acc = compose(acc, fast);
             uint32_t Sk = apply(acc, S);
             if (Sk >= kPhaseLimit) { cross = k; break; }
             if (out) out[k] = bits_of(E, Sk);
@@ -71,7 +76,14 @@ static bool run_case(const char* name, const std::vector<float>& p, int chunk, d
         sum[c].e = e;
         for (int v = 0; v < 2; ++v) {
             Pair acc = identity_pair();
-            for (size_t i = c * chunk; i < n && i < (c + 1) * chunk; ++i) acc = compose(acc, addend_pair(f2b(p[i]), e + v));
+            for (size_t i = c * chunk; i < n && i < (c + 1) * chunk; ++i) {
+                const Pair slow = addend_pair(f2b(p[i]), e + v), fast = addend_pair_fast(f2b(p[i]), e + v);
+                if (slow.d0 != fast.d0 || slow.d1 != fast.d1) {
+                    printf("addend_pair_fast mismatch: p=%08x E=%u slow=(%u,%u) fast=(%u,%u)\n", f2b(p[i]), e + v, slow.d0, slow.d1, fast.d0, fast.d1);
+                    exit(2);
+                }
+                acc = compose(acc, fast);
+            }
             sum[c].q[v] = acc;
         }
     }
