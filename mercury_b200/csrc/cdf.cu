@@ -18,6 +18,9 @@
 // A wrong guess costs time, never correctness.
 #include <math.h>
 
+#include <cstddef>
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "chain.cuh"
@@ -53,19 +56,25 @@ struct WeightSrc {
 
 // ---------------------------------------------------------------------------------------------
 // phase guesses (used only to choose which maps to precompute; a wrong guess costs time, not bits)
-constexpr uint32_t kAnyPhase = 0x3ffu;   // all addends zero: the identity map in every phase
-constexpr uint32_t kFlag = 0x80000000u;  // chunk: sub-summaries present; sub-chunk: phase change expected
+constexpr uint32_t kAnyPhase = 0x3ffu;    // all addends zero: the identity map in every phase
+constexpr uint32_t kPhaseMask = 0x3ffu;
+constexpr uint32_t kFlag = 0x80000000u;   // chunk: pack present; sub-chunk: sum it serially (phase change expected)
+constexpr uint32_t kTie0 = 0x40000000u;   // the map for the guessed phase is not a plain increment (exact ties inside)
+constexpr uint32_t kTie1 = 0x20000000u;   // ... nor is the map for the phase above
+constexpr uint32_t kNoPack = 0x10000000u; // chunk expected to change phase but no pack slot was left for it
 constexpr int kSub = 64, kSubsPerChunk = kChunk / kSub;
-constexpr int kSubSlots = 128;           // flagged chunks that get sub-chunk summaries
-constexpr double kGuessMargin = 1.0 / 1024.0;
+constexpr int kSubSlots = 128;            // flagged chunks that get a pack (compact layout)
+constexpr int kRawPerPack = 6;
+constexpr double kGuessMargin = 1.0 / 4096.0;     // chunks: generous, a flagged chunk only costs a pack
+constexpr double kSubGuessMargin = 1.0 / 16384.0;   // sub-chunks: the fp32 chain drifts ~1e-4 from the exact sum at 1M candidates
 static_assert(kSubsPerChunk == 32, "one sub-chunk per lane of the walking warp");
 
 // Guess the phase of the running sum over a span from its approximate value at both ends, with
 // a margin for the drift of the fp32 chain: returns the low guess, and whether the span may
 // change phase.
-__device__ __forceinline__ bool guess_span(double a_lo, double a_hi, double bias, uint32_t* e_lo) {
-    const uint32_t lo = phase_of(f2b((float)(a_lo * bias * (1.0 - kGuessMargin))));
-    const uint32_t hi = phase_of(f2b((float)(a_hi * bias * (1.0 + kGuessMargin))));
+__device__ __forceinline__ bool guess_span(double a_lo, double a_hi, double bias, uint32_t* e_lo, double margin = kGuessMargin) {
+    const uint32_t lo = phase_of(f2b((float)(a_lo * bias * (1.0 - margin))));
+    const uint32_t hi = phase_of(f2b((float)(a_hi * bias * (1.0 + margin))));
     *e_lo = lo;
     return lo != hi;
 }
@@ -73,7 +82,7 @@ __device__ __forceinline__ bool guess_span(double a_lo, double a_hi, double bias
 // Exclusive scan (fp64) of one value per chunk over a 1024-thread CTA -> approx[0..nchunks], and
 // a compact slot number for every chunk that may change phase -> slotid[c] (-1: none).
 template <typename F>
-__device__ __forceinline__ void scan_chunks(F value_of, int nchunks, double bias, double* __restrict__ approx,
+__device__ __forceinline__ void scan_chunks(F value_of, int nchunks, double bias, int max_slots, double* __restrict__ approx,
                                             int* __restrict__ slotid, double* red, int* redi) {
     __shared__ double carry;
     __shared__ int carry_slots;
@@ -105,7 +114,7 @@ __device__ __forceinline__ void scan_chunks(F value_of, int nchunks, double bias
         before += __popc(bal & ((1u << lane) - 1u));
         if (c < nchunks) {
             approx[c] = a_lo;
-            slotid[c] = flagged && before < kSubSlots ? before : -1;
+            slotid[c] = flagged ? (before < max_slots ? before : -2) : -1;  // -2: flagged, but no slot left
         }
         __syncthreads();
         if (threadIdx.x == 1023) { carry = a_hi; carry_slots = before + (flagged ? 1 : 0); }
@@ -278,7 +287,8 @@ __global__ void __launch_bounds__(1024) stats_finalize_kernel(const float* __res
                                                               const double* __restrict__ sums, int nchunks, Bounds bounds,
                                                               float* ema_state, int ema_first, double ema_alpha,
                                                               double smooth_alpha, float* __restrict__ stats,
-                                                              double* __restrict__ approx, int* __restrict__ slotid, double bias) {
+                                                              double* __restrict__ approx, int* __restrict__ slotid, double bias,
+                                                              int max_slots) {
     __shared__ double red[32];
     __shared__ int redi[32];
     float ema = *ema_state;
@@ -312,15 +322,16 @@ __global__ void __launch_bounds__(1024) stats_finalize_kernel(const float* __res
     scan_chunks([&](int c) {
         const int len = (int)min((int64_t)kChunk, n - (int64_t)c * kChunk);
         return (sums[c] + (double)len * (double)shift) / (double)total;
-    }, nchunks, bias, approx, slotid, red, redi);
+    }, nchunks, bias, max_slots, approx, slotid, red, redi);
 }
 
 // 2b. the same scan for raw weights
 __global__ void __launch_bounds__(1024) prefix_finalize_kernel(const double* __restrict__ sums, int nchunks,
-                                                               double* __restrict__ approx, int* __restrict__ slotid, double bias) {
+                                                               double* __restrict__ approx, int* __restrict__ slotid, double bias,
+                                                              int max_slots) {
     __shared__ double red[32];
     __shared__ int redi[32];
-    scan_chunks([&](int c) { return sums[c]; }, nchunks, bias, approx, slotid, red, redi);
+    scan_chunks([&](int c) { return sums[c]; }, nchunks, bias, max_slots, approx, slotid, red, redi);
 }
 
 __global__ void __launch_bounds__(256) normalize_kernel(const float* __restrict__ scores, int64_t n,
@@ -333,16 +344,30 @@ __global__ void __launch_bounds__(256) normalize_kernel(const float* __restrict_
 // ---------------------------------------------------------------------------------------------
 // 3. summaries: one map per chunk (for the guessed phase; and the next one where the running
 //    sum may change phase), plus, for those "flagged" chunks, one map per 64-candidate sub-chunk
-struct __align__(32) Summary { uint32_t e; Pair q[2]; uint32_t pad[3]; };
-struct __align__(128) SubSummary { uint32_t e[kSubsPerChunk]; Pair q0[kSubsPerChunk]; Pair q1[kSubsPerChunk]; };
-static_assert(sizeof(SubSummary) == 640, "SubSummary layout");
+struct __align__(32) Summary { uint32_t e; Pair q[2]; uint32_t pad[3]; };  // e: guess | flags; pad[0]: pack index
 
-__device__ __forceinline__ Pair pick_map(uint32_t E, uint32_t e, Pair q0, Pair q1) {
-    e &= ~kFlag;
-    if (e == kAnyPhase || E == e) return q0;
-    if (E == e + 1u) return q1;
-    return Pair{kSatCap, kSatCap};  // guessed wrong: looks like a phase change, gets resolved exactly
-}
+// what the spine needs to cross a flagged chunk without scanning: per sub-chunk the guessed phase
+// (| flags), the maps for that phase and the next, the exclusive prefix sums of their increments,
+// and the raw candidates of (up to kRawPerPack) sub-chunks in which the phase should change
+struct __align__(128) Pack {
+    uint32_t e[kSubsPerChunk];
+    Pair q0[kSubsPerChunk], q1[kSubsPerChunk];
+    uint32_t ps0[kSubsPerChunk + 1], ps1[kSubsPerChunk + 1];
+    uint8_t rawsub[8];                // sub-chunks whose raw candidates are in raw[] (0xff: unused)
+    uint32_t nev;                     // the walk through the chunk, precompiled (see EvKind)
+    uint32_t pad_[3];
+    uint32_t raw[kRawPerPack][kSub];  // 16-byte aligned: read with 128-bit loads
+    uint4 ev[kSubsPerChunk + 1];
+};
+static_assert(sizeof(Pack) == 3072 && offsetof(Pack, raw) % 16 == 0 && offsetof(Pack, ev) % 16 == 0, "Pack layout");
+
+// One step of a precompiled walk.  x = kind | guard phase << 8 | first sub-chunk << 20 (packs).
+//   kEvAdd   : the span is a plain increment while the running sum is in the guard phase: y (z: high word at chunk level)
+//   kEvMap   : a span with exact ties inside: 2-state map (z, w)
+//   kEvSerial: a sub-chunk to be summed in fp32: y = raw slot in the pack (0xff: fetch it)
+//   kEvPack  : (chunk level) a flagged chunk: y = shared-memory slot of its pack (0xffffffff: fetch it)
+//   kEvSlow  : (chunk level) a chunk that needs the general code
+enum EvKind : uint32_t { kEvAdd = 0, kEvMap = 1, kEvSerial = 2, kEvPack = 3, kEvSlow = 4 };
 
 double g_guess_bias = 1.0;  // test hook (mercury_test_set_guess_bias): scales every guess
 
@@ -364,7 +389,7 @@ struct FusedStats {
 template <bool FUSED>
 __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_t n, const double* __restrict__ approx,
                                                            const int* __restrict__ slotid, double bias,
-                                                           Summary* __restrict__ out, SubSummary* __restrict__ subs,
+                                                           Summary* __restrict__ out, Pack* __restrict__ subs,
                                                            int32_t* status, int check, FusedStats fs) {
     __shared__ Pair wt[2][kSumNT / 32];
     __shared__ float wsum[kSumNT / 32];
@@ -466,7 +491,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
 #pragma unroll
         for (int i = 0; i < kSumNT / 32; ++i) { t0 = compose(t0, wt[0][i]); t1 = compose(t1, wt[1][i]); any |= wnz[i]; }
         Summary s;
-        s.e = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u);
+        s.e = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u) | (flagged && slot < 0 ? kNoPack : 0u) | (t0.d0 != t0.d1 ? kTie0 : 0u);
         s.q[0] = t0;
         s.q[1] = flagged ? t1 : Pair{kSatCap, kSatCap};
         s.pad[0] = (uint32_t)slot; s.pad[1] = s.pad[2] = 0;
@@ -480,7 +505,9 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
     const int lead = lane & ~7;
     const float s_lo = __shfl_sync(0xffffffffu, t_lo, lead), s_hi = __shfl_sync(0xffffffffu, t_hi, lead + 7);
     uint32_t es;
-    const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, bias, &es);
+    // (a sub-chunk of zeros changes nothing, whatever the phase: never worth a serial pass)
+    const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, bias, &es, kSubGuessMargin) &&
+                             ((nzmask >> lead) & 0xffu) != 0u;
     Pair m0 = identity_pair(), m1 = identity_pair();
 #pragma unroll
     for (int k = 0; k < kSumIPT; ++k) {
@@ -494,56 +521,103 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         o1.d0 = __shfl_down_sync(0xffffffffu, m1.d0, off, 8); o1.d1 = __shfl_down_sync(0xffffffffu, m1.d1, off, 8);
         if ((lane & 7) + off < 8) { m0 = compose(m0, o0); m1 = compose(m1, o1); }
     }
+    __shared__ uint32_t sub_inc[2][kSubsPerChunk];
+    __shared__ uint32_t sub_flag_mask;
+    Pack* pk = subs + slot;
+    const int my_sub = threadIdx.x >> 3;
     if ((lane & 7) == 0) {
-        const int k = threadIdx.x >> 3;
         const bool sub_nz = ((nzmask >> lead) & 0xffu) != 0u;
-        SubSummary* ss = subs + slot;
-        ss->e[k] = (sub_nz ? es : kAnyPhase) | (sub_flagged ? kFlag : 0u);
-        ss->q0[k] = m0;
-        ss->q1[k] = m1;
+        pk->e[my_sub] = (sub_nz ? es : kAnyPhase) | (sub_flagged ? kFlag : 0u) | (m0.d0 != m0.d1 ? kTie0 : 0u) |
+                        (m1.d0 != m1.d1 ? kTie1 : 0u);
+        pk->q0[my_sub] = m0;
+        pk->q1[my_sub] = m1;
+        sub_inc[0][my_sub] = m0.d0;
+        sub_inc[1][my_sub] = m1.d0;
+    }
+    const unsigned lead_flags = __ballot_sync(0xffffffffu, (lane & 7) == 0 && sub_flagged);  // bits 0,8,16,24
+    if (threadIdx.x == 0) sub_flag_mask = 0u;
+    __syncthreads();
+    if (lane == 0) {
+        const uint32_t four = ((lead_flags >> 0) & 1u) | ((lead_flags >> 7) & 2u) | ((lead_flags >> 14) & 4u) | ((lead_flags >> 21) & 8u);
+        atomicOr(&sub_flag_mask, four << (4 * warp));
+    }
+    __syncthreads();
+    const uint32_t fmask = sub_flag_mask;
+    if (warp == 0) {  // exclusive prefix sums of the increments over the 32 sub-chunks (32 * 2^25 fits)
+        uint32_t v0 = sub_inc[0][lane], v1 = sub_inc[1][lane];
+        const uint32_t i0 = v0, i1 = v1;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o0 = __shfl_up_sync(0xffffffffu, v0, off), o1 = __shfl_up_sync(0xffffffffu, v1, off);
+            if (lane >= off) { v0 += o0; v1 += o1; }
+        }
+        pk->ps0[lane] = v0 - i0;
+        pk->ps1[lane] = v1 - i1;
+        if (lane == 31) { pk->ps0[32] = v0; pk->ps1[32] = v1; }
+        // which sub-chunks ship their raw candidates: the first kRawPerPack flagged ones
+        const int rank = __popc(fmask & ((1u << lane) - 1u));
+        if (((fmask >> lane) & 1u) && rank < kRawPerPack) pk->rawsub[rank] = (uint8_t)lane;
+        if (lane < kRawPerPack && lane >= __popc(fmask)) pk->rawsub[lane] = 0xff;
+        // precompiled walk: maximal runs of plain sub-chunks -> one kEvAdd each; flagged -> kEvSerial; ties -> kEvMap
+        const uint32_t ek = pk->e[lane];  // written above by this chunk's leaders (visible after the barrier)
+        const uint32_t gk = ek & kPhaseMask;
+        const unsigned any_m = __ballot_sync(0xffffffffu, gk == kAnyPhase);
+        const unsigned tie_m = __ballot_sync(0xffffffffu, (ek & kTie0) != 0u) & ~fmask;
+        const uint32_t gprev = __shfl_up_sync(0xffffffffu, gk, 1);
+        const unsigned chg_m = __ballot_sync(0xffffffffu, lane > 0 && gk != kAnyPhase && gprev != kAnyPhase && gk != gprev);
+        const unsigned stop_m = fmask | tie_m;
+        const bool is_stop = (stop_m >> lane) & 1u;
+        const bool run_start = !is_stop && (lane == 0 || ((stop_m >> (lane - 1)) & 1u) || ((chg_m >> lane) & 1u));
+        const unsigned ev_m = __ballot_sync(0xffffffffu, is_stop || run_start);
+        const unsigned brk = (stop_m | chg_m) & ~((2u << lane) - 1u);       // where a run starting here ends
+        const int s_end = brk ? __ffs(brk) - 1 : kSubsPerChunk;
+        const uint32_t ps_end = __shfl_sync(0xffffffffu, v0 - i0, s_end & 31);
+        const uint32_t inc_run = (s_end == kSubsPerChunk ? __shfl_sync(0xffffffffu, v0, 31) : ps_end) - (v0 - i0);
+        const unsigned span = (s_end == kSubsPerChunk ? 0xffffffffu : ((1u << s_end) - 1u)) & ~((1u << lane) - 1u);
+        const unsigned live = span & ~any_m;                                 // first sub-chunk of the run with addends
+        const uint32_t g_run = __shfl_sync(0xffffffffu, gk, live ? __ffs(live) - 1 : 0);
+        if (is_stop || run_start) {
+            uint4 ev;
+            if (run_start) ev = make_uint4(kEvAdd | ((live ? g_run : kAnyPhase) << 8) | ((uint32_t)lane << 20), inc_run, 0u, 0u);
+            else if ((fmask >> lane) & 1u) ev = make_uint4(kEvSerial | ((uint32_t)lane << 20), rank < kRawPerPack ? (uint32_t)rank : 0xffu, 0u, 0u);
+            else ev = make_uint4(kEvMap | (gk << 8) | ((uint32_t)lane << 20), 0u, pk->q0[lane].d0, pk->q0[lane].d1);
+            pk->ev[__popc(ev_m & ((1u << lane) - 1u))] = ev;
+        }
+        if (lane == 0) pk->nev = __popc(ev_m);
+    }
+    const int my_rank = __popc(fmask & ((1u << my_sub) - 1u));
+    if (((fmask >> my_sub) & 1u) && my_rank < kRawPerPack) {
+#pragma unroll
+        for (int k = 0; k < kSumIPT; ++k) pk->raw[my_rank][(threadIdx.x & 7) * kSumIPT + k] = pb[k];
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// 4. the spine: exact running sum at every chunk boundary.  One warp walks the chunk maps 32 at
-//    a time (no block barriers on the serial path); the rest of the CTA only prefetches the
-//    summaries -- and, for flagged chunks, the sub-chunk maps and the raw candidates of the
-//    sub-chunks expected to change phase -- into shared memory before the walk starts.
+// 4. the spine: exact running sum at every chunk boundary.
+//
+// The walk is serial by nature (about one step per change of binade, ~20 for a million
+// candidates), so everything it needs is laid out beforehand, in parallel, such that a step costs
+// a few dependent instructions instead of a warp scan:
+//   * chunk level: while the running sum stays in the phase that was guessed, every chunk map is a
+//     plain increment, so a whole run of chunks is crossed with ONE subtraction of prefix sums
+//     (computed by the whole CTA while it loads the summaries into shared memory);
+//   * a flagged chunk (phase change expected) carries a pack: per 64-candidate sub-chunk the maps
+//     for the guessed phase and the next, their prefix sums, and the raw candidates of the
+//     sub-chunks where the change should fall.  Runs of sub-chunks are again one subtraction; the
+//     sub-chunk that changes phase is summed serially in fp32 -- the reference's own loop;
+//   * anything that contradicts a guess falls back to that serial loop over the chunk or the
+//     sub-chunk (slower, exact).
+// One warp walks; the other warps of the CTA only prefetch and, at the end, fill in the boundary
+// values of the chunks that were crossed in runs.
 constexpr int kSpineNT = 512;
-constexpr int kMaxSlots = 24, kRawPerSlot = 4;
+constexpr int kMaxSlots = 32;    // packs prefetched into shared memory (the rest are fetched when reached)
+constexpr int kMaxEvents = 640;  // precompiled chunk-level steps (more: the general walk is used)
 
-struct SlotData {
-    SubSummary sub;
-    uint32_t raw[kRawPerSlot][kSub];
-    uint8_t rawsub[kRawPerSlot];
-    uint8_t pad[12];
-};
-
+__host__ __device__ inline int spine_slots(int nchunks) { return nchunks <= 2048 ? kMaxSlots : 8; }
 __host__ __device__ inline size_t spine_smem_bytes(int nchunks) {
-    size_t b = (size_t)nchunks * 21;                 // 5 words + 1 slot byte per chunk
+    size_t b = (size_t)(nchunks + 1) * 8 + (size_t)nchunks * 13 + (size_t)((nchunks + 32) / 32) * 4;
     b = (b + 127) & ~(size_t)127;
-    return b + (size_t)kMaxSlots * sizeof(SlotData) + (size_t)kChunk * 4;
-}
-
-__device__ __forceinline__ Pair warp_scan_pair(Pair x, int lane) {
-    // Without exact ties every map is a plain integer increment (d0 == d1): the scan is then an
-    // integer prefix sum (32 * 2^25 fits in 32 bits), half the shuffles and no selects.
-    if (__ballot_sync(0xffffffffu, x.d0 != x.d1) == 0u) {
-        uint32_t v = x.d0;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, v, off);
-            if (lane >= off) v += o;
-        }
-        v = sat(v);
-        return Pair{v, v};
-    }
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        Pair o = shfl_up_pair(x, off);
-        if (lane >= off) x = compose(o, x);
-    }
-    return x;
+    return b + (size_t)(spine_slots(nchunks) + 1) * sizeof(Pack) + (size_t)kChunk * 4 + (size_t)kMaxEvents * 20;
 }
 
 // exact pass over `count` consecutive candidates held in shared memory, from state b: this is
@@ -562,141 +636,391 @@ __device__ __forceinline__ uint32_t serial_chain(uint32_t b, const uint32_t* __r
     return f2b(s);
 }
 
-__global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
-                                                         const SubSummary* __restrict__ subs, uint32_t* __restrict__ start_bits,
-                                                         float* __restrict__ total_out, int32_t* status, float* ema_out) {
-    extern __shared__ __align__(128) unsigned char sm[];
-    __shared__ int nslots_s;
-    __shared__ int slot_chunk[kMaxSlots];   // chunk held by each shared-memory slot
-    __shared__ int slot_global[kMaxSlots];  // ... and where its sub-summaries live in `subs`
-    uint32_t* ce = reinterpret_cast<uint32_t*>(sm);
-    uint32_t* qa0 = ce + nchunks; uint32_t* qa1 = qa0 + nchunks; uint32_t* qb0 = qa1 + nchunks; uint32_t* qb1 = qb0 + nchunks;
-    uint8_t* slot_of = reinterpret_cast<uint8_t*>(qb1 + nchunks);
-    const size_t off = (((size_t)nchunks * 21) + 127) & ~(size_t)127;
-    SlotData* slots = reinterpret_cast<SlotData*>(sm + off);
-    uint32_t* stage = reinterpret_cast<uint32_t*>(sm + off + (size_t)kMaxSlots * sizeof(SlotData));  // kChunk words
-    const int tid = threadIdx.x, lane = tid & 31;
-    float shift, totalw;
-    src.prepare(shift, totalw);
+// lowest set bit position >= from in a bitmask stored as 32-bit words (a sentinel bit always exists)
+__device__ __forceinline__ int next_bit(const uint32_t* words, int from) {
+    int w = from >> 5;
+    uint32_t m = words[w] & (0xffffffffu << (from & 31));
+    while (m == 0u) m = words[++w];
+    return (w << 5) + __ffs(m) - 1;
+}
 
-    // ---- prefetch (whole CTA)
-    if (tid == 0) nslots_s = 0;
-    __syncthreads();
-    for (int c = tid; c < nchunks; c += kSpineNT) {
-        const Summary s = sums[c];
-        ce[c] = s.e; qa0[c] = s.q[0].d0; qa1[c] = s.q[0].d1; qb0[c] = s.q[1].d0; qb1[c] = s.q[1].d1;
-        uint8_t so = 0;
-        if (s.e & kFlag) {
-            const int sl = atomicAdd(&nslots_s, 1);
-            if (sl < kMaxSlots) { so = (uint8_t)(sl + 1); slot_chunk[sl] = c; slot_global[sl] = (int)s.pad[0]; }
-        }
-        slot_of[c] = so;
-    }
-    __syncthreads();
-    const int nsl = min(nslots_s, kMaxSlots);
-    constexpr int kSubWords = (int)(sizeof(SubSummary) / 4);
-    for (int i = tid; i < nsl * kSubWords; i += kSpineNT) {
-        const int sl = i / kSubWords, w = i % kSubWords;
-        reinterpret_cast<uint32_t*>(&slots[sl].sub)[w] = reinterpret_cast<const uint32_t*>(subs + slot_global[sl])[w];
-    }
-    __syncthreads();
-    if (tid < nsl) {
-        int cnt = 0;
-        for (int k = 0; k < kSubsPerChunk; ++k)
-            if ((slots[tid].sub.e[k] & kFlag) && cnt < kRawPerSlot) slots[tid].rawsub[cnt++] = (uint8_t)k;
-        for (; cnt < kRawPerSlot; ++cnt) slots[tid].rawsub[cnt] = 0xff;
-    }
-    __syncthreads();
-    for (int i = tid; i < nsl * kRawPerSlot * kSub; i += kSpineNT) {
-        const int sl = i / (kRawPerSlot * kSub), r = (i / kSub) % kRawPerSlot, j = i % kSub;
-        const int k = slots[sl].rawsub[r];
-        if (k != 0xff) {
-            const int64_t idx = (int64_t)slot_chunk[sl] * kChunk + k * kSub + j;
-            slots[sl].raw[r][j] = idx < n ? f2b(src.get(idx, shift, totalw)) : 0u;
-        }
-    }
-    __syncthreads();
-    if (tid >= 32) return;
+struct SpineCtx {
+    WeightSrc src; int64_t n; float shift, totalw; int lane; int* dbg;
+    // shared memory
+    const unsigned long long* pc; const uint32_t* ce; const uint32_t* qd0; const uint32_t* qd1; const uint32_t* stopw;
+    const uint8_t* slot_of; const Pack* slots; Pack* spare; uint32_t* stage;
+    // global
+    const Summary* sums; const Pack* packs; uint32_t* start_bits;
+};
 
-    // ---- the walk (one warp)
-    uint32_t bits = 0u;  // the running sum starts at +0
-    int c = 0;
-    while (c < nchunks) {
-        const uint32_t E = phase_of(bits), S = bits - (E << 23);
-        const int cc = c + lane;
-        const bool valid = cc < nchunks;
-        const Pair m = valid ? pick_map(E, ce[cc], Pair{qa0[cc], qa1[cc]}, Pair{qb0[cc], qb1[cc]}) : identity_pair();
-        const Pair inc = warp_scan_pair(m, lane);
-        Pair ex = shfl_up_pair(inc, 1);
-        if (lane == 0) ex = identity_pair();
-        const uint32_t s_in = apply(ex, S), s_out = apply(inc, S);
-        const unsigned mask = __ballot_sync(0xffffffffu, valid && s_out >= kPhaseLimit);
-        const int f = mask ? __ffs(mask) - 1 : 32;
-        if (valid && lane <= f) start_bits[cc] = bits_of(E, s_in);
-        if (f == 32) {
-            bits = bits_of(E, __shfl_sync(0xffffffffu, s_out, min(31, nchunks - 1 - c)));
-            c += 32;
+// serial fallback over a whole chunk (guess contradicted): stage it, then the reference loop
+__device__ __noinline__ uint32_t serial_chunk(const SpineCtx& x, int c, uint32_t b) {
+    if (x.dbg && x.lane == 0) x.dbg[1]++;
+    const int64_t e0 = (int64_t)c * kChunk;
+    for (int i = x.lane; i < kChunk; i += 32) x.stage[i] = e0 + i < x.n ? f2b(x.src.get(e0 + i, x.shift, x.totalw)) : 0u;
+    __syncwarp();
+    b = serial_chain(b, x.stage, kChunk);
+    __syncwarp();
+    return b;
+}
+
+// serial pass over sub-chunk k of chunk c: raw candidates from the pack if it carries them
+__device__ __forceinline__ uint32_t serial_sub(const SpineCtx& x, const Pack* P, int c, int k, uint32_t b) {
+    int r = -1;
+#pragma unroll
+    for (int q = 0; q < kRawPerPack; ++q) if (P->rawsub[q] == k) r = q;
+    const uint32_t* raw;
+    if (x.dbg && x.lane == 0) x.dbg[r >= 0 ? 2 : 3]++;
+    if (r >= 0) raw = P->raw[r];
+    else {
+        const int64_t i0 = (int64_t)c * kChunk + k * kSub + 2 * x.lane;
+        x.stage[2 * x.lane] = i0 < x.n ? f2b(x.src.get(i0, x.shift, x.totalw)) : 0u;
+        x.stage[2 * x.lane + 1] = i0 + 1 < x.n ? f2b(x.src.get(i0 + 1, x.shift, x.totalw)) : 0u;
+        __syncwarp();
+        raw = x.stage;
+    }
+    b = serial_chain(b, raw, kSub);
+    __syncwarp();
+    return b;
+}
+
+// a flagged chunk from sub-chunk k0 on, the general way: whatever the phase turns out to be
+__device__ __noinline__ uint32_t resolve_flagged(const SpineCtx& x, const Pack* P, int c, uint32_t b, int k0) {
+    const int lane = x.lane;
+    const uint32_t ek_l = P->e[lane];
+    const uint32_t g_l = ek_l & kPhaseMask;
+    const unsigned any_m = __ballot_sync(0xffffffffu, g_l == kAnyPhase);
+    const unsigned flag_m = __ballot_sync(0xffffffffu, (ek_l & kFlag) != 0u);
+    const unsigned tie0_m = __ballot_sync(0xffffffffu, (ek_l & kTie0) != 0u), tie1_m = __ballot_sync(0xffffffffu, (ek_l & kTie1) != 0u);
+    // guess changes against the previous non-zero sub-chunk (defensive: expected only at flagged ones)
+    const uint32_t prev_g = __shfl_up_sync(0xffffffffu, g_l, 1);
+    const unsigned chg_m = __ballot_sync(0xffffffffu, lane > 0 && g_l != kAnyPhase && prev_g != kAnyPhase && prev_g != g_l);
+    int k = k0;
+    while (k < kSubsPerChunk) {
+        const uint32_t E = phase_of(b), S = b - (E << 23);
+        if ((any_m >> k) & 1u) { ++k; continue; }                   // all zeros: nothing happens
+        const uint32_t g = P->e[k] & kPhaseMask;
+        const int w = E == g ? 0 : (E == g + 1u ? 1 : -1);
+        if (((flag_m >> k) & 1u) || w < 0) { b = serial_sub(x, P, c, k, b); ++k; continue; }
+        const unsigned tie_m = w ? tie1_m : tie0_m;
+        if ((tie_m >> k) & 1u) {                                     // exact ties inside: apply the 2-state map
+            const Pair q = w ? P->q1[k] : P->q0[k];
+            const uint32_t Sn = apply(q, S);
+            if (Sn >= kPhaseLimit) b = serial_sub(x, P, c, k, b); else b = bits_of(E, Sn);
+            ++k;
             continue;
         }
-        // chunk d changes phase (or was guessed wrong): resolve it exactly, inside the warp
-        const int d = c + f;
-        uint32_t b = bits_of(E, __shfl_sync(0xffffffffu, s_in, f));
-        const bool have_sub = (ce[d] & kFlag) != 0u;
-        const int slot = (int)slot_of[d] - 1;
-        if (have_sub) {
-            uint32_t se; Pair m0, m1;
-            if (slot >= 0) { se = slots[slot].sub.e[lane]; m0 = slots[slot].sub.q0[lane]; m1 = slots[slot].sub.q1[lane]; }
-            else { const SubSummary* g = subs + sums[d].pad[0]; se = g->e[lane]; m0 = g->q0[lane]; m1 = g->q1[lane]; }
-            int first = 0;
-            while (first < kSubsPerChunk) {
-                const uint32_t E2 = phase_of(b), S2 = b - (E2 << 23);
-                const Pair mm = lane >= first ? pick_map(E2, se, m0, m1) : identity_pair();
-                const Pair inc2 = warp_scan_pair(mm, lane);
-                Pair ex2 = shfl_up_pair(inc2, 1);
-                if (lane == 0) ex2 = identity_pair();
-                const uint32_t si = apply(ex2, S2), so = apply(inc2, S2);
-                const unsigned m2 = __ballot_sync(0xffffffffu, lane >= first && so >= kPhaseLimit);
-                if (!m2) { b = bits_of(E2, __shfl_sync(0xffffffffu, so, 31)); break; }
-                const int f2 = __ffs(m2) - 1;
-                const uint32_t sb = bits_of(E2, __shfl_sync(0xffffffffu, si, f2));
-                // the 64 raw candidates of sub-chunk f2: prefetched, or staged now
-                int r = -1;
-                if (slot >= 0) {
-#pragma unroll
-                    for (int q = 0; q < kRawPerSlot; ++q) if (slots[slot].rawsub[q] == f2) r = q;
-                }
-                const uint32_t* raw;
-                if (r >= 0) raw = slots[slot].raw[r];
-                else {
-                    const int64_t i0 = (int64_t)d * kChunk + f2 * kSub + 2 * lane;
-                    stage[2 * lane] = i0 < n ? f2b(src.get(i0, shift, totalw)) : 0u;
-                    stage[2 * lane + 1] = i0 + 1 < n ? f2b(src.get(i0 + 1, shift, totalw)) : 0u;
-                    __syncwarp();
-                    raw = stage;
-                }
-                b = serial_chain(sb, raw, kSub);
-                __syncwarp();
-                first = f2 + 1;
-            }
-        } else {
-            // no sub-summaries (the chunk was not expected to change phase): stage it and go
-            // through it sub-chunk by sub-chunk.  Slow, rare, exact.
-            const int64_t e0 = (int64_t)d * kChunk;
-            for (int i = lane; i < kChunk; i += 32) stage[i] = e0 + i < n ? f2b(src.get(e0 + i, shift, totalw)) : 0u;
-            __syncwarp();
-            b = serial_chain(b, stage, kChunk);
-            __syncwarp();
-        }
-        bits = b;
-        c = d + 1;
+        // additive run [k, s): up to the next sub-chunk that needs individual treatment
+        const unsigned stops = (flag_m | tie_m | chg_m) & ~((2u << k) - 1u);
+        const int s = stops ? __ffs(stops) - 1 : kSubsPerChunk;
+        const uint32_t* ps = w ? P->ps1 : P->ps0;
+        const uint32_t base = ps[k];
+        const uint32_t Sn = S + (ps[s] - base);
+        if (Sn < kPhaseLimit) { b = bits_of(E, Sn); k = s; continue; }
+        // the phase changes inside the run after all: find the sub-chunk, sum it serially
+        const bool over = lane >= k && lane < s && S + (ps[lane + 1] - base) >= kPhaseLimit;
+        const int f = __ffs(__ballot_sync(0xffffffffu, over)) - 1;
+        b = serial_sub(x, P, c, f, bits_of(E, S + (ps[f] - base)));
+        k = f + 1;
     }
-    if (lane == 0) {
-        if (ema_out) *ema_out = src.stats[MERCURY_STAT_EMA];  // fused statistics: EMAverage.value for the next call
-        start_bits[nchunks] = bits;
-        const float total = b2f(bits);
-        *total_out = total;
-        if (!(total > 0.f)) atomicOr(status, MERCURY_ST_ZERO_SUM);
-        else if (isinf(total)) atomicOr(status, MERCURY_ST_NONFINITE);
+    return b;
+}
+
+// a flagged chunk along its precompiled walk (the expected case); the first contradicted guard
+// hands the rest of the chunk to the general code
+__device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, int c, uint32_t b) {
+    const int nev = (int)P->nev;
+    uint32_t E = phase_of(b), S = b - (E << 23);
+    for (int i = 0; i < nev; ++i) {
+        const uint4 ev = P->ev[i];
+        const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
+        if (kind == kEvAdd) {
+            const uint32_t Sn = S + ev.y;
+            if ((ph == E || ph == kAnyPhase) && Sn < kPhaseLimit) { S = Sn; continue; }
+        } else if (kind == kEvMap) {
+            const uint32_t Sn = S + ((S & 1u) ? ev.w : ev.z);
+            if (ph == E && Sn < kPhaseLimit) { S = Sn; continue; }
+        } else {
+            b = serial_sub(x, P, c, (int)(ev.x >> 20), bits_of(E, S));
+            E = phase_of(b); S = b - (E << 23);
+            continue;
+        }
+        if (x.dbg && x.lane == 0) x.dbg[7]++;
+        return resolve_flagged(x, P, c, bits_of(E, S), (int)(ev.x >> 20));
+    }
+    return bits_of(E, S);
+}
+
+__device__ __forceinline__ const Pack* pack_of(const SpineCtx& x, int c) {
+    const int sl = (int)x.slot_of[c] - 1;
+    if (x.dbg && x.lane == 0) { x.dbg[0]++; if (sl < 0) x.dbg[5]++; }
+    if (sl >= 0) return &x.slots[sl];
+    // not prefetched: one cooperative copy instead of many dependent global reads
+    const uint4* g4 = reinterpret_cast<const uint4*>(x.packs + x.sums[c].pad[0]);
+    uint4* s4 = reinterpret_cast<uint4*>(x.spare);
+    for (int i = x.lane; i < (int)(sizeof(Pack) / 16); i += 32) s4[i] = g4[i];
+    __syncwarp();
+    return x.spare;
+}
+
+// chunks [c, c_end) the general way (no precompiled steps, or one of them was contradicted);
+// writes their boundary values itself
+__device__ __noinline__ uint32_t walk_general(const SpineCtx& x, int c, int c_end, uint32_t b) {
+    const int lane = x.lane;
+    while (c < c_end) {
+        const uint32_t E = phase_of(b), S = b - (E << 23);
+        const uint32_t ec = x.ce[c], g = ec & kPhaseMask;
+        if (lane == 0) x.start_bits[c] = b;
+        if (ec & kFlag) {
+            const Pack* P = pack_of(x, c);
+            b = run_pack(x, P, c, b);
+            __syncwarp();
+            ++c;
+            continue;
+        }
+        if (g == kAnyPhase) { ++c; continue; }  // all zeros
+        if (g != E || (ec & kNoPack)) { b = serial_chunk(x, c, b); ++c; continue; }
+        if (ec & kTie0) {
+            const uint32_t Sn = apply(Pair{x.qd0[c], x.qd1[c]}, S);
+            if (Sn >= kPhaseLimit) b = serial_chunk(x, c, b); else b = bits_of(E, Sn);
+            ++c;
+            continue;
+        }
+        // additive run [c, s): one subtraction of prefix sums
+        const int s = min(next_bit(x.stopw, c + 1), c_end);
+        const unsigned long long base = x.pc[c];
+        const unsigned long long Sn = (unsigned long long)S + (x.pc[s] - base);
+        int end = s;
+        if (Sn >= kPhaseLimit) {  // the phase changes inside the run after all: first chunk that leaves it
+            int lo = c, hi = s;   // state before chunk lo is inside the phase, before chunk hi outside
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if ((unsigned long long)S + (x.pc[mid] - base) >= kPhaseLimit) hi = mid; else lo = mid;
+            }
+            end = lo;
+        }
+        for (int k = c + 1 + lane; k < end; k += 32) x.start_bits[k] = bits_of(E, S + (uint32_t)(x.pc[k] - base));
+        if (end == s) { b = bits_of(E, (uint32_t)Sn); c = s; continue; }
+        const uint32_t bf = bits_of(E, S + (uint32_t)(x.pc[end] - base));
+        if (lane == 0) x.start_bits[end] = bf;
+        b = serial_chunk(x, end, bf);
+        c = end + 1;
+    }
+    return b;
+}
+
+__global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
+                                                         const Pack* __restrict__ packs, uint32_t* __restrict__ start_bits,
+                                                         float* __restrict__ total_out, int32_t* status, float* ema_out, int debug) {
+    extern __shared__ __align__(128) unsigned char sm[];
+    __shared__ int nslots_s, nev_s;
+    __shared__ int slot_global[kMaxSlots];
+    __shared__ unsigned long long wtot[kSpineNT / 32];
+    __shared__ unsigned long long carry_s;
+    __shared__ int wcnt[kSpineNT / 32];
+    __shared__ int carry_ev;
+    __shared__ long long dbg_t[4];
+    __shared__ int dbg_n[8];  // flagged, serial chunks, serial subs (raw at hand), serial subs (fetched), events, late packs, general walks
+    if (debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; }
+    // shared-memory layout
+    unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);               // [nchunks+1] prefix of increments
+    uint32_t* ce = reinterpret_cast<uint32_t*>(pc + nchunks + 1);                      // [nchunks] guess | flags
+    uint32_t* qd0 = ce + nchunks; uint32_t* qd1 = qd0 + nchunks;                      // [nchunks] map for the guess
+    uint32_t* stopw = qd1 + nchunks;                                                   // [(nchunks+32)/32] stop bitmask
+    uint8_t* slot_of = reinterpret_cast<uint8_t*>(stopw + (nchunks + 32) / 32);
+    size_t off = (size_t)(nchunks + 1) * 8 + (size_t)nchunks * 13 + (size_t)((nchunks + 32) / 32) * 4;
+    off = (off + 127) & ~(size_t)127;
+    const int max_slots = spine_slots(nchunks);
+    Pack* slots = reinterpret_cast<Pack*>(sm + off);  // [max_slots] prefetched + 1 spare for late fetches
+    Pack* spare = slots + max_slots;
+    uint32_t* stage = reinterpret_cast<uint32_t*>(sm + off + (size_t)(max_slots + 1) * sizeof(Pack));
+    uint4* evs = reinterpret_cast<uint4*>(stage + kChunk);                              // [kMaxEvents] precompiled steps
+    uint32_t* evb = reinterpret_cast<uint32_t*>(evs + kMaxEvents);                      // [kMaxEvents] state at each step
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // ---- prefetch (whole CTA): summaries -> shared memory, prefix sums of the increments
+    if (tid == 0) { nslots_s = 0; carry_s = 0ull; carry_ev = 0; }
+    __syncthreads();
+    for (int c0 = 0; c0 < nchunks; c0 += kSpineNT) {
+        const int c = c0 + tid;
+        unsigned long long inc = 0ull;
+        if (c < nchunks) {
+            const Summary s = sums[c];
+            ce[c] = s.e; qd0[c] = s.q[0].d0; qd1[c] = s.q[0].d1;
+            uint8_t so = 0;
+            if (s.e & kFlag) {
+                const int sl = atomicAdd(&nslots_s, 1);
+                if (sl < max_slots) { so = (uint8_t)(sl + 1); slot_global[sl] = (int)s.pad[0]; }
+            }
+            slot_of[c] = so;
+            inc = s.q[0].d0;
+        }
+        const unsigned long long mine = inc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        if (lane == 31) wtot[warp] = inc;
+        __syncthreads();
+        unsigned long long pre = carry_s;
+        for (int i = 0; i < warp; ++i) pre += wtot[i];
+        if (c < nchunks) pc[c] = pre + inc - mine;
+        __syncthreads();
+        if (tid == kSpineNT - 1) carry_s = pre + inc;
+        __syncthreads();
+    }
+    if (tid == 0) pc[nchunks] = carry_s;
+    // packs of the flagged chunks (as many as fit)
+    const int nsl = min(nslots_s, max_slots);
+    constexpr int kPackVecs = (int)(sizeof(Pack) / 16);
+    for (int i = tid; i < nsl * kPackVecs; i += kSpineNT) {
+        const int sl = i / kPackVecs, w = i % kPackVecs;
+        reinterpret_cast<uint4*>(&slots[sl])[w] = reinterpret_cast<const uint4*>(packs + slot_global[sl])[w];
+    }
+    // stop mask: chunks that need individual treatment, or where the guess changes
+    for (int w0 = 0; w0 < (nchunks + 32) / 32; w0 += kSpineNT / 32) {
+        const int c = (w0 + warp) * 32 + lane;
+        bool stop = false;
+        if (c < nchunks) {
+            const uint32_t e = ce[c], g = e & kPhaseMask;
+            stop = (e & (kFlag | kTie0 | kNoPack)) != 0u;
+            if (c > 0) { const uint32_t gp = ce[c - 1] & kPhaseMask; if (g != kAnyPhase && gp != kAnyPhase && g != gp) stop = true; }
+        }
+        if (c == nchunks) stop = true;  // sentinel
+        const unsigned bits = __ballot_sync(0xffffffffu, stop);
+        if (lane == 0 && w0 + warp < (nchunks + 32) / 32) stopw[w0 + warp] = bits;
+    }
+    __syncthreads();
+    // precompiled chunk-level walk
+    for (int c0 = 0; c0 < nchunks; c0 += kSpineNT) {
+        const int c = c0 + tid;
+        bool start = false;
+        // (a step starts at chunk 0, at every stop, and after every chunk that is a step of its own)
+        if (c < nchunks) start = c == 0 || ((stopw[c >> 5] >> (c & 31)) & 1u) || (ce[c - 1] & (kFlag | kTie0 | kNoPack)) != 0u;
+        const unsigned bal = __ballot_sync(0xffffffffu, start);
+        if (lane == 0) wcnt[warp] = __popc(bal);
+        __syncthreads();
+        int idx = carry_ev + __popc(bal & ((1u << lane) - 1u));
+        for (int i = 0; i < warp; ++i) idx += wcnt[i];
+        if (start && idx < kMaxEvents) {
+            const uint32_t e = ce[c];
+            uint4 ev;
+            if (e & kFlag) ev = make_uint4(kEvPack, (uint32_t)c | ((uint32_t)(c + 1) << 16), 0u, 0u);
+            else if (e & kNoPack) ev = make_uint4(kEvSlow, (uint32_t)c | ((uint32_t)(c + 1) << 16), 0u, 0u);
+            else if (e & kTie0) ev = make_uint4(kEvMap | ((e & kPhaseMask) << 8), (uint32_t)c | ((uint32_t)(c + 1) << 16), qd0[c], qd1[c]);
+            else {
+                const int s = next_bit(stopw, c + 1);
+                uint32_t g = kAnyPhase;
+                for (int k = c; k < s && g == kAnyPhase; ++k) g = ce[k] & kPhaseMask;  // first chunk of the run with addends
+                const unsigned long long inc = pc[s] - pc[c];
+                ev = make_uint4(kEvAdd | (g << 8), (uint32_t)c | ((uint32_t)s << 16), (uint32_t)inc, (uint32_t)(inc >> 32));
+            }
+            evs[idx] = ev;
+        }
+        __syncthreads();
+        if (tid == kSpineNT - 1) carry_ev = idx + (start ? 1 : 0);
+        __syncthreads();
+    }
+    if (tid == 0) nev_s = carry_ev;
+    __syncthreads();
+    const int nev = nev_s;
+    const bool use_events = nev <= kMaxEvents && nchunks < 65536;
+
+    if (debug && tid == 0) dbg_t[1] = clock64();
+    if (warp == 0) {
+        // ---- the walk (one warp; scalar logic is replicated on all lanes)
+        SpineCtx x;
+        x.dbg = debug ? dbg_n : nullptr;
+        x.src = src; x.n = n; x.lane = lane;
+        src.prepare(x.shift, x.totalw);
+        x.pc = pc; x.ce = ce; x.qd0 = qd0; x.qd1 = qd1; x.stopw = stopw; x.slot_of = slot_of; x.slots = slots; x.spare = spare;
+        x.stage = stage; x.sums = sums; x.packs = packs; x.start_bits = start_bits;
+        uint32_t b = 0u;  // the running sum starts at +0
+        if (!use_events) {
+            b = walk_general(x, 0, nchunks, b);
+        } else {
+            uint32_t E = 0u, S = 0u;
+            for (int i = 0; i < nev; ++i) {
+                const uint4 ev = evs[i];
+                const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
+                const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);
+                if (kind == kEvAdd) {
+                    const unsigned long long Sn = (unsigned long long)S + (((unsigned long long)ev.w << 32) | ev.z);
+                    if ((ph == E || ph == kAnyPhase) && Sn < kPhaseLimit) {
+                        if (lane == 0) evb[i] = bits_of(E, S);  // boundary values of [c, s): filled in by the whole CTA afterwards
+                        S = (uint32_t)Sn;
+                        continue;
+                    }
+                } else if (kind == kEvMap) {
+                    const uint32_t Sn = S + ((S & 1u) ? ev.w : ev.z);
+                    if (ph == E && Sn < kPhaseLimit) {
+                        if (lane == 0) start_bits[c] = bits_of(E, S);
+                        S = Sn;
+                        continue;
+                    }
+                } else if (kind == kEvPack) {
+                    b = bits_of(E, S);
+                    if (lane == 0) start_bits[c] = b;
+                    const Pack* P = pack_of(x, c);
+                    const uint32_t b_in = b;
+                    if (debug > 1) {
+                        const unsigned fm = __ballot_sync(0xffffffffu, (P->e[lane] & kFlag) != 0u);
+                        const unsigned tm = __ballot_sync(0xffffffffu, (P->e[lane] & kTie0) != 0u);
+                        if (lane == 0) printf("  pack chunk %d: nev=%u flagged=%08x ties=%08x guess0=%u guess31=%u E=%u\n", c, P->nev, fm, tm, P->e[0] & kPhaseMask, P->e[31] & kPhaseMask, phase_of(b));
+                    }
+                    b = run_pack(x, P, c, b);
+                    __syncwarp();
+                    if (debug > 1) {
+                        const uint32_t b_ref = resolve_flagged(x, P, c, b_in, 0);
+                        if (b_ref != b && lane == 0) {
+                            printf("PACK MISMATCH chunk %d: in=%08x fast=%08x general=%08x nev=%u\n", c, b_in, b, b_ref, P->nev);
+                            for (int q = 0; q < (int)P->nev; ++q) printf("   ev[%d] = %08x %08x %08x %08x\n", q, P->ev[q].x, P->ev[q].y, P->ev[q].z, P->ev[q].w);
+                            for (int q = 0; q < 32; ++q) printf("   sub %d e=%08x q0=(%u,%u) ps0=%u\n", q, P->e[q], P->q0[q].d0, P->q0[q].d1, P->ps0[q]);
+                        }
+                        b = b_ref;
+                    }
+                    E = phase_of(b); S = b - (E << 23);
+                    continue;
+                }
+                if (debug > 1 && lane == 0) printf("GENERAL step %d kind=%u ph=%u E=%u S=%u c=%d s=%d z=%u w=%u\n", i, kind, ph, E, S, c, s, ev.z, ev.w);
+                // a contradicted guard, or a chunk without a shortcut: the general walk over this step's chunks
+                if (x.dbg && lane == 0) x.dbg[6]++;
+                if (lane == 0) evs[i].x = kEvSlow;  // (so that the fill below skips it)
+                b = walk_general(x, c, s, bits_of(E, S));
+                E = phase_of(b); S = b - (E << 23);
+            }
+            b = bits_of(E, S);
+        }
+        if (debug && lane == 0) { dbg_t[2] = clock64(); dbg_n[4] = nev; }
+        if (lane == 0) {
+            if (ema_out) *ema_out = src.stats[MERCURY_STAT_EMA];  // fused statistics: EMAverage.value for the next call
+            start_bits[nchunks] = b;
+            const float total = b2f(b);
+            *total_out = total;
+            if (!(total > 0.f)) atomicOr(status, MERCURY_ST_ZERO_SUM);
+            else if (isinf(total)) atomicOr(status, MERCURY_ST_NONFINITE);
+        }
+    }
+    __syncthreads();
+    // ---- boundary values inside the additive steps (whole CTA, one warp per step)
+    if (use_events) {
+        for (int i = warp; i < nev; i += kSpineNT / 32) {
+            const uint4 ev = evs[i];
+            if ((ev.x & 0xffu) != kEvAdd) continue;
+            const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);
+            const uint32_t b0 = evb[i], E = phase_of(b0), S = b0 - (E << 23);
+            const unsigned long long base = pc[c];
+            for (int k = c + lane; k < s; k += 32) start_bits[k] = bits_of(E, S + (uint32_t)(pc[k] - base));
+        }
+    }
+    if (debug) {
+        __syncthreads();
+        if (tid == 0)
+            printf("spine: nchunks=%d prefetch=%lld walk=%lld fill=%lld cycles | flagged=%d (late packs %d) serial_chunks=%d "
+                   "serial_subs=%d (+%d fetched) events=%d general_walks=%d pack_fallbacks=%d slots_wanted=%d\n",
+                   nchunks, dbg_t[1] - dbg_t[0], dbg_t[2] - dbg_t[1], (long long)clock64() - dbg_t[2], dbg_n[0], dbg_n[5], dbg_n[1],
+                   dbg_n[2], dbg_n[3], dbg_n[4], dbg_n[6], dbg_n[7], nslots_s);
     }
 }
 
@@ -874,14 +1198,14 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
 
 // workspace carving (all offsets 256-byte aligned)
 struct CdfWs {
-    double* sums; double* approx; int* slotid; Summary* summaries; SubSummary* subs; uint32_t* start_bits; float* total;
+    double* sums; double* approx; int* slotid; Summary* summaries; Pack* subs; uint32_t* start_bits; float* total;
     size_t bytes;
 };
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
-inline CdfWs carve(void* ws, int64_t n, bool direct_subs = false) {
+inline CdfWs carve(void* ws, int64_t n, bool direct_subs = false, int compact_slots = kSubSlots) {
     const size_t nchunks = (size_t)((n + kChunk - 1) / kChunk);
     const size_t nsubs = direct_subs && nchunks <= (size_t)kFusedMaxChunks ? (nchunks > (size_t)kSubSlots ? nchunks : (size_t)kSubSlots)
-                                                                          : (size_t)kSubSlots;
+                                                                          : (size_t)compact_slots;
     const size_t nsums = direct_subs ? (size_t)(n / 128 + 2) : nchunks;
     unsigned char* p = static_cast<unsigned char*>(ws);
     CdfWs w;
@@ -889,7 +1213,7 @@ inline CdfWs carve(void* ws, int64_t n, bool direct_subs = false) {
     w.sums = reinterpret_cast<double*>(p + off); off += align256(nsums * 8);
     w.approx = reinterpret_cast<double*>(p + off); off += align256((nchunks + 1) * 8);
     w.summaries = reinterpret_cast<Summary*>(p + off); off += align256(nchunks * sizeof(Summary));
-    w.subs = reinterpret_cast<SubSummary*>(p + off); off += align256(nsubs * sizeof(SubSummary));
+    w.subs = reinterpret_cast<Pack*>(p + off); off += align256(nsubs * sizeof(Pack));
     w.slotid = reinterpret_cast<int*>(p + off); off += align256(nchunks * 4);
     w.start_bits = reinterpret_cast<uint32_t*>(p + off); off += align256((nchunks + 1) * 4);
     w.total = reinterpret_cast<float*>(p + off); off += 256;
@@ -929,7 +1253,8 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel smem attribute");
         attr_set = true;
     }
-    spine_kernel<<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out);
+    static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
+    spine_kernel<<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, debug);
     MB_CHECK_LAUNCH("spine_kernel");
     return MERCURY_OK;
 }
@@ -954,7 +1279,7 @@ int pool_stats_launch(const float* scores, int64_t n, const int64_t* h_bounds, i
     chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, n, w.sums, nullptr, 0);
     MB_CHECK_LAUNCH("chunk_sums_kernel");
     stats_finalize_kernel<<<1, 1024, 0, st>>>(scores, n, w.sums, nchunks, bd, ema_state, ema_first, ema_alpha, smooth_alpha,
-                                              stats, w.approx, w.slotid, g_guess_bias);
+                                              stats, w.approx, w.slotid, g_guess_bias, kSubSlots);
     MB_CHECK_LAUNCH("stats_finalize_kernel");
     return MERCURY_OK;
 }
@@ -1037,20 +1362,21 @@ extern "C" int mercury_normalize(const float* scores, int64_t n, const float* st
 
 extern "C" size_t mercury_cdf_workspace_bytes(int64_t n) { return cdf_ws_bytes(n); }
 
-extern "C" int mercury_cdf(const float* weights, int64_t n, int mode, float* cdf, float* total, int32_t* status, void* ws,
-                           size_t ws_bytes, void* stream) {
-    MB_CHECK_ARG(n >= 1, "mercury_cdf: empty distribution");
+namespace {
+int cdf_run(const char* who, const float* weights, int64_t n, int mode, float* cdf, float* total, int32_t* status, void* ws,
+            size_t ws_bytes, int slots, void* stream) {
+    MB_CHECK_ARG(n >= 1, "%s: empty distribution", who);
     MB_CHECK_ARG(n <= ((int64_t)1 << 24), "number of categories cannot exceed 2^24");
-    MB_CHECK_ARG(weights && cdf && total && status, "mercury_cdf: null pointer");
-    MB_CHECK_ARG(mode == MERCURY_CDF_EXACT_SERIAL_F32 || mode == MERCURY_CDF_F64, "mercury_cdf: unknown mode %d", mode);
-    int rc = check_ws(ws, ws_bytes, cdf_ws_bytes(n), "mercury_cdf");
+    MB_CHECK_ARG(weights && cdf && total && status, "%s: null pointer", who);
+    MB_CHECK_ARG(mode == MERCURY_CDF_EXACT_SERIAL_F32 || mode == MERCURY_CDF_F64, "%s: unknown mode %d", who, mode);
+    const CdfWs w = carve(ws, n, false, slots);
+    int rc = check_ws(ws, ws_bytes, w.bytes, who);
     if (rc) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const CdfWs w = carve(ws, n);
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
     chunk_sums_kernel<<<nchunks, 256, 0, st>>>(weights, n, w.sums, status, 1);
     MB_CHECK_LAUNCH("chunk_sums_kernel");
-    prefix_finalize_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, w.approx, w.slotid, g_guess_bias);
+    prefix_finalize_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, w.approx, w.slotid, g_guess_bias, slots);
     MB_CHECK_LAUNCH("prefix_finalize_kernel");
     if (mode == MERCURY_CDF_F64) {
         materialize_f64_kernel<<<nchunks, 256, 0, st>>>(weights, n, w.approx, nchunks, cdf, total, status);
@@ -1063,8 +1389,14 @@ extern "C" int mercury_cdf(const float* weights, int64_t n, int mode, float* cdf
     materialize_kernel<<<nchunks, kMatNT, 0, st>>>(src, n, w.start_bits, w.total, cdf);
     MB_CHECK_LAUNCH("materialize_kernel");
     cudaError_t e = cudaMemcpyAsync(total, w.total, sizeof(float), cudaMemcpyDeviceToDevice, st);
-    if (e != cudaSuccess) return cuda_fail(e, "mercury_cdf: total copy");
+    if (e != cudaSuccess) return cuda_fail(e, "cdf: total copy");
     return MERCURY_OK;
+}
+}  // namespace
+
+extern "C" int mercury_cdf(const float* weights, int64_t n, int mode, float* cdf, float* total, int32_t* status, void* ws,
+                           size_t ws_bytes, void* stream) {
+    return cdf_run("mercury_cdf", weights, n, mode, cdf, total, status, ws, ws_bytes, kSubSlots, stream);
 }
 
 extern "C" int mercury_sample_with_replacement(const float* cdf, int64_t n, const double* uniforms, int64_t b, int64_t* idx,
@@ -1098,6 +1430,7 @@ extern "C" int mercury_sample_with_replacement(const float* cdf, int64_t n, cons
 // before any later stage reads it, so nothing in it has to start at zero and nothing is cleared.
 constexpr int64_t kStaticMaxN = (int64_t)MERCURY_STATIC_MAX_N;
 constexpr size_t kStaticScratchBytes = 208 * 1024;
+constexpr int kStaticSlots = 24;  // packs for chunks that change binade; beyond that the exact fallback path is taken
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
 namespace {
@@ -1136,12 +1469,12 @@ extern "C" int mercury_cdf_static(const float* weights, int64_t n, int mode, flo
                  "mercury_cdf_static: n = %lld exceeds the built-in scratch (at most %lld candidates); "
                  "use mercury_cdf with a caller-provided workspace",
                  (long long)n, (long long)kStaticMaxN);
-    if (cdf_ws_bytes(n) > kStaticScratchBytes) {  // cannot happen for n <= kStaticMaxN; kept as a guard
+    if (carve(nullptr, n, false, kStaticSlots).bytes > kStaticScratchBytes) {  // cannot happen for n <= kStaticMaxN; a guard
         set_last_error("mercury_cdf_static: internal scratch too small for n = %lld", (long long)n);
         return MERCURY_ERR_WORKSPACE;
     }
     void* scratch = nullptr;
     const int rc = static_scratch_for_current_device(&scratch);
     if (rc) return rc;
-    return mercury_cdf(weights, n, mode, cdf, total, status, scratch, kStaticScratchBytes, stream);
+    return cdf_run("mercury_cdf_static", weights, n, mode, cdf, total, status, scratch, kStaticScratchBytes, kStaticSlots, stream);
 }
