@@ -622,17 +622,27 @@ __host__ __device__ inline size_t spine_smem_bytes(int nchunks) {
 
 // exact pass over `count` consecutive candidates held in shared memory, from state b: this is
 // the reference's own loop (`sum += val` in fp32), run redundantly by every lane of the warp.
-__device__ __forceinline__ uint32_t serial_chain(uint32_t b, const uint32_t* __restrict__ v, int count) {
-    float s = b2f(b);
-    const uint4* v4 = reinterpret_cast<const uint4*>(v);
-#pragma unroll 4
-    for (int i = 0; i < count / 4; ++i) {
-        const uint4 q = v4[i];
-        s = __fadd_rn(s, b2f(q.x));
-        s = __fadd_rn(s, b2f(q.y));
-        s = __fadd_rn(s, b2f(q.z));
-        s = __fadd_rn(s, b2f(q.w));
+// `v` must point into SHARED memory (16-byte aligned).  All loads are issued first (explicit
+// ld.shared, so that they are neither generic nor throttled by the scheduler's register heuristics);
+// the 64 dependent adds then run back to back, 4 cycles each.
+__device__ __forceinline__ float serial_block(float s, uint32_t saddr) {
+    uint4 q[kSub / 4];
+#pragma unroll
+    for (int i = 0; i < kSub / 4; ++i)
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q[i].x), "=r"(q[i].y), "=r"(q[i].z), "=r"(q[i].w) : "r"(saddr + 16u * i));
+#pragma unroll
+    for (int i = 0; i < kSub / 4; ++i) {
+        s = __fadd_rn(s, b2f(q[i].x));
+        s = __fadd_rn(s, b2f(q[i].y));
+        s = __fadd_rn(s, b2f(q[i].z));
+        s = __fadd_rn(s, b2f(q[i].w));
     }
+    return s;
+}
+__device__ __forceinline__ uint32_t serial_chain(uint32_t b, const uint32_t* v, int count) {
+    float s = b2f(b);
+    const uint32_t saddr = smem_u32(v);
+    for (int blk = 0; blk < count / kSub; ++blk) s = serial_block(s, saddr + blk * kSub * 4u);
     return f2b(s);
 }
 
@@ -645,7 +655,7 @@ __device__ __forceinline__ int next_bit(const uint32_t* words, int from) {
 }
 
 struct SpineCtx {
-    WeightSrc src; int64_t n; float shift, totalw; int lane; int* dbg;
+    WeightSrc src; int64_t n; float shift, totalw; int lane; int* dbg; long long* dbgt;
     // shared memory
     const unsigned long long* pc; const uint32_t* ce; const uint32_t* qd0; const uint32_t* qd1; const uint32_t* stopw;
     const uint8_t* slot_of; const Pack* slots; Pack* spare; uint32_t* stage;
@@ -654,8 +664,9 @@ struct SpineCtx {
 };
 
 // serial fallback over a whole chunk (guess contradicted): stage it, then the reference loop
+template <bool DBG>
 __device__ __noinline__ uint32_t serial_chunk(const SpineCtx& x, int c, uint32_t b) {
-    if (x.dbg && x.lane == 0) x.dbg[1]++;
+    if (DBG && x.lane == 0) x.dbg[1]++;
     const int64_t e0 = (int64_t)c * kChunk;
     for (int i = x.lane; i < kChunk; i += 32) x.stage[i] = e0 + i < x.n ? f2b(x.src.get(e0 + i, x.shift, x.totalw)) : 0u;
     __syncwarp();
@@ -665,12 +676,14 @@ __device__ __noinline__ uint32_t serial_chunk(const SpineCtx& x, int c, uint32_t
 }
 
 // serial pass over sub-chunk k of chunk c: raw candidates from the pack if it carries them
+template <bool DBG>
 __device__ __forceinline__ uint32_t serial_sub(const SpineCtx& x, const Pack* P, int c, int k, uint32_t b) {
+    const long long t0 = DBG ? clock64() : 0;
     int r = -1;
 #pragma unroll
     for (int q = 0; q < kRawPerPack; ++q) if (P->rawsub[q] == k) r = q;
     const uint32_t* raw;
-    if (x.dbg && x.lane == 0) x.dbg[r >= 0 ? 2 : 3]++;
+    if (DBG && x.lane == 0) x.dbg[r >= 0 ? 2 : 3]++;
     if (r >= 0) raw = P->raw[r];
     else {
         const int64_t i0 = (int64_t)c * kChunk + k * kSub + 2 * x.lane;
@@ -681,10 +694,12 @@ __device__ __forceinline__ uint32_t serial_sub(const SpineCtx& x, const Pack* P,
     }
     b = serial_chain(b, raw, kSub);
     __syncwarp();
+    if (DBG && x.lane == 0) x.dbgt[0] += clock64() - t0;
     return b;
 }
 
 // a flagged chunk from sub-chunk k0 on, the general way: whatever the phase turns out to be
+template <bool DBG>
 __device__ __noinline__ uint32_t resolve_flagged(const SpineCtx& x, const Pack* P, int c, uint32_t b, int k0) {
     const int lane = x.lane;
     const uint32_t ek_l = P->e[lane];
@@ -701,12 +716,12 @@ __device__ __noinline__ uint32_t resolve_flagged(const SpineCtx& x, const Pack* 
         if ((any_m >> k) & 1u) { ++k; continue; }                   // all zeros: nothing happens
         const uint32_t g = P->e[k] & kPhaseMask;
         const int w = E == g ? 0 : (E == g + 1u ? 1 : -1);
-        if (((flag_m >> k) & 1u) || w < 0) { b = serial_sub(x, P, c, k, b); ++k; continue; }
+        if (((flag_m >> k) & 1u) || w < 0) { b = serial_sub<DBG>(x, P, c, k, b); ++k; continue; }
         const unsigned tie_m = w ? tie1_m : tie0_m;
         if ((tie_m >> k) & 1u) {                                     // exact ties inside: apply the 2-state map
             const Pair q = w ? P->q1[k] : P->q0[k];
             const uint32_t Sn = apply(q, S);
-            if (Sn >= kPhaseLimit) b = serial_sub(x, P, c, k, b); else b = bits_of(E, Sn);
+            if (Sn >= kPhaseLimit) b = serial_sub<DBG>(x, P, c, k, b); else b = bits_of(E, Sn);
             ++k;
             continue;
         }
@@ -720,7 +735,7 @@ __device__ __noinline__ uint32_t resolve_flagged(const SpineCtx& x, const Pack* 
         // the phase changes inside the run after all: find the sub-chunk, sum it serially
         const bool over = lane >= k && lane < s && S + (ps[lane + 1] - base) >= kPhaseLimit;
         const int f = __ffs(__ballot_sync(0xffffffffu, over)) - 1;
-        b = serial_sub(x, P, c, f, bits_of(E, S + (ps[f] - base)));
+        b = serial_sub<DBG>(x, P, c, f, bits_of(E, S + (ps[f] - base)));
         k = f + 1;
     }
     return b;
@@ -728,6 +743,7 @@ __device__ __noinline__ uint32_t resolve_flagged(const SpineCtx& x, const Pack* 
 
 // a flagged chunk along its precompiled walk (the expected case); the first contradicted guard
 // hands the rest of the chunk to the general code
+template <bool DBG>
 __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, int c, uint32_t b) {
     const int nev = (int)P->nev;
     uint32_t E = phase_of(b), S = b - (E << 23);
@@ -741,30 +757,35 @@ __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, i
             const uint32_t Sn = S + ((S & 1u) ? ev.w : ev.z);
             if (ph == E && Sn < kPhaseLimit) { S = Sn; continue; }
         } else {
-            b = serial_sub(x, P, c, (int)(ev.x >> 20), bits_of(E, S));
+            b = serial_sub<DBG>(x, P, c, (int)(ev.x >> 20), bits_of(E, S));
             E = phase_of(b); S = b - (E << 23);
             continue;
         }
-        if (x.dbg && x.lane == 0) x.dbg[7]++;
-        return resolve_flagged(x, P, c, bits_of(E, S), (int)(ev.x >> 20));
+        if (DBG && x.lane == 0) x.dbg[7]++;
+        return resolve_flagged<DBG>(x, P, c, bits_of(E, S), (int)(ev.x >> 20));
     }
     return bits_of(E, S);
 }
 
-__device__ __forceinline__ const Pack* pack_of(const SpineCtx& x, int c) {
-    const int sl = (int)x.slot_of[c] - 1;
-    if (x.dbg && x.lane == 0) { x.dbg[0]++; if (sl < 0) x.dbg[5]++; }
-    if (sl >= 0) return &x.slots[sl];
-    // not prefetched: one cooperative copy instead of many dependent global reads
+// a pack that was not prefetched: one cooperative copy instead of many dependent global reads
+template <bool DBG>
+__device__ __noinline__ const Pack* fetch_pack(const SpineCtx& x, int c) {
     const uint4* g4 = reinterpret_cast<const uint4*>(x.packs + x.sums[c].pad[0]);
     uint4* s4 = reinterpret_cast<uint4*>(x.spare);
     for (int i = x.lane; i < (int)(sizeof(Pack) / 16); i += 32) s4[i] = g4[i];
     __syncwarp();
     return x.spare;
 }
+template <bool DBG>
+__device__ __forceinline__ const Pack* pack_of(const SpineCtx& x, int c) {
+    const int sl = (int)x.slot_of[c] - 1;
+    if (DBG && x.lane == 0) { x.dbg[0]++; if (sl < 0) x.dbg[5]++; }
+    return sl >= 0 ? &x.slots[sl] : fetch_pack<DBG>(x, c);
+}
 
 // chunks [c, c_end) the general way (no precompiled steps, or one of them was contradicted);
 // writes their boundary values itself
+template <bool DBG>
 __device__ __noinline__ uint32_t walk_general(const SpineCtx& x, int c, int c_end, uint32_t b) {
     const int lane = x.lane;
     while (c < c_end) {
@@ -772,17 +793,17 @@ __device__ __noinline__ uint32_t walk_general(const SpineCtx& x, int c, int c_en
         const uint32_t ec = x.ce[c], g = ec & kPhaseMask;
         if (lane == 0) x.start_bits[c] = b;
         if (ec & kFlag) {
-            const Pack* P = pack_of(x, c);
-            b = run_pack(x, P, c, b);
+            const Pack* P = pack_of<DBG>(x, c);
+            b = run_pack<DBG>(x, P, c, b);
             __syncwarp();
             ++c;
             continue;
         }
         if (g == kAnyPhase) { ++c; continue; }  // all zeros
-        if (g != E || (ec & kNoPack)) { b = serial_chunk(x, c, b); ++c; continue; }
+        if (g != E || (ec & kNoPack)) { b = serial_chunk<DBG>(x, c, b); ++c; continue; }
         if (ec & kTie0) {
             const uint32_t Sn = apply(Pair{x.qd0[c], x.qd1[c]}, S);
-            if (Sn >= kPhaseLimit) b = serial_chunk(x, c, b); else b = bits_of(E, Sn);
+            if (Sn >= kPhaseLimit) b = serial_chunk<DBG>(x, c, b); else b = bits_of(E, Sn);
             ++c;
             continue;
         }
@@ -803,15 +824,28 @@ __device__ __noinline__ uint32_t walk_general(const SpineCtx& x, int c, int c_en
         if (end == s) { b = bits_of(E, (uint32_t)Sn); c = s; continue; }
         const uint32_t bf = bits_of(E, S + (uint32_t)(x.pc[end] - base));
         if (lane == 0) x.start_bits[end] = bf;
-        b = serial_chunk(x, end, bf);
+        b = serial_chunk<DBG>(x, end, bf);
         c = end + 1;
     }
     return b;
 }
 
+// developer aid (MERCURY_SPINE_DEBUG=2): the precompiled walk through a pack against the general code
+template <bool DBG>
+__device__ __noinline__ uint32_t debug_check_pack(const SpineCtx& x, const Pack* P, int c, uint32_t b_in, uint32_t b_fast) {
+    const uint32_t b_ref = resolve_flagged<DBG>(x, P, c, b_in, 0);
+    if (b_ref != b_fast && x.lane == 0) {
+        printf("PACK MISMATCH chunk %d: in=%08x fast=%08x general=%08x nev=%u\n", c, b_in, b_fast, b_ref, P->nev);
+        for (int q = 0; q < (int)P->nev; ++q) printf("   ev[%d] = %08x %08x %08x %08x\n", q, P->ev[q].x, P->ev[q].y, P->ev[q].z, P->ev[q].w);
+    }
+    return b_ref;
+}
+
+template <bool DBG>
 __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
                                                          const Pack* __restrict__ packs, uint32_t* __restrict__ start_bits,
-                                                         float* __restrict__ total_out, int32_t* status, float* ema_out, int debug) {
+                                                         float* __restrict__ total_out, int32_t* status, float* ema_out, int debug_level) {
+    const int debug = DBG ? debug_level : 0;
     extern __shared__ __align__(128) unsigned char sm[];
     __shared__ int nslots_s, nev_s;
     __shared__ int slot_global[kMaxSlots];
@@ -820,8 +854,9 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     __shared__ int wcnt[kSpineNT / 32];
     __shared__ int carry_ev;
     __shared__ long long dbg_t[4];
+    __shared__ long long dbg_t2[4];  // cycles in serial passes, in packs (total), fetching packs
     __shared__ int dbg_n[8];  // flagged, serial chunks, serial subs (raw at hand), serial subs (fetched), events, late packs, general walks
-    if (debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; }
+    if (DBG && debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; for (int i = 0; i < 4; ++i) dbg_t2[i] = 0; }
     // shared-memory layout
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);               // [nchunks+1] prefix of increments
     uint32_t* ce = reinterpret_cast<uint32_t*>(pc + nchunks + 1);                      // [nchunks] guess | flags
@@ -927,18 +962,29 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     const int nev = nev_s;
     const bool use_events = nev <= kMaxEvents && nchunks < 65536;
 
-    if (debug && tid == 0) dbg_t[1] = clock64();
+    if (DBG && debug && tid == 0) dbg_t[1] = clock64();
     if (warp == 0) {
         // ---- the walk (one warp; scalar logic is replicated on all lanes)
         SpineCtx x;
-        x.dbg = debug ? dbg_n : nullptr;
+        x.dbg = dbg_n;
+        x.dbgt = dbg_t2;
         x.src = src; x.n = n; x.lane = lane;
         src.prepare(x.shift, x.totalw);
         x.pc = pc; x.ce = ce; x.qd0 = qd0; x.qd1 = qd1; x.stopw = stopw; x.slot_of = slot_of; x.slots = slots; x.spare = spare;
         x.stage = stage; x.sums = sums; x.packs = packs; x.start_bits = start_bits;
         uint32_t b = 0u;  // the running sum starts at +0
+        if (DBG && debug == 3) {  // micro-timing of the primitives
+            uint32_t t = 1u;
+            long long c0 = clock64();
+            for (int r = 0; r < 8; ++r) t = serial_chain(t, stage, kSub);
+            long long c1 = clock64();
+            uint32_t acc = t;
+            for (int r = 0; r < 64; ++r) { const uint4 ev = evs[r & 15]; acc += ev.x + ev.y; if (acc & 1u) acc ^= ev.z; }
+            long long c2 = clock64();
+            if (lane == 0) printf("micro: serial_chain(64) = %lld cycles each; 64 dependent smem loads+alu = %lld cycles each (%u)\n", (c1 - c0) / 8, (c2 - c1) / 64, acc);
+        }
         if (!use_events) {
-            b = walk_general(x, 0, nchunks, b);
+            b = walk_general<DBG>(x, 0, nchunks, b);
         } else {
             uint32_t E = 0u, S = 0u;
             for (int i = 0; i < nev; ++i) {
@@ -962,37 +1008,30 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
                 } else if (kind == kEvPack) {
                     b = bits_of(E, S);
                     if (lane == 0) start_bits[c] = b;
-                    const Pack* P = pack_of(x, c);
+                    const long long tp0 = DBG ? clock64() : 0;
+                    const int sl = (int)slot_of[c] - 1;
+                    if (DBG && debug && lane == 0) { dbg_n[0]++; if (sl < 0) dbg_n[5]++; }
+                    if (sl < 0) fetch_pack<DBG>(x, c);
+                    const Pack* P = sl >= 0 ? &slots[sl] : spare;  // (both in shared memory: plain LDS below)
+                    if (DBG && debug && lane == 0) dbg_t2[2] += clock64() - tp0;
                     const uint32_t b_in = b;
-                    if (debug > 1) {
-                        const unsigned fm = __ballot_sync(0xffffffffu, (P->e[lane] & kFlag) != 0u);
-                        const unsigned tm = __ballot_sync(0xffffffffu, (P->e[lane] & kTie0) != 0u);
-                        if (lane == 0) printf("  pack chunk %d: nev=%u flagged=%08x ties=%08x guess0=%u guess31=%u E=%u\n", c, P->nev, fm, tm, P->e[0] & kPhaseMask, P->e[31] & kPhaseMask, phase_of(b));
-                    }
-                    b = run_pack(x, P, c, b);
+                    b = run_pack<DBG>(x, P, c, b);
                     __syncwarp();
-                    if (debug > 1) {
-                        const uint32_t b_ref = resolve_flagged(x, P, c, b_in, 0);
-                        if (b_ref != b && lane == 0) {
-                            printf("PACK MISMATCH chunk %d: in=%08x fast=%08x general=%08x nev=%u\n", c, b_in, b, b_ref, P->nev);
-                            for (int q = 0; q < (int)P->nev; ++q) printf("   ev[%d] = %08x %08x %08x %08x\n", q, P->ev[q].x, P->ev[q].y, P->ev[q].z, P->ev[q].w);
-                            for (int q = 0; q < 32; ++q) printf("   sub %d e=%08x q0=(%u,%u) ps0=%u\n", q, P->e[q], P->q0[q].d0, P->q0[q].d1, P->ps0[q]);
-                        }
-                        b = b_ref;
-                    }
+                    if (DBG && debug > 1) b = debug_check_pack<DBG>(x, P, c, b_in, b);
                     E = phase_of(b); S = b - (E << 23);
+                    if (DBG && debug && lane == 0) dbg_t2[1] += clock64() - tp0;
                     continue;
                 }
-                if (debug > 1 && lane == 0) printf("GENERAL step %d kind=%u ph=%u E=%u S=%u c=%d s=%d z=%u w=%u\n", i, kind, ph, E, S, c, s, ev.z, ev.w);
+                if (DBG && debug > 1 && lane == 0) printf("GENERAL step %d kind=%u ph=%u E=%u S=%u c=%d s=%d z=%u w=%u\n", i, kind, ph, E, S, c, s, ev.z, ev.w);
                 // a contradicted guard, or a chunk without a shortcut: the general walk over this step's chunks
-                if (x.dbg && lane == 0) x.dbg[6]++;
+                if (DBG && lane == 0) x.dbg[6]++;
                 if (lane == 0) evs[i].x = kEvSlow;  // (so that the fill below skips it)
-                b = walk_general(x, c, s, bits_of(E, S));
+                b = walk_general<DBG>(x, c, s, bits_of(E, S));
                 E = phase_of(b); S = b - (E << 23);
             }
             b = bits_of(E, S);
         }
-        if (debug && lane == 0) { dbg_t[2] = clock64(); dbg_n[4] = nev; }
+        if (DBG && debug && lane == 0) { dbg_t[2] = clock64(); dbg_n[4] = nev; }
         if (lane == 0) {
             if (ema_out) *ema_out = src.stats[MERCURY_STAT_EMA];  // fused statistics: EMAverage.value for the next call
             start_bits[nchunks] = b;
@@ -1014,13 +1053,13 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             for (int k = c + lane; k < s; k += 32) start_bits[k] = bits_of(E, S + (uint32_t)(pc[k] - base));
         }
     }
-    if (debug) {
+    if (DBG && debug) {
         __syncthreads();
         if (tid == 0)
             printf("spine: nchunks=%d prefetch=%lld walk=%lld fill=%lld cycles | flagged=%d (late packs %d) serial_chunks=%d "
-                   "serial_subs=%d (+%d fetched) events=%d general_walks=%d pack_fallbacks=%d slots_wanted=%d\n",
+                   "serial_subs=%d (+%d fetched) events=%d general_walks=%d pack_fallbacks=%d slots_wanted=%d | cycles: serial=%lld packs=%lld pack_of=%lld\n",
                    nchunks, dbg_t[1] - dbg_t[0], dbg_t[2] - dbg_t[1], (long long)clock64() - dbg_t[2], dbg_n[0], dbg_n[5], dbg_n[1],
-                   dbg_n[2], dbg_n[3], dbg_n[4], dbg_n[6], dbg_n[7], nslots_s);
+                   dbg_n[2], dbg_n[3], dbg_n[4], dbg_n[6], dbg_n[7], nslots_s, dbg_t2[0], dbg_t2[1], dbg_t2[2]);
     }
 }
 
@@ -1249,12 +1288,14 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     const size_t smem = spine_smem_bytes(nchunks);
     static bool attr_set = false;  // per process; the attribute is sticky per device function
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(spine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spine_smem_bytes(8192));
+        cudaError_t e = cudaFuncSetAttribute(spine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spine_smem_bytes(8192));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spine_smem_bytes(8192));
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel smem attribute");
         attr_set = true;
     }
     static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
-    spine_kernel<<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, debug);
+    if (debug) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, debug);
+    else spine_kernel<false><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, 0);
     MB_CHECK_LAUNCH("spine_kernel");
     return MERCURY_OK;
 }
