@@ -437,12 +437,12 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         load_chunk<kSumNT, kSumIPT>(src, start, len, pb);
     }
     // Guess the phase from the approximate running total at both ends of the chunk.  If both ends
-    // agree the chunk is expected to stay in one phase; otherwise it is flagged: it also gets the
-    // map for the next phase and (if a slot was assigned by the prefix scan) sub-chunk summaries.
+    // agree the chunk is expected to stay in one phase; otherwise it is flagged and (if a slot was
+    // assigned to it) gets a pack of sub-chunk summaries for the spine.
     uint32_t e;
     const bool flagged = guess_span(a_lo, a_hi, bias, &e);  // block-uniform
     if (FUSED) slot = flagged ? (int)blockIdx.x : -1;
-    Pair a0 = identity_pair(), a1 = identity_pair();
+    Pair a0 = identity_pair();
     int bad = 0;
     bool nz = false;
     float tsum = 0.f;
@@ -456,22 +456,19 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         nz |= pb[k] != 0u;
         tsum += x;
         a0 = compose(a0, addend_pair_fast(pb[k], e));
-        if (flagged) a1 = compose(a1, addend_pair_fast(pb[k], e + 1u));
     }
     if (bad) atomicOr(status, bad);
     const unsigned nzmask = __ballot_sync(0xffffffffu, nz);
     // ordered reduction: lane 0 ends with the composition of the whole warp.  Without exact ties
     // every map is a plain increment and the composition is one integer warp reduction.
-    if (__ballot_sync(0xffffffffu, a0.d0 != a0.d1 || a1.d0 != a1.d1) == 0u) {
+    if (__ballot_sync(0xffffffffu, a0.d0 != a0.d1) == 0u) {
         a0.d0 = a0.d1 = sat(__reduce_add_sync(0xffffffffu, a0.d0));
-        a1.d0 = a1.d1 = sat(__reduce_add_sync(0xffffffffu, a1.d0));
     } else {
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
-            Pair o0, o1;
+            Pair o0;
             o0.d0 = __shfl_down_sync(0xffffffffu, a0.d0, off); o0.d1 = __shfl_down_sync(0xffffffffu, a0.d1, off);
-            o1.d0 = __shfl_down_sync(0xffffffffu, a1.d0, off); o1.d1 = __shfl_down_sync(0xffffffffu, a1.d1, off);
-            if (lane + off < 32) { a0 = compose(a0, o0); a1 = compose(a1, o1); }
+            if (lane + off < 32) a0 = compose(a0, o0);
         }
     }
     float inc = tsum;  // inclusive scan of the thread sums (approximate, only feeds sub-chunk guesses)
@@ -482,18 +479,18 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
             if (lane >= off) inc += o;
         }
     }
-    if (lane == 0) { wt[0][warp] = a0; wt[1][warp] = a1; wnz[warp] = nzmask != 0u; }
+    if (lane == 0) { wt[0][warp] = a0; wnz[warp] = nzmask != 0u; }
     if (lane == 31) wsum[warp] = inc;
     __syncthreads();
     if (threadIdx.x == 0) {
-        Pair t0 = identity_pair(), t1 = identity_pair();
+        Pair t0 = identity_pair();
         int any = 0;
 #pragma unroll
-        for (int i = 0; i < kSumNT / 32; ++i) { t0 = compose(t0, wt[0][i]); t1 = compose(t1, wt[1][i]); any |= wnz[i]; }
+        for (int i = 0; i < kSumNT / 32; ++i) { t0 = compose(t0, wt[0][i]); any |= wnz[i]; }
         Summary s;
         s.e = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u) | (flagged && slot < 0 ? kNoPack : 0u) | (t0.d0 != t0.d1 ? kTie0 : 0u);
         s.q[0] = t0;
-        s.q[1] = flagged ? t1 : Pair{kSatCap, kSatCap};
+        s.q[1] = Pair{kSatCap, kSatCap};  // (unused: flagged chunks are crossed through their packs)
         s.pad[0] = (uint32_t)slot; s.pad[1] = s.pad[2] = 0;
         out[blockIdx.x] = s;
     }
