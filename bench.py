@@ -38,6 +38,16 @@ def algorithmic_bytes(n, c, s, b, row_bytes):
     return n * (c * s + 8 + 4) + b * (2 * row_bytes + 2 * 8 + 2 * 8 + 4 + 4 + 8)
 
 
+def k1_traffic(workload):
+    """DRAM bytes (read + write) of one K1 launch from the committed `ncu --set full` capture."""
+    p = os.path.join(ROOT, "profiles", "r1_k1_traffic.json")
+    try:
+        t = json.load(open(p))[workload]
+        return t["dram_bytes_read"] + t["dram_bytes_write"]
+    except Exception:
+        return None
+
+
 def peak_hbm():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -372,7 +382,7 @@ def main():
             "step_roofline": {"algorithmic_bytes": step_bytes, "achieved_gbs": step_bytes / (ms * 1e-3) / 1e9,
                               "frac": step_bytes / (ms * 1e-3) / 1e9 / peak},
             "roofline": {"kernel": "K1 score (mercury_score)", "bound": "hbm", "achieved": k1_gbs, "peak": peak, "unit": "GB/s",
-                         "frac": k1_gbs / peak, "traffic": None, "peak_source": peak_src, "ms_per_launch": k1_ms,
+                         "frac": k1_gbs / peak, "traffic": k1_traffic(args.workload) if world == 1 else None, "peak_source": peak_src, "ms_per_launch": k1_ms,
                          "algorithmic_bytes_per_launch": k1_bytes},
             "e2e": {"value": total_candidates / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps},
