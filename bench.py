@@ -174,6 +174,10 @@ def run_reference(args, wl):
 
 
 def main():
+    if os.environ.get("MERCURY_BENCH_FAULT_TIMEOUT"):  # developer aid: dump every thread's stack if the run stalls
+        import faulthandler
+
+        faulthandler.dump_traceback_later(float(os.environ["MERCURY_BENCH_FAULT_TIMEOUT"]), exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=40)
@@ -246,9 +250,10 @@ def main():
         r = step(i, first=(i == 0))
     barrier()
     # One CUDA graph per pool (the pools differ only in their pointers): the step is replayed with
-    # no host work between its kernels.  Multi-rank steps contain an NCCL collective and stay eager.
+    # no host work between its kernels.  Multi-rank steps capture their NCCL all-gather in the graph
+    # as well (MERCURY_BENCH_GRAPH_NCCL=0 keeps them eager).
     graphs = None
-    if args.graph and world == 1:
+    if args.graph and (world == 1 or os.environ.get("MERCURY_BENCH_GRAPH_NCCL", "1") == "1"):
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -280,18 +285,16 @@ def main():
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1) / args.steps
-        # keep the clocks sampled over a region long enough for nvidia-smi to see it
-        t_end = time.time() + 0.6
-        i = 0
-        while time.time() < t_end:
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        # keep the clocks sampled over a region long enough for nvidia-smi to see it (~0.6 s; the
+        # SAME number of steps on every rank: a step contains a collective)
+        for i in range(max(1, min(20000, int(600.0 / max(ms, 1e-3))))):
             run(i)
-            i += 1
         torch.cuda.synchronize()
     ops.check_status(r["status"])
-    if dist is not None:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t)
     total_candidates = n * world
     value = total_candidates / (ms * 1e-3)
 
@@ -306,18 +309,29 @@ def main():
         for i in range(3):
             ops.score(*pools[i % npools], status=st, out=sc)
     torch.cuda.synchronize()
-    kg = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(kg, stream=kstream):
-        for i in range(npools):
-            ops.score(*pools[i], status=st, out=sc)
     reps = max(2, -(-max(args.steps, 10) // npools))
-    with torch.cuda.stream(kstream):
-        kg.replay()
-        a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(kstream)
-        for _ in range(reps):
+    if world == 1:
+        kg = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(kg, stream=kstream):
+            for i in range(npools):
+                ops.score(*pools[i], status=st, out=sc)
+        with torch.cuda.stream(kstream):
             kg.replay()
-        z.record(kstream)
+            a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(kstream)
+            for _ in range(reps):
+                kg.replay()
+            z.record(kstream)
+    else:
+        # multi-rank: no graph capture beside NCCL's watchdog; stall the stream so that the launches queue up
+        with torch.cuda.stream(kstream):
+            torch.cuda._sleep(int(4e6))
+            a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(kstream)
+            for _ in range(reps):
+                for i in range(npools):
+                    ops.score(*pools[i], status=st, out=sc)
+            z.record(kstream)
     torch.cuda.synchronize()
     k1_ms = a.elapsed_time(z) / (reps * npools)
     peak, peak_src = peak_hbm()
@@ -393,8 +407,13 @@ def main():
             line["cpu_baseline"] = cpu_baseline(wl)
         print(json.dumps(line))
     if dist is not None:
+        # Graphs that captured NCCL work keep the communicator busy at teardown (destroy_process_group
+        # was seen to block): agree that everybody is done, then leave without the collective teardown.
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
