@@ -65,8 +65,8 @@ constexpr uint32_t kNoPack = 0x10000000u; // chunk expected to change phase but 
 constexpr int kSub = 64, kSubsPerChunk = kChunk / kSub;
 constexpr int kSubSlots = 128;            // flagged chunks that get a pack (compact layout)
 constexpr int kRawPerPack = 6;
-constexpr double kGuessMargin = 1.0 / 4096.0;     // chunks: generous, a flagged chunk only costs a pack
-constexpr double kSubGuessMargin = 1.0 / 16384.0;   // sub-chunks: the fp32 chain drifts ~1e-4 from the exact sum at 1M candidates
+constexpr double kGuessMargin = 1.0 / 1024.0;     // chunks: generous, a flagged chunk only costs a pack
+constexpr double kSubGuessMargin = 1.0 / 8192.0;   // sub-chunks: the fp32 chain drifts ~1e-4 from the exact sum at 1M candidates
 static_assert(kSubsPerChunk == 32, "one sub-chunk per lane of the walking warp");
 
 // Guess the phase of the running sum over a span from its approximate value at both ends, with
@@ -378,7 +378,7 @@ static_assert(kSumIPT * 8 == kSub, "a sub-chunk is 8 consecutive threads");
 // every CTA reduces the partial sums of the scores itself -- same data, same order, so all CTAs
 // agree to the bit on mean / EMA / shift / total -- which removes a single-CTA kernel from the
 // dependency chain.  CTA 0 publishes the statistics block; the spine stores the new EMA state.
-constexpr int kFusedMaxChunks = 2048;
+constexpr int kFusedMaxChunks = 8192;
 struct FusedStats {
     const double* part;  // sums of `per` consecutive scores each (per divides kChunk)
     int npart, per;
@@ -608,13 +608,19 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
 // values of the chunks that were crossed in runs.
 constexpr int kSpineNT = 512;
 constexpr int kMaxSlots = 32;    // packs prefetched into shared memory (the rest are fetched when reached)
+constexpr int kStageWords = kSub + kSubsPerChunk * (kSub + 1) + 32;  // scratch line + one padded chunk
 constexpr int kMaxEvents = 640;  // precompiled chunk-level steps (more: the general walk is used)
 
-__host__ __device__ inline int spine_slots(int nchunks) { return nchunks <= 2048 ? kMaxSlots : 8; }
+__host__ __device__ inline int spine_slots(int nchunks) {  // as many as fit beside the per-chunk arrays
+    const long room = 214L * 1024 - ((long)(nchunks + 1) * 8 + (long)nchunks * 13 + (long)((nchunks + 32) / 32) * 4) -
+                      (long)kStageWords * 4 - (long)kMaxEvents * 20;
+    const long fit = room / (long)sizeof(Pack) - 1;
+    return (int)(fit > kMaxSlots ? kMaxSlots : (fit < 4 ? 4 : fit));
+}
 __host__ __device__ inline size_t spine_smem_bytes(int nchunks) {
     size_t b = (size_t)(nchunks + 1) * 8 + (size_t)nchunks * 13 + (size_t)((nchunks + 32) / 32) * 4;
     b = (b + 127) & ~(size_t)127;
-    return b + (size_t)(spine_slots(nchunks) + 1) * sizeof(Pack) + (size_t)kChunk * 4 + (size_t)kMaxEvents * 20;
+    return b + (size_t)(spine_slots(nchunks) + 1) * sizeof(Pack) + (size_t)kStageWords * 4 + (size_t)kMaxEvents * 20;
 }
 
 // exact pass over `count` consecutive candidates held in shared memory, from state b: this is
@@ -660,14 +666,65 @@ struct SpineCtx {
     const Summary* sums; const Pack* packs; uint32_t* start_bits;
 };
 
-// serial fallback over a whole chunk (guess contradicted): stage it, then the reference loop
+// inclusive scan of one map per lane, in lane order.  Without exact ties every map is a plain
+// integer increment (d0 == d1): an integer prefix sum then does (32 * 2^25 fits in 32 bits).
+__device__ __forceinline__ Pair warp_scan_pair(Pair x, int lane) {
+    if (__ballot_sync(0xffffffffu, x.d0 != x.d1) == 0u) {
+        uint32_t v = x.d0;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, v, off);
+            if (lane >= off) v += o;
+        }
+        v = sat(v);
+        return Pair{v, v};
+    }
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        Pair o = shfl_up_pair(x, off);
+        if (lane >= off) x = compose(o, x);
+    }
+    return x;
+}
+
+// fallback over a whole chunk whose guess was contradicted (no usable summary): stage it in shared
+// memory, then go phase by phase -- every lane reduces "its" 64-candidate sub-chunk to a map for
+// the current phase, a warp scan finds the sub-chunk in which the phase changes, that one is
+// summed serially (the reference loop), and the remaining sub-chunks are redone in the new phase.
 template <bool DBG>
 __device__ __noinline__ uint32_t serial_chunk(const SpineCtx& x, int c, uint32_t b) {
     if (DBG && x.lane == 0) x.dbg[1]++;
+    const int lane = x.lane;
     const int64_t e0 = (int64_t)c * kChunk;
-    for (int i = x.lane; i < kChunk; i += 32) x.stage[i] = e0 + i < x.n ? f2b(x.src.get(e0 + i, x.shift, x.totalw)) : 0u;
+    // layout: stage[0..63] is an aligned scratch line; sub-chunk k lives at stage[64 + 65*k ..] (the odd
+    // stride keeps the 32 lanes, each walking its own sub-chunk, on different banks)
+    uint32_t* padded = x.stage + kSub;
+#pragma unroll 8
+    for (int i = lane; i < kChunk; i += 32)
+        padded[(i >> 6) * (kSub + 1) + (i & (kSub - 1))] = e0 + i < x.n ? f2b(x.src.get(e0 + i, x.shift, x.totalw)) : 0u;
     __syncwarp();
-    b = serial_chain(b, x.stage, kChunk);
+    int first = 0;
+    while (first < kSubsPerChunk) {
+        const uint32_t E = phase_of(b), S = b - (E << 23);
+        Pair m = identity_pair();
+        if (lane >= first) {
+            const uint32_t* v = padded + lane * (kSub + 1);
+            for (int j = 0; j < kSub; ++j) m = compose(m, addend_pair_fast(v[j], E));
+        }
+        const Pair inc = warp_scan_pair(m, lane);
+        Pair ex = shfl_up_pair(inc, 1);
+        if (lane == 0) ex = identity_pair();
+        const uint32_t s_in = apply(ex, S), s_out = apply(inc, S);
+        const unsigned over = __ballot_sync(0xffffffffu, lane >= first && s_out >= kPhaseLimit);
+        if (!over) { b = bits_of(E, __shfl_sync(0xffffffffu, s_out, 31)); break; }
+        const int f = __ffs(over) - 1;
+        x.stage[2 * lane] = padded[f * (kSub + 1) + 2 * lane];
+        x.stage[2 * lane + 1] = padded[f * (kSub + 1) + 2 * lane + 1];
+        __syncwarp();
+        b = serial_chain(bits_of(E, __shfl_sync(0xffffffffu, s_in, f)), x.stage, kSub);
+        __syncwarp();
+        first = f + 1;
+    }
     __syncwarp();
     return b;
 }
@@ -769,7 +826,8 @@ template <bool DBG>
 __device__ __noinline__ const Pack* fetch_pack(const SpineCtx& x, int c) {
     const uint4* g4 = reinterpret_cast<const uint4*>(x.packs + x.sums[c].pad[0]);
     uint4* s4 = reinterpret_cast<uint4*>(x.spare);
-    for (int i = x.lane; i < (int)(sizeof(Pack) / 16); i += 32) s4[i] = g4[i];
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(Pack) / 16) / 32; ++i) s4[x.lane + 32 * i] = g4[x.lane + 32 * i];
     __syncwarp();
     return x.spare;
 }
@@ -866,7 +924,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     Pack* slots = reinterpret_cast<Pack*>(sm + off);  // [max_slots] prefetched + 1 spare for late fetches
     Pack* spare = slots + max_slots;
     uint32_t* stage = reinterpret_cast<uint32_t*>(sm + off + (size_t)(max_slots + 1) * sizeof(Pack));
-    uint4* evs = reinterpret_cast<uint4*>(stage + kChunk);                              // [kMaxEvents] precompiled steps
+    uint4* evs = reinterpret_cast<uint4*>(stage + kStageWords);                              // [kMaxEvents] precompiled steps
     uint32_t* evb = reinterpret_cast<uint32_t*>(evs + kMaxEvents);                      // [kMaxEvents] state at each step
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -1285,8 +1343,8 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     const size_t smem = spine_smem_bytes(nchunks);
     static bool attr_set = false;  // per process; the attribute is sticky per device function
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(spine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spine_smem_bytes(8192));
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spine_smem_bytes(8192));
+        cudaError_t e = cudaFuncSetAttribute(spine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel smem attribute");
         attr_set = true;
     }
