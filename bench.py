@@ -165,7 +165,9 @@ def run_reference(args, wl):
         "impl": "reference", "metric": "importance-scored+sampled candidates/sec", "value": base["value"], "unit": "candidates/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": 1e3 * wl["n"] / base["value"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
-        "config": {"workload": args.workload, "note": wl["note"], "candidates": wl["n"], "classes": wl["c"], "draws": wl["b"]},
+        "config": {"workload": args.workload, "note": wl["note"], "candidates_per_gpu": wl["n"], "classes": wl["c"],
+                   "draws": wl["b"], "payload_row_bytes": 4 * (wl["payload"][0] * wl["payload"][1] * wl["payload"][2]) if wl["payload"] else 0,
+                   "cdf": "torch.multinomial on CPU (serial fp32)", "launch": "torch CPU ops, all host threads"},
         "cpu_baseline": base,
         "e2e": {"value": base["value"], "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -379,11 +381,12 @@ def main():
         t = torch.tensor([e2e_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t)
-    h2d = n * (c * s + 8) + b * 8
-    d2h = b * (8 + 4 + 4) + 32
+    h2d = world * (n * (c * s + 8) + b * 8)   # whole job: every rank copies its shard's logits, labels and the uniforms in
+    d2h = world * (b * (8 + 4 + 4) + 32)      # ... and idx / N*p / seed / stats out
 
     if rank == 0:
-        launches_per_step = 6 + (0 if world == 1 else 0)
+        # our kernels per step and rank: score, summarize (statistics folded in), spine, draw; sharded: + chunk sums, gather_owned
+        launches_per_step = 4 if world == 1 else 6 * world
         line = {
             "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
