@@ -12,6 +12,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 
 from . import _lib, ops
+from .pool import ResidentPool
 from .sampler import EMAverage, reweighted_mean
 
 
@@ -32,7 +33,7 @@ class Trainer(object):
         self.next_batch_iter = None
         self.should_compute_importance = True
         self.last = None       # full result of the last update_samples (scores, seed, idx, ...)
-        self._pool = None      # preallocated pool buffers: no torch.cat (pytorch_collab.py:108,116-117)
+        self._pool = None      # ResidentPool: preallocated, written in place (no torch.cat, pytorch_collab.py:108,116-117)
         self._grad_bucket = None
 
     # ---- pool feeder (pytorch_collab.py:74-82, with next(it) for Python 3)
@@ -52,42 +53,32 @@ class Trainer(object):
                 dist.all_reduce(p.data, op=dist.ReduceOp.SUM)
                 p.data /= float(self.world_size)
 
-    def _buffers(self, n, data, out):
-        if self._pool is None or self._pool["logits"].shape != (n, out.shape[1]) or self._pool["data"].shape[1:] != data.shape[1:]:
-            self._pool = dict(logits=torch.empty(n, out.shape[1], dtype=out.dtype, device=self.device),
-                              data=torch.empty((n,) + tuple(data.shape[1:]), dtype=data.dtype, device=self.device),
-                              labels=torch.empty(n, dtype=torch.int64, device=self.device),
-                              index=torch.empty(n, dtype=torch.int64, device=self.device))
-        return self._pool
-
     def update_samples(self, ema_loss: EMAverage, alpha=0.5):
         """pytorch_collab.py:89-117: same 5-tuple ``(N*p_i, data, label, index, pool_mean_loss)``.
 
         The ten presample batches are scored by the model (stock PyTorch, no_grad) straight into a
-        preallocated pool; one fused call then does what :102-117 do, including the ten EMA updates
-        on the growing pools and the generator advancing by ten draws (the last draw is returned).
+        device-resident pool (``ResidentPool``: no ``torch.cat``); one fused call then does what
+        :102-117 do, including the ten EMA updates on the growing pools and the generator advancing
+        by ten draws (the last draw is returned).
         """
         B = self.train_loader.batch_size
-        bounds, pos, pool = [], 0, None
+        pool = self._pool
+        if pool is not None:
+            pool.reset()
         for _ in range(self.POOL_BATCHES if self.should_compute_importance else 0):
             with torch.no_grad():
                 idx, data, label = self.get_next()
                 data = data.to(self.device, non_blocking=True)
-                label = label.to(self.device, non_blocking=True)
                 output = self.net(data)
                 if pool is None:
-                    pool = self._buffers(self.POOL_BATCHES * data.shape[0], data, output)
-                m = data.shape[0]
-                pool["logits"][pos:pos + m] = output
-                pool["data"][pos:pos + m] = data
-                pool["labels"][pos:pos + m] = label
-                pool["index"][pos:pos + m] = torch.as_tensor(idx).to(self.device, non_blocking=True)
-                pos += m
-                bounds.append(pos)
+                    pool = self._pool = ResidentPool(self.POOL_BATCHES * data.shape[0], output.shape[1], tuple(data.shape[1:]),
+                                                     device=self.device, logits_dtype=output.dtype, payload_dtype=data.dtype)
+                pool.append(idx, data, label, output)
+        logits, labels, datas, index = pool.tensors()
+        bounds = pool.growing_bounds()
         u = torch.rand(len(bounds) * B, dtype=torch.float64)[(len(bounds) - 1) * B:].to(self.device, non_blocking=True)
-        r = ops.update_samples(pool["logits"][:pos], pool["labels"][:pos], u, ema_loss.state, ema_loss.first_update,
-                               ema_alpha=ema_loss.alpha, smooth_alpha=alpha, data=pool["data"][:pos],
-                               index=pool["index"][:pos], bounds=bounds)
+        r = ops.update_samples(logits, labels, u, ema_loss.state, ema_loss.first_update, ema_alpha=ema_loss.alpha,
+                               smooth_alpha=alpha, data=datas, index=index, bounds=bounds)
         ema_loss.first_update = False
         self.last = r
         return r.nprob, r.data, r.labels, r.index, r.stats[_lib.STAT_MEAN]

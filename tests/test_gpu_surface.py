@@ -183,3 +183,27 @@ def test_gather_owned_zero_fills_foreign_rows():
     assert torch.equal(d[1], data[50]) and torch.equal(d[3], data[0]) and torch.equal(d[4], data[99])
     assert float(d[0].abs().sum() + d[2].abs().sum() + d[5].abs().sum() + d[6].abs().sum()) == 0.0
     assert l.tolist() == [0, int(labels[50]), 0, int(labels[0]), int(labels[99]), 0, 0] and ix is None
+
+
+def test_graphed_update_equals_eager_calls():
+    from mercury_b200 import ops
+
+    gen = torch.Generator().manual_seed(12)
+    n, c, b = 40000, 10, 64
+    logits = (torch.randn(n, c, generator=gen) * 2).to(DEV)
+    labels = torch.randint(0, c, (n,), generator=gen).to(DEV)
+    data = torch.rand(n, 16, generator=gen).to(DEV)
+    u = torch.rand(b, dtype=torch.float64, generator=gen).to(DEV)
+    ema_g, ema_e = torch.zeros(1, device=DEV), torch.zeros(1, device=DEV)
+    g = ops.GraphedUpdate(logits, labels, u, ema_g, data=data)   # one eager step (first EMA update), then capture
+    ops.update_samples(logits, labels, u, ema_e, True, data=data)  # the same first step on the eager side
+    assert torch.equal(ema_g, ema_e)
+    for step in range(3):
+        logits.add_(0.1 * (step + 1))                              # refill the static inputs in place
+        u.copy_(torch.rand(b, dtype=torch.float64, generator=gen))
+        r = g.replay()
+        torch.cuda.synchronize()
+        e = ops.update_samples(logits, labels, u, ema_e, False, data=data)
+        assert torch.equal(r.idx, e.idx) and torch.equal(r.nprob, e.nprob) and torch.equal(r.seed, e.seed)
+        assert torch.equal(r.data, e.data) and torch.equal(r.labels, e.labels) and torch.equal(ema_g, ema_e)
+    ops.check_status(g.status)
