@@ -65,14 +65,19 @@ constexpr uint32_t kNoPack = 0x10000000u; // chunk expected to change phase but 
 constexpr int kSub = 64, kSubsPerChunk = kChunk / kSub;
 constexpr int kSubSlots = 128;            // flagged chunks that get a pack (compact layout)
 constexpr int kRawPerPack = 6;
-constexpr double kGuessMargin = 1.0 / 1024.0;     // chunks: generous, a flagged chunk only costs a pack
-constexpr double kSubGuessMargin = 1.0 / 8192.0;   // sub-chunks: the fp32 chain drifts ~1e-4 from the exact sum at 1M candidates
+// Margins around the guesses.  The fp32 chain drifts away from the exact running total (the
+// guesses come from the exact one): ~1e-5 relative at a million candidates, up to several 1e-3 at
+// 4-8 million, where an addend is only a few ulps of the sum.  A flagged chunk costs a pack
+// (~1.5k cycles of the walk), a flagged sub-chunk a serial pass (~450 cycles): generous margins
+// only where they are needed.
+__host__ __device__ inline double chunk_margin(int nchunks) { return nchunks <= 1024 ? 1.0 / 4096.0 : 1.0 / 1024.0; }
+__host__ __device__ inline double sub_margin(int nchunks) { return nchunks <= 1024 ? 1.0 / 16384.0 : 1.0 / 8192.0; }
 static_assert(kSubsPerChunk == 32, "one sub-chunk per lane of the walking warp");
 
 // Guess the phase of the running sum over a span from its approximate value at both ends, with
 // a margin for the drift of the fp32 chain: returns the low guess, and whether the span may
 // change phase.
-__device__ __forceinline__ bool guess_span(double a_lo, double a_hi, double bias, uint32_t* e_lo, double margin = kGuessMargin) {
+__device__ __forceinline__ bool guess_span(double a_lo, double a_hi, double bias, uint32_t* e_lo, double margin) {
     const uint32_t lo = phase_of(f2b((float)(a_lo * bias * (1.0 - margin))));
     const uint32_t hi = phase_of(f2b((float)(a_hi * bias * (1.0 + margin))));
     *e_lo = lo;
@@ -105,7 +110,7 @@ __device__ __forceinline__ void scan_chunks(F value_of, int nchunks, double bias
         for (int i = 0; i < warp; ++i) pre += red[i];
         const double a_lo = pre + inc - v, a_hi = pre + inc;
         uint32_t e;
-        const bool flagged = c < nchunks && guess_span(a_lo, a_hi, bias, &e);
+        const bool flagged = c < nchunks && guess_span(a_lo, a_hi, bias, &e, chunk_margin(nchunks));
         const unsigned bal = __ballot_sync(0xffffffffu, flagged);
         if (lane == 0) redi[warp] = __popc(bal);
         __syncthreads();
@@ -404,11 +409,17 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
     if constexpr (FUSED) {
         const int first_part = (int)(start / fs.per), parts_per_chunk = kChunk / fs.per;
         double tot = 0.0, pre = 0.0, own = 0.0;
-        for (int i = threadIdx.x; i < fs.npart; i += kSumNT) {
-            const double v = fs.part[i];
-            tot += v;
-            if (i < first_part) pre += v;
-            else if (i < first_part + parts_per_chunk) own += v;
+        for (int i0 = threadIdx.x; i0 < fs.npart; i0 += 8 * kSumNT) {  // 8 loads in flight per thread
+            double v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const int i = i0 + k * kSumNT; v[k] = i < fs.npart ? fs.part[i] : 0.0; }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int i = i0 + k * kSumNT;
+                tot += v[k];
+                if (i < first_part) pre += v[k];
+                else if (i < first_part + parts_per_chunk) own += v[k];
+            }
         }
         tot = warp_sum(tot); pre = warp_sum(pre); own = warp_sum(own);
         if (lane == 0) { dred[0][warp] = tot; dred[1][warp] = pre; dred[2][warp] = own; }
@@ -440,7 +451,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
     // agree the chunk is expected to stay in one phase; otherwise it is flagged and (if a slot was
     // assigned to it) gets a pack of sub-chunk summaries for the spine.
     uint32_t e;
-    const bool flagged = guess_span(a_lo, a_hi, bias, &e);  // block-uniform
+    const bool flagged = guess_span(a_lo, a_hi, bias, &e, chunk_margin((int)gridDim.x));  // block-uniform
     if (FUSED) slot = flagged ? (int)blockIdx.x : -1;
     Pair a0 = identity_pair();
     int bad = 0;
@@ -503,7 +514,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
     const float s_lo = __shfl_sync(0xffffffffu, t_lo, lead), s_hi = __shfl_sync(0xffffffffu, t_hi, lead + 7);
     uint32_t es;
     // (a sub-chunk of zeros changes nothing, whatever the phase: never worth a serial pass)
-    const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, bias, &es, kSubGuessMargin) &&
+    const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, bias, &es, sub_margin((int)gridDim.x)) &&
                              ((nzmask >> lead) & 0xffu) != 0u;
     Pair m0 = identity_pair(), m1 = identity_pair();
 #pragma unroll

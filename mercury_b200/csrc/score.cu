@@ -11,6 +11,7 @@
 //                                              bulk-copy ring in 16 KB chunks, online softmax.
 // A scalar warp-per-row kernel covers everything unaligned or strided.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "internal.cuh"
@@ -426,12 +427,19 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
 
     if (row_stride == c && base16 && lab16 && row_bytes <= 256) {
         constexpr int STAGES = 3, CONSUMERS = 256;
-        // ~24 KB per stage: three CTAs (27 warps) share an SM and cover each other's stalls
-        int tile_rows = row_bytes <= 40 ? 512 : row_bytes <= 88 ? 256 : row_bytes <= 184 ? 128 : 64;
+        // one row per consumer thread and tile (~12 KB per stage at 10 classes): three CTAs (27 warps) share an
+        // SM and cover each other's stalls; measured best of {128..1024} rows x {1..8} CTAs/SM at 1M x 10
+        int tile_rows = row_bytes <= 40 ? 256 : row_bytes <= 88 ? 256 : row_bytes <= 184 ? 128 : 64;
+        int ctas_per_sm = 3;
+        if (const char* e = getenv("MERCURY_K1_TILE")) tile_rows = atoi(e);        // developer knobs
+        if (const char* e = getenv("MERCURY_K1_CTAS")) ctas_per_sm = atoi(e);
+        const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
+        // every CTA gets the same number of tiles (the last ones one fewer at most): size the grid for that
+        const int64_t slots = (int64_t)ctas_per_sm * kSMs;
+        const int64_t per_cta = (ntiles + slots - 1) / slots;
+        const int grid = (int)min_i64(ntiles, (ntiles + per_cta - 1) / per_cta);
         const size_t logit_slot = ((size_t)tile_rows * row_bytes + 127) & ~(size_t)127;
         const size_t smem = kSmallHeader + STAGES * (logit_slot + (size_t)tile_rows * 8);
-        const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
-        const int grid = (int)min_i64(ntiles, 3 * kSMs);
         auto go = [&](auto kern) -> int {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (e != cudaSuccess) return cuda_fail(e, "score_small smem attribute");
