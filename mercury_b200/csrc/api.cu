@@ -2,6 +2,7 @@
 // K1 -> stats -> exact CDF boundaries -> fused draw/gather (reference pytorch_collab.py:102-117).
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "internal.cuh"
@@ -15,6 +16,11 @@ void set_last_error(const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("MERCURY_PDL"); return !(e && e[0] == '0'); }();
+    return on;
 }
 
 int cuda_fail(cudaError_t e, const char* what) {
@@ -62,7 +68,7 @@ extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, si
     if (!scores) {
         double* part_buf = update_ws_part_sums(ws, a->n);
         rc = score_dispatch(a->logits, a->dtype, a->labels, a->n, a->c, a->row_stride, a->ignore_index, a->scores, a->status, st,
-                            part_buf, &per);
+                            part_buf, &per, true);
         if (rc) return rc;
         scores = a->scores;
         part = part_buf;

@@ -400,6 +400,8 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
     __shared__ float wsum[kSumNT / 32];
     __shared__ int wnz[kSumNT / 32];
     __shared__ double dred[3][kSumNT / 32];
+    pdl_wait();
+    pdl_launch_dependents();
     const int64_t start = (int64_t)blockIdx.x * kChunk;
     const int len = (int)min((int64_t)kChunk, n - start);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -922,6 +924,8 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     __shared__ long long dbg_t[4];
     __shared__ long long dbg_t2[4];  // cycles in serial passes, in packs (total), fetching packs
     __shared__ int dbg_n[8];  // flagged, serial chunks, serial subs (raw at hand), serial subs (fetched), events, late packs, general walks
+    pdl_wait();
+    pdl_launch_dependents();
     if (DBG && debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; for (int i = 0; i < 4; ++i) dbg_t2[i] = 0; }
     // shared-memory layout
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);               // [nchunks+1] prefix of increments
@@ -1237,6 +1241,8 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     __shared__ float cdf_s[kChunk];
     __shared__ int wcnt[kDrawNT / 32];
     __shared__ int64_t chosen;
+    pdl_wait();
+    pdl_launch_dependents();
     const int64_t j = blockIdx.x;
     const double uj = a.u[j];
     const float total = *a.total_ptr;
@@ -1344,8 +1350,9 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
                          const FusedStats* fused = nullptr, float* ema_out = nullptr) {
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
     if (fused) {
-        summarize_kernel<true><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status,
-                                                           check, *fused);
+        cudaError_t e = launch_chain(true, summarize_kernel<true>, dim3(nchunks), dim3(kSumNT), 0, st, src, n, (const double*)w.approx,
+                                     (const int*)w.slotid, g_guess_bias, w.summaries, w.subs, status, check, *fused);
+        if (e != cudaSuccess) return cuda_fail(e, "summarize_kernel launch");
     } else {
         summarize_kernel<false><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status,
                                                             check, FusedStats{});
@@ -1361,7 +1368,11 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     }
     static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
     if (debug) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, debug);
-    else spine_kernel<false><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, 0);
+    else {
+        cudaError_t e = launch_chain(true, spine_kernel<false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
+                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, 0);
+        if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
+    }
     MB_CHECK_LAUNCH("spine_kernel");
     return MERCURY_OK;
 }
@@ -1424,8 +1435,8 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
         d.out_labels = a.out_labels; d.out_index = a.out_index;
-        draw_kernel<<<(unsigned)a.b, kDrawNT, 0, st>>>(d);
-        MB_CHECK_LAUNCH("draw_kernel");
+        cudaError_t e = launch_chain(true, draw_kernel, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
+        if (e != cudaSuccess) return cuda_fail(e, "draw_kernel launch");
     }
     return MERCURY_OK;
 }

@@ -13,7 +13,7 @@ constexpr int kCdfChunk = 2048;  // candidates per CDF chunk (one CTA's worth)
 // consecutive scores (fp64, fixed order); *per_out == 0 means it did not.
 int score_dispatch(const void* logits, int dtype, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride,
                    int64_t ignore_index, float* scores, int32_t* status, cudaStream_t st, double* part_sums = nullptr,
-                   int* per_out = nullptr);
+                   int* per_out = nullptr, bool chained = false);  // chained: first kernel of the whole-step chain (PDL)
 
 size_t cdf_ws_bytes(int64_t n);
 int check_ws(void* ws, size_t have, size_t need, const char* who);

@@ -191,6 +191,8 @@ score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ lab
     unsigned char* stage0 = smem + kSmallHeader;
     static_assert(sizeof(Ring<STAGES>) <= 128 && 128 + 2 * (CONSUMERS / 32) * 8 <= kSmallHeader, "header layout");
     ring_init(ring, CONSUMERS / 32);
+    pdl_wait();                // (the previous step's draw kernel may still be reading the scores we overwrite)
+    pdl_launch_dependents();
 
     const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -418,7 +420,7 @@ score_wide_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labe
 
 template <typename T>
 int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride, int64_t ignore_index,
-                 float* scores, int32_t* status, cudaStream_t st, double* part_sums, int* per_out) {
+                 float* scores, int32_t* status, cudaStream_t st, double* part_sums, int* per_out, bool chained) {
     if (per_out) *per_out = 0;
     const int64_t row_bytes = c * (int64_t)sizeof(T);
     const bool base16 = (reinterpret_cast<uintptr_t>(logits) & 15) == 0;
@@ -443,9 +445,9 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
         auto go = [&](auto kern) -> int {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (e != cudaSuccess) return cuda_fail(e, "score_small smem attribute");
-            kern<<<grid, CONSUMERS + kProducerThreads, smem, st>>>(logits, labels, n, (int)c, tile_rows, ignore_index, scores, status,
-                                                                   part_sums);
-            MB_CHECK_LAUNCH("score_small_kernel");
+            e = launch_chain(chained, kern, dim3(grid), dim3(CONSUMERS + kProducerThreads), smem, st, logits, labels, n, (int)c, tile_rows,
+                             ignore_index, scores, status, part_sums);
+            if (e != cudaSuccess) return cuda_fail(e, "score_small_kernel launch");
             if (per_out && part_sums) *per_out = tile_rows;
             return MERCURY_OK;
         };
@@ -487,14 +489,15 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
 }  // namespace
 
 int score_dispatch(const void* logits, int dtype, const int64_t* labels, int64_t n, int64_t c, int64_t row_stride,
-                   int64_t ignore_index, float* scores, int32_t* status, cudaStream_t st, double* part_sums, int* per_out) {
+                   int64_t ignore_index, float* scores, int32_t* status, cudaStream_t st, double* part_sums, int* per_out,
+                   bool chained) {
     if (per_out) *per_out = 0;
     if (n == 0) return MERCURY_OK;
     if (dtype == MERCURY_F32)
         return launch_score(static_cast<const float*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st,
-                            part_sums, per_out);
+                            part_sums, per_out, chained);
     return launch_score(static_cast<const __nv_bfloat16*>(logits), labels, n, c, row_stride, ignore_index, scores, status, st,
-                        part_sums, per_out);
+                        part_sums, per_out, chained);
 }
 
 }  // namespace mercury
