@@ -35,6 +35,8 @@ class Trainer(object):
         self.last = None       # full result of the last update_samples (scores, seed, idx, ...)
         self._pool = None      # ResidentPool: preallocated, written in place (no torch.cat, pytorch_collab.py:108,116-117)
         self._grad_bucket = None
+        self.overlap_sampling = True   # run update_samples on a side stream beside average_gradients
+        self._side = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" and torch.cuda.is_available() else None
 
     # ---- pool feeder (pytorch_collab.py:74-82, with next(it) for Python 3)
     def get_next(self):
@@ -96,9 +98,21 @@ class Trainer(object):
             self.optimizer.zero_grad()
             loss.backward()                                                  # :148
             self.should_compute_importance = True
-            probs, i_data, i_label, _, _ = self.update_samples(presam_ema_loss)   # :159 next batch, pre-step weights
+            if self.overlap_sampling and self.device.type == "cuda":
+                # the reference's intent (:154-156, commented out there): score + sample the next batch
+                # while the gradients are averaged -- sampling on a side stream, the all-reduce on the main one
+                main = torch.cuda.current_stream()
+                self._side.wait_stream(main)
+                with torch.cuda.stream(self._side):
+                    probs, i_data, i_label, _, _ = self.update_samples(presam_ema_loss)   # :159, pre-step weights
+                self.average_gradients()                                     # :160
+                main.wait_stream(self._side)
+                for t in (probs, i_data, i_label, self.last.seed):
+                    t.record_stream(main)
+            else:
+                probs, i_data, i_label, _, _ = self.update_samples(presam_ema_loss)   # :159 next batch, pre-step weights
+                self.average_gradients()                                     # :160
             seed = self.last.seed
-            self.average_gradients()                                         # :160
             self.optimizer.step()                                            # :164
             losses_seen.append(loss.detach())
             self.step += 1

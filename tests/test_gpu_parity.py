@@ -273,7 +273,8 @@ def test_gather_reweight(ops):
 
 # ------------------------------------------------------------------------------ the whole step
 @pytest.mark.parametrize("n,c,dtype,b", [(320, 10, torch.float32, 32), (50000, 10, torch.float32, 128),
-                                         (1000000, 10, torch.float32, 128), (20000, 1000, torch.bfloat16, 256)])
+                                         (1000000, 10, torch.float32, 128), (20000, 1000, torch.bfloat16, 256),
+                                         (3000001, 2, torch.float32, 64)])  # multi-million pool: the chain drifts, guesses get contradicted
 def test_update_samples_end_to_end(ops, n, c, dtype, b):
     x, y = _logits(n, c, dtype)
     g = torch.Generator().manual_seed(3)
