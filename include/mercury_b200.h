@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define MERCURY_ABI_VERSION 1
+#define MERCURY_ABI_VERSION 2
 
 enum { MERCURY_OK = 0, MERCURY_ERR_ARG = -1, MERCURY_ERR_CUDA = -2, MERCURY_ERR_WORKSPACE = -3 };
 
@@ -57,6 +57,7 @@ enum {
     MERCURY_STAT_EMA = 1,      /* EMAverage.value afterwards util.py:207-213      */
     MERCURY_STAT_SHIFT = 2,    /* alpha * ema                pytorch_collab.py:111 */
     MERCURY_STAT_TOTAL = 3,    /* sum(scores + shift)        pytorch_collab.py:112 */
+    MERCURY_STAT_CHAIN_TOTAL = 4, /* last value of the serial fp32 running sum over p (whole-step call only) */
     MERCURY_STAT_COUNT = 8
 };
 
@@ -148,6 +149,20 @@ int mercury_gather_owned(const int64_t* idx, int64_t b, int64_t shard_lo, int64_
  * unchanged; the tests use it to force the mis-guess paths.  Process-global; not for production. */
 void mercury_test_set_guess_bias(double bias);
 
+/* ---- sharded pools, totals-only exchange (north_star: "per-shard score totals and CDFs are exchanged
+ * with NCCL allgather ... the global draw is resolved locally") ------------------------------------
+ * No counterpart in the reference (its workers never exchange importance, pytorch_collab.py:282-287).
+ * Per rank: mercury_score -> mercury_sum_scores -> all-gather of the G sums -> mercury_update_samples
+ * with b = 0 draws on the local shard (global_sums/n_global set: whole-pool mean/EMA/shift/total; the
+ * shard's own exact chain, whose last value lands in stats[MERCURY_STAT_CHAIN_TOTAL]) -> all-gather of
+ * the G chain totals -> mercury_shard_select maps every uniform to (shard, uniform inside the shard)
+ * -> mercury_update_samples again for the draws (uniforms < 0 = "not mine": all-zero outputs, so a SUM
+ * all-reduce assembles the batch).  The two-level draw is exact for its own definition (oracle:
+ * oracle.sharded_draw_two_level); it is not index-identical to torch.multinomial on the flat pool. */
+int mercury_sum_scores(const float* scores, int64_t n, double* out_sum, void* ws, size_t ws_bytes, void* stream);
+int mercury_shard_select(const float* shard_totals, int nshards, int rank, const double* uniforms, int64_t b,
+                         double* local_uniforms, void* stream);
+
 /* ---- the whole step ---------------------------------------------------------------------------
  * replaces Trainer.update_samples' arithmetic (pytorch_collab.py:102-117) on an assembled pool:
  * score -> stats -> exact CDF -> b draws from caller-supplied uniforms -> gather + weights + seed.
@@ -167,6 +182,12 @@ typedef struct mercury_update_args {
     float* nprob; float* seed;        /* out fp32 [b]                                            */
     void* out_data; int64_t* out_labels; int64_t* out_index;    /* out, gathered rows             */
     int32_t* status;                  /* in/out device status word                               */
+    /* sharded pools (optional, see mercury_shard_select): this call covers ONE shard of n candidates;   */
+    const double* global_sums; int n_global_sums; /* per-shard sums of scores of the whole pool [n_global_sums] */
+    int64_t n_global;                 /* candidates in the whole pool (statistics and N*p use it)    */
+    int64_t index_base;               /* added to idx[]: global position of the shard's first candidate */
+    int draw_only;                    /* != 0: only draw + gather, from the boundaries / statistics that the  */
+                                      /* previous call with the same workspace, scores and stats left behind  */
 } mercury_update_args;
 
 size_t mercury_update_samples_workspace_bytes(int64_t n, int64_t b);

@@ -10,13 +10,13 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(HERE, "libmercury_b200.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK, ERR_ARG, ERR_CUDA, ERR_WORKSPACE = 0, -1, -2, -3
 F32, BF16 = 0, 1
 CDF_EXACT_SERIAL_F32, CDF_F64 = 0, 1
 ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES = 1, 2, 4, 8, 16
-STAT_MEAN, STAT_EMA, STAT_SHIFT, STAT_TOTAL, STAT_COUNT = 0, 1, 2, 3, 8
+STAT_MEAN, STAT_EMA, STAT_SHIFT, STAT_TOTAL, STAT_CHAIN_TOTAL, STAT_COUNT = 0, 1, 2, 3, 4, 8
 STATIC_MAX_N = 1 << 22
 
 c_i64, c_f64, c_int, c_vp, c_sz = ctypes.c_int64, ctypes.c_double, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
@@ -36,6 +36,7 @@ class UpdateArgs(ctypes.Structure):
         ("scores", c_vp), ("stats", c_vp), ("idx", c_vp), ("nprob", c_vp), ("seed", c_vp),
         ("out_data", c_vp), ("out_labels", c_vp), ("out_index", c_vp),
         ("status", c_vp),
+        ("global_sums", c_vp), ("n_global_sums", c_int), ("n_global", c_i64), ("index_base", c_i64), ("draw_only", c_int),
     ]
 
 
@@ -56,6 +57,8 @@ SIGNATURES = {
     "mercury_gather_reweight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mercury_gather_owned": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mercury_test_set_guess_bias": (None, [c_f64]),
+    "mercury_sum_scores": (c_int, [c_vp, c_i64, c_vp, c_vp, c_sz, c_vp]),
+    "mercury_shard_select": (c_int, [c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp]),
     "mercury_update_samples_workspace_bytes": (c_sz, [c_i64, c_i64]),
     "mercury_update_samples": (c_int, [ctypes.POINTER(UpdateArgs), c_vp, c_sz, c_vp]),
 }

@@ -48,6 +48,10 @@ extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, si
     MB_CHECK_ARG(a->stats && a->ema_state && a->status, "mercury_update_samples: stats / ema_state / status are required");
     MB_CHECK_ARG(a->b == 0 || (a->uniforms && a->idx && a->nprob && a->seed),
                  "mercury_update_samples: uniforms / idx / nprob / seed are required when b > 0");
+    MB_CHECK_ARG(!a->global_sums || (a->n_global_sums >= 1 && a->n_global >= a->n && a->n_bounds == 0),
+                 "mercury_update_samples: sharded call needs n_global_sums >= 1, n_global >= n and no pool-size list");
+    MB_CHECK_ARG(!a->global_sums || a->n <= ((int64_t)8192 * 2048), "mercury_update_samples: shard too large");
+    MB_CHECK_ARG(!a->draw_only || a->scores_in, "mercury_update_samples: draw_only needs scores_in");
     const float* scores = a->scores_in;
     if (!scores) {
         MB_CHECK_ARG(a->logits && a->labels && a->scores, "mercury_update_samples: logits / labels / scores are required");

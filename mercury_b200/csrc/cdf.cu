@@ -389,6 +389,9 @@ struct FusedStats {
     int npart, per;
     const float* ema_in; int ema_first; double ema_alpha, smooth_alpha;
     float* stats;
+    // sharded pools: this launch covers one shard, the statistics are those of the WHOLE pool --
+    // gsums[0..ngsums) are the per-shard sums of scores (all-gathered), n_global the pool size
+    const double* gsums; int ngsums; int64_t n_global;
 };
 
 template <bool FUSED>
@@ -430,11 +433,17 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
 #pragma unroll
         for (int i = 0; i < kSumNT / 32; ++i) { tot += dred[0][i]; pre += dred[1][i]; own += dred[2][i]; }
         // pytorch_collab.py:109-112 -- mean, EMA (util.py:207-213), shift = alpha*ema, total = sum(s + shift)
-        const float mean = (float)(tot / (double)n);
+        double n_stat = (double)n;
+        if (fs.gsums) {  // whole-pool statistics from the shard sums (same order on every rank)
+            tot = 0.0;
+            for (int i = 0; i < fs.ngsums; ++i) tot += fs.gsums[i];
+            n_stat = (double)fs.n_global;
+        }
+        const float mean = (float)(tot / n_stat);
         const float a = (float)fs.ema_alpha, one_minus_a = (float)(1.0 - fs.ema_alpha);
         const float ema = fs.ema_first ? mean : __fadd_rn(__fmul_rn(a, *fs.ema_in), __fmul_rn(one_minus_a, mean));
         const float shift = __fmul_rn((float)fs.smooth_alpha, ema);
-        const float total = (float)(tot + (double)n * (double)shift);
+        const float total = (float)(tot + n_stat * (double)shift);
         if (blockIdx.x == 0 && threadIdx.x == 0) {
             fs.stats[MERCURY_STAT_MEAN] = mean; fs.stats[MERCURY_STAT_EMA] = ema;
             fs.stats[MERCURY_STAT_SHIFT] = shift; fs.stats[MERCURY_STAT_TOTAL] = total;
@@ -912,7 +921,7 @@ __device__ __noinline__ uint32_t debug_check_pack(const SpineCtx& x, const Pack*
 template <bool DBG>
 __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
                                                          const Pack* __restrict__ packs, uint32_t* __restrict__ start_bits,
-                                                         float* __restrict__ total_out, int32_t* status, float* ema_out, int debug_level) {
+                                                         float* __restrict__ total_out, int32_t* status, float* ema_out, float* chain_total_out, int debug_level) {
     const int debug = DBG ? debug_level : 0;
     extern __shared__ __align__(128) unsigned char sm[];
     __shared__ int nslots_s, nev_s;
@@ -1107,6 +1116,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             start_bits[nchunks] = b;
             const float total = b2f(b);
             *total_out = total;
+            if (chain_total_out) *chain_total_out = total;
             if (!(total > 0.f)) atomicOr(status, MERCURY_ST_ZERO_SUM);
             else if (isinf(total)) atomicOr(status, MERCURY_ST_NONFINITE);
         }
@@ -1229,6 +1239,8 @@ __global__ void __launch_bounds__(256) search_kernel(const float* __restrict__ c
 constexpr int kDrawNT = 256, kDrawIPT = kChunk / kDrawNT;
 
 struct DrawArgs {
+    int64_t n_weight;    // the N of N*p_i: the whole pool's size (== n unless the pool is sharded)
+    int64_t idx_base;    // added to the positions written to idx[] (global position of this shard's first candidate)
     WeightSrc src; int64_t n; int nchunks;
     const uint32_t* start_bits; const float* total_ptr;
     const double* u; int64_t b;
@@ -1247,6 +1259,18 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     const double uj = a.u[j];
     const float total = *a.total_ptr;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (uj < 0.0) {  // sharded pools: this draw belongs to another shard -> all-zero outputs (summed across ranks later)
+        if (threadIdx.x == 0) {
+            a.idx[j] = 0; a.nprob[j] = 0.f; a.seed[j] = 0.f;
+            if (a.labels && a.out_labels) a.out_labels[j] = 0;
+            if (a.index && a.out_index) a.out_index[j] = 0;
+        }
+        if (a.data && a.out_data) {
+            unsigned char* drow = a.out_data + j * a.row_bytes;
+            for (int64_t i = threadIdx.x; i < a.row_bytes; i += kDrawNT) drow[i] = 0;
+        }
+        return;
+    }
     // (a) chunks whose last cdf value is < u
     int cnt = 0;
     for (int c = threadIdx.x; c < a.nchunks; c += kDrawNT) {
@@ -1281,12 +1305,12 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
         if (t > len - 1) t = len - 1;
         const int64_t pick = start + t;
         chosen = pick;
-        a.idx[j] = pick;
+        a.idx[j] = a.idx_base + pick;
         float shift, tot2;
         a.src.prepare(shift, tot2);
         const float p = a.src.get(pick, shift, tot2);
         // pytorch_collab.py:116: losses_pros[idx] * N ; :137,:145: grad = (1/B) / probs
-        const float np_ = __fmul_rn(p, (float)a.n);
+        const float np_ = __fmul_rn(p, (float)a.n_weight);
         a.nprob[j] = np_;
         a.seed[j] = __fdiv_rn(__fdiv_rn(1.f, (float)a.b), np_);
         if (a.labels && a.out_labels) a.out_labels[j] = a.labels[pick];
@@ -1367,10 +1391,11 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
         attr_set = true;
     }
     static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
-    if (debug) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, debug);
+    float* chain_total_out = fused ? fused->stats + MERCURY_STAT_CHAIN_TOTAL : nullptr;
+    if (debug) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
     else {
         cudaError_t e = launch_chain(true, spine_kernel<false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
-                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, 0);
+                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, 0);
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
     }
     MB_CHECK_LAUNCH("spine_kernel");
@@ -1408,8 +1433,10 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
     const CdfWs w = carve(ws, a.n, true);
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
     WeightSrc src{scores, a.stats};
-    int rc;
-    if (a.n_bounds == 0 && nchunks <= kFusedMaxChunks) {
+    int rc = MERCURY_OK;
+    if (a.draw_only) {
+        // boundaries, total and statistics are those a previous call on this workspace left behind
+    } else if (a.n_bounds == 0 && nchunks <= kFusedMaxChunks) {
         if (per == 0) {
             chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, a.n, w.sums, nullptr, 0);
             MB_CHECK_LAUNCH("chunk_sums_kernel");
@@ -1420,6 +1447,7 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
         fs.part = part; fs.per = per; fs.npart = (int)((a.n + per - 1) / per);
         fs.ema_in = a.ema_state; fs.ema_first = a.ema_first; fs.ema_alpha = a.ema_alpha; fs.smooth_alpha = a.smooth_alpha;
         fs.stats = a.stats;
+        fs.gsums = a.global_sums; fs.ngsums = a.n_global_sums; fs.n_global = a.global_sums ? a.n_global : a.n;
         rc = run_exact_boundaries(src, a.n, w, a.status, 1, st, &fs, a.ema_state);
     } else {
         rc = pool_stats_launch(scores, a.n, a.h_bounds, a.n_bounds, a.ema_state, a.ema_first, a.ema_alpha, a.smooth_alpha, a.stats,
@@ -1430,6 +1458,7 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
     if (rc) return rc;
     if (a.b > 0) {
         DrawArgs d;
+        d.n_weight = a.global_sums ? a.n_global : a.n; d.idx_base = a.global_sums ? a.index_base : 0;
         d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
         d.u = a.uniforms; d.b = a.b;
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
@@ -1524,6 +1553,74 @@ extern "C" int mercury_sample_with_replacement(const float* cdf, int64_t n, cons
     if (b == 0) return MERCURY_OK;
     search_kernel<<<(unsigned)((b + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(cdf, n, uniforms, b, idx);
     MB_CHECK_LAUNCH("search_kernel");
+    return MERCURY_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sharded pools, "totals only" exchange (mode B).
+namespace mercury {
+namespace {
+// deterministic sum of the chunk sums (single CTA, fixed order)
+__global__ void __launch_bounds__(1024) reduce_sums_kernel(const double* __restrict__ sums, int nchunks, double* __restrict__ out) {
+    __shared__ double red[32];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < nchunks; i += 1024) acc += sums[i];
+    const double t = block_sum<1024>(acc, red);
+    if (threadIdx.x == 0) *out = t;
+}
+
+constexpr int kMaxShards = 64;
+// first level of the two-level draw: which shard a uniform falls in (serial fp32 CDF over the shard
+// totals, searched as ATen does), and where inside that shard's own CDF
+__global__ void __launch_bounds__(256) shard_select_kernel(const float* __restrict__ shard_totals, int nshards, int rank,
+                                                           const double* __restrict__ u, int64_t b, double* __restrict__ local_u) {
+    __shared__ float cdf[kMaxShards];
+    if (threadIdx.x == 0) {
+        float s = 0.f;
+        for (int g = 0; g < nshards; ++g) { s = __fadd_rn(s, shard_totals[g]); cdf[g] = s; }
+        for (int g = 0; g < nshards; ++g) cdf[g] = __fdiv_rn(cdf[g], s);
+    }
+    __syncthreads();
+    for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < b; j += (int64_t)gridDim.x * 256) {
+        const double uj = u[j];
+        int g = 0;
+        while (g < nshards - 1 && (double)cdf[g] < uj) ++g;   // first shard with cdf >= u (last one catches the rest)
+        double out = -1.0;
+        if (g == rank) {
+            const double lo = g > 0 ? (double)cdf[g - 1] : 0.0, hi = (double)cdf[g];
+            out = hi > lo ? (uj - lo) / (hi - lo) : 0.0;
+            if (out < 0.0) out = 0.0;
+            if (out >= 1.0) out = 0.99999999999999989;  // largest double below 1
+        }
+        local_u[j] = out;
+    }
+}
+}  // namespace
+}  // namespace mercury
+
+extern "C" int mercury_sum_scores(const float* scores, int64_t n, double* out_sum, void* ws, size_t ws_bytes, void* stream) {
+    MB_CHECK_ARG(n >= 1 && scores && out_sum, "mercury_sum_scores: bad arguments");
+    const CdfWs w = carve(ws, n, true);
+    int rc = check_ws(ws, ws_bytes, w.bytes, "mercury_sum_scores");
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nchunks = (int)((n + kChunk - 1) / kChunk);
+    chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, n, w.sums, nullptr, 0);
+    MB_CHECK_LAUNCH("chunk_sums_kernel");
+    reduce_sums_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, out_sum);
+    MB_CHECK_LAUNCH("reduce_sums_kernel");
+    return MERCURY_OK;
+}
+
+extern "C" int mercury_shard_select(const float* shard_totals, int nshards, int rank, const double* uniforms, int64_t b,
+                                    double* local_uniforms, void* stream) {
+    MB_CHECK_ARG(nshards >= 1 && nshards <= kMaxShards, "mercury_shard_select: 1..%d shards", kMaxShards);
+    MB_CHECK_ARG(rank >= 0 && rank < nshards && b >= 0, "mercury_shard_select: bad rank or draw count");
+    if (b == 0) return MERCURY_OK;
+    MB_CHECK_ARG(shard_totals && uniforms && local_uniforms, "mercury_shard_select: null pointer");
+    shard_select_kernel<<<(unsigned)((b + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(shard_totals, nshards, rank, uniforms, b,
+                                                                                                    local_uniforms);
+    MB_CHECK_LAUNCH("shard_select_kernel");
     return MERCURY_OK;
 }
 

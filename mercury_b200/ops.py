@@ -297,7 +297,9 @@ def update_samples(logits: Optional[torch.Tensor], labels: Optional[torch.Tensor
                    ema_state: torch.Tensor, ema_first: bool, *, ema_alpha: float = 0.9, smooth_alpha: float = 0.5,
                    data: Optional[torch.Tensor] = None, index: Optional[torch.Tensor] = None,
                    scores_in: Optional[torch.Tensor] = None, bounds: Optional[Sequence[int]] = None,
-                   ignore_index: int = -100, status: Optional[torch.Tensor] = None, out: Optional[dict] = None) -> UpdateResult:
+                   ignore_index: int = -100, status: Optional[torch.Tensor] = None, out: Optional[dict] = None,
+                   global_sums: Optional[torch.Tensor] = None, n_global: Optional[int] = None, index_base: int = 0,
+                   draw_only: bool = False) -> UpdateResult:
     """Score -> statistics -> exact CDF -> B draws -> gather + weights + seed, in one C-ABI call.
 
     The arithmetic of Trainer.update_samples (pytorch_collab.py:102-117) on an assembled pool.
@@ -364,10 +366,38 @@ def update_samples(logits: Optional[torch.Tensor], labels: Optional[torch.Tensor
         a.index = index.data_ptr()
         out_index = buf("index", (b,), torch.int64)
         a.out_index = out_index.data_ptr()
+    if global_sums is not None:  # one shard of a larger pool (see sharded.ShardedPool, mode "totals")
+        _cuda(global_sums, "global_sums", torch.float64)
+        a.global_sums, a.n_global_sums = global_sums.data_ptr(), global_sums.numel()
+        a.n_global, a.index_base = int(n_global), int(index_base)
+    a.draw_only = int(bool(draw_only))
     ws = workspace(dev, lib.mercury_update_samples_workspace_bytes(n, b))
     _lib.check(lib.mercury_update_samples(ctypes.byref(a), ws.data_ptr(), ws.numel(), _stream()))
     return UpdateResult(scores=scores, stats=stats, idx=idx, nprob=nprob, seed=seed, data=out_data, labels=out_labels,
                         index=out_index, status=status)
+
+
+def sum_scores(scores: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Deterministic fp64 sum of a shard's scores (one double), for the all-gather of shard sums."""
+    _cuda(scores, "scores", torch.float32)
+    lib = _lib.load()
+    if out is None:
+        out = torch.empty(1, dtype=torch.float64, device=scores.device)
+    ws = workspace(scores.device, lib.mercury_update_samples_workspace_bytes(max(scores.numel(), 1), 0))
+    _lib.check(lib.mercury_sum_scores(scores.contiguous().data_ptr(), scores.numel(), out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
+    return out
+
+
+def shard_select(shard_totals: torch.Tensor, rank: int, uniforms: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """First level of the two-level draw: for every uniform, its position inside THIS rank's shard CDF
+    (fp64 in [0,1)) if it falls in this shard, else -1."""
+    _cuda(shard_totals, "shard_totals", torch.float32)
+    _cuda(uniforms, "uniforms", torch.float64)
+    if out is None:
+        out = torch.empty_like(uniforms)
+    _lib.check(_lib.load().mercury_shard_select(shard_totals.data_ptr(), shard_totals.numel(), int(rank), uniforms.data_ptr(),
+                                                uniforms.numel(), out.data_ptr(), _stream()))
+    return out
 
 
 class GraphedUpdate:

@@ -47,6 +47,26 @@ class CudaBackend:
     def gather_owned(self, idx, lo, n, data, labels, index, out):
         return self.ops.gather_owned(idx, lo, n, data, labels, index, out=out)
 
+    # ---- mode "totals": shard-local chains, only sums / totals are exchanged
+    def sum_scores(self, scores, out):
+        self.ops.sum_scores(scores, out=out)
+
+    def local_chain(self, scores, sums_all, n_global, ema_state, ema_first, ema_alpha, smooth_alpha, out):
+        empty_u = out.setdefault("_no_draws", torch.empty(0, dtype=torch.float64, device=scores.device))
+        r = self.ops.update_samples(None, None, empty_u, ema_state, ema_first, ema_alpha=ema_alpha, smooth_alpha=smooth_alpha,
+                                    scores_in=scores, global_sums=sums_all, n_global=n_global, out=out)
+        out["stats"] = r.stats
+        return r.stats, r.status
+
+    def shard_select(self, totals_all, rank, uniforms, out):
+        return self.ops.shard_select(totals_all, rank, uniforms, out=out)
+
+    def local_draw(self, scores, local_u, stats, sums_all, n_global, lo, ema_state, data, labels, index, out, status):
+        out = dict(out, stats=stats)
+        r = self.ops.update_samples(None, labels, local_u, ema_state, False, scores_in=scores, data=data, index=index,
+                                    global_sums=sums_all, n_global=n_global, index_base=lo, draw_only=True, out=out, status=status)
+        return r
+
 
 def shard_bounds(n_global: int, world: int, rank: int):
     """Contiguous equal shards in rank order: shard g = [g*N/G, (g+1)*N/G)."""
@@ -57,13 +77,21 @@ def shard_bounds(n_global: int, world: int, rank: int):
 
 
 class ShardedPool:
-    def __init__(self, n_local: int, device, group=None, ema_alpha: float = 0.9, smooth_alpha: float = 0.5, backend=None):
+    """mode="scores": all-gather the scores, replicate the exact CDF (index-identical to the flat pool);
+    mode="totals": every rank builds the exact CDF of its own shard only, the ranks exchange one sum and
+    one total each, and the draw is two-level (shard, then position) -- constant work per rank."""
+
+    def __init__(self, n_local: int, device, group=None, ema_alpha: float = 0.9, smooth_alpha: float = 0.5, backend=None,
+                 mode: str = "scores"):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.n_local = n_local
         self.n_global = n_local * self.world
-        if self.n_global > (1 << 24):
+        if mode not in ("scores", "totals"):
+            raise ValueError("mode must be 'scores' or 'totals'")
+        self.mode = mode
+        if (self.n_global if mode == "scores" else n_local) > (1 << 24):
             raise RuntimeError("number of categories cannot exceed 2^24")
         self.lo, _ = shard_bounds(self.n_global, self.world, self.rank)
         self.device = torch.device(device)
@@ -74,10 +102,50 @@ class ShardedPool:
         self.ema_alpha, self.smooth_alpha = ema_alpha, smooth_alpha
         self._draw_out: dict = {}
         self._gather_out: dict = {}
+        if mode == "totals":
+            self.scores_all = torch.empty(n_local, dtype=torch.float32, device=self.device)  # (local shard only)
+            self.sums_all = torch.zeros(self.world, dtype=torch.float64, device=self.device)
+            self.totals_all = torch.zeros(self.world, dtype=torch.float32, device=self.device)
+            self.local_u = None
+            self._chain_out: dict = {}
 
     @property
     def local_scores(self) -> torch.Tensor:
-        return self.scores_all[self.lo:self.lo + self.n_local]
+        return self.scores_all if self.mode == "totals" else self.scores_all[self.lo:self.lo + self.n_local]
+
+    def _all_gather_small(self, full: torch.Tensor):
+        if self.world == 1:
+            return
+        mine = full[self.rank:self.rank + 1]
+        try:
+            dist.all_gather_into_tensor(full, mine, group=self.group)
+        except (RuntimeError, NotImplementedError):
+            parts = list(full.split(1))
+            dist.all_gather(parts, mine.clone(), group=self.group)
+
+    def _update_totals(self, logits_local, labels_local, uniforms, data, index, assemble):
+        b = self.backend
+        b.score(logits_local, labels_local, self.local_scores)
+        b.sum_scores(self.local_scores, self.sums_all[self.rank:self.rank + 1])
+        self._all_gather_small(self.sums_all)                      # G doubles
+        stats, status = b.local_chain(self.local_scores, self.sums_all, self.n_global, self.ema_state, self.ema_first,
+                                      self.ema_alpha, self.smooth_alpha, self._chain_out)
+        self.ema_first = False
+        self.totals_all[self.rank:self.rank + 1].copy_(stats[_lib.STAT_CHAIN_TOTAL:_lib.STAT_CHAIN_TOTAL + 1])
+        self._all_gather_small(self.totals_all)                    # G floats
+        if self.local_u is None or self.local_u.shape != uniforms.shape:
+            self.local_u = torch.empty_like(uniforms)
+        b.shard_select(self.totals_all, self.rank, uniforms, self.local_u)
+        r = b.local_draw(self.local_scores, self.local_u, stats, self.sums_all, self.n_global, self.lo, self.ema_state, data,
+                         labels_local, index, self._draw_out, status)
+        self._draw_out.update({k: r[k] for k in ("idx", "nprob", "seed", "data", "labels", "index") if r[k] is not None})
+        owned = self.local_u >= 0
+        if assemble and self.world > 1:
+            for t in (r["idx"], r["nprob"], r["seed"], r["data"], r["labels"], r["index"]):
+                if t is not None:
+                    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return dict(idx=r["idx"], nprob=r["nprob"], seed=r["seed"], stats=stats, status=status, data=r["data"], labels=r["labels"],
+                    index=r["index"], owned=owned, scores=self.local_scores)
 
     def _all_gather_scores(self):
         if self.world == 1:
@@ -93,6 +161,8 @@ class ShardedPool:
         """One global importance-sampling step.  Returns a dict with the replicated ``idx`` (global
         positions), ``nprob``, ``seed``, ``stats``, ``status`` and this rank's ``data`` / ``labels`` /
         ``index`` rows (zero where another rank owns the draw) plus the ``owned`` mask."""
+        if self.mode == "totals":
+            return self._update_totals(logits_local, labels_local, uniforms, data, index, assemble)
         b = self.backend
         b.score(logits_local, labels_local, self.local_scores)
         self._all_gather_scores()

@@ -226,3 +226,28 @@ def sharded_draw_flat(score_shards, u, ema: EMAverage, alpha=0.5):
     losses = torch.cat(list(score_shards))
     mean, w, p = pool_stats(losses, ema, alpha)
     return p, torch.from_numpy(draw_with_replacement(p.numpy(), np.asarray(u)))
+
+
+def sharded_draw_two_level(p_shards, u):
+    """North-star mode B: per-shard totals are exchanged, the draw is two-level.
+
+    p_shards: list of fp32 arrays, the shards of the globally normalised p.  First level: serial
+    fp32 CDF over the shards' serial-chain totals, searched like ATen (first shard with
+    double(cdf) >= u, the last shard catching the rest); second level: the uniform rescaled into
+    the shard, u' = (u - lo) / (hi - lo), searched in the shard's own serial fp32 CDF.
+    Returns global positions.  (Not index-identical to torch.multinomial on the flat vector.)
+    """
+    totals = np.asarray([serial_chain_f32(p)[-1] for p in p_shards], dtype=np.float32)
+    c = np.cumsum(totals, dtype=np.float32)
+    cdf = (c / c[-1]).astype(np.float32).astype(np.float64)
+    offsets = np.concatenate([[0], np.cumsum([len(p) for p in p_shards])])
+    out = np.empty(len(u), dtype=np.int64)
+    for j, uj in enumerate(np.asarray(u, dtype=np.float64)):
+        g = 0
+        while g < len(p_shards) - 1 and cdf[g] < uj:
+            g += 1
+        lo, hi = (cdf[g - 1] if g > 0 else 0.0), cdf[g]
+        ul = (uj - lo) / (hi - lo) if hi > lo else 0.0
+        ul = min(max(ul, 0.0), 0.99999999999999989)
+        out[j] = offsets[g] + lower_bound(serial_cdf_f32(p_shards[g]), np.asarray([ul]))[0]
+    return out

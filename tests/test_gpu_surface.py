@@ -207,3 +207,63 @@ def test_graphed_update_equals_eager_calls():
         assert torch.equal(r.idx, e.idx) and torch.equal(r.nprob, e.nprob) and torch.equal(r.seed, e.seed)
         assert torch.equal(r.data, e.data) and torch.equal(r.labels, e.labels) and torch.equal(ema_g, ema_e)
     ops.check_status(g.status)
+
+
+def test_two_level_sharded_draw_matches_its_oracle():
+    """Mode "totals" (north-star literal): three shards emulated one after the other on one GPU --
+    the kernels are the ones ShardedPool(mode="totals") calls, the exchanges are plain concatenations."""
+    from mercury_b200 import _lib, ops
+
+    gen = torch.Generator().manual_seed(21)
+    G, n_local, c, b = 3, 40000, 10, 200
+    N = G * n_local
+    logits = [(torch.randn(n_local, c, generator=gen) * 2).to(DEV) for _ in range(G)]
+    labels = [torch.randint(0, c, (n_local,), generator=gen).to(DEV) for _ in range(G)]
+    data = [torch.rand(n_local, 6, generator=gen).to(DEV) for _ in range(G)]
+    u = torch.rand(b, dtype=torch.float64, generator=gen).to(DEV)
+    none = torch.empty(0, dtype=torch.float64, device=DEV)
+    scores = [ops.score(logits[r], labels[r]) for r in range(G)]
+    sums_all = torch.cat([ops.sum_scores(s) for s in scores])              # "all-gather" of the shard sums
+    np.testing.assert_allclose(sums_all.cpu().numpy(), [float(s.double().sum()) for s in scores], rtol=1e-12)
+
+    def chain(r):
+        return ops.update_samples(None, None, none, torch.zeros(1, device=DEV), True, scores_in=scores[r],
+                                  global_sums=sums_all, n_global=N)
+
+    stats = [chain(r).stats.clone() for r in range(G)]
+    for r in range(1, G):                                                   # whole-pool statistics: identical on all ranks
+        assert torch.equal(stats[r][:4], stats[0][:4])
+    allscores = torch.cat(scores).cpu()
+    np.testing.assert_allclose(float(stats[0][0]), float(allscores.mean()), rtol=1e-6)
+    totals_all = torch.stack([s[_lib.STAT_CHAIN_TOTAL] for s in stats])    # "all-gather" of the chain totals
+    shift, total = np.float32(stats[0][2].item()), np.float32(stats[0][3].item())
+    p_shards = [((s.cpu().numpy() + shift).astype(np.float32) / total).astype(np.float32) for s in scores]
+    for r in range(G):
+        assert totals_all[r].cpu().numpy().view(np.uint32) == orc.serial_chain_f32(p_shards[r])[-1:].view(np.uint32)
+    want = orc.sharded_draw_two_level(p_shards, u.cpu().numpy())
+    got_idx = torch.zeros(b, dtype=torch.int64, device=DEV)
+    got_np = torch.zeros(b, device=DEV)
+    got_data = torch.zeros(b, 6, device=DEV)
+    owners = torch.zeros(b, dtype=torch.int64, device=DEV)
+    for r in range(G):
+        local_u = ops.shard_select(totals_all, r, u)
+        st = chain(r)                                                       # (this rank's boundaries back into the workspace)
+        d = ops.update_samples(None, labels[r], local_u, torch.zeros(1, device=DEV), False, scores_in=scores[r], data=data[r],
+                               global_sums=sums_all, n_global=N, index_base=r * n_local, draw_only=True, out={"stats": st.stats})
+        got_idx += d.idx
+        got_np += d.nprob
+        got_data += d.data
+        owners += (local_u >= 0).long()
+    assert torch.all(owners == 1)                                           # every draw has exactly one owner
+    assert np.array_equal(got_idx.cpu().numpy(), want)
+    p_all = np.concatenate(p_shards)
+    np.testing.assert_allclose(got_np.cpu().numpy(), p_all[want] * np.float32(N), rtol=1e-6)
+    assert torch.equal(got_data.cpu(), torch.cat(data).cpu()[want])
+    # with a single shard the two-level draw is the flat draw
+    one = ops.update_samples(None, None, u, torch.zeros(1, device=DEV), True, scores_in=scores[0])
+    su = ops.sum_scores(scores[0])
+    st1 = ops.update_samples(None, None, none, torch.zeros(1, device=DEV), True, scores_in=scores[0], global_sums=su, n_global=n_local)
+    lu = ops.shard_select(st1.stats[_lib.STAT_CHAIN_TOTAL:_lib.STAT_CHAIN_TOTAL + 1].clone(), 0, u)
+    two = ops.update_samples(None, None, lu, torch.zeros(1, device=DEV), False, scores_in=scores[0], global_sums=su,
+                             n_global=n_local, draw_only=True, out={"stats": st1.stats})
+    assert torch.equal(one.idx, two.idx) and torch.equal(one.nprob, two.nprob)

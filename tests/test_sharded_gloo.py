@@ -47,6 +47,57 @@ class OracleBackend:
         return take(data), take(labels), take(index), mine.to(torch.int32)
 
 
+    # ---- mode "totals"
+    @staticmethod
+    def _p(scores, stats):
+        return ((scores.numpy() + np.float32(stats[2])).astype(np.float32) / np.float32(stats[3])).astype(np.float32)
+
+    def sum_scores(self, scores, out):
+        out.copy_(scores.double().sum().reshape(1))
+
+    def local_chain(self, scores, sums_all, n_global, ema_state, ema_first, ema_alpha, smooth_alpha, out):
+        tot = float(sums_all.sum())
+        mean = np.float32(tot / n_global)
+        ema = mean if ema_first else np.float32(np.float32(ema_alpha) * np.float32(ema_state[0]) + np.float32(1.0 - ema_alpha) * mean)
+        ema_state[0] = float(ema)
+        shift = np.float32(np.float32(smooth_alpha) * ema)
+        total = np.float32(tot + n_global * float(shift))
+        stats = torch.tensor([mean, ema, shift, total, 0, 0, 0, 0], dtype=torch.float32)
+        stats[4] = float(orc.serial_chain_f32(self._p(scores, stats))[-1])
+        return stats, torch.zeros(1, dtype=torch.int32)
+
+    def shard_select(self, totals_all, rank, uniforms, out):
+        c = np.cumsum(totals_all.numpy(), dtype=np.float32)
+        cdf = (c / c[-1]).astype(np.float32).astype(np.float64)
+        for j, uj in enumerate(uniforms.numpy()):
+            g = 0
+            while g < len(cdf) - 1 and cdf[g] < uj:
+                g += 1
+            lo, hi = (cdf[g - 1] if g else 0.0), cdf[g]
+            out[j] = min(max((uj - lo) / (hi - lo), 0.0), 0.99999999999999989) if g == rank else -1.0
+        return out
+
+    def local_draw(self, scores, local_u, stats, sums_all, n_global, lo, ema_state, data, labels, index, out, status):
+        p = self._p(scores, stats)
+        mine = local_u >= 0
+        idx_l = torch.zeros(local_u.numel(), dtype=torch.int64)
+        if mine.any():
+            idx_l[mine] = torch.from_numpy(orc.lower_bound(orc.serial_cdf_f32(p), local_u[mine].numpy()))
+        nprob = torch.from_numpy(p)[idx_l] * n_global
+        nprob[~mine] = 0
+        seed = torch.where(mine, (1.0 / local_u.numel()) / nprob.clamp_min(1e-30), torch.zeros_like(nprob))
+
+        def take(t):
+            if t is None:
+                return None
+            rows = t[idx_l].clone()
+            rows[~mine] = 0
+            return rows
+
+        idx = torch.where(mine, idx_l + lo, torch.zeros_like(idx_l))
+        return dict(idx=idx, nprob=nprob, seed=seed, data=take(data), labels=take(labels), index=take(index))
+
+
 def _pool(n, c, seed=0):
     g = torch.Generator().manual_seed(seed)
     logits = torch.randn(n, c, generator=g) * 2
@@ -75,6 +126,46 @@ def _worker(rank, world, port, n, c, ret):
         ret[rank] = outs
     finally:
         dist.destroy_process_group()
+
+
+def _worker_totals(rank, world, port, n, c, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mercury_b200.sharded import ShardedPool, shard_bounds
+
+        logits, labels, data, index, u = _pool(n, c)
+        lo, nl = shard_bounds(n, world, rank)
+        sp = ShardedPool(nl, "cpu", backend=OracleBackend(), mode="totals")
+        outs = []
+        for step in range(2):
+            r = sp.update_samples(logits[lo:lo + nl] + step, labels[lo:lo + nl], u, data=data[lo:lo + nl], index=index[lo:lo + nl],
+                                  assemble=True)
+            outs.append({k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in r.items()})
+        ret[rank] = outs
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_pool_totals_mode_world2_matches_two_level_oracle():
+    n, c, world = 4096, 10, 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker_totals, args=(world, _free_port(), n, c, ret), nprocs=world, join=True)
+    logits, labels, data, index, u = _pool(n, c)
+    for step in range(2):
+        a, b = ret[0][step], ret[1][step]
+        assert torch.equal(a["stats"][:4], b["stats"][:4])                       # whole-pool statistics agree
+        assert torch.equal(a["idx"], b["idx"]) and torch.equal(a["data"], b["data"])   # assembled batch on both ranks
+        assert int(a["owned"].sum() + b["owned"].sum()) == len(u)
+        losses = orc.score(logits + step, labels)
+        st = a["stats"]
+        p = ((losses.numpy() + np.float32(st[2])).astype(np.float32) / np.float32(st[3])).astype(np.float32)
+        want = orc.sharded_draw_two_level([p[:n // 2], p[n // 2:]], u.numpy())
+        assert np.array_equal(a["idx"].numpy(), want)
+        assert torch.equal(a["data"], data[want]) and torch.equal(a["labels"], labels[want]) and torch.equal(a["index"], index[want])
+        np.testing.assert_allclose(float(st[0]), float(losses.mean()), rtol=1e-6)
 
 
 def _free_port():
