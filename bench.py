@@ -175,6 +175,19 @@ def run_reference(args, wl):
     print(json.dumps(line))
 
 
+MULTI_GPU_NOTE = {
+    "totals": "pool sharded by rank; every rank builds the exact chain of its own shard; NCCL all-gather of one fp64 sum and one "
+              "fp32 chain total per rank; two-level draw (shard by totals, then position) by the owning rank",
+    "scores": "pool sharded by rank; NCCL all-gather of scores; replicated exact CDF of the whole pool; rows gathered by their owner",
+}
+
+
+EXCHANGE_NOTE = {
+    "peer": "in-kernel stores into the peers' exchange boxes (CUDA IPC over NVLink/NVSwitch), no collective in the step",
+    "nccl": "NCCL all-gather",
+}
+
+
 def main():
     if os.environ.get("MERCURY_BENCH_FAULT_TIMEOUT"):  # developer aid: dump every thread's stack if the run stalls
         import faulthandler
@@ -188,6 +201,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pools", type=int, default=0, help="distinct pools rotated to defeat L2 (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard-mode", choices=["totals", "scores"], default=os.environ.get("MERCURY_SHARD_MODE", "totals"),
+                    help="N>1 only: 'totals' = shard-local exact chains, only per-shard sums/totals exchanged, two-level draw; "
+                         "'scores' = all-gather the scores and replicate the flat pool's exact CDF on every rank")
+    ap.add_argument("--exchange", choices=["peer", "nccl"], default=os.environ.get("MERCURY_EXCHANGE", "peer"),
+                    help="N>1, --shard-mode totals: 'peer' = the sums/totals travel by stores into the peers' mapped memory from "
+                         "inside our kernels (CUDA IPC over NVLink); 'nccl' = two small NCCL all-gathers")
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="launch every step eagerly (no CUDA graph)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -231,7 +250,21 @@ def main():
     if world > 1:
         from mercury_b200.sharded import ShardedPool
 
-        sp = ShardedPool(n_local=n, device=dev)
+        exchange = args.exchange if args.shard_mode == "totals" else "nccl"
+        if exchange == "peer":
+            # peer mapping is a set-up step that a box may refuse (no IPC between these GPUs): agree on it across ranks
+            try:
+                sp = ShardedPool(n_local=n, device=dev, mode="totals", exchange="peer")
+                ok = 1
+            except Exception as e:  # noqa: BLE001
+                print(f"[bench] rank {rank}: peer exchange unavailable ({e}); using NCCL", file=sys.stderr)
+                ok = 0
+            t = torch.tensor([ok], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            if int(t) == 0:
+                exchange = "nccl"
+        if exchange == "nccl":
+            sp = ShardedPool(n_local=n, device=dev, mode=args.shard_mode)
 
     status = ops.new_status(dev)
 
@@ -386,7 +419,8 @@ def main():
 
     if rank == 0:
         # our kernels per step and rank: score, summarize (statistics folded in), spine, draw; sharded: + chunk sums, gather_owned
-        launches_per_step = 4 if world == 1 else 6 * world
+        # totals: score, chunk sums, sum(+exchange), summarize, spine, select(+exchange), draw; scores: + gather_owned
+        launches_per_step = 4 if world == 1 else (7 if args.shard_mode == "totals" else 6) * world
         line = {
             "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -395,7 +429,8 @@ def main():
                        "payload_row_bytes": row_bytes, "l2": f"{npools} distinct pools rotated ({npools * pool_bytes >> 20} MiB > 126 MiB L2)",
                        "cdf": "exact serial-fp32 (bit-identical to torch.multinomial on CPU)",
                        "launch": "CUDA graph replay, one graph per pool" if graphs is not None else "eager launches",
-                       "multi_gpu": None if world == 1 else "pool sharded by rank; NCCL all-gather of scores; replicated exact CDF; local draw"},
+                       "multi_gpu": None if world == 1 else MULTI_GPU_NOTE[args.shard_mode],
+                       "exchange": None if world == 1 else EXCHANGE_NOTE[exchange]},
             "step_roofline": {"algorithmic_bytes": step_bytes, "achieved_gbs": step_bytes / (ms * 1e-3) / 1e9,
                               "frac": step_bytes / (ms * 1e-3) / 1e9 / peak},
             "roofline": {"kernel": "K1 score (mercury_score)", "bound": "hbm", "achieved": k1_gbs, "peak": peak, "unit": "GB/s",

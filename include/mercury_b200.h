@@ -48,7 +48,8 @@ enum {
     MERCURY_ST_NEGATIVE = 2,   /* multinomial: "encountering probability entry < 0" (NaN included) */
     MERCURY_ST_NONFINITE = 4,  /* multinomial: "probability entry = infinity or NaN"               */
     MERCURY_ST_ZERO_SUM = 8,   /* multinomial: "sum of probabilities <= 0"                         */
-    MERCURY_ST_TOPK_TIES = 16  /* exponential race: more exact ties at the k-th key than buffered  */
+    MERCURY_ST_TOPK_TIES = 16, /* exponential race: more exact ties at the k-th key than buffered  */
+    MERCURY_ST_PEER_TIMEOUT = 32 /* peer exchange: a peer's word did not arrive within 4 s          */
 };
 
 /* layout of the 8-float statistics block written by mercury_pool_stats */
@@ -162,6 +163,29 @@ void mercury_test_set_guess_bias(double bias);
 int mercury_sum_scores(const float* scores, int64_t n, double* out_sum, void* ws, size_t ws_bytes, void* stream);
 int mercury_shard_select(const float* shard_totals, int nshards, int rank, const double* uniforms, int64_t b,
                          double* local_uniforms, void* stream);
+
+/* ---- the same exchange over peer memory instead of a collective (no counterpart in the reference) ----
+ * Set-up, once per rank: mercury_peer_create allocates this rank's zeroed exchange box
+ * (MERCURY_PEER_BOX_BYTES of device memory) and returns a 64-byte CUDA IPC handle for it; the host
+ * passes the handles round (any channel), maps every peer's box with mercury_peer_open and keeps the G
+ * box addresses, in rank order with its own box at [rank], in a DEVICE array `peer_boxes`.
+ * mercury_peer_close unmaps a peer's box, mercury_peer_destroy frees the own one.
+ * Per step: mercury_sum_scores_exchange = mercury_sum_scores + all-gather (sums_all fp64 [nshards] is
+ * filled for every rank); mercury_shard_select_exchange = all-gather of the chain totals (my_total: device
+ * fp32, e.g. &stats[MERCURY_STAT_CHAIN_TOTAL]; totals_all fp32 [nshards] out) + mercury_shard_select.
+ * The kernels store into the peers' boxes and wait, for at most 4 s (then MERCURY_ST_PEER_TIMEOUT), for
+ * the peers' stores: every rank must make the same sequence of exchange calls, each on a GPU of its own. */
+#define MERCURY_PEER_BOX_BYTES 4096
+#define MERCURY_PEER_HANDLE_BYTES 64
+int mercury_peer_create(void** box, unsigned char* handle);
+int mercury_peer_open(const unsigned char* handle, void** peer_box);
+int mercury_peer_close(void* peer_box);
+int mercury_peer_destroy(void* box);
+int mercury_sum_scores_exchange(const float* scores, int64_t n, void* const* peer_boxes, int nshards, int rank,
+                                double* sums_all, int32_t* status, void* ws, size_t ws_bytes, void* stream);
+int mercury_shard_select_exchange(const float* my_total, void* const* peer_boxes, int nshards, int rank,
+                                  const double* uniforms, int64_t b, float* totals_all, double* local_uniforms,
+                                  int32_t* status, void* stream);
 
 /* ---- the whole step ---------------------------------------------------------------------------
  * replaces Trainer.update_samples' arithmetic (pytorch_collab.py:102-117) on an assembled pool:

@@ -15,7 +15,8 @@ ABI_VERSION = 2
 OK, ERR_ARG, ERR_CUDA, ERR_WORKSPACE = 0, -1, -2, -3
 F32, BF16 = 0, 1
 CDF_EXACT_SERIAL_F32, CDF_F64 = 0, 1
-ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES = 1, 2, 4, 8, 16
+ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES, ST_PEER_TIMEOUT = 1, 2, 4, 8, 16, 32
+PEER_BOX_BYTES, PEER_HANDLE_BYTES = 4096, 64
 STAT_MEAN, STAT_EMA, STAT_SHIFT, STAT_TOTAL, STAT_CHAIN_TOTAL, STAT_COUNT = 0, 1, 2, 3, 4, 8
 STATIC_MAX_N = 1 << 22
 
@@ -59,6 +60,12 @@ SIGNATURES = {
     "mercury_test_set_guess_bias": (None, [c_f64]),
     "mercury_sum_scores": (c_int, [c_vp, c_i64, c_vp, c_vp, c_sz, c_vp]),
     "mercury_shard_select": (c_int, [c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp]),
+    "mercury_peer_create": (c_int, [c_vp, c_vp]),
+    "mercury_peer_open": (c_int, [c_vp, c_vp]),
+    "mercury_peer_close": (c_int, [c_vp]),
+    "mercury_peer_destroy": (c_int, [c_vp]),
+    "mercury_sum_scores_exchange": (c_int, [c_vp, c_i64, c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "mercury_shard_select_exchange": (c_int, [c_vp, c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "mercury_update_samples_workspace_bytes": (c_sz, [c_i64, c_i64]),
     "mercury_update_samples": (c_int, [ctypes.POINTER(UpdateArgs), c_vp, c_sz, c_vp]),
 }

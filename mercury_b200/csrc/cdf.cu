@@ -1595,8 +1595,157 @@ __global__ void __launch_bounds__(256) shard_select_kernel(const float* __restri
         local_u[j] = out;
     }
 }
+
+// ---- the same two steps with the exchange inside the kernel: every rank owns one PeerBox in
+// memory its peers have mapped (CUDA IPC over NVLink / NVSwitch).  A rank stores its value, tagged
+// with the step's sequence number in the same 64-bit word, straight into slot [rank] of every
+// peer's box and then polls its OWN box until all G slots carry this step's tag: one NVLink store
+// latency instead of a collective launch.  A word is (payload32 << 32 | seq32): written by one
+// 8-byte store, so a reader never sees a payload without its tag and no fence is needed.  Slots
+// are double-buffered by the tag's parity; a rank cannot be more than one exchange ahead of a peer
+// (it needs that peer's next word to get any further).  Waits are bounded (kPeerWaitNs) and
+// report MERCURY_ST_PEER_TIMEOUT instead of hanging the device.
+struct PeerBox {
+    unsigned long long sum_hi[2][kMaxShards];
+    unsigned long long sum_lo[2][kMaxShards];
+    unsigned long long total[2][kMaxShards];
+    unsigned int seq_sum, seq_total;      // local step counters (peers never touch them)
+    unsigned int dead;                    // set by the first timed-out wait: later waits give up at once
+};
+static_assert(sizeof(PeerBox) <= MERCURY_PEER_BOX_BYTES, "PeerBox must fit the size the header promises");
+constexpr unsigned long long kPeerWaitNs = 4000000000ull;
+
+__device__ __forceinline__ void peer_store(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long peer_load(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// polls *p until its low half equals seq; false on timeout
+__device__ __forceinline__ bool peer_wait(const unsigned long long* p, unsigned int seq, unsigned long long& word,
+                                          volatile unsigned int* dead) {
+    word = peer_load(p);
+    if ((unsigned int)word == seq) return true;
+    if (*dead) return false;
+    const unsigned long long t0 = global_ns();
+    for (;;) {
+        for (int i = 0; i < 64; ++i) {
+            word = peer_load(p);
+            if ((unsigned int)word == seq) return true;
+        }
+        if (global_ns() - t0 > kPeerWaitNs) {
+            *dead = 1u;
+            return false;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024) sum_exchange_kernel(const double* __restrict__ sums, int nchunks, PeerBox* const* __restrict__ peers,
+                                                            int nshards, int rank, double* __restrict__ sums_all,
+                                                            int32_t* __restrict__ status) {
+    __shared__ double red[32];
+    __shared__ unsigned int s_seq;
+    __shared__ double s_sum;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < nchunks; i += 1024) acc += sums[i];
+    const double t = block_sum<1024>(acc, red);
+    PeerBox* mine = peers[rank];
+    if (threadIdx.x == 0) {
+        s_seq = ++mine->seq_sum;
+        s_sum = t;
+    }
+    __syncthreads();
+    const unsigned int seq = s_seq;
+    const int par = seq & 1u, g = threadIdx.x;
+    if (g < nshards) {
+        const unsigned long long bits = (unsigned long long)__double_as_longlong(s_sum);
+        peer_store(&peers[g]->sum_hi[par][rank], (bits >> 32 << 32) | seq);
+        peer_store(&peers[g]->sum_lo[par][rank], (bits << 32) | seq);
+        unsigned long long hi, lo;
+        const bool ok = peer_wait(&mine->sum_hi[par][g], seq, hi, &mine->dead) & peer_wait(&mine->sum_lo[par][g], seq, lo, &mine->dead);
+        if (!ok) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
+        sums_all[g] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
+    }
+}
+
+__global__ void __launch_bounds__(256) select_exchange_kernel(const float* __restrict__ my_total, PeerBox* const* __restrict__ peers,
+                                                              int nshards, int rank, const double* __restrict__ u, int64_t b,
+                                                              float* __restrict__ totals_all, double* __restrict__ local_u,
+                                                              int32_t* __restrict__ status) {
+    __shared__ float tot[kMaxShards];
+    __shared__ float cdf[kMaxShards];
+    __shared__ unsigned int s_seq;
+    PeerBox* mine = peers[rank];
+    if (threadIdx.x == 0) s_seq = ++mine->seq_total;
+    __syncthreads();
+    const unsigned int seq = s_seq;
+    const int par = seq & 1u, g = threadIdx.x;
+    if (g < nshards) {
+        peer_store(&peers[g]->total[par][rank], ((unsigned long long)__float_as_uint(*my_total) << 32) | seq);
+        unsigned long long w;
+        if (!peer_wait(&mine->total[par][g], seq, w, &mine->dead)) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
+        tot[g] = __uint_as_float((unsigned int)(w >> 32));
+        totals_all[g] = tot[g];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float s = 0.f;
+        for (int k = 0; k < nshards; ++k) { s = __fadd_rn(s, tot[k]); cdf[k] = s; }
+        for (int k = 0; k < nshards; ++k) cdf[k] = __fdiv_rn(cdf[k], s);
+    }
+    __syncthreads();
+    for (int64_t j = threadIdx.x; j < b; j += 256) {
+        const double uj = u[j];
+        int k = 0;
+        while (k < nshards - 1 && (double)cdf[k] < uj) ++k;
+        double out = -1.0;
+        if (k == rank) {
+            const double lo = k > 0 ? (double)cdf[k - 1] : 0.0, hi = (double)cdf[k];
+            out = hi > lo ? (uj - lo) / (hi - lo) : 0.0;
+            if (out < 0.0) out = 0.0;
+            if (out >= 1.0) out = 0.99999999999999989;
+        }
+        local_u[j] = out;
+    }
+}
 }  // namespace
 }  // namespace mercury
+
+extern "C" int mercury_sum_scores_exchange(const float* scores, int64_t n, void* const* peer_boxes, int nshards, int rank,
+                                           double* sums_all, int32_t* status, void* ws, size_t ws_bytes, void* stream) {
+    MB_CHECK_ARG(n >= 1 && scores && sums_all && peer_boxes && status, "mercury_sum_scores_exchange: bad arguments");
+    MB_CHECK_ARG(nshards >= 1 && nshards <= kMaxShards && rank >= 0 && rank < nshards, "mercury_sum_scores_exchange: 1..%d shards", kMaxShards);
+    const CdfWs w = carve(ws, n, true);
+    int rc = check_ws(ws, ws_bytes, w.bytes, "mercury_sum_scores_exchange");
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nchunks = (int)((n + kChunk - 1) / kChunk);
+    chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, n, w.sums, nullptr, 0);
+    MB_CHECK_LAUNCH("chunk_sums_kernel");
+    sum_exchange_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, reinterpret_cast<PeerBox* const*>(peer_boxes), nshards, rank, sums_all, status);
+    MB_CHECK_LAUNCH("sum_exchange_kernel");
+    return MERCURY_OK;
+}
+
+extern "C" int mercury_shard_select_exchange(const float* my_total, void* const* peer_boxes, int nshards, int rank,
+                                             const double* uniforms, int64_t b, float* totals_all, double* local_uniforms,
+                                             int32_t* status, void* stream) {
+    MB_CHECK_ARG(nshards >= 1 && nshards <= kMaxShards, "mercury_shard_select_exchange: 1..%d shards", kMaxShards);
+    MB_CHECK_ARG(rank >= 0 && rank < nshards && b >= 0, "mercury_shard_select_exchange: bad rank or draw count");
+    MB_CHECK_ARG(my_total && peer_boxes && totals_all && status && (b == 0 || (uniforms && local_uniforms)),
+                 "mercury_shard_select_exchange: null pointer");
+    select_exchange_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(my_total, reinterpret_cast<PeerBox* const*>(peer_boxes), nshards,
+                                                                             rank, uniforms, b, totals_all, local_uniforms, status);
+    MB_CHECK_LAUNCH("select_exchange_kernel");
+    return MERCURY_OK;
+}
 
 extern "C" int mercury_sum_scores(const float* scores, int64_t n, double* out_sum, void* ws, size_t ws_bytes, void* stream) {
     MB_CHECK_ARG(n >= 1 && scores && out_sum, "mercury_sum_scores: bad arguments");

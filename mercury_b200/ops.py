@@ -69,6 +69,8 @@ def check_status(status: torch.Tensor) -> None:
         raise RuntimeError("invalid multinomial distribution (encountering probability entry = infinity or NaN)")
     if bits & _lib.ST_ZERO_SUM:
         raise RuntimeError("invalid multinomial distribution (sum of probabilities <= 0)")
+    if bits & _lib.ST_PEER_TIMEOUT:
+        raise RuntimeError("mercury_b200: a peer's exchange word did not arrive within 4 s (ranks out of step?)")
     if bits & _lib.ST_TOPK_TIES:
         raise RuntimeError("mercury_b200: too many exactly tied keys at the k-th place of the exponential race")
 
@@ -397,6 +399,35 @@ def shard_select(shard_totals: torch.Tensor, rank: int, uniforms: torch.Tensor, 
         out = torch.empty_like(uniforms)
     _lib.check(_lib.load().mercury_shard_select(shard_totals.data_ptr(), shard_totals.numel(), int(rank), uniforms.data_ptr(),
                                                 uniforms.numel(), out.data_ptr(), _stream()))
+    return out
+
+
+def sum_scores_exchange(scores: torch.Tensor, peer_boxes: torch.Tensor, rank: int, sums_all: torch.Tensor,
+                        status: torch.Tensor) -> torch.Tensor:
+    """``sum_scores`` plus the all-gather of the shard sums, done by the kernel through the peers' exchange
+    boxes (``peer_boxes``: int64 device tensor of G box addresses, see sharded.PeerExchange)."""
+    _cuda(scores, "scores", torch.float32)
+    _cuda(sums_all, "sums_all", torch.float64)
+    _cuda(peer_boxes, "peer_boxes", torch.int64)
+    lib = _lib.load()
+    ws = workspace(scores.device, lib.mercury_update_samples_workspace_bytes(max(scores.numel(), 1), 0))
+    _lib.check(lib.mercury_sum_scores_exchange(scores.contiguous().data_ptr(), scores.numel(), peer_boxes.data_ptr(), peer_boxes.numel(),
+                                               int(rank), sums_all.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
+    return sums_all
+
+
+def shard_select_exchange(my_total: torch.Tensor, peer_boxes: torch.Tensor, rank: int, uniforms: torch.Tensor, totals_all: torch.Tensor,
+                          status: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """All-gather of the shard chain totals through the exchange boxes, then ``shard_select``, in one kernel."""
+    _cuda(my_total, "my_total", torch.float32)
+    _cuda(totals_all, "totals_all", torch.float32)
+    _cuda(uniforms, "uniforms", torch.float64)
+    _cuda(peer_boxes, "peer_boxes", torch.int64)
+    if out is None:
+        out = torch.empty_like(uniforms)
+    _lib.check(_lib.load().mercury_shard_select_exchange(my_total.data_ptr(), peer_boxes.data_ptr(), peer_boxes.numel(), int(rank),
+                                                         uniforms.data_ptr(), uniforms.numel(), totals_all.data_ptr(), out.data_ptr(),
+                                                         status.data_ptr(), _stream()))
     return out
 
 

@@ -61,11 +61,59 @@ class CudaBackend:
     def shard_select(self, totals_all, rank, uniforms, out):
         return self.ops.shard_select(totals_all, rank, uniforms, out=out)
 
+    # ---- the two exchanges done by the kernels themselves over peer memory (PeerExchange)
+    def sum_scores_exchange(self, scores, boxes, rank, sums_all, status):
+        self.ops.sum_scores_exchange(scores, boxes, rank, sums_all, status)
+
+    def shard_select_exchange(self, my_total, boxes, rank, uniforms, totals_all, status, out):
+        return self.ops.shard_select_exchange(my_total, boxes, rank, uniforms, totals_all, status, out=out)
+
     def local_draw(self, scores, local_u, stats, sums_all, n_global, lo, ema_state, data, labels, index, out, status):
         out = dict(out, stats=stats)
         r = self.ops.update_samples(None, labels, local_u, ema_state, False, scores_in=scores, data=data, index=index,
                                     global_sums=sums_all, n_global=n_global, index_base=lo, draw_only=True, out=out, status=status)
         return r
+
+
+class PeerExchange:
+    """This rank's exchange box plus every peer's box mapped over CUDA IPC (NVLink / NVSwitch peer memory).
+    ``boxes`` is the int64 device tensor of G box addresses the exchange kernels take.  Set-up uses one
+    all_gather_object of the 64-byte handles; after that the per-step exchange involves no collective."""
+
+    def __init__(self, device, group=None):
+        import ctypes
+
+        lib = _lib.load()
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self._lib, self._opened = lib, []
+        box = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * _lib.PEER_HANDLE_BYTES)()
+        with torch.cuda.device(device):
+            _lib.check(lib.mercury_peer_create(ctypes.byref(box), handle))
+            self._box = box.value
+            ptrs = [self._box]
+            if self.world > 1:
+                handles = [None] * self.world
+                dist.all_gather_object(handles, bytes(handle), group=group)
+                ptrs = []
+                for g, h in enumerate(handles):
+                    if g == self.rank:
+                        ptrs.append(self._box)
+                        continue
+                    p = ctypes.c_void_p()
+                    _lib.check(lib.mercury_peer_open((ctypes.c_ubyte * _lib.PEER_HANDLE_BYTES).from_buffer_copy(h), ctypes.byref(p)))
+                    self._opened.append(p.value)
+                    ptrs.append(p.value)
+        self.boxes = torch.tensor(ptrs, dtype=torch.int64, device=device)
+
+    def close(self):
+        for p in self._opened:
+            self._lib.mercury_peer_close(p)
+        self._opened = []
+        if self._box:
+            self._lib.mercury_peer_destroy(self._box)
+            self._box = None
 
 
 def shard_bounds(n_global: int, world: int, rank: int):
@@ -82,7 +130,7 @@ class ShardedPool:
     one total each, and the draw is two-level (shard, then position) -- constant work per rank."""
 
     def __init__(self, n_local: int, device, group=None, ema_alpha: float = 0.9, smooth_alpha: float = 0.5, backend=None,
-                 mode: str = "scores"):
+                 mode: str = "scores", exchange: str = "nccl"):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -108,6 +156,12 @@ class ShardedPool:
             self.totals_all = torch.zeros(self.world, dtype=torch.float32, device=self.device)
             self.local_u = None
             self._chain_out: dict = {}
+            if exchange not in ("nccl", "peer"):
+                raise ValueError("exchange must be 'nccl' or 'peer'")
+            # "peer": the sums and totals travel by stores into the peers' mapped boxes from inside the kernels
+            self.peer = PeerExchange(self.device, group) if exchange == "peer" else None
+            self._xstatus = torch.zeros(1, dtype=torch.int32, device=self.device) if self.peer else None
+        self.exchange = exchange if mode == "totals" else "nccl"
 
     @property
     def local_scores(self) -> torch.Tensor:
@@ -126,16 +180,23 @@ class ShardedPool:
     def _update_totals(self, logits_local, labels_local, uniforms, data, index, assemble):
         b = self.backend
         b.score(logits_local, labels_local, self.local_scores)
-        b.sum_scores(self.local_scores, self.sums_all[self.rank:self.rank + 1])
-        self._all_gather_small(self.sums_all)                      # G doubles
+        if self.peer is not None:
+            b.sum_scores_exchange(self.local_scores, self.peer.boxes, self.rank, self.sums_all, self._xstatus)
+        else:
+            b.sum_scores(self.local_scores, self.sums_all[self.rank:self.rank + 1])
+            self._all_gather_small(self.sums_all)                      # G doubles
         stats, status = b.local_chain(self.local_scores, self.sums_all, self.n_global, self.ema_state, self.ema_first,
                                       self.ema_alpha, self.smooth_alpha, self._chain_out)
         self.ema_first = False
-        self.totals_all[self.rank:self.rank + 1].copy_(stats[_lib.STAT_CHAIN_TOTAL:_lib.STAT_CHAIN_TOTAL + 1])
-        self._all_gather_small(self.totals_all)                    # G floats
         if self.local_u is None or self.local_u.shape != uniforms.shape:
             self.local_u = torch.empty_like(uniforms)
-        b.shard_select(self.totals_all, self.rank, uniforms, self.local_u)
+        if self.peer is not None:
+            b.shard_select_exchange(stats[_lib.STAT_CHAIN_TOTAL:_lib.STAT_CHAIN_TOTAL + 1], self.peer.boxes, self.rank, uniforms,
+                                    self.totals_all, self._xstatus, self.local_u)
+        else:
+            self.totals_all[self.rank:self.rank + 1].copy_(stats[_lib.STAT_CHAIN_TOTAL:_lib.STAT_CHAIN_TOTAL + 1])
+            self._all_gather_small(self.totals_all)                    # G floats
+            b.shard_select(self.totals_all, self.rank, uniforms, self.local_u)
         r = b.local_draw(self.local_scores, self.local_u, stats, self.sums_all, self.n_global, self.lo, self.ema_state, data,
                          labels_local, index, self._draw_out, status)
         self._draw_out.update({k: r[k] for k in ("idx", "nprob", "seed", "data", "labels", "index") if r[k] is not None})
@@ -145,7 +206,7 @@ class ShardedPool:
                 if t is not None:
                     dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return dict(idx=r["idx"], nprob=r["nprob"], seed=r["seed"], stats=stats, status=status, data=r["data"], labels=r["labels"],
-                    index=r["index"], owned=owned, scores=self.local_scores)
+                    index=r["index"], owned=owned, scores=self.local_scores, xstatus=self._xstatus)
 
     def _all_gather_scores(self):
         if self.world == 1:

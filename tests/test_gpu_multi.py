@@ -1,0 +1,80 @@
+"""Two real GPUs, one process each (NCCL): ShardedPool(mode="totals") with the exchange done by our kernels
+over peer memory must give what the NCCL exchange gives, and both must match the two-level oracle.
+Skipped on single-GPU boxes (the world-1 version of the peer path is in test_gpu_surface.py, the host logic
+under gloo in test_sharded_gloo.py)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import mercury_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _pool(n, c, b):
+    g = torch.Generator().manual_seed(5)
+    logits = torch.randn(n, c, generator=g) * 2
+    labels = torch.randint(0, c, (n,), generator=g)
+    data = torch.rand(n, 7, generator=g)
+    u = torch.rand(b, dtype=torch.float64, generator=g)
+    return logits, labels, data, u
+
+
+def _worker(rank, world, port, n, c, b, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from mercury_b200 import ops
+    from mercury_b200.sharded import ShardedPool, shard_bounds
+
+    logits, labels, data, u = _pool(n, c, b)
+    lo, nl = shard_bounds(n, world, rank)
+    sl = slice(lo, lo + nl)
+    pools = {x: ShardedPool(nl, dev, mode="totals", exchange=x) for x in ("nccl", "peer")}
+    outs = {}
+    for x, sp in pools.items():
+        steps = []
+        for step in range(3):
+            r = sp.update_samples((logits[sl] + step).to(dev), labels[sl].to(dev), u.to(dev), data=data[sl].to(dev), assemble=True)
+            if r["xstatus"] is not None:
+                ops.check_status(r["xstatus"])
+            ops.check_status(r["status"])
+            steps.append({k: r[k].cpu() for k in ("idx", "nprob", "seed", "data", "labels", "stats")})
+        outs[x] = steps
+    ret[rank] = outs
+    dist.barrier()
+    torch.cuda.synchronize()
+    pools["peer"].peer.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_peer_exchange_two_gpus_matches_nccl_and_oracle():
+    n, c, b, world = 200000, 10, 128, 2
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, _free_port(), n, c, b, ret), nprocs=world, join=True)
+    logits, labels, data, u = _pool(n, c, b)
+    for step in range(3):
+        for k in ("idx", "nprob", "seed", "data", "labels"):
+            assert torch.equal(ret[0]["peer"][step][k], ret[0]["nccl"][step][k]), (step, k)   # peer == NCCL exchange
+            assert torch.equal(ret[0]["peer"][step][k], ret[1]["peer"][step][k]), (step, k)   # assembled on both ranks
+        st = ret[0]["peer"][step]["stats"]
+        assert torch.equal(st[:4], ret[1]["peer"][step]["stats"][:4]) and torch.equal(st[:4], ret[0]["nccl"][step]["stats"][:4])
+        losses = orc.score(logits + step, labels)
+        p = ((losses.numpy() + np.float32(st[2])).astype(np.float32) / np.float32(st[3])).astype(np.float32)
+        want = orc.sharded_draw_two_level([p[:n // 2], p[n // 2:]], u.numpy())
+        assert np.array_equal(ret[0]["peer"][step]["idx"].numpy(), want)
+        assert torch.equal(ret[0]["peer"][step]["data"], data[want])

@@ -267,3 +267,31 @@ def test_two_level_sharded_draw_matches_its_oracle():
     two = ops.update_samples(None, None, lu, torch.zeros(1, device=DEV), False, scores_in=scores[0], global_sums=su,
                              n_global=n_local, draw_only=True, out={"stats": st1.stats})
     assert torch.equal(one.idx, two.idx) and torch.equal(one.nprob, two.nprob)
+
+
+def test_peer_exchange_world1_equals_collective_path():
+    """exchange="peer" with a single rank: the kernels store into / poll their own box.  Three steps in a
+    row (both parities of the double-buffered slots, EMA carried) must equal the exchange="nccl" path."""
+    from mercury_b200 import ops
+    from mercury_b200.sharded import ShardedPool
+
+    gen = torch.Generator().manual_seed(33)
+    n, c, b = 50000, 10, 96
+    data = torch.rand(n, 5, generator=gen).to(DEV)
+    index = torch.randperm(n, generator=gen).to(DEV)
+    u = torch.rand(b, dtype=torch.float64, generator=gen).to(DEV)
+    a = ShardedPool(n, DEV, mode="totals", exchange="nccl")
+    p = ShardedPool(n, DEV, mode="totals", exchange="peer")
+    try:
+        for step in range(3):
+            logits = (torch.randn(n, c, generator=gen) * 2).to(DEV)
+            labels = torch.randint(0, c, (n,), generator=gen).to(DEV)
+            ra = a.update_samples(logits, labels, u, data=data, index=index)
+            rp = p.update_samples(logits, labels, u, data=data, index=index)
+            for k in ("idx", "nprob", "seed", "data", "labels", "index", "stats"):
+                assert torch.equal(ra[k], rp[k]), (step, k)
+            assert torch.equal(a.sums_all, p.sums_all) and torch.equal(a.totals_all, p.totals_all)
+            ops.check_status(rp["xstatus"])
+            ops.check_status(rp["status"])
+    finally:
+        p.peer.close()
