@@ -176,8 +176,8 @@ def run_reference(args, wl):
 
 
 MULTI_GPU_NOTE = {
-    "totals": "pool sharded by rank; every rank builds the exact chain of its own shard; NCCL all-gather of one fp64 sum and one "
-              "fp32 chain total per rank; two-level draw (shard by totals, then position) by the owning rank",
+    "totals": "pool sharded by rank; every rank builds the exact chain of its own shard; one fp64 sum and one fp32 chain total "
+              "per rank are exchanged; two-level draw (shard by totals, then position) by the owning rank",
     "scores": "pool sharded by rank; NCCL all-gather of scores; replicated exact CDF of the whole pool; rows gathered by their owner",
 }
 
@@ -420,7 +420,9 @@ def main():
     if rank == 0:
         # our kernels per step and rank: score, summarize (statistics folded in), spine, draw; sharded: + chunk sums, gather_owned
         # totals: score, chunk sums, sum(+exchange), summarize, spine, select(+exchange), draw; scores: + gather_owned
-        launches_per_step = 4 if world == 1 else (7 if args.shard_mode == "totals" else 6) * world
+        # totals over peer memory: score, sum+exchange, summarize, spine, select+exchange, draw (one PDL chain)
+        per_rank = 4 if world == 1 else 6 if (args.shard_mode == "scores" or exchange == "peer") else 7
+        launches_per_step = per_rank * world
         line = {
             "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",

@@ -212,6 +212,15 @@ typedef struct mercury_update_args {
     int64_t index_base;               /* added to idx[]: global position of the shard's first candidate */
     int draw_only;                    /* != 0: only draw + gather, from the boundaries / statistics that the  */
                                       /* previous call with the same workspace, scores and stats left behind  */
+    /* the whole sharded step in ONE call, exchanges over peer memory (optional; see mercury_peer_create):       */
+    /* score -> sum + exchange -> shard-local exact chain -> total exchange + shard select -> draw of the        */
+    /* uniforms that fall in this shard (others: all-zero outputs).  global_sums must be NULL, draw_only 0;      */
+    /* n_global / index_base as above.                                                                           */
+    void* const* peer_boxes;          /* DEVICE array of the n_shards exchange boxes, own box at [shard_rank]  */
+    int n_shards, shard_rank;
+    double* sums_all;                 /* out fp64 [n_shards]: every shard's sum of scores                      */
+    float* totals_all;                /* out fp32 [n_shards]: every shard's chain total                        */
+    double* local_uniforms;           /* out fp64 [b]: position inside this shard's CDF, or -1 (not mine)      */
 } mercury_update_args;
 
 size_t mercury_update_samples_workspace_bytes(int64_t n, int64_t b);

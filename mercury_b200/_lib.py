@@ -38,6 +38,8 @@ class UpdateArgs(ctypes.Structure):
         ("out_data", c_vp), ("out_labels", c_vp), ("out_index", c_vp),
         ("status", c_vp),
         ("global_sums", c_vp), ("n_global_sums", c_int), ("n_global", c_i64), ("index_base", c_i64), ("draw_only", c_int),
+        ("peer_boxes", c_vp), ("n_shards", c_int), ("shard_rank", c_int), ("sums_all", c_vp), ("totals_all", c_vp),
+        ("local_uniforms", c_vp),
     ]
 
 

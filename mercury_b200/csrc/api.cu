@@ -52,6 +52,15 @@ extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, si
                  "mercury_update_samples: sharded call needs n_global_sums >= 1, n_global >= n and no pool-size list");
     MB_CHECK_ARG(!a->global_sums || a->n <= ((int64_t)8192 * 2048), "mercury_update_samples: shard too large");
     MB_CHECK_ARG(!a->draw_only || a->scores_in, "mercury_update_samples: draw_only needs scores_in");
+    if (a->peer_boxes) {
+        MB_CHECK_ARG(!a->global_sums && !a->draw_only && a->n_bounds == 0,
+                     "mercury_update_samples: peer_boxes excludes global_sums, draw_only and a pool-size list");
+        MB_CHECK_ARG(a->n_shards >= 1 && a->n_shards <= 64 && a->shard_rank >= 0 && a->shard_rank < a->n_shards,
+                     "mercury_update_samples: 1..64 shards, rank inside");
+        MB_CHECK_ARG(a->sums_all && a->totals_all && (a->b == 0 || a->local_uniforms) && a->n_global >= a->n,
+                     "mercury_update_samples: sharded step needs sums_all, totals_all, local_uniforms and n_global >= n");
+        MB_CHECK_ARG(a->n <= ((int64_t)8192 * 2048), "mercury_update_samples: shard too large");
+    }
     const float* scores = a->scores_in;
     if (!scores) {
         MB_CHECK_ARG(a->logits && a->labels && a->scores, "mercury_update_samples: logits / labels / scores are required");

@@ -1427,9 +1427,12 @@ int pool_stats_launch(const float* scores, int64_t n, const int64_t* h_bounds, i
     return MERCURY_OK;
 }
 
+int sharded_step_launch(const mercury_update_args& a, const float* scores, const double* part, int per, void* ws, cudaStream_t st);
+
 // statistics + boundaries + draw for the whole-step entry point.  `part`/`per` are the partial
 // sums K1 produced on the way (per == 0: none, a chunk-sum pass runs instead).
 int update_tail_launch(const mercury_update_args& a, const float* scores, const double* part, int per, void* ws, cudaStream_t st) {
+    if (a.peer_boxes) return sharded_step_launch(a, scores, part, per, ws, st);
     const CdfWs w = carve(ws, a.n, true);
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
     WeightSrc src{scores, a.stats};
@@ -1653,6 +1656,8 @@ __global__ void __launch_bounds__(1024) sum_exchange_kernel(const double* __rest
     __shared__ double red[32];
     __shared__ unsigned int s_seq;
     __shared__ double s_sum;
+    pdl_wait();
+    pdl_launch_dependents();
     double acc = 0.0;
     for (int i = threadIdx.x; i < nchunks; i += 1024) acc += sums[i];
     const double t = block_sum<1024>(acc, red);
@@ -1682,6 +1687,8 @@ __global__ void __launch_bounds__(256) select_exchange_kernel(const float* __res
     __shared__ float tot[kMaxShards];
     __shared__ float cdf[kMaxShards];
     __shared__ unsigned int s_seq;
+    pdl_wait();
+    pdl_launch_dependents();
     PeerBox* mine = peers[rank];
     if (threadIdx.x == 0) s_seq = ++mine->seq_total;
     __syncthreads();
@@ -1716,6 +1723,48 @@ __global__ void __launch_bounds__(256) select_exchange_kernel(const float* __res
     }
 }
 }  // namespace
+}  // namespace mercury
+
+namespace mercury {
+// the whole sharded step behind mercury_update_samples (args.peer_boxes set): one PDL chain
+int sharded_step_launch(const mercury_update_args& a, const float* scores, const double* part, int per, void* ws, cudaStream_t st) {
+    const CdfWs w = carve(ws, a.n, true);
+    const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
+    if (per == 0) {
+        chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, a.n, w.sums, nullptr, 0);
+        MB_CHECK_LAUNCH("chunk_sums_kernel");
+        part = w.sums;
+        per = kChunk;
+    }
+    const int npart = (int)((a.n + per - 1) / per);
+    PeerBox* const* peers = reinterpret_cast<PeerBox* const*>(a.peer_boxes);
+    cudaError_t e = launch_chain(true, sum_exchange_kernel, dim3(1), dim3(1024), 0, st, part, npart, peers, a.n_shards, a.shard_rank,
+                                 a.sums_all, a.status);
+    if (e != cudaSuccess) return cuda_fail(e, "sum_exchange_kernel launch");
+    WeightSrc src{scores, a.stats};
+    FusedStats fs;
+    fs.part = part; fs.per = per; fs.npart = npart;
+    fs.ema_in = a.ema_state; fs.ema_first = a.ema_first; fs.ema_alpha = a.ema_alpha; fs.smooth_alpha = a.smooth_alpha;
+    fs.stats = a.stats;
+    fs.gsums = a.sums_all; fs.ngsums = a.n_shards; fs.n_global = a.n_global;
+    int rc = run_exact_boundaries(src, a.n, w, a.status, 1, st, &fs, a.ema_state);
+    if (rc) return rc;
+    e = launch_chain(true, select_exchange_kernel, dim3(1), dim3(256), 0, st, (const float*)(a.stats + MERCURY_STAT_CHAIN_TOTAL), peers,
+                     a.n_shards, a.shard_rank, a.uniforms, a.b, a.totals_all, a.local_uniforms, a.status);
+    if (e != cudaSuccess) return cuda_fail(e, "select_exchange_kernel launch");
+    if (a.b > 0) {
+        DrawArgs d;
+        d.n_weight = a.n_global; d.idx_base = a.index_base;
+        d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
+        d.u = a.local_uniforms; d.b = a.b;
+        d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
+        d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
+        d.out_labels = a.out_labels; d.out_index = a.out_index;
+        e = launch_chain(true, draw_kernel, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
+        if (e != cudaSuccess) return cuda_fail(e, "draw_kernel launch");
+    }
+    return MERCURY_OK;
+}
 }  // namespace mercury
 
 extern "C" int mercury_sum_scores_exchange(const float* scores, int64_t n, void* const* peer_boxes, int nshards, int rank,

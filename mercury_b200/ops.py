@@ -301,7 +301,7 @@ def update_samples(logits: Optional[torch.Tensor], labels: Optional[torch.Tensor
                    scores_in: Optional[torch.Tensor] = None, bounds: Optional[Sequence[int]] = None,
                    ignore_index: int = -100, status: Optional[torch.Tensor] = None, out: Optional[dict] = None,
                    global_sums: Optional[torch.Tensor] = None, n_global: Optional[int] = None, index_base: int = 0,
-                   draw_only: bool = False) -> UpdateResult:
+                   draw_only: bool = False, peer: Optional[dict] = None) -> UpdateResult:
     """Score -> statistics -> exact CDF -> B draws -> gather + weights + seed, in one C-ABI call.
 
     The arithmetic of Trainer.update_samples (pytorch_collab.py:102-117) on an assembled pool.
@@ -373,6 +373,13 @@ def update_samples(logits: Optional[torch.Tensor], labels: Optional[torch.Tensor
         a.global_sums, a.n_global_sums = global_sums.data_ptr(), global_sums.numel()
         a.n_global, a.index_base = int(n_global), int(index_base)
     a.draw_only = int(bool(draw_only))
+    if peer is not None:  # the whole sharded step in this one call (sharded.ShardedPool, mode "totals", exchange "peer")
+        boxes = _cuda(peer["boxes"], "peer boxes", torch.int64)
+        a.peer_boxes, a.n_shards, a.shard_rank = boxes.data_ptr(), boxes.numel(), int(peer["rank"])
+        a.sums_all = _cuda(peer["sums_all"], "sums_all", torch.float64).data_ptr()
+        a.totals_all = _cuda(peer["totals_all"], "totals_all", torch.float32).data_ptr()
+        a.local_uniforms = _cuda(peer["local_u"], "local_u", torch.float64).data_ptr()
+        a.n_global, a.index_base = int(n_global), int(index_base)
     ws = workspace(dev, lib.mercury_update_samples_workspace_bytes(n, b))
     _lib.check(lib.mercury_update_samples(ctypes.byref(a), ws.data_ptr(), ws.numel(), _stream()))
     return UpdateResult(scores=scores, stats=stats, idx=idx, nprob=nprob, seed=seed, data=out_data, labels=out_labels,

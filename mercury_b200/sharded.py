@@ -68,6 +68,13 @@ class CudaBackend:
     def shard_select_exchange(self, my_total, boxes, rank, uniforms, totals_all, status, out):
         return self.ops.shard_select_exchange(my_total, boxes, rank, uniforms, totals_all, status, out=out)
 
+    def sharded_step(self, logits, labels, uniforms, scores_out, peer, n_global, lo, ema_state, ema_first, ema_alpha, smooth_alpha,
+                     data, index, out):
+        """score -> sum+exchange -> local chain -> total exchange + select -> draw: ONE C call, one PDL chain."""
+        return self.ops.update_samples(logits, labels, uniforms, ema_state, ema_first, ema_alpha=ema_alpha, smooth_alpha=smooth_alpha,
+                                       data=data, index=index, n_global=n_global, index_base=lo, peer=peer,
+                                       out=dict(out, scores=scores_out))
+
     def local_draw(self, scores, local_u, stats, sums_all, n_global, lo, ema_state, data, labels, index, out, status):
         out = dict(out, stats=stats)
         r = self.ops.update_samples(None, labels, local_u, ema_state, False, scores_in=scores, data=data, index=index,
@@ -130,7 +137,7 @@ class ShardedPool:
     one total each, and the draw is two-level (shard, then position) -- constant work per rank."""
 
     def __init__(self, n_local: int, device, group=None, ema_alpha: float = 0.9, smooth_alpha: float = 0.5, backend=None,
-                 mode: str = "scores", exchange: str = "nccl"):
+                 mode: str = "scores", exchange: str = "nccl", fused: bool = True):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -162,6 +169,7 @@ class ShardedPool:
             self.peer = PeerExchange(self.device, group) if exchange == "peer" else None
             self._xstatus = torch.zeros(1, dtype=torch.int32, device=self.device) if self.peer else None
         self.exchange = exchange if mode == "totals" else "nccl"
+        self.fused = fused     # exchange="peer": the whole step as one C call / PDL chain (False: one call per stage)
 
     @property
     def local_scores(self) -> torch.Tensor:
@@ -179,6 +187,8 @@ class ShardedPool:
 
     def _update_totals(self, logits_local, labels_local, uniforms, data, index, assemble):
         b = self.backend
+        if self.peer is not None and self.fused and hasattr(b, "sharded_step"):
+            return self._update_totals_fused(logits_local, labels_local, uniforms, data, index, assemble)
         b.score(logits_local, labels_local, self.local_scores)
         if self.peer is not None:
             b.sum_scores_exchange(self.local_scores, self.peer.boxes, self.rank, self.sums_all, self._xstatus)
@@ -207,6 +217,21 @@ class ShardedPool:
                     dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return dict(idx=r["idx"], nprob=r["nprob"], seed=r["seed"], stats=stats, status=status, data=r["data"], labels=r["labels"],
                     index=r["index"], owned=owned, scores=self.local_scores, xstatus=self._xstatus)
+
+    def _update_totals_fused(self, logits_local, labels_local, uniforms, data, index, assemble):
+        if self.local_u is None or self.local_u.shape != uniforms.shape:
+            self.local_u = torch.empty_like(uniforms)
+        peer = dict(boxes=self.peer.boxes, rank=self.rank, sums_all=self.sums_all, totals_all=self.totals_all, local_u=self.local_u)
+        r = self.backend.sharded_step(logits_local, labels_local, uniforms, self.local_scores, peer, self.n_global, self.lo,
+                                      self.ema_state, self.ema_first, self.ema_alpha, self.smooth_alpha, data, index, self._draw_out)
+        self.ema_first = False
+        self._draw_out.update({k: r[k] for k in ("idx", "nprob", "seed", "data", "labels", "index", "stats") if r[k] is not None})
+        if assemble and self.world > 1:
+            for t in (r.idx, r.nprob, r.seed, r.data, r.labels, r.index):
+                if t is not None:
+                    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return dict(idx=r.idx, nprob=r.nprob, seed=r.seed, stats=r.stats, status=r.status, data=r.data, labels=r.labels,
+                    index=r.index, owned=self.local_u >= 0, scores=self.local_scores, xstatus=r.status)
 
     def _all_gather_scores(self):
         if self.world == 1:

@@ -43,7 +43,9 @@ def _worker(rank, world, port, n, c, b, ret):
     logits, labels, data, u = _pool(n, c, b)
     lo, nl = shard_bounds(n, world, rank)
     sl = slice(lo, lo + nl)
-    pools = {x: ShardedPool(nl, dev, mode="totals", exchange=x) for x in ("nccl", "peer")}
+    pools = {"nccl": ShardedPool(nl, dev, mode="totals", exchange="nccl"),
+             "peer": ShardedPool(nl, dev, mode="totals", exchange="peer"),                  # one C call per step
+             "peer_staged": ShardedPool(nl, dev, mode="totals", exchange="peer", fused=False)}  # one call per stage
     outs = {}
     for x, sp in pools.items():
         steps = []
@@ -58,6 +60,7 @@ def _worker(rank, world, port, n, c, b, ret):
     dist.barrier()
     torch.cuda.synchronize()
     pools["peer"].peer.close()
+    pools["peer_staged"].peer.close()
     dist.destroy_process_group()
 
 
@@ -70,6 +73,7 @@ def test_peer_exchange_two_gpus_matches_nccl_and_oracle():
     for step in range(3):
         for k in ("idx", "nprob", "seed", "data", "labels"):
             assert torch.equal(ret[0]["peer"][step][k], ret[0]["nccl"][step][k]), (step, k)   # peer == NCCL exchange
+            assert torch.equal(ret[0]["peer_staged"][step][k], ret[0]["nccl"][step][k]), (step, k)
             assert torch.equal(ret[0]["peer"][step][k], ret[1]["peer"][step][k]), (step, k)   # assembled on both ranks
         st = ret[0]["peer"][step]["stats"]
         assert torch.equal(st[:4], ret[1]["peer"][step]["stats"][:4]) and torch.equal(st[:4], ret[0]["nccl"][step]["stats"][:4])

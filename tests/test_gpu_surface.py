@@ -269,7 +269,8 @@ def test_two_level_sharded_draw_matches_its_oracle():
     assert torch.equal(one.idx, two.idx) and torch.equal(one.nprob, two.nprob)
 
 
-def test_peer_exchange_world1_equals_collective_path():
+@pytest.mark.parametrize("fused", [True, False])
+def test_peer_exchange_world1_equals_collective_path(fused):
     """exchange="peer" with a single rank: the kernels store into / poll their own box.  Three steps in a
     row (both parities of the double-buffered slots, EMA carried) must equal the exchange="nccl" path."""
     from mercury_b200 import ops
@@ -281,7 +282,7 @@ def test_peer_exchange_world1_equals_collective_path():
     index = torch.randperm(n, generator=gen).to(DEV)
     u = torch.rand(b, dtype=torch.float64, generator=gen).to(DEV)
     a = ShardedPool(n, DEV, mode="totals", exchange="nccl")
-    p = ShardedPool(n, DEV, mode="totals", exchange="peer")
+    p = ShardedPool(n, DEV, mode="totals", exchange="peer", fused=fused)
     try:
         for step in range(3):
             logits = (torch.randn(n, c, generator=gen) * 2).to(DEV)
