@@ -28,6 +28,8 @@ WORKLOADS = {
     "cfg3": dict(n=1_280_000, c=1000, dtype="bf16", b=256, payload=None, note="BASELINE configs[2]: 1.28M x 1000 bf16"),
     "cfg5": dict(n=131_072, c=32768, dtype="bf16", b=256, payload=None,
                  note="BASELINE configs[4] row shape (32k-class bf16), 128k-candidate resident slice per GPU"),
+    "cfg5shard": dict(n=1 << 21, c=32768, dtype="bf16", b=256, payload=None,
+                      note="BASELINE configs[4] at full size: one GPU's shard of the 2^24 x 32768 bf16 pool split 8 ways (137 GB resident)"),
 }
 FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md
 
@@ -123,7 +125,7 @@ def make_pool(wl, dev, seed, with_payload=True):
     return logits, labels
 
 
-def cpu_baseline(wl, budget_s=12.0, max_rows=None):
+def cpu_baseline(wl, budget_s=12.0, max_rows=None, one_thread_s=4.0):
     """The reference's own CPU arithmetic (oracle restatement on torch CPU ops), all host threads."""
     from oracle import mercury_oracle as orc
 
@@ -148,11 +150,51 @@ def cpu_baseline(wl, budget_s=12.0, max_rows=None):
         _ = orc.reweighted_loss(torch.ones(b), r["nprob"])
         reps += 1
         el = time.perf_counter() - t0
-        if el > budget_s or reps >= 200:
+        if el > budget_s or reps >= 5000:
             break
-    return {"value": rows * reps / el, "unit": "candidates/s", "cores": torch.get_num_threads(), "kind": "port",
+    one = None
+    if one_thread_s:
+        torch.set_num_threads(1)
+        t1, r1 = time.perf_counter(), 0
+        while True:
+            r = orc.update_samples_flat(x, y, b, orc.EMAverage(), generator=gen)
+            r1 += 1
+            e1 = time.perf_counter() - t1
+            if e1 > one_thread_s or r1 >= 50:
+                break
+        one = rows * r1 / e1
+        torch.set_num_threads(os.cpu_count() or 1)
+    return {"value": rows * reps / el, "unit": "candidates/s", "cores": torch.get_num_threads(), "kind": "port", "one_thread_value": one,
             "sample": f"{reps} passes over {rows} x {c} {wl['dtype']} candidates, B={b} "
                       f"({'full pool' if rows == n else 'row slice of the pool, rate per candidate'}), {el:.1f} s"}
+
+
+def library_baseline(pools, payload, index, u, b, steps=20):
+    """Stock ATen kernels on this GPU for the same step (SURVEY 8d "library" baseline): F.cross_entropy, mean,
+    EMA, normalise, torch.multinomial (Philox: not reproducible against the CPU reference), index gathers."""
+    import torch.nn.functional as F
+
+    def one(lg, lb):
+        loss = F.cross_entropy(lg.float(), lb, reduction="none")
+        w = loss + 0.5 * loss.mean()
+        p = w / w.sum()
+        idx = torch.multinomial(p, b, replacement=True)
+        nprob = p[idx] * p.numel()
+        out = (idx, nprob, (1.0 / b) / nprob, lb[idx], index[idx])
+        return out + ((payload[idx],) if payload is not None else ())
+
+    for i in range(3):
+        one(*pools[i % len(pools)])
+    torch.cuda.synchronize()
+    a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(steps):
+        one(*pools[i % len(pools)])
+    z.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(z) / steps
+    return {"value": pools[0][0].shape[0] / (ms * 1e-3), "unit": "candidates/s", "ms_per_step": ms,
+            "what": "stock ATen CUDA ops, eager, same pools (results not reproducible against the CPU reference)"}
 
 
 def run_reference(args, wl):
@@ -239,7 +281,8 @@ def main():
         row_bytes = payload[0].numel() * 4
     index = torch.arange(n, device=dev) + rank * n
     pool_bytes = n * (c * s + 8)
-    npools = args.pools or max(2, min(8, -(-(300 << 20) // pool_bytes)))  # >= 300 MB in rotation (> 126 MB L2)
+    # >= 300 MB in rotation (> 126 MB L2); a pool of tens of GB is its own L2 flush
+    npools = args.pools or (1 if pool_bytes >= (16 << 30) else max(2, min(8, -(-(300 << 20) // pool_bytes))))
     pools = [make_pool(wl, dev, seed=100 * rank + i) for i in range(npools)]
     gen = torch.Generator().manual_seed(3)
     u_host = torch.rand(b, dtype=torch.float64, generator=gen).pin_memory()
@@ -345,7 +388,7 @@ def main():
             ops.score(*pools[i % npools], status=st, out=sc)
     torch.cuda.synchronize()
     reps = max(2, -(-max(args.steps, 10) // npools))
-    if world == 1:
+    if world == 1 or os.environ.get("MERCURY_BENCH_GRAPH_NCCL", "1") == "1":
         kg = torch.cuda.CUDAGraph()
         with torch.cuda.graph(kg, stream=kstream):
             for i in range(npools):
@@ -375,7 +418,16 @@ def main():
     step_bytes = algorithmic_bytes(n, c, s, b, row_bytes)
 
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
-    lg0, lb0 = pools[0]
+    e2e_rows = n
+    if pool_bytes > (8 << 30) and world > 1:
+        raise SystemExit("bench.py: workloads with pools above 8 GB per GPU are single-GPU runs (their host path is timed on a slice)")
+    if pool_bytes > (8 << 30):
+        # a pool that does not fit pinned host memory comfortably: time the host path on a 64 Ki-row slice and
+        # report the rate per candidate (the copy dominates and is linear in the rows)
+        e2e_rows = 1 << 16
+    lg0, lb0 = pools[0][0][:e2e_rows], pools[0][1][:e2e_rows]
+    e2e_payload = payload[:e2e_rows] if payload is not None else None
+    e2e_index = index[:e2e_rows]
     h_logits = torch.empty(lg0.shape, dtype=lg0.dtype).pin_memory()
     h_labels = torch.empty(lb0.shape, dtype=lb0.dtype).pin_memory()
     h_logits.copy_(lg0)
@@ -386,6 +438,7 @@ def main():
     h_seed = torch.empty(b, dtype=torch.float32).pin_memory()
     h_stats = torch.empty(8, dtype=torch.float32).pin_memory()
     ema2 = torch.zeros(1, device=dev)
+    e2e_out = out if e2e_rows == n else {}
 
     def e2e_step(first=False):
         d_logits.copy_(h_logits, non_blocking=True)
@@ -394,7 +447,7 @@ def main():
         if world > 1:
             rr = sp.update_samples(d_logits, d_labels, d_u, data=payload, index=index, out=out)
         else:
-            rr = ops.update_samples(d_logits, d_labels, d_u, ema2, first, data=payload, index=index, out=out)
+            rr = ops.update_samples(d_logits, d_labels, d_u, ema2, first, data=e2e_payload, index=e2e_index, out=e2e_out)
         h_idx.copy_(rr["idx"], non_blocking=True)
         h_np.copy_(rr["nprob"], non_blocking=True)
         h_seed.copy_(rr["seed"], non_blocking=True)
@@ -414,7 +467,7 @@ def main():
         t = torch.tensor([e2e_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t)
-    h2d = world * (n * (c * s + 8) + b * 8)   # whole job: every rank copies its shard's logits, labels and the uniforms in
+    h2d = world * (e2e_rows * (c * s + 8) + b * 8)   # whole job: every rank copies its shard's logits, labels and the uniforms in
     d2h = world * (b * (8 + 4 + 4) + 32)      # ... and idx / N*p / seed / stats out
 
     if rank == 0:
@@ -438,11 +491,14 @@ def main():
             "roofline": {"kernel": "K1 score (mercury_score)", "bound": "hbm", "achieved": k1_gbs, "peak": peak, "unit": "GB/s",
                          "frac": k1_gbs / peak, "traffic": k1_traffic(args.workload) if world == 1 else None, "peak_source": peak_src, "ms_per_launch": k1_ms,
                          "algorithmic_bytes_per_launch": k1_bytes},
-            "e2e": {"value": total_candidates / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps},
+            "e2e": {"value": e2e_rows * world / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps,
+                    "rows_per_step": e2e_rows * world},
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks.summary(),
         }
+        if world == 1 and n * c * 4 <= (32 << 30):   # (ATen upcasts the logits: needs N*C*4 bytes of scratch)
+            line["library_baseline"] = library_baseline(pools, payload, index, u, b)
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
         print(json.dumps(line))

@@ -349,3 +349,47 @@ def test_exact_cdf_is_exact_whatever_the_phase_guesses(ops, kind, n, bias):
         lib.mercury_test_set_guess_bias(1.0)
     assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
     assert total.cpu().numpy().view(np.uint32)[0] == chain[-1:].view(np.uint32)[0]
+
+
+# ------------------------------------------------------------------------------ maximum sizes
+@pytest.mark.parametrize("kind", ["ce_like", "uniform", "lognormal_raw"])
+def test_largest_pool_2_pow_24_is_bit_exact(ops, kind):
+    """N = 2^24, the most categories torch.multinomial accepts (and BASELINE cfg5's pool size): the chain total,
+    draws from the materialised CDF and the whole-step draw must equal the serial fp32 chain."""
+    n, b = 1 << 24, 512
+    w = _weights(kind, n, seed=9)
+    chain = orc.serial_chain_f32(w.numpy())
+    ref_cdf = (chain / chain[-1]).astype(np.float32)
+    u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(4))
+    u[0], u[1] = 0.0, 1.0 - 2.0 ** -53
+    want = orc.lower_bound(ref_cdf, u.numpy())
+    cdf, total = ops.cdf(w.to(DEV), "exact")
+    assert total.cpu().numpy().view(np.uint32)[0] == chain[-1:].view(np.uint32)[0]
+    assert np.array_equal(cdf.cpu().numpy().view(np.uint32), ref_cdf.view(np.uint32))
+    got = ops.sample_with_replacement(cdf, u.to(DEV))
+    assert np.array_equal(got.cpu().numpy(), want)
+    # the whole-step entry never materialises the CDF: draw straight from the weights as precomputed scores
+    # (smooth_alpha = 0: p = w / fp64-sum(w), then the chain over p)
+    r = ops.update_samples(None, None, u.to(DEV), torch.zeros(1, device=DEV), True, smooth_alpha=0.0, scores_in=w.to(DEV))
+    ops.check_status(r.status)
+    p = (w.numpy() / np.float32(r.stats[3].item())).astype(np.float32)
+    chain_p = orc.serial_chain_f32(p)
+    want_p = orc.lower_bound((chain_p / chain_p[-1]).astype(np.float32), u.numpy())
+    assert np.array_equal(r.idx.cpu().numpy(), want_p)
+
+
+def test_score_rows_beyond_2_pow_31_elements(ops):
+    """70 000 x 32 768 bf16 = 2.3e9 logits (4.6 GB): element offsets pass 2^31; rows on both sides are checked."""
+    n, c = 70000, 32768
+    g = torch.Generator(device=DEV).manual_seed(12)
+    x = torch.empty(n, c, dtype=torch.bfloat16, device=DEV)
+    for i in range(0, n, 4096):
+        x[i:i + 4096] = (torch.randn(min(4096, n - i), c, generator=g, device=DEV) * 2).to(torch.bfloat16)
+    y = torch.randint(0, c, (n,), generator=g, device=DEV)
+    got = ops.score(x, y).cpu()
+    for lo in (0, 65536 - 300, n - 600):   # 65536 rows * 32768 = 2^31 elements
+        sl = slice(lo, lo + 600)
+        ref = orc.score(x[sl].cpu(), y[sl].cpu())
+        np.testing.assert_allclose(got[sl].numpy(), ref.numpy(), rtol=RTOL_F32, atol=ATOL_LOSS)
+    del x
+    torch.cuda.empty_cache()
