@@ -412,6 +412,22 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
     double a_lo, a_hi;
     int slot;
     if constexpr (FUSED) {
+        // the chunk's raw scores first: their latency overlaps the reduction of the partial sums below
+        float raw[kSumIPT];
+        {
+            const int base = threadIdx.x * kSumIPT;
+            const float* wp = src.w + start + base;
+            if (base + kSumIPT <= len && (reinterpret_cast<uintptr_t>(wp) & 15) == 0) {
+#pragma unroll
+                for (int k = 0; k < kSumIPT; k += 4) {
+                    const float4 v = *reinterpret_cast<const float4*>(wp + k);
+                    raw[k] = v.x; raw[k + 1] = v.y; raw[k + 2] = v.z; raw[k + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < kSumIPT; ++k) raw[k] = base + k < len ? wp[k] : 0.f;
+            }
+        }
         const int first_part = (int)(start / fs.per), parts_per_chunk = kChunk / fs.per;
         double tot = 0.0, pre = 0.0, own = 0.0;
         for (int i0 = threadIdx.x; i0 < fs.npart; i0 += 8 * kSumNT) {  // 8 loads in flight per thread
@@ -451,7 +467,11 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         }
         a_lo = (pre + (double)start * (double)shift) / (double)total;
         a_hi = a_lo + (own + (double)len * (double)shift) / (double)total;
-        load_chunk<kSumNT, kSumIPT>(WeightSrc{src.w, fs.stats}, start, len, pb, shift, total);
+        {
+            const int base = threadIdx.x * kSumIPT;
+#pragma unroll
+            for (int k = 0; k < kSumIPT; ++k) pb[k] = base + k < len ? f2b(__fdiv_rn(__fadd_rn(raw[k], shift), total)) : 0u;
+        }
         slot = -2;  // decided below: flagged chunks index `subs` directly
     } else {
         a_lo = approx[blockIdx.x]; a_hi = approx[blockIdx.x + 1];
@@ -1303,8 +1323,24 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
 #pragma unroll
         for (int i = 0; i < kDrawNT / 32; ++i) t += wcnt[i];
         if (t > len - 1) t = len - 1;
-        const int64_t pick = start + t;
-        chosen = pick;
+        chosen = start + t;
+    }
+    __syncthreads();
+    // (d) payload row: everybody issues its first loads as soon as the slot is known; the scalar outputs ride along
+    const int64_t pick = chosen;
+    const bool copy = a.data && a.out_data;
+    const unsigned char* srow = copy ? a.data + pick * a.row_bytes : nullptr;
+    unsigned char* drow = copy ? a.out_data + j * a.row_bytes : nullptr;
+    const bool vec = copy && ((reinterpret_cast<uintptr_t>(srow) | reinterpret_cast<uintptr_t>(drow) | (uintptr_t)a.row_bytes) & 15) == 0;
+    const int64_t nvec = vec ? (a.row_bytes >> 4) : 0;
+    constexpr int kAhead = 4;
+    uint4 v[kAhead];
+#pragma unroll
+    for (int k = 0; k < kAhead; ++k) {
+        const int64_t i = threadIdx.x + (int64_t)k * kDrawNT;
+        if (i < nvec) v[k] = ldg_stream(reinterpret_cast<const uint4*>(srow) + i);
+    }
+    if (threadIdx.x == 0) {
         a.idx[j] = a.idx_base + pick;
         float shift, tot2;
         a.src.prepare(shift, tot2);
@@ -1316,18 +1352,16 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
         if (a.labels && a.out_labels) a.out_labels[j] = a.labels[pick];
         if (a.index && a.out_index) a.out_index[j] = a.index[pick];
     }
-    __syncthreads();
-    // (d) payload row
-    if (a.data && a.out_data) {
-        const unsigned char* srow = a.data + chosen * a.row_bytes;
-        unsigned char* drow = a.out_data + j * a.row_bytes;
-        if (((reinterpret_cast<uintptr_t>(srow) | reinterpret_cast<uintptr_t>(drow) | (uintptr_t)a.row_bytes) & 15) == 0) {
-            const uint4* s4 = reinterpret_cast<const uint4*>(srow);
-            uint4* d4 = reinterpret_cast<uint4*>(drow);
-            for (int64_t i = threadIdx.x; i < (a.row_bytes >> 4); i += kDrawNT) d4[i] = s4[i];
-        } else {
-            for (int64_t i = threadIdx.x; i < a.row_bytes; i += kDrawNT) drow[i] = srow[i];
+    if (vec) {
+#pragma unroll
+        for (int k = 0; k < kAhead; ++k) {
+            const int64_t i = threadIdx.x + (int64_t)k * kDrawNT;
+            if (i < nvec) reinterpret_cast<uint4*>(drow)[i] = v[k];
         }
+        for (int64_t i = threadIdx.x + (int64_t)kAhead * kDrawNT; i < nvec; i += kDrawNT)
+            reinterpret_cast<uint4*>(drow)[i] = reinterpret_cast<const uint4*>(srow)[i];
+    } else if (copy) {
+        for (int64_t i = threadIdx.x; i < a.row_bytes; i += kDrawNT) drow[i] = srow[i];
     }
 }
 
