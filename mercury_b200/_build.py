@@ -31,7 +31,8 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale():
         return SO
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + sources()
+    extra = os.environ.get("MERCURY_NVCC_EXTRA", "").split()  # developer aid, e.g. -DMB_PACK_PROF=1
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + sources()
     subprocess.check_call(cmd)
     return SO
 

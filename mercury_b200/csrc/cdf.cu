@@ -369,7 +369,9 @@ static_assert(sizeof(Pack) == 3072 && offsetof(Pack, raw) % 16 == 0 && offsetof(
 // One step of a precompiled walk.  x = kind | guard phase << 8 | first sub-chunk << 20 (packs).
 //   kEvAdd   : the span is a plain increment while the running sum is in the guard phase: y (z: high word at chunk level)
 //   kEvMap   : a span with exact ties inside: 2-state map (z, w)
-//   kEvSerial: a sub-chunk to be summed in fp32: y = raw slot in the pack (0xff: fetch it)
+//   kEvSerial: a sub-chunk in which the phase may change: x also carries its guessed phase, z / w its plain increments for
+//              that phase and the next (y bits 8 / 9: not plain, exact ties inside); it is summed serially in fp32 only if
+//              neither increment keeps the sum inside its phase.  y low byte = raw slot in the pack (0xff: fetch it)
 //   kEvPack  : (chunk level) a flagged chunk: y = shared-memory slot of its pack (0xffffffff: fetch it)
 //   kEvSlow  : (chunk level) a chunk that needs the general code
 enum EvKind : uint32_t { kEvAdd = 0, kEvMap = 1, kEvSerial = 2, kEvPack = 3, kEvSlow = 4 };
@@ -428,14 +430,16 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
                 for (int k = 0; k < kSumIPT; ++k) raw[k] = base + k < len ? wp[k] : 0.f;
             }
         }
+        const float ema_prev = *fs.ema_in;  // (early: its latency hides behind the loads below)
         const int first_part = (int)(start / fs.per), parts_per_chunk = kChunk / fs.per;
         double tot = 0.0, pre = 0.0, own = 0.0;
-        for (int i0 = threadIdx.x; i0 < fs.npart; i0 += 8 * kSumNT) {  // 8 loads in flight per thread
-            double v[8];
+        constexpr int kInFlight = 16;
+        for (int i0 = threadIdx.x; i0 < fs.npart; i0 += kInFlight * kSumNT) {  // 16 loads in flight per thread
+            double v[kInFlight];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { const int i = i0 + k * kSumNT; v[k] = i < fs.npart ? fs.part[i] : 0.0; }
+            for (int k = 0; k < kInFlight; ++k) { const int i = i0 + k * kSumNT; v[k] = i < fs.npart ? fs.part[i] : 0.0; }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < kInFlight; ++k) {
                 const int i = i0 + k * kSumNT;
                 tot += v[k];
                 if (i < first_part) pre += v[k];
@@ -457,7 +461,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         }
         const float mean = (float)(tot / n_stat);
         const float a = (float)fs.ema_alpha, one_minus_a = (float)(1.0 - fs.ema_alpha);
-        const float ema = fs.ema_first ? mean : __fadd_rn(__fmul_rn(a, *fs.ema_in), __fmul_rn(one_minus_a, mean));
+        const float ema = fs.ema_first ? mean : __fadd_rn(__fmul_rn(a, ema_prev), __fmul_rn(one_minus_a, mean));
         const float shift = __fmul_rn((float)fs.smooth_alpha, ema);
         const float total = (float)(tot + n_stat * (double)shift);
         if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -618,7 +622,14 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         if (is_stop || run_start) {
             uint4 ev;
             if (run_start) ev = make_uint4(kEvAdd | ((live ? g_run : kAnyPhase) << 8) | ((uint32_t)lane << 20), inc_run, 0u, 0u);
-            else if ((fmask >> lane) & 1u) ev = make_uint4(kEvSerial | ((uint32_t)lane << 20), rank < kRawPerPack ? (uint32_t)rank : 0xffu, 0u, 0u);
+            else if ((fmask >> lane) & 1u) {
+                // a flagged sub-chunk only MIGHT hold the phase change: carry its plain increments for the guessed phase
+                // and the next, so that the walk sums it serially only when the change really falls inside
+                const Pair f0 = pk->q0[lane], f1 = pk->q1[lane];
+                ev = make_uint4(kEvSerial | (gk << 8) | ((uint32_t)lane << 20),
+                                (rank < kRawPerPack ? (uint32_t)rank : 0xffu) | (f0.d0 != f0.d1 ? 0x100u : 0u) | (f1.d0 != f1.d1 ? 0x200u : 0u),
+                                f0.d0, f1.d0);
+            }
             else ev = make_uint4(kEvMap | (gk << 8) | ((uint32_t)lane << 20), 0u, pk->q0[lane].d0, pk->q0[lane].d1);
             pk->ev[__popc(ev_m & ((1u << lane) - 1u))] = ev;
         }
@@ -701,6 +712,10 @@ __device__ __forceinline__ int next_bit(const uint32_t* words, int from) {
 
 struct SpineCtx {
     WeightSrc src; int64_t n; float shift, totalw; int lane; int* dbg; long long* dbgt;
+#ifndef MB_PACK_PROF
+#define MB_PACK_PROF 0
+#endif
+    bool prof_; long long* pacc;  // developer aid (MERCURY_SPINE_DEBUG=9): cycle accounting of the production walk
     // shared memory
     const unsigned long long* pc; const uint32_t* ce; const uint32_t* qd0; const uint32_t* qd1; const uint32_t* stopw;
     const uint8_t* slot_of; const Pack* slots; Pack* spare; uint32_t* stage;
@@ -812,9 +827,9 @@ __device__ __noinline__ uint32_t resolve_flagged(const SpineCtx& x, const Pack* 
         if ((any_m >> k) & 1u) { ++k; continue; }                   // all zeros: nothing happens
         const uint32_t g = P->e[k] & kPhaseMask;
         const int w = E == g ? 0 : (E == g + 1u ? 1 : -1);
-        if (((flag_m >> k) & 1u) || w < 0) { b = serial_sub<DBG>(x, P, c, k, b); ++k; continue; }
+        if (w < 0) { b = serial_sub<DBG>(x, P, c, k, b); ++k; continue; }
         const unsigned tie_m = w ? tie1_m : tie0_m;
-        if ((tie_m >> k) & 1u) {                                     // exact ties inside: apply the 2-state map
+        if (((tie_m | flag_m) >> k) & 1u) {                          // exact ties inside, or a possible phase change: apply the 2-state map
             const Pair q = w ? P->q1[k] : P->q0[k];
             const uint32_t Sn = apply(q, S);
             if (Sn >= kPhaseLimit) b = serial_sub<DBG>(x, P, c, k, b); else b = bits_of(E, Sn);
@@ -843,8 +858,9 @@ template <bool DBG>
 __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, int c, uint32_t b) {
     const int nev = (int)P->nev;
     uint32_t E = phase_of(b), S = b - (E << 23);
+    long long tq = (MB_PACK_PROF && x.prof_) ? clock64() : 0;
     for (int i = 0; i < nev; ++i) {
-        const uint4 ev = P->ev[i];
+        const uint4 ev = P->ev[i];  // (loading the next step ahead of time was measured: 1.2 us slower per walk)
         const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
         if (kind == kEvAdd) {
             const uint32_t Sn = S + ev.y;
@@ -853,13 +869,22 @@ __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, i
             const uint32_t Sn = S + ((S & 1u) ? ev.w : ev.z);
             if (ph == E && Sn < kPhaseLimit) { S = Sn; continue; }
         } else {
+            // (the map of a sub-chunk is exact iff the sum stays in the map's phase, i.e. iff S ends below 2^24)
+            if (ph == E && !(ev.y & 0x100u) && S + ev.z < kPhaseLimit) { S += ev.z; continue; }
+            if (ph + 1u == E && !(ev.y & 0x200u) && S + ev.w < kPhaseLimit) { S += ev.w; continue; }
+            if (MB_PACK_PROF && x.prof_) { const long long t = clock64(); x.pacc[0] += t - tq; tq = t; }
             b = serial_sub<DBG>(x, P, c, (int)(ev.x >> 20), bits_of(E, S));
             E = phase_of(b); S = b - (E << 23);
+            if (MB_PACK_PROF && x.prof_) { const long long t = clock64(); x.pacc[2] += t - tq; x.pacc[3]++; tq = t; }
             continue;
         }
         if (DBG && x.lane == 0) x.dbg[7]++;
-        return resolve_flagged<DBG>(x, P, c, bits_of(E, S), (int)(ev.x >> 20));
+        if (MB_PACK_PROF && x.prof_) { const long long t = clock64(); x.pacc[0] += t - tq; tq = t; }
+        const uint32_t rb = resolve_flagged<DBG>(x, P, c, bits_of(E, S), (int)(ev.x >> 20));
+        if (MB_PACK_PROF && x.prof_) { x.pacc[4] += clock64() - tq; x.pacc[5]++; }
+        return rb;
     }
+    if (MB_PACK_PROF && x.prof_) { x.pacc[0] += clock64() - tq; x.pacc[1] += nev; }
     return bits_of(E, S);
 }
 
@@ -951,10 +976,14 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     __shared__ int wcnt[kSpineNT / 32];
     __shared__ int carry_ev;
     __shared__ long long dbg_t[4];
-    __shared__ long long dbg_t2[4];  // cycles in serial passes, in packs (total), fetching packs
+    __shared__ long long dbg_t2[8];  // cycles in serial passes, in packs (total), fetching packs
     __shared__ int dbg_n[8];  // flagged, serial chunks, serial subs (raw at hand), serial subs (fetched), events, late packs, general walks
+    const bool prof = !DBG && debug_level == 9;   // developer aid: phase timestamps from the production kernel
+    long long pt0 = 0, pt1 = 0, pt2 = 0, ptw = 0;
+    if (prof && threadIdx.x == 0) ptw = clock64();
     pdl_wait();
     pdl_launch_dependents();
+    if (prof && threadIdx.x == 0) pt0 = clock64();
     if (DBG && debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; for (int i = 0; i < 4; ++i) dbg_t2[i] = 0; }
     // shared-memory layout
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);               // [nchunks+1] prefix of increments
@@ -1062,11 +1091,15 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     const bool use_events = nev <= kMaxEvents && nchunks < 65536;
 
     if (DBG && debug && tid == 0) dbg_t[1] = clock64();
+    if (prof && tid == 0) pt1 = clock64();
     if (warp == 0) {
         // ---- the walk (one warp; scalar logic is replicated on all lanes)
         SpineCtx x;
         x.dbg = dbg_n;
         x.dbgt = dbg_t2;
+        x.prof_ = prof; x.pacc = dbg_t2 + 0;
+        if (prof && lane == 0) for (int i = 0; i < 8; ++i) dbg_t2[i] = 0;
+        __syncwarp();
         x.src = src; x.n = n; x.lane = lane;
         src.prepare(x.shift, x.totalw);
         x.pc = pc; x.ce = ce; x.qd0 = qd0; x.qd1 = qd1; x.stopw = stopw; x.slot_of = slot_of; x.slots = slots; x.spare = spare;
@@ -1086,6 +1119,8 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             b = walk_general<DBG>(x, 0, nchunks, b);
         } else {
             uint32_t E = 0u, S = 0u;
+            long long ppack = 0;
+            int npack = 0, nsub = 0;
             for (int i = 0; i < nev; ++i) {
                 const uint4 ev = evs[i];
                 const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
@@ -1107,7 +1142,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
                 } else if (kind == kEvPack) {
                     b = bits_of(E, S);
                     if (lane == 0) start_bits[c] = b;
-                    const long long tp0 = DBG ? clock64() : 0;
+                    const long long tp0 = (DBG || prof) ? clock64() : 0;
                     const int sl = (int)slot_of[c] - 1;
                     if (DBG && debug && lane == 0) { dbg_n[0]++; if (sl < 0) dbg_n[5]++; }
                     if (sl < 0) fetch_pack<DBG>(x, c);
@@ -1119,6 +1154,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
                     if (DBG && debug > 1) b = debug_check_pack<DBG>(x, P, c, b_in, b);
                     E = phase_of(b); S = b - (E << 23);
                     if (DBG && debug && lane == 0) dbg_t2[1] += clock64() - tp0;
+                    if (prof) { ppack += clock64() - tp0; npack += 1; nsub += (int)P->nev; }
                     continue;
                 }
                 if (DBG && debug > 1 && lane == 0) printf("GENERAL step %d kind=%u ph=%u E=%u S=%u c=%d s=%d z=%u w=%u\n", i, kind, ph, E, S, c, s, ev.z, ev.w);
@@ -1129,8 +1165,12 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
                 E = phase_of(b); S = b - (E << 23);
             }
             b = bits_of(E, S);
+            if (prof && lane == 0)
+                printf("spine(prod): %d packs took %lld cycles, %d pack events | events %lld cyc | serial %lld cyc in %lld | fallbacks %lld cyc in %lld\n",
+                       npack, ppack, nsub, dbg_t2[0], dbg_t2[2], dbg_t2[3], dbg_t2[4], dbg_t2[5]);
         }
         if (DBG && debug && lane == 0) { dbg_t[2] = clock64(); dbg_n[4] = nev; }
+        if (prof && tid == 0) pt2 = clock64();
         if (lane == 0) {
             if (ema_out) *ema_out = src.stats[MERCURY_STAT_EMA];  // fused statistics: EMAverage.value for the next call
             start_bits[nchunks] = b;
@@ -1152,6 +1192,11 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             const unsigned long long base = pc[c];
             for (int k = c + lane; k < s; k += 32) start_bits[k] = bits_of(E, S + (uint32_t)(pc[k] - base));
         }
+    }
+    if (prof) {
+        __syncthreads();
+        if (tid == 0) printf("spine(prod): wait=%lld prefetch=%lld walk=%lld fill=%lld cycles, events=%d\n", pt0 - ptw, pt1 - pt0, pt2 - pt1,
+                             (long long)clock64() - pt2, nev);
     }
     if (DBG && debug) {
         __syncthreads();
@@ -1341,16 +1386,19 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
         if (i < nvec) v[k] = ldg_stream(reinterpret_cast<const uint4*>(srow) + i);
     }
     if (threadIdx.x == 0) {
-        a.idx[j] = a.idx_base + pick;
+        // all loads first (a store in between would order them one latency after the other)
+        const bool want_l = a.labels && a.out_labels, want_i = a.index && a.out_index;
+        const int64_t lab = want_l ? a.labels[pick] : 0, ind = want_i ? a.index[pick] : 0;
         float shift, tot2;
         a.src.prepare(shift, tot2);
         const float p = a.src.get(pick, shift, tot2);
         // pytorch_collab.py:116: losses_pros[idx] * N ; :137,:145: grad = (1/B) / probs
         const float np_ = __fmul_rn(p, (float)a.n_weight);
+        a.idx[j] = a.idx_base + pick;
         a.nprob[j] = np_;
         a.seed[j] = __fdiv_rn(__fdiv_rn(1.f, (float)a.b), np_);
-        if (a.labels && a.out_labels) a.out_labels[j] = a.labels[pick];
-        if (a.index && a.out_index) a.out_index[j] = a.index[pick];
+        if (want_l) a.out_labels[j] = lab;
+        if (want_i) a.out_index[j] = ind;
     }
     if (vec) {
 #pragma unroll
@@ -1426,10 +1474,10 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     }
     static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
     float* chain_total_out = fused ? fused->stats + MERCURY_STAT_CHAIN_TOTAL : nullptr;
-    if (debug) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
+    if (debug && debug != 9) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
     else {
         cudaError_t e = launch_chain(true, spine_kernel<false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
-                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, 0);
+                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
     }
     MB_CHECK_LAUNCH("spine_kernel");
