@@ -788,11 +788,14 @@ __device__ __noinline__ uint32_t serial_chunk(const SpineCtx& x, int c, uint32_t
 
 // serial pass over sub-chunk k of chunk c: raw candidates from the pack if it carries them
 template <bool DBG>
-__device__ __forceinline__ uint32_t serial_sub(const SpineCtx& x, const Pack* P, int c, int k, uint32_t b) {
+__device__ __forceinline__ uint32_t serial_sub(const SpineCtx& x, const Pack* P, int c, int k, uint32_t b, int raw_slot = -2) {
     const long long t0 = DBG ? clock64() : 0;
-    int r = -1;
+    int r = raw_slot;  // (the precompiled walk knows where the raw candidates are; -2: look them up)
+    if (r == -2) {
+        r = -1;
 #pragma unroll
-    for (int q = 0; q < kRawPerPack; ++q) if (P->rawsub[q] == k) r = q;
+        for (int q = 0; q < kRawPerPack; ++q) if (P->rawsub[q] == k) r = q;
+    }
     const uint32_t* raw;
     if (DBG && x.lane == 0) x.dbg[r >= 0 ? 2 : 3]++;
     if (r >= 0) raw = P->raw[r];
@@ -873,7 +876,7 @@ __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, i
             if (ph == E && !(ev.y & 0x100u) && S + ev.z < kPhaseLimit) { S += ev.z; continue; }
             if (ph + 1u == E && !(ev.y & 0x200u) && S + ev.w < kPhaseLimit) { S += ev.w; continue; }
             if (MB_PACK_PROF && x.prof_) { const long long t = clock64(); x.pacc[0] += t - tq; tq = t; }
-            b = serial_sub<DBG>(x, P, c, (int)(ev.x >> 20), bits_of(E, S));
+            b = serial_sub<DBG>(x, P, c, (int)(ev.x >> 20), bits_of(E, S), (ev.y & 0xffu) == 0xffu ? -1 : (int)(ev.y & 0xffu));
             E = phase_of(b); S = b - (E << 23);
             if (MB_PACK_PROF && x.prof_) { const long long t = clock64(); x.pacc[2] += t - tq; x.pacc[3]++; tq = t; }
             continue;
@@ -984,6 +987,10 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     pdl_wait();
     pdl_launch_dependents();
     if (prof && threadIdx.x == 0) pt0 = clock64();
+    // the statistics the walk may need (fallback paths) and the EMA it publishes: loaded now, used microseconds later
+    float stat_shift, stat_total;
+    src.prepare(stat_shift, stat_total);
+    const float stat_ema = (ema_out && src.stats) ? src.stats[MERCURY_STAT_EMA] : 0.f;
     if (DBG && debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; for (int i = 0; i < 4; ++i) dbg_t2[i] = 0; }
     // shared-memory layout
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);               // [nchunks+1] prefix of increments
@@ -1101,7 +1108,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
         if (prof && lane == 0) for (int i = 0; i < 8; ++i) dbg_t2[i] = 0;
         __syncwarp();
         x.src = src; x.n = n; x.lane = lane;
-        src.prepare(x.shift, x.totalw);
+        x.shift = stat_shift; x.totalw = stat_total;
         x.pc = pc; x.ce = ce; x.qd0 = qd0; x.qd1 = qd1; x.stopw = stopw; x.slot_of = slot_of; x.slots = slots; x.spare = spare;
         x.stage = stage; x.sums = sums; x.packs = packs; x.start_bits = start_bits;
         uint32_t b = 0u;  // the running sum starts at +0
@@ -1172,7 +1179,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
         if (DBG && debug && lane == 0) { dbg_t[2] = clock64(); dbg_n[4] = nev; }
         if (prof && tid == 0) pt2 = clock64();
         if (lane == 0) {
-            if (ema_out) *ema_out = src.stats[MERCURY_STAT_EMA];  // fused statistics: EMAverage.value for the next call
+            if (ema_out) *ema_out = stat_ema;  // fused statistics: EMAverage.value for the next call
             start_bits[nchunks] = b;
             const float total = b2f(b);
             *total_out = total;
