@@ -363,8 +363,11 @@ struct __align__(128) Pack {
     uint32_t pad_[3];
     uint32_t raw[kRawPerPack][kSub];  // 16-byte aligned: read with 128-bit loads
     uint4 ev[kSubsPerChunk + 1];
+    // written by the spine: exact running sum at the start of every sub-chunk (valid iff pad_[0] == 1), so that a
+    // draw landing in this chunk resolves ONE sub-chunk instead of iterating over the chunk's phase changes
+    uint32_t sb[kSubsPerChunk];
 };
-static_assert(sizeof(Pack) == 3072 && offsetof(Pack, raw) % 16 == 0 && offsetof(Pack, ev) % 16 == 0, "Pack layout");
+static_assert(sizeof(Pack) == 3200 && offsetof(Pack, raw) % 16 == 0 && offsetof(Pack, ev) % 16 == 0, "Pack layout");
 
 // One step of a precompiled walk.  x = kind | guard phase << 8 | first sub-chunk << 20 (packs).
 //   kEvAdd   : the span is a plain increment while the running sum is in the guard phase: y (z: high word at chunk level)
@@ -633,7 +636,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
             else ev = make_uint4(kEvMap | (gk << 8) | ((uint32_t)lane << 20), 0u, pk->q0[lane].d0, pk->q0[lane].d1);
             pk->ev[__popc(ev_m & ((1u << lane) - 1u))] = ev;
         }
-        if (lane == 0) pk->nev = __popc(ev_m);
+        if (lane == 0) { pk->nev = __popc(ev_m); pk->pad_[0] = 0u; }
     }
     const int my_rank = __popc(fmask & ((1u << my_sub) - 1u));
     if (((fmask >> my_sub) & 1u) && my_rank < kRawPerPack) {
@@ -861,10 +864,12 @@ template <bool DBG>
 __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, int c, uint32_t b) {
     const int nev = (int)P->nev;
     uint32_t E = phase_of(b), S = b - (E << 23);
+    Pack* Pm = const_cast<Pack*>(P);  // (a shared-memory copy; sb[] of the steps' first sub-chunks is filled in here)
     long long tq = (MB_PACK_PROF && x.prof_) ? clock64() : 0;
     for (int i = 0; i < nev; ++i) {
         const uint4 ev = P->ev[i];  // (loading the next step ahead of time was measured: 1.2 us slower per walk)
         const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
+        if (x.lane == 0) Pm->sb[ev.x >> 20] = bits_of(E, S);
         if (kind == kEvAdd) {
             const uint32_t Sn = S + ev.y;
             if ((ph == E || ph == kAnyPhase) && Sn < kPhaseLimit) { S = Sn; continue; }
@@ -888,6 +893,7 @@ __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, i
         return rb;
     }
     if (MB_PACK_PROF && x.prof_) { x.pacc[0] += clock64() - tq; x.pacc[1] += nev; }
+    if (x.lane == 0) Pm->pad_[0] = 1u;  // every step went as precompiled: the fill may derive all sub-chunk starts
     return bits_of(E, S);
 }
 
@@ -968,7 +974,7 @@ __device__ __noinline__ uint32_t debug_check_pack(const SpineCtx& x, const Pack*
 
 template <bool DBG>
 __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
-                                                         const Pack* __restrict__ packs, uint32_t* __restrict__ start_bits,
+                                                         Pack* packs, uint32_t* __restrict__ start_bits,
                                                          float* __restrict__ total_out, int32_t* status, float* ema_out, float* chain_total_out, int debug_level) {
     const int debug = DBG ? debug_level : 0;
     extern __shared__ __align__(128) unsigned char sm[];
@@ -1200,6 +1206,23 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             for (int k = c + lane; k < s; k += 32) start_bits[k] = bits_of(E, S + (uint32_t)(pc[k] - base));
         }
     }
+    // ---- sub-chunk boundaries of the packs that were walked as precompiled (one warp per pack)
+    for (int sl = warp; sl < nsl; sl += kSpineNT / 32) {
+        const Pack* P = &slots[sl];
+        if (P->pad_[0] != 1u) continue;
+        Pack* gp = packs + slot_global[sl];
+        const int pn = (int)P->nev;
+        uint32_t mine = 0u;
+        for (int i = 0; i < pn; ++i) {
+            const int k0 = (int)(P->ev[i].x >> 20), k1 = i + 1 < pn ? (int)(P->ev[i + 1].x >> 20) : kSubsPerChunk;
+            const uint32_t b0 = P->sb[k0], E = phase_of(b0), S = b0 - (E << 23);
+            // (a run of plain sub-chunks was crossed in its guessed phase: increments ps0; other steps are one sub-chunk)
+            if (lane >= k0 && lane < k1) mine = bits_of(E, S + (P->ps0[lane] - P->ps0[k0]));
+        }
+        gp->sb[lane] = mine;
+        __syncwarp();
+        if (lane == 0) gp->pad_[0] = 1u;
+    }
     if (prof) {
         __syncthreads();
         if (tid == 0) printf("spine(prod): wait=%lld prefetch=%lld walk=%lld fill=%lld cycles, events=%d\n", pt0 - ptw, pt1 - pt0, pt2 - pt1,
@@ -1315,6 +1338,7 @@ struct DrawArgs {
     int64_t idx_base;    // added to the positions written to idx[] (global position of this shard's first candidate)
     WeightSrc src; int64_t n; int nchunks;
     const uint32_t* start_bits; const float* total_ptr;
+    const Summary* sums; const Pack* packs;   // optional: sub-chunk boundaries of the flagged chunks (see Pack::sb)
     const double* u; int64_t b;
     const unsigned char* data; int64_t row_bytes; const int64_t* labels; const int64_t* index;
     int64_t* idx; float* nprob; float* seed; unsigned char* out_data; int64_t* out_labels; int64_t* out_index;
@@ -1325,6 +1349,7 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     __shared__ float cdf_s[kChunk];
     __shared__ int wcnt[kDrawNT / 32];
     __shared__ int64_t chosen;
+    __shared__ float sub_s[kSub];
     pdl_wait();
     pdl_launch_dependents();
     const int64_t j = blockIdx.x;
@@ -1357,27 +1382,65 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     for (int i = 0; i < kDrawNT / 32; ++i) chunk += wcnt[i];
     if (chunk > a.nchunks - 1) chunk = a.nchunks - 1;
     __syncthreads();
-    // (b) exact CDF of that chunk
     const int64_t start = (int64_t)chunk * kChunk;
     const int len = (int)min((int64_t)kChunk, a.n - start);
-    uint32_t pb[kDrawIPT];
-    load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
-    resolve_chunk<kDrawNT, kDrawIPT>(pb, len, a.start_bits[chunk], cdf_s, total, &rs);
-    __syncthreads();
-    // (c) slots of the chunk below u
-    cnt = 0;
-    for (int i = threadIdx.x; i < len; i += kDrawNT) cnt += ((double)cdf_s[i] < uj) ? 1 : 0;
-    cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if (lane == 0) wcnt[warp] = cnt;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int t = 0;
-#pragma unroll
-        for (int i = 0; i < kDrawNT / 32; ++i) t += wcnt[i];
-        if (t > len - 1) t = len - 1;
-        chosen = start + t;
+    // A chunk in which the running sum changes phase carries the exact sum at the start of each of its 64-candidate
+    // sub-chunks (left by the spine): find the sub-chunk, then run the reference's own loop over that one only.
+    const Pack* gp = nullptr;
+    if (a.sums) {
+        const uint32_t se = a.sums[chunk].e;
+        if (se & kFlag) {
+            gp = a.packs + a.sums[chunk].pad[0];
+            if (gp->pad_[0] != 1u) gp = nullptr;
+        }
     }
-    __syncthreads();
+    if (gp) {  // (block-uniform)
+        if (warp == 0) {
+            const uint32_t endb = lane < kSubsPerChunk - 1 ? gp->sb[lane + 1] : a.start_bits[chunk + 1];
+            int ks = __popc(__ballot_sync(0xffffffffu, (double)__fdiv_rn(b2f(endb), total) < uj));  // sub-chunks wholly below u
+            if (ks > kSubsPerChunk - 1) ks = kSubsPerChunk - 1;
+            float shift, tot2;
+            a.src.prepare(shift, tot2);
+            const int64_t i0 = start + (int64_t)ks * kSub + 2 * lane;
+            sub_s[2 * lane] = i0 < a.n ? a.src.get(i0, shift, tot2) : 0.f;
+            sub_s[2 * lane + 1] = i0 + 1 < a.n ? a.src.get(i0 + 1, shift, tot2) : 0.f;
+            const uint32_t sb0 = gp->sb[ks];
+            __syncwarp();
+            if (lane == 0) {
+                float sacc = b2f(sb0);
+                int t = 0;
+#pragma unroll 16
+                for (int i = 0; i < kSub; ++i) {
+                    sacc = __fadd_rn(sacc, sub_s[i]);
+                    t += ((double)__fdiv_rn(sacc, total) < uj) ? 1 : 0;
+                }
+                t += ks * kSub;
+                if (t > len - 1) t = len - 1;
+                chosen = start + t;
+            }
+        }
+        __syncthreads();
+    } else {
+        // (b) exact CDF of that chunk
+        uint32_t pb[kDrawIPT];
+        load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
+        resolve_chunk<kDrawNT, kDrawIPT>(pb, len, a.start_bits[chunk], cdf_s, total, &rs);
+        __syncthreads();
+        // (c) slots of the chunk below u
+        cnt = 0;
+        for (int i = threadIdx.x; i < len; i += kDrawNT) cnt += ((double)cdf_s[i] < uj) ? 1 : 0;
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0) wcnt[warp] = cnt;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+#pragma unroll
+            for (int i = 0; i < kDrawNT / 32; ++i) t += wcnt[i];
+            if (t > len - 1) t = len - 1;
+            chosen = start + t;
+        }
+        __syncthreads();
+    }
     // (d) payload row: everybody issues its first loads as soon as the slot is known; the scalar outputs ride along
     const int64_t pick = chosen;
     const bool copy = a.data && a.out_data;
@@ -1484,7 +1547,7 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     if (debug && debug != 9) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
     else {
         cudaError_t e = launch_chain(true, spine_kernel<false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
-                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
+                                     w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
     }
     MB_CHECK_LAUNCH("spine_kernel");
@@ -1552,6 +1615,7 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
         DrawArgs d;
         d.n_weight = a.global_sums ? a.n_global : a.n; d.idx_base = a.global_sums ? a.index_base : 0;
         d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
+        d.sums = w.summaries; d.packs = w.subs;
         d.u = a.uniforms; d.b = a.b;
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
@@ -1845,6 +1909,7 @@ int sharded_step_launch(const mercury_update_args& a, const float* scores, const
         DrawArgs d;
         d.n_weight = a.n_global; d.idx_base = a.index_base;
         d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
+        d.sums = w.summaries; d.packs = w.subs;
         d.u = a.local_uniforms; d.b = a.b;
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);

@@ -94,24 +94,41 @@ class PeerExchange:
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self._lib, self._opened = lib, []
-        box = ctypes.c_void_p()
-        handle = (ctypes.c_ubyte * _lib.PEER_HANDLE_BYTES)()
+        self._box = None
+        err = None
+        handle_bytes = None
         with torch.cuda.device(device):
-            _lib.check(lib.mercury_peer_create(ctypes.byref(box), handle))
-            self._box = box.value
+            try:
+                box = ctypes.c_void_p()
+                handle = (ctypes.c_ubyte * _lib.PEER_HANDLE_BYTES)()
+                _lib.check(lib.mercury_peer_create(ctypes.byref(box), handle))
+                self._box = box.value
+                handle_bytes = bytes(handle)
+            except Exception as e:  # noqa: BLE001 -- still take part in the collective below, then report
+                err = e
             ptrs = [self._box]
             if self.world > 1:
                 handles = [None] * self.world
-                dist.all_gather_object(handles, bytes(handle), group=group)
+                dist.all_gather_object(handles, handle_bytes, group=group)
+                if err is None and any(h is None for h in handles):
+                    err = RuntimeError("mercury_b200: a peer could not create its exchange box")
                 ptrs = []
                 for g, h in enumerate(handles):
+                    if err is not None:
+                        break
                     if g == self.rank:
                         ptrs.append(self._box)
                         continue
-                    p = ctypes.c_void_p()
-                    _lib.check(lib.mercury_peer_open((ctypes.c_ubyte * _lib.PEER_HANDLE_BYTES).from_buffer_copy(h), ctypes.byref(p)))
-                    self._opened.append(p.value)
-                    ptrs.append(p.value)
+                    try:
+                        p = ctypes.c_void_p()
+                        _lib.check(lib.mercury_peer_open((ctypes.c_ubyte * _lib.PEER_HANDLE_BYTES).from_buffer_copy(h), ctypes.byref(p)))
+                        self._opened.append(p.value)
+                        ptrs.append(p.value)
+                    except Exception as e:  # noqa: BLE001
+                        err = e
+            if err is not None:
+                self.close()
+                raise err
         self.boxes = torch.tensor(ptrs, dtype=torch.int64, device=device)
 
     def close(self):

@@ -393,3 +393,27 @@ def test_score_rows_beyond_2_pow_31_elements(ops):
         np.testing.assert_allclose(got[sl].numpy(), ref.numpy(), rtol=RTOL_F32, atol=ATOL_LOSS)
     del x
     torch.cuda.empty_cache()
+
+
+@pytest.mark.parametrize("n", [100, 6250, 50000, 1000000, 3000001])
+def test_whole_step_draws_cover_every_chunk(ops, n):
+    """Many draws (incl. u = 0 and u -> 1) so that every kind of chunk is hit: the first chunks, where the running
+    sum changes binade many times (sub-chunk boundaries left by the spine), and plain single-binade chunks."""
+    b = 4096
+    g = torch.Generator().manual_seed(n)
+    scores = (-torch.log(torch.rand(n, generator=g) + 1e-9) * 0.7 + 0.01).float()
+    u = torch.rand(b, dtype=torch.float64, generator=g)
+    u[0], u[1], u[2] = 0.0, 1.0 - 2.0 ** -53, 1e-9
+    u[3:1000] = u[3:1000] * (5000.0 / n if n > 5000 else 1.0)          # crowd the head of the pool
+    u.clamp_(0.0, 1.0 - 2.0 ** -53)
+    r = ops.update_samples(None, None, u.to(DEV), torch.zeros(1, device=DEV), True, scores_in=scores.to(DEV))
+    ops.check_status(r.status)
+    # (the pool total is an fp64 reduction on the device, ATen's is an fp32 cascade: last-bit differences of the total are
+    # within the stated 1e-6; the draw is checked bit-exactly against the chain over the device's own probabilities)
+    mean, w, p_ref = orc.pool_stats(scores, orc.EMAverage(), 0.5)
+    np.testing.assert_allclose(float(r.stats[3]), float(w.sum()), rtol=1e-6)
+    p = ((scores.numpy() + np.float32(r.stats[2].item())).astype(np.float32) / np.float32(r.stats[3].item())).astype(np.float32)
+    assert np.array_equal(ops.normalize(scores.to(DEV), r.stats).cpu().numpy(), p)
+    want = orc.draw_with_replacement(p, u.numpy())
+    assert np.array_equal(r.idx.cpu().numpy(), want)
+    np.testing.assert_array_equal(r.nprob.cpu().numpy(), p[want] * np.float32(n))

@@ -12,7 +12,7 @@ import torch  # noqa: E402
 from mercury_b200 import ops  # noqa: E402
 
 dev = torch.device("cuda", 0)
-n, c, b = 1_000_000, 10, 128
+n, c, b = int(os.environ.get("N", "1000000")), 10, 128
 g = torch.Generator(device=dev).manual_seed(100)
 pools = []
 for i in range(3):
