@@ -363,11 +363,8 @@ struct __align__(128) Pack {
     uint32_t pad_[3];
     uint32_t raw[kRawPerPack][kSub];  // 16-byte aligned: read with 128-bit loads
     uint4 ev[kSubsPerChunk + 1];
-    // written by the spine: exact running sum at the start of every sub-chunk (valid iff pad_[0] == 1), so that a
-    // draw landing in this chunk resolves ONE sub-chunk instead of iterating over the chunk's phase changes
-    uint32_t sb[kSubsPerChunk];
 };
-static_assert(sizeof(Pack) == 3200 && offsetof(Pack, raw) % 16 == 0 && offsetof(Pack, ev) % 16 == 0, "Pack layout");
+static_assert(sizeof(Pack) == 3072 && offsetof(Pack, raw) % 16 == 0 && offsetof(Pack, ev) % 16 == 0, "Pack layout");
 
 // One step of a precompiled walk.  x = kind | guard phase << 8 | first sub-chunk << 20 (packs).
 //   kEvAdd   : the span is a plain increment while the running sum is in the guard phase: y (z: high word at chunk level)
@@ -636,7 +633,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
             else ev = make_uint4(kEvMap | (gk << 8) | ((uint32_t)lane << 20), 0u, pk->q0[lane].d0, pk->q0[lane].d1);
             pk->ev[__popc(ev_m & ((1u << lane) - 1u))] = ev;
         }
-        if (lane == 0) { pk->nev = __popc(ev_m); pk->pad_[0] = 0u; }
+        if (lane == 0) pk->nev = __popc(ev_m);
     }
     const int my_rank = __popc(fmask & ((1u << my_sub) - 1u));
     if (((fmask >> my_sub) & 1u) && my_rank < kRawPerPack) {
@@ -864,12 +861,10 @@ template <bool DBG>
 __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, int c, uint32_t b) {
     const int nev = (int)P->nev;
     uint32_t E = phase_of(b), S = b - (E << 23);
-    Pack* Pm = const_cast<Pack*>(P);  // (a shared-memory copy; sb[] of the steps' first sub-chunks is filled in here)
     long long tq = (MB_PACK_PROF && x.prof_) ? clock64() : 0;
     for (int i = 0; i < nev; ++i) {
         const uint4 ev = P->ev[i];  // (loading the next step ahead of time was measured: 1.2 us slower per walk)
         const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
-        if (x.lane == 0) Pm->sb[ev.x >> 20] = bits_of(E, S);
         if (kind == kEvAdd) {
             const uint32_t Sn = S + ev.y;
             if ((ph == E || ph == kAnyPhase) && Sn < kPhaseLimit) { S = Sn; continue; }
@@ -893,7 +888,6 @@ __device__ __forceinline__ uint32_t run_pack(const SpineCtx& x, const Pack* P, i
         return rb;
     }
     if (MB_PACK_PROF && x.prof_) { x.pacc[0] += clock64() - tq; x.pacc[1] += nev; }
-    if (x.lane == 0) Pm->pad_[0] = 1u;  // every step went as precompiled: the fill may derive all sub-chunk starts
     return bits_of(E, S);
 }
 
@@ -974,7 +968,7 @@ __device__ __noinline__ uint32_t debug_check_pack(const SpineCtx& x, const Pack*
 
 template <bool DBG>
 __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
-                                                         Pack* packs, uint32_t* __restrict__ start_bits,
+                                                         const Pack* __restrict__ packs, uint32_t* __restrict__ start_bits,
                                                          float* __restrict__ total_out, int32_t* status, float* ema_out, float* chain_total_out, int debug_level) {
     const int debug = DBG ? debug_level : 0;
     extern __shared__ __align__(128) unsigned char sm[];
@@ -1206,23 +1200,6 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             for (int k = c + lane; k < s; k += 32) start_bits[k] = bits_of(E, S + (uint32_t)(pc[k] - base));
         }
     }
-    // ---- sub-chunk boundaries of the packs that were walked as precompiled (one warp per pack)
-    for (int sl = warp; sl < nsl; sl += kSpineNT / 32) {
-        const Pack* P = &slots[sl];
-        if (P->pad_[0] != 1u) continue;
-        Pack* gp = packs + slot_global[sl];
-        const int pn = (int)P->nev;
-        uint32_t mine = 0u;
-        for (int i = 0; i < pn; ++i) {
-            const int k0 = (int)(P->ev[i].x >> 20), k1 = i + 1 < pn ? (int)(P->ev[i + 1].x >> 20) : kSubsPerChunk;
-            const uint32_t b0 = P->sb[k0], E = phase_of(b0), S = b0 - (E << 23);
-            // (a run of plain sub-chunks was crossed in its guessed phase: increments ps0; other steps are one sub-chunk)
-            if (lane >= k0 && lane < k1) mine = bits_of(E, S + (P->ps0[lane] - P->ps0[k0]));
-        }
-        gp->sb[lane] = mine;
-        __syncwarp();
-        if (lane == 0) gp->pad_[0] = 1u;
-    }
     if (prof) {
         __syncthreads();
         if (tid == 0) printf("spine(prod): wait=%lld prefetch=%lld walk=%lld fill=%lld cycles, events=%d\n", pt0 - ptw, pt1 - pt0, pt2 - pt1,
@@ -1338,7 +1315,6 @@ struct DrawArgs {
     int64_t idx_base;    // added to the positions written to idx[] (global position of this shard's first candidate)
     WeightSrc src; int64_t n; int nchunks;
     const uint32_t* start_bits; const float* total_ptr;
-    const Summary* sums; const Pack* packs;   // optional: sub-chunk boundaries of the flagged chunks (see Pack::sb)
     const double* u; int64_t b;
     const unsigned char* data; int64_t row_bytes; const int64_t* labels; const int64_t* index;
     int64_t* idx; float* nprob; float* seed; unsigned char* out_data; int64_t* out_labels; int64_t* out_index;
@@ -1349,7 +1325,6 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     __shared__ float cdf_s[kChunk];
     __shared__ int wcnt[kDrawNT / 32];
     __shared__ int64_t chosen;
-    __shared__ float sub_s[kSub];
     pdl_wait();
     pdl_launch_dependents();
     const int64_t j = blockIdx.x;
@@ -1382,65 +1357,93 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     for (int i = 0; i < kDrawNT / 32; ++i) chunk += wcnt[i];
     if (chunk > a.nchunks - 1) chunk = a.nchunks - 1;
     __syncthreads();
+    // (b) the slot inside that chunk, sub-chunk by sub-chunk (64 candidates, 8 consecutive threads each).  Per round:
+    //     every sub-chunk is reduced to its map for the current phase; warp 0 scans the 32 maps from the sub-chunk at
+    //     which the exact sum is known, which gives the exact sum after every sub-chunk up to the one where the phase
+    //     changes; if u falls before that one, its sub-chunk is walked with the reference's own loop and we are done;
+    //     otherwise the sub-chunk with the phase change is walked that way and the round repeats behind it.  A chunk
+    //     in one phase takes one round; the head of the pool, where the sum doubles every few candidates, a handful
+    //     (all the early changes fall inside the first sub-chunks and cost one serial walk each, not one round each).
     const int64_t start = (int64_t)chunk * kChunk;
     const int len = (int)min((int64_t)kChunk, a.n - start);
-    // A chunk in which the running sum changes phase carries the exact sum at the start of each of its 64-candidate
-    // sub-chunks (left by the spine): find the sub-chunk, then run the reference's own loop over that one only.
-    const Pack* gp = nullptr;
-    if (a.sums) {
-        const uint32_t se = a.sums[chunk].e;
-        if (se & kFlag) {
-            gp = a.packs + a.sums[chunk].pad[0];
-            if (gp->pad_[0] != 1u) gp = nullptr;
-        }
+    uint32_t pb[kDrawIPT];
+    load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
+    uint32_t bits = a.start_bits[chunk];
+    float* pv = cdf_s;                       // the chunk's probabilities, for the serial walks
+    Pair* subm = rs.tot;                     // [32] one map per sub-chunk
+    {
+        const int base = threadIdx.x * kDrawIPT;
+#pragma unroll
+        for (int k = 0; k < kDrawIPT; ++k) pv[base + k] = b2f(pb[k]);
     }
-    if (gp) {  // (block-uniform)
+    int cur = 0;                             // the exact sum `bits` is the one before sub-chunk `cur`
+    for (;;) {                               // (block-uniform control flow: decisions travel through rs)
+        const uint32_t E = phase_of(bits), S = bits - (E << 23);
+        Pair m = identity_pair();
+#pragma unroll
+        for (int k = 0; k < kDrawIPT; ++k) m = compose(m, addend_pair_fast(pb[k], E));
+#pragma unroll
+        for (int off = 1; off < 8; off <<= 1) {
+            Pair o;
+            o.d0 = __shfl_down_sync(0xffffffffu, m.d0, off, 8); o.d1 = __shfl_down_sync(0xffffffffu, m.d1, off, 8);
+            if ((lane & 7) + off < 8) m = compose(m, o);
+        }
+        if ((lane & 7) == 0) subm[threadIdx.x >> 3] = m;
+        __syncthreads();
         if (warp == 0) {
-            const uint32_t endb = lane < kSubsPerChunk - 1 ? gp->sb[lane + 1] : a.start_bits[chunk + 1];
-            int ks = __popc(__ballot_sync(0xffffffffu, (double)__fdiv_rn(b2f(endb), total) < uj));  // sub-chunks wholly below u
-            if (ks > kSubsPerChunk - 1) ks = kSubsPerChunk - 1;
-            float shift, tot2;
-            a.src.prepare(shift, tot2);
-            const int64_t i0 = start + (int64_t)ks * kSub + 2 * lane;
-            sub_s[2 * lane] = i0 < a.n ? a.src.get(i0, shift, tot2) : 0.f;
-            sub_s[2 * lane + 1] = i0 + 1 < a.n ? a.src.get(i0 + 1, shift, tot2) : 0.f;
-            const uint32_t sb0 = gp->sb[ks];
-            __syncwarp();
-            if (lane == 0) {
-                float sacc = b2f(sb0);
-                int t = 0;
+            const Pair mine = lane >= cur ? subm[lane] : identity_pair();
+            const Pair inc = warp_scan_pair(mine, lane);
+            const uint32_t s_out = apply(inc, S);                                 // state after sub-chunk `lane` ...
+            const unsigned over = __ballot_sync(0xffffffffu, lane >= cur && s_out >= kPhaseLimit);
+            const int f = over ? __ffs(over) - 1 : kSubsPerChunk;                 // ... exact for lane < f
+            const bool reach = lane >= cur && lane < f && !((double)__fdiv_rn(b2f(bits_of(E, s_out)), total) < uj);
+            const unsigned hit = __ballot_sync(0xffffffffu, reach);
+            int target = -1;                 // sub-chunk to walk serially
+            bool final_walk = false;
+            if (hit) { target = __ffs(hit) - 1; final_walk = true; }
+            else if (f < kSubsPerChunk) target = f;
+            if (target < 0) {                // every sub-chunk ends below u (only the clamped last chunk): last slot
+                if (lane == 0) { rs.cross = len - 1; rs.next_bits = 0u; rs.end_bits = 1u; }
+            } else {
+                const uint32_t s_prev = __shfl_sync(0xffffffffu, s_out, target > 0 ? target - 1 : 0);
+                const uint32_t b_in = bits_of(E, target > cur ? s_prev : S);
+                // the reference's loop over the 64 candidates; prefix values are kept for the count below
+                float acc = b2f(b_in);
+                const float* v = pv + target * kSub;
+                float pre0 = 0.f, pre1 = 0.f;
 #pragma unroll 16
                 for (int i = 0; i < kSub; ++i) {
-                    sacc = __fadd_rn(sacc, sub_s[i]);
-                    t += ((double)__fdiv_rn(sacc, total) < uj) ? 1 : 0;
+                    acc = __fadd_rn(acc, v[i]);
+                    if (i == 2 * lane) pre0 = acc;
+                    if (i == 2 * lane + 1) pre1 = acc;
                 }
-                t += ks * kSub;
-                if (t > len - 1) t = len - 1;
-                chosen = start + t;
+                const uint32_t b_out = f2b(acc);
+                const int below = (((double)__fdiv_rn(pre0, total) < uj) ? 1 : 0) + (((double)__fdiv_rn(pre1, total) < uj) ? 1 : 0);
+                const int cnt_in = __reduce_add_sync(0xffffffffu, below);
+                if (final_walk || cnt_in < kSub) {           // u falls inside this sub-chunk
+                    int t = target * kSub + cnt_in;
+                    if (t > len - 1) t = len - 1;
+                    if (lane == 0) { rs.cross = t; rs.end_bits = 1u; }
+                } else if (target + 1 >= kSubsPerChunk) {    // walked the last sub-chunk and still below u: clamp
+                    if (lane == 0) { rs.cross = len - 1; rs.end_bits = 1u; }
+                } else {
+                    if (lane == 0) { rs.cross = target + 1; rs.next_bits = b_out; rs.end_bits = 0u; }
+                }
             }
         }
         __syncthreads();
-    } else {
-        // (b) exact CDF of that chunk
-        uint32_t pb[kDrawIPT];
-        load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
-        resolve_chunk<kDrawNT, kDrawIPT>(pb, len, a.start_bits[chunk], cdf_s, total, &rs);
+        const bool done = rs.end_bits != 0u;
+        const int val = rs.cross;
+        const uint32_t nb = rs.next_bits;
         __syncthreads();
-        // (c) slots of the chunk below u
-        cnt = 0;
-        for (int i = threadIdx.x; i < len; i += kDrawNT) cnt += ((double)cdf_s[i] < uj) ? 1 : 0;
-        cnt = __reduce_add_sync(0xffffffffu, cnt);
-        if (lane == 0) wcnt[warp] = cnt;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            int t = 0;
-#pragma unroll
-            for (int i = 0; i < kDrawNT / 32; ++i) t += wcnt[i];
-            if (t > len - 1) t = len - 1;
-            chosen = start + t;
+        if (done) {
+            if (threadIdx.x == 0) chosen = start + val;
+            break;
         }
-        __syncthreads();
+        cur = val;
+        bits = nb;
     }
+    __syncthreads();
     // (d) payload row: everybody issues its first loads as soon as the slot is known; the scalar outputs ride along
     const int64_t pick = chosen;
     const bool copy = a.data && a.out_data;
@@ -1547,7 +1550,7 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     if (debug && debug != 9) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
     else {
         cudaError_t e = launch_chain(true, spine_kernel<false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
-                                     w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
+                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
     }
     MB_CHECK_LAUNCH("spine_kernel");
@@ -1615,7 +1618,6 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
         DrawArgs d;
         d.n_weight = a.global_sums ? a.n_global : a.n; d.idx_base = a.global_sums ? a.index_base : 0;
         d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
-        d.sums = w.summaries; d.packs = w.subs;
         d.u = a.uniforms; d.b = a.b;
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
@@ -1909,7 +1911,6 @@ int sharded_step_launch(const mercury_update_args& a, const float* scores, const
         DrawArgs d;
         d.n_weight = a.n_global; d.idx_base = a.index_base;
         d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
-        d.sums = w.summaries; d.packs = w.subs;
         d.u = a.local_uniforms; d.b = a.b;
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
