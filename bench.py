@@ -473,8 +473,9 @@ def main():
     if rank == 0:
         # our kernels per step and rank: score, summarize (statistics folded in), spine, draw; sharded: + chunk sums, gather_owned
         # totals: score, chunk sums, sum(+exchange), summarize, spine, select(+exchange), draw; scores: + gather_owned
-        # totals over peer memory: score, sum+exchange, summarize, spine, select+exchange, draw (one PDL chain)
-        per_rank = 4 if world == 1 else 6 if (args.shard_mode == "scores" or exchange == "peer") else 7
+        # totals over peer memory: score, summarize (+ exchange of the shard sums), spine (+ publishes the chain total),
+        # draw (+ shard selection): the same four launches as on one GPU
+        per_rank = 4 if (world == 1 or exchange == "peer") else 6 if args.shard_mode == "scores" else 7
         launches_per_step = per_rank * world
         line = {
             "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,

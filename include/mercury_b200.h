@@ -213,9 +213,11 @@ typedef struct mercury_update_args {
     int draw_only;                    /* != 0: only draw + gather, from the boundaries / statistics that the  */
                                       /* previous call with the same workspace, scores and stats left behind  */
     /* the whole sharded step in ONE call, exchanges over peer memory (optional; see mercury_peer_create):       */
-    /* score -> sum + exchange -> shard-local exact chain -> total exchange + shard select -> draw of the        */
-    /* uniforms that fall in this shard (others: all-zero outputs).  global_sums must be NULL, draw_only 0;      */
-    /* n_global / index_base as above.                                                                           */
+    /* the same four kernels as on one GPU, the exchanges inside them: score -> summaries (CTA 0 stores this     */
+    /* shard's sum of scores into every peer's box, all CTAs wait for the G sums) -> spine (stores the shard's   */
+    /* chain total into every peer's box) -> draw (waits for the G totals, picks each uniform's shard, resolves  */
+    /* those of this shard; others: all-zero outputs).  global_sums must be NULL, draw_only 0; n_global /        */
+    /* index_base as above.  Ranks must call in step (see mercury_peer_create).                                  */
     void* const* peer_boxes;          /* DEVICE array of the n_shards exchange boxes, own box at [shard_rank]  */
     int n_shards, shard_rank;
     double* sums_all;                 /* out fp64 [n_shards]: every shard's sum of scores                      */

@@ -381,6 +381,59 @@ double g_guess_bias = 1.0;  // test hook (mercury_test_set_guess_bias): scales e
 constexpr int kSumNT = 256, kSumIPT = kChunk / kSumNT;
 static_assert(kSumIPT * 8 == kSub, "a sub-chunk is 8 consecutive threads");
 
+constexpr int kMaxShards = 64;
+// ---- the same two steps with the exchange inside the kernel: every rank owns one PeerBox in
+// memory its peers have mapped (CUDA IPC over NVLink / NVSwitch).  A rank stores its value, tagged
+// with the step's sequence number in the same 64-bit word, straight into slot [rank] of every
+// peer's box and then polls its OWN box until all G slots carry this step's tag: one NVLink store
+// latency instead of a collective launch.  A word is (payload32 << 32 | seq32): written by one
+// 8-byte store, so a reader never sees a payload without its tag and no fence is needed.  Slots
+// are double-buffered by the tag's parity; a rank cannot be more than one exchange ahead of a peer
+// (it needs that peer's next word to get any further).  Waits are bounded (kPeerWaitNs) and
+// report MERCURY_ST_PEER_TIMEOUT instead of hanging the device.
+struct PeerBox {
+    unsigned long long sum_hi[2][kMaxShards];
+    unsigned long long sum_lo[2][kMaxShards];
+    unsigned long long total[2][kMaxShards];
+    unsigned int seq_sum, seq_total;      // local step counters (peers never touch them)
+    unsigned int dead;                    // set by the first timed-out wait: later waits give up at once
+};
+static_assert(sizeof(PeerBox) <= MERCURY_PEER_BOX_BYTES, "PeerBox must fit the size the header promises");
+constexpr unsigned long long kPeerWaitNs = 4000000000ull;
+
+__device__ __forceinline__ void peer_store(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long peer_load(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// polls *p until its low half equals seq; false on timeout
+__device__ __forceinline__ bool peer_wait(const unsigned long long* p, unsigned int seq, unsigned long long& word,
+                                          volatile unsigned int* dead) {
+    word = peer_load(p);
+    if ((unsigned int)word == seq) return true;
+    if (*dead) return false;
+    const unsigned long long t0 = global_ns();
+    for (;;) {
+        for (int i = 0; i < 64; ++i) {
+            word = peer_load(p);
+            if ((unsigned int)word == seq) return true;
+        }
+        if (global_ns() - t0 > kPeerWaitNs) {
+            *dead = 1u;
+            return false;
+        }
+    }
+}
+
+
 // Statistics folded into the summaries (pools of up to kFusedMaxChunks chunks, one EMA update):
 // every CTA reduces the partial sums of the scores itself -- same data, same order, so all CTAs
 // agree to the bit on mean / EMA / shift / total -- which removes a single-CTA kernel from the
@@ -394,6 +447,10 @@ struct FusedStats {
     // sharded pools: this launch covers one shard, the statistics are those of the WHOLE pool --
     // gsums[0..ngsums) are the per-shard sums of scores (all-gathered), n_global the pool size
     const double* gsums; int ngsums; int64_t n_global;
+    // ... or exchanged right here through the peers' boxes (the whole sharded step as one chain of four kernels):
+    // CTA 0 pushes this shard's sum, every CTA waits for all G sums in its own box; gsums_out (fp64 [nshards]) is
+    // filled by CTA 0 for the caller
+    PeerBox* const* peers; int nshards, rank; double* gsums_out;
 };
 
 template <bool FUSED>
@@ -431,6 +488,8 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
             }
         }
         const float ema_prev = *fs.ema_in;  // (early: its latency hides behind the loads below)
+        PeerBox* const my_box = fs.peers ? fs.peers[fs.rank] : nullptr;
+        const unsigned int sum_tag = my_box ? my_box->seq_sum + 1u : 0u;  // (the spine advances seq_sum once the step's sums are in)
         const int first_part = (int)(start / fs.per), parts_per_chunk = kChunk / fs.per;
         double tot = 0.0, pre = 0.0, own = 0.0;
         constexpr int kInFlight = 16;
@@ -454,7 +513,27 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         for (int i = 0; i < kSumNT / 32; ++i) { tot += dred[0][i]; pre += dred[1][i]; own += dred[2][i]; }
         // pytorch_collab.py:109-112 -- mean, EMA (util.py:207-213), shift = alpha*ema, total = sum(s + shift)
         double n_stat = (double)n;
-        if (fs.gsums) {  // whole-pool statistics from the shard sums (same order on every rank)
+        if (my_box) {  // sharded pool, sums exchanged here: push (CTA 0), then every CTA waits for all G in its own box
+            __shared__ double gs[kMaxShards];
+            const int par = sum_tag & 1u, g = threadIdx.x;
+            if (g < fs.nshards) {
+                if (blockIdx.x == 0) {
+                    const unsigned long long bits = (unsigned long long)__double_as_longlong(tot);
+                    peer_store(&fs.peers[g]->sum_hi[par][fs.rank], (bits >> 32 << 32) | sum_tag);
+                    peer_store(&fs.peers[g]->sum_lo[par][fs.rank], (bits << 32) | sum_tag);
+                }
+                unsigned long long hi, lo;
+                const bool ok = peer_wait(&my_box->sum_hi[par][g], sum_tag, hi, &my_box->dead) &
+                                peer_wait(&my_box->sum_lo[par][g], sum_tag, lo, &my_box->dead);
+                if (!ok) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
+                gs[g] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
+                if (blockIdx.x == 0) fs.gsums_out[g] = gs[g];
+            }
+            __syncthreads();
+            tot = 0.0;
+            for (int i = 0; i < fs.nshards; ++i) tot += gs[i];   // (same order on every rank and in every CTA)
+            n_stat = (double)fs.n_global;
+        } else if (fs.gsums) {  // whole-pool statistics from the shard sums (same order on every rank)
             tot = 0.0;
             for (int i = 0; i < fs.ngsums; ++i) tot += fs.gsums[i];
             n_stat = (double)fs.n_global;
@@ -969,7 +1048,8 @@ __device__ __noinline__ uint32_t debug_check_pack(const SpineCtx& x, const Pack*
 template <bool DBG>
 __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
                                                          const Pack* __restrict__ packs, uint32_t* __restrict__ start_bits,
-                                                         float* __restrict__ total_out, int32_t* status, float* ema_out, float* chain_total_out, int debug_level) {
+                                                         float* __restrict__ total_out, int32_t* status, float* ema_out, float* chain_total_out, int debug_level,
+                                                         PeerBox* const* peers, int nshards, int rank) {
     const int debug = DBG ? debug_level : 0;
     extern __shared__ __align__(128) unsigned char sm[];
     __shared__ int nslots_s, nev_s;
@@ -991,6 +1071,9 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     float stat_shift, stat_total;
     src.prepare(stat_shift, stat_total);
     const float stat_ema = (ema_out && src.stats) ? src.stats[MERCURY_STAT_EMA] : 0.f;
+    // sharded pool with the exchange inside the chain: this kernel publishes the shard's chain total to every peer
+    PeerBox* const my_box = peers ? peers[rank] : nullptr;
+    const unsigned int total_tag = my_box ? my_box->seq_total + 1u : 0u, sum_seq = my_box ? my_box->seq_sum : 0u;
     if (DBG && debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; for (int i = 0; i < 4; ++i) dbg_t2[i] = 0; }
     // shared-memory layout
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);               // [nchunks+1] prefix of increments
@@ -1187,6 +1270,11 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             if (!(total > 0.f)) atomicOr(status, MERCURY_ST_ZERO_SUM);
             else if (isinf(total)) atomicOr(status, MERCURY_ST_NONFINITE);
         }
+        if (my_box) {
+            for (int g = lane; g < nshards; g += 32)
+                peer_store(&peers[g]->total[total_tag & 1u][rank], ((unsigned long long)b << 32) | total_tag);
+            if (lane == 0) { my_box->seq_total = total_tag; my_box->seq_sum = sum_seq + 1u; }  // (read by the draw / the next step)
+        }
     }
     __syncthreads();
     // ---- boundary values inside the additive steps (whole CTA, one warp per step)
@@ -1315,6 +1403,9 @@ struct DrawArgs {
     int64_t idx_base;    // added to the positions written to idx[] (global position of this shard's first candidate)
     WeightSrc src; int64_t n; int nchunks;
     const uint32_t* start_bits; const float* total_ptr;
+    // sharded pool with the exchange inside the chain: `u` are the GLOBAL uniforms; every CTA waits for the G chain totals
+    // in its own box, picks the shard of its uniform and goes on only if that is this rank (shard_select_kernel's arithmetic)
+    PeerBox* const* peers; int nshards, rank; float* totals_all; double* local_u; int32_t* status;
     const double* u; int64_t b;
     const unsigned char* data; int64_t row_bytes; const int64_t* labels; const int64_t* index;
     int64_t* idx; float* nprob; float* seed; unsigned char* out_data; int64_t* out_labels; int64_t* out_index;
@@ -1328,9 +1419,46 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     pdl_wait();
     pdl_launch_dependents();
     const int64_t j = blockIdx.x;
-    const double uj = a.u[j];
+    double uj = a.u[j];
     const float total = *a.total_ptr;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (a.peers) {
+        __shared__ float sh_tot[kMaxShards];
+        __shared__ double sh_u;
+        PeerBox* mine = a.peers[a.rank];
+        const unsigned int tag = mine->seq_total;   // (set by this step's spine)
+        const int g = threadIdx.x;
+        if (g < a.nshards) {
+            unsigned long long w;
+            if (!peer_wait(&mine->total[tag & 1u][g], tag, w, &mine->dead)) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
+            sh_tot[g] = __uint_as_float((unsigned int)(w >> 32));
+            if (j == 0) a.totals_all[g] = sh_tot[g];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {   // serial fp32 CDF over the shard totals, searched as ATen does (as shard_select_kernel)
+            float cs = 0.f;
+            for (int k = 0; k < a.nshards; ++k) cs = __fadd_rn(cs, sh_tot[k]);
+            float run = 0.f, lo_f = 0.f, hi_f = 0.f;
+            int k = 0;
+            for (;; ++k) {
+                lo_f = __fdiv_rn(run, cs);            // (cdf of the previous shard: run / total, 0 for the first)
+                run = __fadd_rn(run, sh_tot[k]);
+                hi_f = __fdiv_rn(run, cs);
+                if (k >= a.nshards - 1 || !((double)hi_f < uj)) break;
+            }
+            double out = -1.0;
+            if (k == a.rank) {
+                const double lo = k > 0 ? (double)lo_f : 0.0, hi = (double)hi_f;
+                out = hi > lo ? (uj - lo) / (hi - lo) : 0.0;
+                if (out < 0.0) out = 0.0;
+                if (out >= 1.0) out = 0.99999999999999989;
+            }
+            sh_u = out;
+            a.local_u[j] = out;
+        }
+        __syncthreads();
+        uj = sh_u;
+    }
     if (uj < 0.0) {  // sharded pools: this draw belongs to another shard -> all-zero outputs (summed across ranks later)
         if (threadIdx.x == 0) {
             a.idx[j] = 0; a.nprob[j] = 0.f; a.seed[j] = 0.f;
@@ -1547,10 +1675,12 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     }
     static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
     float* chain_total_out = fused ? fused->stats + MERCURY_STAT_CHAIN_TOTAL : nullptr;
-    if (debug && debug != 9) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
+    if (debug && debug != 9) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug,
+                                                                           fused ? fused->peers : nullptr, fused ? fused->nshards : 0, fused ? fused->rank : 0);
     else {
         cudaError_t e = launch_chain(true, spine_kernel<false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
-                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug);
+                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug,
+                                     fused ? fused->peers : (PeerBox* const*)nullptr, fused ? fused->nshards : 0, fused ? fused->rank : 0);
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
     }
     MB_CHECK_LAUNCH("spine_kernel");
@@ -1601,7 +1731,7 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
             part = w.sums;
             per = kChunk;
         }
-        FusedStats fs;
+        FusedStats fs{};
         fs.part = part; fs.per = per; fs.npart = (int)((a.n + per - 1) / per);
         fs.ema_in = a.ema_state; fs.ema_first = a.ema_first; fs.ema_alpha = a.ema_alpha; fs.smooth_alpha = a.smooth_alpha;
         fs.stats = a.stats;
@@ -1615,7 +1745,7 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
     }
     if (rc) return rc;
     if (a.b > 0) {
-        DrawArgs d;
+        DrawArgs d{};
         d.n_weight = a.global_sums ? a.n_global : a.n; d.idx_base = a.global_sums ? a.index_base : 0;
         d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
         d.u = a.uniforms; d.b = a.b;
@@ -1727,7 +1857,6 @@ __global__ void __launch_bounds__(1024) reduce_sums_kernel(const double* __restr
     if (threadIdx.x == 0) *out = t;
 }
 
-constexpr int kMaxShards = 64;
 // first level of the two-level draw: which shard a uniform falls in (serial fp32 CDF over the shard
 // totals, searched as ATen does), and where inside that shard's own CDF
 __global__ void __launch_bounds__(256) shard_select_kernel(const float* __restrict__ shard_totals, int nshards, int rank,
@@ -1754,57 +1883,7 @@ __global__ void __launch_bounds__(256) shard_select_kernel(const float* __restri
     }
 }
 
-// ---- the same two steps with the exchange inside the kernel: every rank owns one PeerBox in
-// memory its peers have mapped (CUDA IPC over NVLink / NVSwitch).  A rank stores its value, tagged
-// with the step's sequence number in the same 64-bit word, straight into slot [rank] of every
-// peer's box and then polls its OWN box until all G slots carry this step's tag: one NVLink store
-// latency instead of a collective launch.  A word is (payload32 << 32 | seq32): written by one
-// 8-byte store, so a reader never sees a payload without its tag and no fence is needed.  Slots
-// are double-buffered by the tag's parity; a rank cannot be more than one exchange ahead of a peer
-// (it needs that peer's next word to get any further).  Waits are bounded (kPeerWaitNs) and
-// report MERCURY_ST_PEER_TIMEOUT instead of hanging the device.
-struct PeerBox {
-    unsigned long long sum_hi[2][kMaxShards];
-    unsigned long long sum_lo[2][kMaxShards];
-    unsigned long long total[2][kMaxShards];
-    unsigned int seq_sum, seq_total;      // local step counters (peers never touch them)
-    unsigned int dead;                    // set by the first timed-out wait: later waits give up at once
-};
-static_assert(sizeof(PeerBox) <= MERCURY_PEER_BOX_BYTES, "PeerBox must fit the size the header promises");
-constexpr unsigned long long kPeerWaitNs = 4000000000ull;
-
-__device__ __forceinline__ void peer_store(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long peer_load(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-// polls *p until its low half equals seq; false on timeout
-__device__ __forceinline__ bool peer_wait(const unsigned long long* p, unsigned int seq, unsigned long long& word,
-                                          volatile unsigned int* dead) {
-    word = peer_load(p);
-    if ((unsigned int)word == seq) return true;
-    if (*dead) return false;
-    const unsigned long long t0 = global_ns();
-    for (;;) {
-        for (int i = 0; i < 64; ++i) {
-            word = peer_load(p);
-            if ((unsigned int)word == seq) return true;
-        }
-        if (global_ns() - t0 > kPeerWaitNs) {
-            *dead = 1u;
-            return false;
-        }
-    }
-}
-
+// (PeerBox and its helpers are defined near the top of this file, before FusedStats)
 __global__ void __launch_bounds__(1024) sum_exchange_kernel(const double* __restrict__ sums, int nchunks, PeerBox* const* __restrict__ peers,
                                                             int nshards, int rank, double* __restrict__ sums_all,
                                                             int32_t* __restrict__ status) {
@@ -1883,6 +1962,9 @@ __global__ void __launch_bounds__(256) select_exchange_kernel(const float* __res
 namespace mercury {
 // the whole sharded step behind mercury_update_samples (args.peer_boxes set): one PDL chain
 int sharded_step_launch(const mercury_update_args& a, const float* scores, const double* part, int per, void* ws, cudaStream_t st) {
+    // Four kernels, as on one GPU: score (done by the caller) -> summarize (pushes this shard's sum of scores, waits for all
+    // G) -> spine (publishes the shard's chain total) -> draw (waits for the G totals, picks the shard of each uniform,
+    // resolves the ones that are its own).  No kernel exists only to communicate.
     const CdfWs w = carve(ws, a.n, true);
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
     if (per == 0) {
@@ -1891,31 +1973,27 @@ int sharded_step_launch(const mercury_update_args& a, const float* scores, const
         part = w.sums;
         per = kChunk;
     }
-    const int npart = (int)((a.n + per - 1) / per);
     PeerBox* const* peers = reinterpret_cast<PeerBox* const*>(a.peer_boxes);
-    cudaError_t e = launch_chain(true, sum_exchange_kernel, dim3(1), dim3(1024), 0, st, part, npart, peers, a.n_shards, a.shard_rank,
-                                 a.sums_all, a.status);
-    if (e != cudaSuccess) return cuda_fail(e, "sum_exchange_kernel launch");
     WeightSrc src{scores, a.stats};
-    FusedStats fs;
-    fs.part = part; fs.per = per; fs.npart = npart;
+    FusedStats fs{};
+    fs.part = part; fs.per = per; fs.npart = (int)((a.n + per - 1) / per);
     fs.ema_in = a.ema_state; fs.ema_first = a.ema_first; fs.ema_alpha = a.ema_alpha; fs.smooth_alpha = a.smooth_alpha;
     fs.stats = a.stats;
-    fs.gsums = a.sums_all; fs.ngsums = a.n_shards; fs.n_global = a.n_global;
+    fs.n_global = a.n_global;
+    fs.peers = peers; fs.nshards = a.n_shards; fs.rank = a.shard_rank; fs.gsums_out = a.sums_all;
     int rc = run_exact_boundaries(src, a.n, w, a.status, 1, st, &fs, a.ema_state);
     if (rc) return rc;
-    e = launch_chain(true, select_exchange_kernel, dim3(1), dim3(256), 0, st, (const float*)(a.stats + MERCURY_STAT_CHAIN_TOTAL), peers,
-                     a.n_shards, a.shard_rank, a.uniforms, a.b, a.totals_all, a.local_uniforms, a.status);
-    if (e != cudaSuccess) return cuda_fail(e, "select_exchange_kernel launch");
     if (a.b > 0) {
-        DrawArgs d;
+        DrawArgs d{};
         d.n_weight = a.n_global; d.idx_base = a.index_base;
         d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
-        d.u = a.local_uniforms; d.b = a.b;
+        d.peers = peers; d.nshards = a.n_shards; d.rank = a.shard_rank; d.totals_all = a.totals_all; d.local_u = a.local_uniforms;
+        d.status = a.status;
+        d.u = a.uniforms; d.b = a.b;
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
         d.out_labels = a.out_labels; d.out_index = a.out_index;
-        e = launch_chain(true, draw_kernel, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
+        cudaError_t e = launch_chain(true, draw_kernel, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
         if (e != cudaSuccess) return cuda_fail(e, "draw_kernel launch");
     }
     return MERCURY_OK;
