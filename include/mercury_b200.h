@@ -187,6 +187,19 @@ int mercury_shard_select_exchange(const float* my_total, void* const* peer_boxes
                                   const double* uniforms, int64_t b, float* totals_all, double* local_uniforms,
                                   int32_t* status, void* stream);
 
+/* ---- K1 with the classifier head folded in ---------------------------------------
+ * replaces  out = self.linear(features)            pytorch_model.py:94-96 (ResNet: 512 -> num_classes)
+ *           F.cross_entropy(out, label, reduction='none')              pytorch_collab.py:102
+ * scores[i] = CE(features[i] @ weight^T + bias, labels[i]); the logits are never written.  features
+ * [n, d] fp32 or bf16 (dtype as in mercury_score), row_stride in elements, rows 16-byte aligned, d a
+ * multiple of 128; weight fp32 [c, d] row-major (nn.Linear.weight), bias fp32 [c] or NULL; 1 <= c <= 16
+ * and c * d <= 51200 (the matrix lives in shared memory): the reference's 512 -> 10 head.  Accumulation is
+ * fp32 in a fixed order that is not cuBLAS's: scores agree with the reference's to ~1e-6 absolute per unit
+ * of |logit| (tests: rtol 2e-5, atol 2e-5).  Labels as in mercury_score. */
+int mercury_score_head(const void* features, int dtype, int64_t n, int64_t d, int64_t row_stride,
+                       const float* weight, const float* bias, int64_t c, const int64_t* labels,
+                       int64_t ignore_index, float* scores, int32_t* status, void* stream);
+
 /* ---- the whole step ---------------------------------------------------------------------------
  * replaces Trainer.update_samples' arithmetic (pytorch_collab.py:102-117) on an assembled pool:
  * score -> stats -> exact CDF -> b draws from caller-supplied uniforms -> gather + weights + seed.

@@ -62,6 +62,7 @@ SIGNATURES = {
     "mercury_test_set_guess_bias": (None, [c_f64]),
     "mercury_sum_scores": (c_int, [c_vp, c_i64, c_vp, c_vp, c_sz, c_vp]),
     "mercury_shard_select": (c_int, [c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp]),
+    "mercury_score_head": (c_int, [c_vp, c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "mercury_peer_create": (c_int, [c_vp, c_vp]),
     "mercury_peer_open": (c_int, [c_vp, c_vp]),
     "mercury_peer_close": (c_int, [c_vp]),

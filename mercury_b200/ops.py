@@ -105,6 +105,33 @@ def score(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int = -100,
     return out
 
 
+def score_head(features: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], labels: torch.Tensor,
+               ignore_index: int = -100, status: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Scores straight from the penultimate features: ``F.cross_entropy(F.linear(features, weight, bias), labels,
+    reduction='none')`` without materialising the logits (pytorch_model.py:96 + pytorch_collab.py:102).
+    features [N, D] fp32/bf16 with D a multiple of 128, weight fp32 [C, D] with C <= 16 (the reference's 512 -> 10 head)."""
+    _cuda(features, "features")
+    _cuda(weight, "weight", torch.float32)
+    _cuda(labels, "labels", torch.int64)
+    if features.dim() != 2 or weight.dim() != 2 or weight.shape[1] != features.shape[1] or labels.shape != features.shape[:1]:
+        raise RuntimeError("mercury_b200.score_head: expected features [N, D], weight [C, D] and labels [N]")
+    if features.stride(1) != 1:
+        features = features.contiguous()
+    weight = weight.contiguous()
+    if bias is not None:
+        bias = _cuda(bias, "bias", torch.float32).contiguous()
+    labels = labels.contiguous()
+    n, d = features.shape
+    if status is None:
+        status = new_status(features.device)
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=features.device)
+    _lib.check(_lib.load().mercury_score_head(features.data_ptr(), _dtype_code(features), n, d, features.stride(0) if n > 1 else d,
+                                              weight.data_ptr(), _ptr(bias), weight.shape[0], labels.data_ptr(), ignore_index,
+                                              out.data_ptr(), status.data_ptr(), _stream()))
+    return out
+
+
 # -------------------------------------------------------------------------------------- stats
 def _bounds_array(bounds: Optional[Sequence[int]]):
     if not bounds:

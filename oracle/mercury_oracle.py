@@ -43,6 +43,12 @@ def score(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int = -100) 
     return F.cross_entropy(logits.float(), labels, reduction="none", ignore_index=ignore_index)
 
 
+def score_head(features: torch.Tensor, weight: torch.Tensor, bias, labels: torch.Tensor, ignore_index: int = -100) -> torch.Tensor:
+    """Score from the penultimate features: the reference's classifier head followed by its
+    scoring call -- ``self.linear(out)`` pytorch_model.py:96, then pytorch_collab.py:102.  bf16 features are upcast."""
+    return score(F.linear(features.float(), weight.float(), None if bias is None else bias.float()), labels, ignore_index)
+
+
 # --------------------------------------------------------------------------- a4
 class EMAverage:
     """util.py:200-217, restated (first update copies, then alpha*old + (1-alpha)*new)."""

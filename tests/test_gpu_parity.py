@@ -417,3 +417,62 @@ def test_whole_step_draws_cover_every_chunk(ops, n):
     want = orc.draw_with_replacement(p, u.numpy())
     assert np.array_equal(r.idx.cpu().numpy(), want)
     np.testing.assert_array_equal(r.nprob.cpu().numpy(), p[want] * np.float32(n))
+
+
+# ------------------------------------------------------------------ f4: classifier head folded into K1
+@pytest.mark.parametrize("n,d,c,dtype,bias", [
+    (1000, 512, 10, torch.float32, True),      # the reference's ResNet18 head
+    (1003, 512, 10, torch.bfloat16, True),     # ragged tail (n % 4 != 0), bf16 features
+    (1, 128, 2, torch.float32, False),
+    (257, 2048, 16, torch.float32, True),      # Bottleneck head width, padded class count == c
+    (300, 1024, 7, torch.bfloat16, False),     # c below its padded count
+    (64, 256, 3, torch.float32, True),
+])
+def test_score_head_matches_linear_then_cross_entropy(ops, n, d, c, dtype, bias):
+    g = torch.Generator().manual_seed(n + d + c)
+    x = torch.relu(torch.randn(n, d, generator=g)).to(dtype)          # post-ReLU, pooled features
+    w = torch.randn(c, d, generator=g) * (2.0 / d ** 0.5)
+    b = torch.randn(c, generator=g) * 0.1 if bias else None
+    y = torch.randint(0, c, (n,), generator=g)
+    if n > 3:
+        y[2] = -100
+    got = ops.score_head(x.to(DEV), w.to(DEV), None if b is None else b.to(DEV), y.to(DEV)).cpu()
+    ref = orc.score_head(x, w, b, y)
+    # fp32 accumulation in an order that is not the BLAS's: 2e-5 (stated in include/mercury_b200.h)
+    np.testing.assert_allclose(got.numpy(), ref.numpy(), rtol=2e-5, atol=2e-5)
+    ref64 = F.cross_entropy(F.linear(x.double(), w.double(), None if b is None else b.double()), y, reduction="none")
+    np.testing.assert_allclose(got.numpy(), ref64.numpy(), rtol=2e-5, atol=2e-5)
+    if n > 3:
+        assert got[2] == 0.0
+    # same scores as K1 on the materialised logits (to the same tolerance), same bad-label behaviour
+    logits = F.linear(x.float(), w, b)
+    np.testing.assert_allclose(got.numpy(), ops.score(logits.to(DEV), y.to(DEV)).cpu().numpy(), rtol=2e-5, atol=2e-5)
+    y_bad = y.clone()
+    y_bad[0] = c
+    st = ops.new_status(DEV)
+    ops.score_head(x.to(DEV), w.to(DEV), None, y_bad.to(DEV), status=st)
+    with pytest.raises(IndexError):
+        ops.check_status(st)
+
+
+def test_score_head_on_the_reference_resnet18_head(ops):
+    """The reference's own model: ResNet18(10).linear applied to its pooled features (pytorch_model.py:94-96)."""
+    import importlib.util
+    import sys
+    ref_model = os.path.join("/root/reference", "pytorch_model.py")
+    torch.manual_seed(0)
+    if os.path.exists(ref_model):       # (only in the build container; the GPU box has no /root/reference)
+        spec = importlib.util.spec_from_file_location("ref_pytorch_model", ref_model)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules["ref_pytorch_model"] = mod
+        spec.loader.exec_module(mod)
+        lin = mod.ResNet18(10).linear
+    else:
+        lin = torch.nn.Linear(512, 10)  # the same layer: nn.Linear(512 * expansion, num_classes)
+    g = torch.Generator().manual_seed(1)
+    feats = torch.relu(torch.randn(5000, 512, generator=g))
+    y = torch.randint(0, 10, (5000,), generator=g)
+    with torch.no_grad():
+        ref = F.cross_entropy(lin(feats), y, reduction="none")
+    got = ops.score_head(feats.to(DEV), lin.weight.detach().to(DEV), lin.bias.detach().to(DEV), y.to(DEV)).cpu()
+    np.testing.assert_allclose(got.numpy(), ref.numpy(), rtol=2e-5, atol=2e-5)

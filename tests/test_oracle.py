@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from oracle import c_oracle
 from oracle import mercury_oracle as orc
@@ -181,3 +182,21 @@ def test_ema_matches_reference_definition():
     assert float(e.value) == 2.0
     e.update(torch.tensor(4.0))
     np.testing.assert_allclose(float(e.value), 0.9 * 2.0 + 0.1 * 4.0, rtol=1e-6)
+
+
+def test_score_head_is_linear_then_cross_entropy():
+    """f4: the fused-head oracle is the reference's two calls, checked against fp64 and against its own ResNet head."""
+    g = torch.Generator().manual_seed(8)
+    x, w, b = torch.randn(64, 512, generator=g), torch.randn(10, 512, generator=g) * 0.05, torch.randn(10, generator=g) * 0.1
+    y = torch.randint(0, 10, (64,), generator=g)
+    got = orc.score_head(x, w, b, y)
+    ref64 = F.cross_entropy(F.linear(x.double(), w.double(), b.double()), y, reduction="none")
+    np.testing.assert_allclose(got.numpy(), ref64.numpy(), rtol=2e-5, atol=2e-5)
+    lin = torch.nn.Linear(512, 10)
+    with torch.no_grad():
+        lin.weight.copy_(w)
+        lin.bias.copy_(b)
+    assert torch.equal(got, F.cross_entropy(lin(x), y, reduction="none"))
+    y2 = y.clone()
+    y2[3] = -100
+    assert orc.score_head(x, w, None, y2)[3] == 0.0
