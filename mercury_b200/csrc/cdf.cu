@@ -453,7 +453,9 @@ struct FusedStats {
     PeerBox* const* peers; int nshards, rank; double* gsums_out;
 };
 
-template <bool FUSED>
+// PEER: sharded pool with the sums exchanged inside this kernel (a separate instantiation, so that the one-GPU kernel
+// carries none of it)
+template <bool FUSED, bool PEER = false>
 __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_t n, const double* __restrict__ approx,
                                                            const int* __restrict__ slotid, double bias,
                                                            Summary* __restrict__ out, Pack* __restrict__ subs,
@@ -488,8 +490,8 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
             }
         }
         const float ema_prev = *fs.ema_in;  // (early: its latency hides behind the loads below)
-        PeerBox* const my_box = fs.peers ? fs.peers[fs.rank] : nullptr;
-        const unsigned int sum_tag = my_box ? my_box->seq_sum + 1u : 0u;  // (the spine advances seq_sum once the step's sums are in)
+        PeerBox* const my_box = PEER ? fs.peers[fs.rank] : nullptr;
+        const unsigned int sum_tag = PEER ? my_box->seq_sum + 1u : 0u;  // (the spine advances seq_sum once the step's sums are in)
         const int first_part = (int)(start / fs.per), parts_per_chunk = kChunk / fs.per;
         double tot = 0.0, pre = 0.0, own = 0.0;
         constexpr int kInFlight = 16;
@@ -513,7 +515,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         for (int i = 0; i < kSumNT / 32; ++i) { tot += dred[0][i]; pre += dred[1][i]; own += dred[2][i]; }
         // pytorch_collab.py:109-112 -- mean, EMA (util.py:207-213), shift = alpha*ema, total = sum(s + shift)
         double n_stat = (double)n;
-        if (my_box) {  // sharded pool, sums exchanged here: push (CTA 0), then every CTA waits for all G in its own box
+        if constexpr (PEER) {  // sharded pool, sums exchanged here: push (CTA 0), then every CTA waits for all G in its own box
             __shared__ double gs[kMaxShards];
             const int par = sum_tag & 1u, g = threadIdx.x;
             if (g < fs.nshards) {
@@ -1045,7 +1047,7 @@ __device__ __noinline__ uint32_t debug_check_pack(const SpineCtx& x, const Pack*
     return b_ref;
 }
 
-template <bool DBG>
+template <bool DBG, bool PEER = false>
 __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t n, int nchunks, const Summary* __restrict__ sums,
                                                          const Pack* __restrict__ packs, uint32_t* __restrict__ start_bits,
                                                          float* __restrict__ total_out, int32_t* status, float* ema_out, float* chain_total_out, int debug_level,
@@ -1072,8 +1074,8 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
     src.prepare(stat_shift, stat_total);
     const float stat_ema = (ema_out && src.stats) ? src.stats[MERCURY_STAT_EMA] : 0.f;
     // sharded pool with the exchange inside the chain: this kernel publishes the shard's chain total to every peer
-    PeerBox* const my_box = peers ? peers[rank] : nullptr;
-    const unsigned int total_tag = my_box ? my_box->seq_total + 1u : 0u, sum_seq = my_box ? my_box->seq_sum : 0u;
+    PeerBox* const my_box = PEER ? peers[rank] : nullptr;
+    const unsigned int total_tag = PEER ? my_box->seq_total + 1u : 0u, sum_seq = PEER ? my_box->seq_sum : 0u;
     if (DBG && debug && threadIdx.x == 0) { dbg_t[0] = clock64(); for (int i = 0; i < 8; ++i) dbg_n[i] = 0; for (int i = 0; i < 4; ++i) dbg_t2[i] = 0; }
     // shared-memory layout
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);               // [nchunks+1] prefix of increments
@@ -1270,7 +1272,7 @@ __global__ void __launch_bounds__(kSpineNT) spine_kernel(WeightSrc src, int64_t 
             if (!(total > 0.f)) atomicOr(status, MERCURY_ST_ZERO_SUM);
             else if (isinf(total)) atomicOr(status, MERCURY_ST_NONFINITE);
         }
-        if (my_box) {
+        if constexpr (PEER) {
             for (int g = lane; g < nshards; g += 32)
                 peer_store(&peers[g]->total[total_tag & 1u][rank], ((unsigned long long)b << 32) | total_tag);
             if (lane == 0) { my_box->seq_total = total_tag; my_box->seq_sum = sum_seq + 1u; }  // (read by the draw / the next step)
@@ -1411,6 +1413,7 @@ struct DrawArgs {
     int64_t* idx; float* nprob; float* seed; unsigned char* out_data; int64_t* out_labels; int64_t* out_index;
 };
 
+template <bool PEER>
 __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     __shared__ ResolveSmem rs;
     __shared__ float cdf_s[kChunk];
@@ -1422,7 +1425,7 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     double uj = a.u[j];
     const float total = *a.total_ptr;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (a.peers) {
+    if constexpr (PEER) {
         __shared__ float sh_tot[kMaxShards];
         __shared__ double sh_u;
         PeerBox* mine = a.peers[a.rank];
@@ -1657,32 +1660,44 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
                          const FusedStats* fused = nullptr, float* ema_out = nullptr) {
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
     if (fused) {
-        cudaError_t e = launch_chain(true, summarize_kernel<true>, dim3(nchunks), dim3(kSumNT), 0, st, src, n, (const double*)w.approx,
-                                     (const int*)w.slotid, g_guess_bias, w.summaries, w.subs, status, check, *fused);
+        cudaError_t e = fused->peers
+            ? launch_chain(true, summarize_kernel<true, true>, dim3(nchunks), dim3(kSumNT), 0, st, src, n, (const double*)w.approx,
+                           (const int*)w.slotid, g_guess_bias, w.summaries, w.subs, status, check, *fused)
+            : launch_chain(true, summarize_kernel<true, false>, dim3(nchunks), dim3(kSumNT), 0, st, src, n, (const double*)w.approx,
+                           (const int*)w.slotid, g_guess_bias, w.summaries, w.subs, status, check, *fused);
         if (e != cudaSuccess) return cuda_fail(e, "summarize_kernel launch");
     } else {
-        summarize_kernel<false><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status,
+        summarize_kernel<false, false><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status,
                                                             check, FusedStats{});
     }
     MB_CHECK_LAUNCH("summarize_kernel");
     const size_t smem = spine_smem_bytes(nchunks);
     static bool attr_set = false;  // per process; the attribute is sticky per device function
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(spine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(spine_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
         if (e != cudaSuccess) return cuda_fail(e, "spine_kernel smem attribute");
         attr_set = true;
     }
     static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
     float* chain_total_out = fused ? fused->stats + MERCURY_STAT_CHAIN_TOTAL : nullptr;
-    if (debug && debug != 9) spine_kernel<true><<<1, kSpineNT, smem, st>>>(src, n, nchunks, w.summaries, w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug,
-                                                                           fused ? fused->peers : nullptr, fused ? fused->nshards : 0, fused ? fused->rank : 0);
-    else {
-        cudaError_t e = launch_chain(true, spine_kernel<false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
-                                     (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug,
-                                     fused ? fused->peers : (PeerBox* const*)nullptr, fused ? fused->nshards : 0, fused ? fused->rank : 0);
-        if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
+    PeerBox* const* peers = fused ? fused->peers : nullptr;
+    const int nshards = fused ? fused->nshards : 0, rank = fused ? fused->rank : 0;
+    cudaError_t e;
+    if (debug && debug != 9) {
+        e = peers ? launch_chain(false, spine_kernel<true, true>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
+                                 (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug, peers, nshards, rank)
+                  : launch_chain(false, spine_kernel<true, false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
+                                 (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug, peers, nshards, rank);
+    } else {
+        e = peers ? launch_chain(true, spine_kernel<false, true>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
+                                 (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug, peers, nshards, rank)
+                  : launch_chain(true, spine_kernel<false, false>, dim3(1), dim3(kSpineNT), smem, st, src, n, nchunks, (const Summary*)w.summaries,
+                                 (const Pack*)w.subs, w.start_bits, w.total, status, ema_out, chain_total_out, debug, peers, nshards, rank);
     }
+    if (e != cudaSuccess) return cuda_fail(e, "spine_kernel launch");
     MB_CHECK_LAUNCH("spine_kernel");
     return MERCURY_OK;
 }
@@ -1752,7 +1767,7 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
         d.out_labels = a.out_labels; d.out_index = a.out_index;
-        cudaError_t e = launch_chain(true, draw_kernel, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
+        cudaError_t e = launch_chain(true, draw_kernel<false>, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
         if (e != cudaSuccess) return cuda_fail(e, "draw_kernel launch");
     }
     return MERCURY_OK;
@@ -1993,7 +2008,7 @@ int sharded_step_launch(const mercury_update_args& a, const float* scores, const
         d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
         d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
         d.out_labels = a.out_labels; d.out_index = a.out_index;
-        cudaError_t e = launch_chain(true, draw_kernel, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
+        cudaError_t e = launch_chain(true, draw_kernel<true>, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d);
         if (e != cudaSuccess) return cuda_fail(e, "draw_kernel launch");
     }
     return MERCURY_OK;
