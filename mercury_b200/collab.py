@@ -16,6 +16,19 @@ from .pool import ResidentPool
 from .sampler import EMAverage, reweighted_mean
 
 
+def split_head(net):
+    """``(features, linear)`` for the reference's ResNets: ``features(x)`` is ResNet.forward up to the pooled activations
+    (pytorch_model.py:89-95), ``linear`` the classifier head of :96, so that presample batches can be scored with
+    ``ops.score_head(features(x), linear.weight, linear.bias, label)`` without materialising the logits."""
+    def features(x):
+        out = F.relu(net.bn1(net.conv1(x)))
+        out = net.layer4(net.layer3(net.layer2(net.layer1(out))))
+        out = F.avg_pool2d(out, 4)
+        return out.view(out.size(0), -1)
+
+    return features, net.linear
+
+
 class Trainer(object):
     POOL_BATCHES = 10  # pytorch_collab.py:95
 

@@ -200,3 +200,25 @@ def test_score_head_is_linear_then_cross_entropy():
     y2 = y.clone()
     y2[3] = -100
     assert orc.score_head(x, w, None, y2)[3] == 0.0
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/pytorch_model.py"), reason="needs the reference checkout")
+def test_split_head_reproduces_the_reference_resnet_forward():
+    import importlib.util
+    import sys
+    spec = importlib.util.spec_from_file_location("ref_pytorch_model", "/root/reference/pytorch_model.py")
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["ref_pytorch_model"] = mod
+    spec.loader.exec_module(mod)
+    from mercury_b200.collab import split_head
+
+    torch.manual_seed(0)
+    net = mod.ResNet18(10).eval()
+    x = torch.randn(6, 3, 32, 32)
+    y = torch.randint(0, 10, (6,))
+    features, lin = split_head(net)
+    with torch.no_grad():
+        f = features(x)
+        assert f.shape == (6, 512)
+        assert torch.equal(lin(f), net(x))
+        assert torch.equal(orc.score_head(f, lin.weight, lin.bias, y), F.cross_entropy(net(x), y, reduction="none"))
