@@ -51,8 +51,53 @@ __device__ __forceinline__ X4 load4<uint16_t>(const uint16_t* row, int col) {  /
 
 constexpr int kSlots = 16;  // class slots per row in the cross-warp reduction (c <= 16)
 
+// Sums the kRows x CP packed partial dot products across the warp and finishes the cross-entropy of the group's rows.
+// Reduce-scatter: 64 slots (row r, class k at r * 16 + k) halved five times -- after the step with offset o a lane keeps
+// the half selected by its bit o -- so that lane l ends with slots 2l and 2l + 1, i.e. row l >> 3, classes 2 (l & 7) and
+// the next (62 shuffles instead of 5 per accumulator); 8 lanes per row then do the log-sum-exp.
+template <int CP>
+__device__ __forceinline__ void head_finish(const u64 (&acc2)[kRows][CP], int lane, int c, float bias0, float bias1, int64_t y,
+                                            int64_t my_row, int64_t n, int64_t ignore_index, float* __restrict__ scores, int& bad) {
+    float v[kRows * kSlots];
+#pragma unroll
+    for (int r = 0; r < kRows; ++r)
+#pragma unroll
+        for (int k = 0; k < kSlots; ++k)
+            v[r * kSlots + k] = k < CP ? __uint_as_float((unsigned)acc2[r][k < CP ? k : 0]) + __uint_as_float((unsigned)(acc2[r][k < CP ? k : 0] >> 32)) : 0.f;
+#pragma unroll
+    for (int half = (kRows * kSlots) / 2, o = 16; o >= 1; half >>= 1, o >>= 1) {
+        const bool upper = (lane & o) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const float send = upper ? v[i] : v[i + half], keep = upper ? v[i + half] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    // F.cross_entropy(reduction='none'): log sum exp(x - m) - (x_y - m)
+    const int k0 = 2 * (lane & 7);
+    const float a0 = v[0] + bias0, a1 = v[1] + bias1;
+    const bool ok0 = k0 < c, ok1 = k0 + 1 < c;
+    float m = fmaxf(ok0 ? a0 : -INFINITY, ok1 ? a1 : -INFINITY);
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float sum = (ok0 ? expf(a0 - m) : 0.f) + (ok1 ? expf(a1 - m) : 0.f);
+    float xy = ((int64_t)k0 == y ? a0 : 0.f) + ((int64_t)(k0 + 1) == y ? a1 : 0.f);
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        xy += __shfl_xor_sync(0xffffffffu, xy, o);
+    }
+    float loss = logf(sum) - (xy - m);
+    if (y == ignore_index) loss = 0.f;
+    else if (y < 0 || y >= c) { loss = 0.f; if (my_row < n) bad = MERCURY_ST_BAD_LABEL; }
+    if ((lane & 7) == 0 && my_row < n) scores[my_row] = loss;
+}
+
 // CP: classes padded to a compile-time count (accumulators live in registers); c <= CP are real.
-// SLABS: d / 128 when known at compile time (all loads of a group issued before any arithmetic), 0 = run-time loop.
+// SLABS: d / 128 when known at compile time, 0 = run-time loop.  With SLABS known a group's 4 x SLABS feature vectors live
+// in registers and the NEXT group's are requested slab by slab as soon as the current group's slab has been consumed, so
+// that the memory system stays busy through the arithmetic, the reduction and the cross-entropy (same registers, no
+// extra buffer).
 template <typename T, int CP, int SLABS>
 __global__ void __launch_bounds__(kHeadNT) score_head_kernel(const T* __restrict__ feats, int64_t n, int d, int64_t row_stride,
                                                              const float* __restrict__ weight, const float* __restrict__ bias, int c,
@@ -65,39 +110,63 @@ __global__ void __launch_bounds__(kHeadNT) score_head_kernel(const T* __restrict
     // after the reduction lane l holds row (l >> 3)'s logits for classes k0 = 2 (l & 7) and k0 + 1
     const int k0 = 2 * (lane & 7), my_r = lane >> 3;
     const float bias0 = (bias && k0 < c) ? bias[k0] : 0.f, bias1 = (bias && k0 + 1 < c) ? bias[k0 + 1] : 0.f;
-    const int slabs = SLABS ? SLABS : (d >> 7);
     const int64_t groups = (n + kRows - 1) / kRows;
+    const int64_t gstride = (int64_t)gridDim.x * (kHeadNT / 32);
+    const int col0 = lane << 2;
     int bad = 0;
-    for (int64_t g = (int64_t)blockIdx.x * (kHeadNT / 32) + warp; g < groups; g += (int64_t)gridDim.x * (kHeadNT / 32)) {
-        const int64_t r0 = g * kRows;
-        u64 acc2[kRows][CP];
-#pragma unroll
-        for (int r = 0; r < kRows; ++r)
-#pragma unroll
-            for (int k = 0; k < CP; ++k) acc2[r][k] = 0ull;
+    int64_t g = (int64_t)blockIdx.x * (kHeadNT / 32) + warp;
+    if constexpr (SLABS > 0) {
+        if (g >= groups) return;
+        X4 x[SLABS][kRows];
         const T* rows[kRows];
 #pragma unroll
-        for (int r = 0; r < kRows; ++r) rows[r] = feats + (r0 + r < n ? r0 + r : n - 1) * row_stride;  // (tail rows re-read the last one)
-        const int64_t my_row = r0 + my_r;
-        const int64_t y = my_row < n ? labels[my_row] : 0;   // (early: used after the reduction)
-        if constexpr (SLABS > 0) {
-            X4 x[SLABS][kRows];
+        for (int r = 0; r < kRows; ++r) rows[r] = feats + (g * kRows + r < n ? g * kRows + r : n - 1) * row_stride;  // (tail rows re-read the last one)
 #pragma unroll
-            for (int j = 0; j < SLABS; ++j)
+        for (int j = 0; j < SLABS; ++j)
 #pragma unroll
-                for (int r = 0; r < kRows; ++r) x[j][r] = load4<T>(rows[r], (j << 7) + (lane << 2));
+            for (int r = 0; r < kRows; ++r) x[j][r] = load4<T>(rows[r], (j << 7) + col0);
+        int64_t y = g * kRows + my_r < n ? labels[g * kRows + my_r] : 0;
+        for (; g < groups; g += gstride) {
+            const int64_t gn = g + gstride < groups ? g + gstride : g;   // (the last group is simply requested again)
 #pragma unroll
-            for (int j = 0; j < SLABS; ++j)
+            for (int r = 0; r < kRows; ++r) rows[r] = feats + (gn * kRows + r < n ? gn * kRows + r : n - 1) * row_stride;
+            const int64_t y_next = gn * kRows + my_r < n ? labels[gn * kRows + my_r] : 0;
+            u64 acc2[kRows][CP];
+#pragma unroll
+            for (int r = 0; r < kRows; ++r)
+#pragma unroll
+                for (int k = 0; k < CP; ++k) acc2[r][k] = 0ull;
+#pragma unroll
+            for (int j = 0; j < SLABS; ++j) {
 #pragma unroll
                 for (int k = 0; k < CP; ++k) {
-                    const ulonglong2 w = *reinterpret_cast<const ulonglong2*>(w_s + k * d + (j << 7) + (lane << 2));
+                    const ulonglong2 w = *reinterpret_cast<const ulonglong2*>(w_s + k * d + (j << 7) + col0);
 #pragma unroll
                     for (int r = 0; r < kRows; ++r) { fma2(acc2[r][k], x[j][r].lo, w.x); fma2(acc2[r][k], x[j][r].hi, w.y); }
                 }
-        } else {
+#pragma unroll
+                for (int r = 0; r < kRows; ++r) x[j][r] = load4<T>(rows[r], (j << 7) + col0);   // next group's slab j
+            }
+            head_finish<CP>(acc2, lane, c, bias0, bias1, y, g * kRows + my_r, n, ignore_index, scores, bad);
+            y = y_next;
+        }
+    } else {
+        const int slabs = d >> 7;
+        for (; g < groups; g += gstride) {
+            const int64_t r0 = g * kRows;
+            u64 acc2[kRows][CP];
+#pragma unroll
+            for (int r = 0; r < kRows; ++r)
+#pragma unroll
+                for (int k = 0; k < CP; ++k) acc2[r][k] = 0ull;
+            const T* rows[kRows];
+#pragma unroll
+            for (int r = 0; r < kRows; ++r) rows[r] = feats + (r0 + r < n ? r0 + r : n - 1) * row_stride;
+            const int64_t my_row = r0 + my_r;
+            const int64_t y = my_row < n ? labels[my_row] : 0;   // (early: used after the reduction)
 #pragma unroll 2
             for (int j = 0; j < slabs; ++j) {
-                const int col = (j << 7) + (lane << 2);
+                const int col = (j << 7) + col0;
                 X4 x[kRows];
 #pragma unroll
                 for (int r = 0; r < kRows; ++r) x[r] = load4<T>(rows[r], col);
@@ -108,42 +177,8 @@ __global__ void __launch_bounds__(kHeadNT) score_head_kernel(const T* __restrict
                     for (int r = 0; r < kRows; ++r) { fma2(acc2[r][k], x[r].lo, w.x); fma2(acc2[r][k], x[r].hi, w.y); }
                 }
             }
+            head_finish<CP>(acc2, lane, c, bias0, bias1, y, my_row, n, ignore_index, scores, bad);
         }
-        // cross-warp sums as a reduce-scatter: 64 slots (row r, class k at r * 16 + k), halved five times -- after the
-        // step with offset o a lane keeps the half selected by its bit o -- so that lane l ends with slots 2l and 2l + 1
-        // (62 shuffles instead of 5 per accumulator)
-        float v[kRows * kSlots];
-#pragma unroll
-        for (int r = 0; r < kRows; ++r)
-#pragma unroll
-            for (int k = 0; k < kSlots; ++k)
-                v[r * kSlots + k] = k < CP ? __uint_as_float((unsigned)acc2[r][k < CP ? k : 0]) + __uint_as_float((unsigned)(acc2[r][k < CP ? k : 0] >> 32)) : 0.f;
-#pragma unroll
-        for (int half = (kRows * kSlots) / 2, o = 16; o >= 1; half >>= 1, o >>= 1) {
-            const bool upper = (lane & o) != 0;
-#pragma unroll
-            for (int i = 0; i < half; ++i) {
-                const float send = upper ? v[i] : v[i + half], keep = upper ? v[i + half] : v[i];
-                v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
-            }
-        }
-        // cross-entropy of row my_r over its 8 lanes (F.cross_entropy, reduction='none'): log sum exp(x - m) - (x_y - m)
-        const float a0 = v[0] + bias0, a1 = v[1] + bias1;
-        const bool ok0 = k0 < c, ok1 = k0 + 1 < c;
-        float m = fmaxf(ok0 ? a0 : -INFINITY, ok1 ? a1 : -INFINITY);
-#pragma unroll
-        for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        float sum = (ok0 ? expf(a0 - m) : 0.f) + (ok1 ? expf(a1 - m) : 0.f);
-        float xy = ((int64_t)k0 == y ? a0 : 0.f) + ((int64_t)(k0 + 1) == y ? a1 : 0.f);
-#pragma unroll
-        for (int o = 4; o > 0; o >>= 1) {
-            sum += __shfl_xor_sync(0xffffffffu, sum, o);
-            xy += __shfl_xor_sync(0xffffffffu, xy, o);
-        }
-        float loss = logf(sum) - (xy - m);
-        if (y == ignore_index) loss = 0.f;
-        else if (y < 0 || y >= c) { loss = 0.f; if (my_row < n) bad = MERCURY_ST_BAD_LABEL; }
-        if ((lane & 7) == 0 && my_row < n) scores[my_row] = loss;
     }
     if (bad) atomicOr(status, bad);
 }
