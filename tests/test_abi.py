@@ -87,3 +87,29 @@ def test_chain_arithmetic_on_host():
     out = subprocess.run([exe, "300000"], capture_output=True, text=True)
     assert out.returncode == 0, out.stdout[-2000:]
     assert "ALL OK" in out.stdout
+
+
+def test_header_is_plain_c(built):
+    """include/mercury_b200.h is the C-ABI contract: it must compile as C99 (what a cgo / JNI / FFI binding would include)
+    and link against the built library from a C program that makes no compute call."""
+    from mercury_b200 import _lib
+
+    src = os.path.join(ROOT, "build", "abi_probe.c")
+    os.makedirs(os.path.dirname(src), exist_ok=True)
+    with open(src, "w") as f:
+        f.write('#include <stdio.h>\n#include "mercury_b200.h"\n'
+                'int main(void) {\n'
+                '    mercury_update_args a = {0};\n'
+                '    (void)a;\n'
+                '    printf("%d %zu\\n", mercury_abi_version(), mercury_update_samples_workspace_bytes(1000000, 128));\n'
+                '    return mercury_cdf(NULL, -1, 0, NULL, NULL, NULL, NULL, 0, NULL) == MERCURY_ERR_ARG ? 0 : 1;\n'
+                '}\n')
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-I", os.path.join(ROOT, "include"), src])
+    exe = os.path.join(ROOT, "build", "abi_probe")
+    libdir = os.path.join(ROOT, "mercury_b200")
+    subprocess.check_call(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), src, "-o", exe, "-L", libdir, "-lmercury_b200",
+                           "-Wl,-rpath," + libdir])
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    ver, ws = out.stdout.split()
+    assert int(ver) == _lib.ABI_VERSION and int(ws) > 0
