@@ -23,7 +23,11 @@ Parity pin: the reference ships no tests or golden vectors for this path, so the
 reference itself leaves parity unpinned.  The explicit-uniform restatements below
 are pinned against ``torch.multinomial`` run in this repository's test-suite
 (``tests/test_oracle.py``) and against committed fixtures generated from
-``torch.multinomial`` / ``F.cross_entropy`` (``tests/golden/make_golden.py``).
+``torch.multinomial`` / ``F.cross_entropy`` (``tests/golden/make_golden.py``), and
+against outputs of the reference's OWN code run in the build container
+(``tests/golden/ref_update_samples_*.npz``, ``ref_groupwise.npz``: ``pytorch_collab.Trainer.update_samples``,
+``util.EMAverage``, ``util.Groupwise_Sampler`` and ``pytorch_model.ResNet18`` imported unmodified by the
+same script): pinned.
 """
 from __future__ import annotations
 
