@@ -224,7 +224,11 @@ extern "C" int mercury_score_head(const void* features, int dtype, int64_t n, in
                                   int32_t* status, void* stream) {
     MB_CHECK_ARG(n >= 0 && d >= 128 && d % 128 == 0 && row_stride >= d, "mercury_score_head: need n >= 0, d a multiple of 128, row_stride >= d");
     MB_CHECK_ARG(c >= 1 && c <= 16, "mercury_score_head: 1..16 classes (wider heads: score the logits with mercury_score)");
-    MB_CHECK_ARG(c * d * 4 <= 200 * 1024, "mercury_score_head: the weight matrix must fit shared memory (c * d <= 51200)");
+    {
+        const int64_t cp = c <= 2 ? 2 : c <= 4 ? 4 : c <= 8 ? 8 : c <= 10 ? 10 : 16;   // (class count as padded by launch_head)
+        MB_CHECK_ARG(c * d <= 51200 && cp * d * 4 <= 224 * 1024,
+                     "mercury_score_head: the weight matrix must fit shared memory (c * d <= 51200, padded classes * d * 4 <= 224 KiB)");
+    }
     MB_CHECK_ARG(dtype == MERCURY_F32 || dtype == MERCURY_BF16, "mercury_score_head: bad dtype");
     if (n == 0) return MERCURY_OK;
     MB_CHECK_ARG(features && weight && labels && scores && status, "mercury_score_head: null pointer");
