@@ -14,6 +14,14 @@ north-star mode implemented here makes the draw GLOBAL:
   4. rows are gathered by their owner (zero elsewhere); ``assemble=True`` SUM-all-reduces the
      B gathered rows so that every rank ends up with the whole batch.
 
+That is ``mode="scores"`` (index-identical to the flat pool, K2 replicated).  ``mode="totals"`` is the north
+star read literally and the one that scales: every rank builds the exact chain of its own shard only, the
+ranks exchange one fp64 sum of scores and one fp32 chain total each, and the draw is two-level (shard by the
+totals, then position inside the owner's exact CDF).  With ``exchange="peer"`` those two scalars travel by
+stores into the peers' mapped memory from inside the step's own kernels (``PeerExchange``, CUDA IPC over
+NVLink/NVSwitch) and the whole sharded step is one C call; ``exchange="nccl"`` uses two small all-gathers.
+See DESIGN.md section 5.
+
 The compute steps go through a small backend object so that the host-side logic (shard
 arithmetic, collectives, ownership) can be exercised on CPU with gloo in the tests; the default
 backend is the CUDA ops and has no CPU path.
@@ -174,6 +182,8 @@ class ShardedPool:
         self.ema_alpha, self.smooth_alpha = ema_alpha, smooth_alpha
         self._draw_out: dict = {}
         self._gather_out: dict = {}
+        self.peer = None
+        self._xstatus = None
         if mode == "totals":
             self.scores_all = torch.empty(n_local, dtype=torch.float32, device=self.device)  # (local shard only)
             self.sums_all = torch.zeros(self.world, dtype=torch.float64, device=self.device)
