@@ -32,7 +32,6 @@ constexpr int kRows = 4;       // candidates per warp iteration
 typedef unsigned long long u64;
 struct X4 { u64 lo, hi; };  // four consecutive fp32 values as two packed pairs (x, y) and (z, w)
 
-__device__ __forceinline__ u64 pack2(float a, float b) { return (u64)__float_as_uint(a) | ((u64)__float_as_uint(b) << 32); }
 // d += a * b on both halves (SASS FFMA2: two fp32 multiply-adds per issue slot)
 __device__ __forceinline__ void fma2(u64& d, u64 a, u64 b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b)); }
 
