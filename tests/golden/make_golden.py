@@ -224,14 +224,43 @@ def aten_cross_entropy():
     return out
 
 
+def ref_head(seed, n=64):
+    """The reference's ResNet18 run on synthetic images with its own forward (pytorch_model.py:88-97): the input of its
+    ``linear`` layer (the pooled features), that layer's parameters, its output and the scores pytorch_collab.py:102
+    computes from it -- the golden vector for the fused head (mercury_score_head)."""
+    import torch.nn.functional as F
+    from pytorch_model import ResNet18  # reference, unmodified
+
+    torch.manual_seed(seed)
+    net = ResNet18(num_classes=10)
+    net.train()
+    g = torch.Generator().manual_seed(seed + 1)
+    data = torch.rand(n, 3, 32, 32, generator=g)
+    label = torch.randint(0, 10, (n,), generator=g)
+    seen = {}
+    hook = net.linear.register_forward_hook(lambda m, i, o: seen.update(features=i[0].detach().clone(), logits=o.detach().clone()))
+    with torch.no_grad():
+        out = net(data)
+    hook.remove()
+    assert torch.equal(out, seen["logits"])
+    scores = F.cross_entropy(out, label, reduction="none")  # pytorch_collab.py:102
+    return dict(features=seen["features"].numpy(), weight=net.linear.weight.detach().numpy(), bias=net.linear.bias.detach().numpy(),
+                label=label.numpy(), logits=out.numpy(), scores=scores.numpy(), seed=np.int64(seed))
+
+
 def main():
     _install_stubs()
     torch.set_num_threads(1)
+    if len(sys.argv) > 1 and sys.argv[1] == "head":   # only the fixture added after the others were committed
+        np.savez_compressed(os.path.join(HERE, "ref_head.npz"), **ref_head(800))
+        print("ref_head.npz", os.path.getsize(os.path.join(HERE, "ref_head.npz")))
+        return
     np.savez_compressed(os.path.join(HERE, "aten_multinomial.npz"), **aten_multinomial())
     np.savez_compressed(os.path.join(HERE, "aten_cross_entropy.npz"), **aten_cross_entropy())
     np.savez_compressed(os.path.join(HERE, "ref_update_samples_linear.npz"), **ref_update_samples("linear", 32, 500))
     np.savez_compressed(os.path.join(HERE, "ref_update_samples_resnet18.npz"), **ref_update_samples("resnet18", 128, 600))
     np.savez_compressed(os.path.join(HERE, "ref_groupwise.npz"), **ref_groupwise(700))
+    np.savez_compressed(os.path.join(HERE, "ref_head.npz"), **ref_head(800))
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

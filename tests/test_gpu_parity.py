@@ -476,3 +476,12 @@ def test_score_head_on_the_reference_resnet18_head(ops):
         ref = F.cross_entropy(lin(feats), y, reduction="none")
     got = ops.score_head(feats.to(DEV), lin.weight.detach().to(DEV), lin.bias.detach().to(DEV), y.to(DEV)).cpu()
     np.testing.assert_allclose(got.numpy(), ref.numpy(), rtol=2e-5, atol=2e-5)
+
+
+def test_score_head_matches_the_reference_run(ops, golden_dir):
+    """Golden vector recorded from the reference's own ResNet18 forward (tests/golden/make_golden.py, ref_head)."""
+    z = np.load(os.path.join(golden_dir, "ref_head.npz"))
+    f, w, b, y = (torch.from_numpy(z[k]).to(DEV) for k in ("features", "weight", "bias", "label"))
+    got = ops.score_head(f, w, b, y).cpu().numpy()
+    np.testing.assert_allclose(got, z["scores"], rtol=2e-5, atol=2e-5)
+    np.testing.assert_allclose(ops.score(torch.from_numpy(z["logits"]).to(DEV), y).cpu().numpy(), z["scores"], rtol=RTOL_F32, atol=ATOL_LOSS)

@@ -222,3 +222,13 @@ def test_split_head_reproduces_the_reference_resnet_forward():
         assert f.shape == (6, 512)
         assert torch.equal(lin(f), net(x))
         assert torch.equal(orc.score_head(f, lin.weight, lin.bias, y), F.cross_entropy(net(x), y, reduction="none"))
+
+
+def test_score_head_oracle_reproduces_the_reference_run(golden_dir):
+    """tests/golden/ref_head.npz: the reference's ResNet18 forward, hooked at its linear layer."""
+    z = np.load(os.path.join(golden_dir, "ref_head.npz"))
+    f, w, b, y = (torch.from_numpy(z[k]) for k in ("features", "weight", "bias", "label"))
+    assert f.shape == (64, 512) and w.shape == (10, 512)
+    assert torch.equal(F.linear(f, w, b), torch.from_numpy(z["logits"]))          # same layer, same arithmetic
+    assert torch.equal(orc.score_head(f, w, b, y), torch.from_numpy(z["scores"]))
+    assert torch.equal(orc.score(torch.from_numpy(z["logits"]), y), torch.from_numpy(z["scores"]))
