@@ -86,3 +86,27 @@ def gather_weights(p: np.ndarray, idx: np.ndarray):
     lib().orc_gather_weights(_p(p, ctypes.c_float), ctypes.c_int64(p.size), _p(idx, ctypes.c_int64),
                              ctypes.c_int64(idx.size), _p(nprob, ctypes.c_float), _p(seed, ctypes.c_float))
     return nprob, seed
+
+
+def score_head(features: np.ndarray, weight: np.ndarray, bias, labels: np.ndarray, ignore_index: int = -100):
+    n, d = features.shape
+    c = weight.shape[0]
+    f = np.ascontiguousarray(features, dtype=np.float32)
+    w = np.ascontiguousarray(weight, dtype=np.float32)
+    bb = None if bias is None else np.ascontiguousarray(bias, dtype=np.float32)
+    labels = np.ascontiguousarray(labels, dtype=np.int64)
+    out = np.empty(n, dtype=np.float32)
+    st = lib().orc_score_head_f32(_p(f, ctypes.c_float), _p(w, ctypes.c_float), None if bb is None else _p(bb, ctypes.c_float),
+                                  _p(labels, ctypes.c_int64), ctypes.c_int64(n), ctypes.c_int64(d), ctypes.c_int64(c),
+                                  ctypes.c_int64(ignore_index), _p(out, ctypes.c_float))
+    return st, out
+
+
+def two_level_draw(p_shards, u: np.ndarray):
+    p = np.ascontiguousarray(np.concatenate(p_shards), dtype=np.float32)
+    offsets = np.ascontiguousarray(np.concatenate([[0], np.cumsum([len(s) for s in p_shards])]), dtype=np.int64)
+    u = np.ascontiguousarray(u, dtype=np.float64)
+    idx = np.empty(len(u), dtype=np.int64)
+    st = lib().orc_two_level_draw(_p(p, ctypes.c_float), _p(offsets, ctypes.c_int64), ctypes.c_int64(len(p_shards)),
+                                  _p(u, ctypes.c_double), ctypes.c_int64(len(u)), _p(idx, ctypes.c_int64))
+    return st, idx

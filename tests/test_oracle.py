@@ -232,3 +232,21 @@ def test_score_head_oracle_reproduces_the_reference_run(golden_dir):
     assert torch.equal(F.linear(f, w, b), torch.from_numpy(z["logits"]))          # same layer, same arithmetic
     assert torch.equal(orc.score_head(f, w, b, y), torch.from_numpy(z["scores"]))
     assert torch.equal(orc.score(torch.from_numpy(z["logits"]), y), torch.from_numpy(z["scores"]))
+
+
+def test_c_oracle_head_and_two_level_draw_agree_with_the_python_oracle(golden_dir):
+    z = np.load(os.path.join(golden_dir, "ref_head.npz"))
+    st, got = c_oracle.score_head(z["features"], z["weight"], z["bias"], z["label"])
+    assert st == 0
+    np.testing.assert_allclose(got, z["scores"], rtol=2e-5, atol=2e-5)           # (index-order sums vs the BLAS)
+    g = torch.Generator().manual_seed(77)
+    shards = []
+    for n in (5000, 1, 12345, 700):
+        shards.append((torch.rand(n, generator=g) + 0.01).numpy().astype(np.float32))
+    tot = np.float32(sum(float(s.astype(np.float64).sum()) for s in shards))
+    shards = [(s / tot).astype(np.float32) for s in shards]
+    u = torch.rand(500, dtype=torch.float64, generator=g).numpy()
+    u[0], u[1] = 0.0, 1.0 - 2.0 ** -53
+    st, idx = c_oracle.two_level_draw(shards, u)
+    assert st == 0
+    assert np.array_equal(idx, orc.sharded_draw_two_level(shards, u))
