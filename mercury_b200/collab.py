@@ -32,7 +32,14 @@ def split_head(net):
 class Trainer(object):
     POOL_BATCHES = 10  # pytorch_collab.py:95
 
-    def __init__(self, net, optimizer, train_loader, presam_loader, test_loader, device):
+    def __init__(self, net, optimizer, train_loader, presam_loader, test_loader, device, score_from_features: bool = False,
+                 ops_module=None):
+        # score_from_features: presample batches stop before the classifier head (``split_head``) and are scored by
+        # ``ops.score_head`` -- the logits of the pool are never materialised; needs a ResNet-shaped net.
+        # ops_module: the operator module (default: the CUDA ops; the CPU tests inject an oracle-backed stand-in).
+        self.ops = ops_module if ops_module is not None else ops
+        self.score_from_features = score_from_features
+        self._head = split_head(net) if score_from_features else None
         self.net = net
         self.optimizer = optimizer
         self.train_loader = train_loader
@@ -84,16 +91,25 @@ class Trainer(object):
             with torch.no_grad():
                 idx, data, label = self.get_next()
                 data = data.to(self.device, non_blocking=True)
-                output = self.net(data)
+                if self._head is not None:
+                    features, linear = self._head
+                    output = self.ops.score_head(features(data), linear.weight, linear.bias, label.to(self.device, non_blocking=True))
+                else:
+                    output = self.net(data)
                 if pool is None:
-                    pool = self._pool = ResidentPool(self.POOL_BATCHES * data.shape[0], output.shape[1], tuple(data.shape[1:]),
-                                                     device=self.device, logits_dtype=output.dtype, payload_dtype=data.dtype)
+                    pool = self._pool = ResidentPool(self.POOL_BATCHES * data.shape[0], None if self._head is not None else output.shape[1],
+                                                     tuple(data.shape[1:]), device=self.device, logits_dtype=output.dtype,
+                                                     payload_dtype=data.dtype)
                 pool.append(idx, data, label, output)
         logits, labels, datas, index = pool.tensors()
         bounds = pool.growing_bounds()
         u = torch.rand(len(bounds) * B, dtype=torch.float64)[(len(bounds) - 1) * B:].to(self.device, non_blocking=True)
-        r = ops.update_samples(logits, labels, u, ema_loss.state, ema_loss.first_update, ema_alpha=ema_loss.alpha,
-                               smooth_alpha=alpha, data=datas, index=index, bounds=bounds)
+        if self._head is not None:   # the pool holds scores
+            r = self.ops.update_samples(None, labels, u, ema_loss.state, ema_loss.first_update, ema_alpha=ema_loss.alpha,
+                                        smooth_alpha=alpha, data=datas, index=index, bounds=bounds, scores_in=logits)
+        else:
+            r = self.ops.update_samples(logits, labels, u, ema_loss.state, ema_loss.first_update, ema_alpha=ema_loss.alpha,
+                                        smooth_alpha=alpha, data=datas, index=index, bounds=bounds)
         ema_loss.first_update = False
         self.last = r
         return r.nprob, r.data, r.labels, r.index, r.stats[_lib.STAT_MEAN]

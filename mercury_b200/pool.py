@@ -16,11 +16,14 @@ import torch
 
 
 class ResidentPool:
-    def __init__(self, capacity: int, num_classes: int, payload_shape=(), device="cuda", logits_dtype=torch.float32,
+    def __init__(self, capacity: int, num_classes: Optional[int], payload_shape=(), device="cuda", logits_dtype=torch.float32,
                  payload_dtype=torch.float32, ring: bool = False):
         self.capacity, self.ring = int(capacity), ring
         dev = torch.device(device)
-        self.logits = torch.empty(capacity, num_classes, dtype=logits_dtype, device=dev)
+        # num_classes=None: the pool keeps per-candidate SCORES (fp32 [capacity]) instead of logits -- for callers that
+        # score from the features (ops.score_head) and never hold logits
+        self.logits = (torch.empty(capacity, dtype=torch.float32, device=dev) if num_classes is None
+                       else torch.empty(capacity, num_classes, dtype=logits_dtype, device=dev))
         self.labels = torch.empty(capacity, dtype=torch.int64, device=dev)
         self.index = torch.empty(capacity, dtype=torch.int64, device=dev)
         self.data = torch.empty((capacity,) + tuple(payload_shape), dtype=payload_dtype, device=dev) if payload_shape else None
