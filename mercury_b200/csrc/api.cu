@@ -4,6 +4,10 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "common.cuh"
 #include "internal.cuh"
 
@@ -21,6 +25,51 @@ void set_last_error(const char* fmt, ...) {
 bool pdl_enabled() {
     static const bool on = [] { const char* e = getenv("MERCURY_PDL"); return !(e && e[0] == '0'); }();
     return on;
+}
+
+namespace {
+constexpr int kMaxDevicesTracked = 64;
+std::mutex g_attr_mu;
+std::map<std::pair<int, const void*>, size_t> g_attr_done;  // (device ordinal, function) -> bytes already granted
+int g_sm_count[kMaxDevicesTracked] = {};
+}  // namespace
+
+int ensure_dynamic_smem(const void* func, size_t bytes, const char* what) {
+    if (bytes <= 48 * 1024) return MERCURY_OK;  // within the default limit: nothing to opt in to
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, what);
+    std::lock_guard<std::mutex> lock(g_attr_mu);
+    size_t& have = g_attr_done[std::make_pair(dev, func)];
+    if (have >= bytes) return MERCURY_OK;
+    e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return cuda_fail(e, what);
+    have = bytes;
+    return MERCURY_OK;
+}
+
+int device_sm_count() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevicesTracked) return 0;
+    std::lock_guard<std::mutex> lock(g_attr_mu);
+    if (g_sm_count[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+        g_sm_count[dev] = v;
+    }
+    return g_sm_count[dev];
+}
+
+int env_knob(const char* name, int dflt, int lo, int hi) {
+    const char* e = getenv(name);
+    if (!e || !*e) return dflt;
+    char* end = nullptr;
+    const long v = strtol(e, &end, 10);
+    if (end == e || *end != '\0' || v < lo || v > hi) {
+        fprintf(stderr, "mercury_b200: ignoring %s=%s (expected an integer in [%d, %d])\n", name, e, lo, hi);
+        return dflt;
+    }
+    return (int)v;
 }
 
 int cuda_fail(cudaError_t e, const char* what) {

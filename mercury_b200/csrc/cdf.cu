@@ -1672,16 +1672,17 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     }
     MB_CHECK_LAUNCH("summarize_kernel");
     const size_t smem = spine_smem_bytes(nchunks);
-    static bool attr_set = false;  // per process; the attribute is sticky per device function
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(spine_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(spine_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-        if (e != cudaSuccess) return cuda_fail(e, "spine_kernel smem attribute");
-        attr_set = true;
+    // opt in to the large dynamic shared memory, once per DEVICE and instantiation (a function's attributes belong to
+    // one context: a second GPU of the same process needs its own call)
+    {
+        const size_t want = 226 * 1024;
+        int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(spine_kernel<false, false>), want, "spine_kernel smem attribute");
+        if (!rc) rc = ensure_dynamic_smem(reinterpret_cast<const void*>(spine_kernel<false, true>), want, "spine_kernel smem attribute");
+        if (!rc) rc = ensure_dynamic_smem(reinterpret_cast<const void*>(spine_kernel<true, false>), want, "spine_kernel smem attribute");
+        if (!rc) rc = ensure_dynamic_smem(reinterpret_cast<const void*>(spine_kernel<true, true>), want, "spine_kernel smem attribute");
+        if (rc) return rc;
     }
-    static const int debug = getenv("MERCURY_SPINE_DEBUG") ? atoi(getenv("MERCURY_SPINE_DEBUG")) : 0;  // developer aid (printf)
+    static const int debug = env_knob("MERCURY_SPINE_DEBUG", 0, 0, 9);  // developer aid (printf)
     float* chain_total_out = fused ? fused->stats + MERCURY_STAT_CHAIN_TOTAL : nullptr;
     PeerBox* const* peers = fused ? fused->peers : nullptr;
     const int nshards = fused ? fused->nshards : 0, rank = fused ? fused->rank : 0;

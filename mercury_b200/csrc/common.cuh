@@ -76,6 +76,15 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 
 bool pdl_enabled();  // api.cu: on unless MERCURY_PDL=0
 
+// api.cu -- per-DEVICE launch set-up (a CUfunction belongs to one context, so its attributes are per device):
+// raises cudaFuncAttributeMaxDynamicSharedMemorySize of `func` on the CURRENT device to at least `bytes`, once
+// (remembered per device ordinal and function, thread-safe); returns MERCURY_OK or MERCURY_ERR_CUDA.
+int ensure_dynamic_smem(const void* func, size_t bytes, const char* what);
+// multiprocessors of the current device (cached per ordinal); 0 on error
+int device_sm_count();
+// developer knob read once from the environment: an integer in [lo, hi], else `dflt`
+int env_knob(const char* name, int dflt, int lo, int hi);
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_chain(bool chained, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};

@@ -191,7 +191,8 @@ int launch_head(const T* feats, int64_t n, int d, int64_t row_stride, const floa
     const int grid = (int)min_i64((groups + kHeadNT / 32 - 1) / (kHeadNT / 32), (int64_t)148 * 2);
     cudaError_t e = cudaSuccess;
 #define MB_HEAD_LAUNCH(CPV, SL)                                                                                                 \
-    e = cudaFuncSetAttribute(score_head_kernel<T, CPV, SL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);            \
+    if (ensure_dynamic_smem(reinterpret_cast<const void*>(score_head_kernel<T, CPV, SL>), smem, "score_head smem attribute"))   \
+        return MERCURY_ERR_CUDA;                                                                                                \
     if (e == cudaSuccess)                                                                                                       \
         score_head_kernel<T, CPV, SL><<<grid, kHeadNT, smem, st>>>(feats, n, d, row_stride, weight, bias, c, labels,           \
                                                                    ignore_index, scores, status);

@@ -15,59 +15,12 @@
 
 #include "common.cuh"
 #include "internal.cuh"
+#include "score_small.cuh"
 
 namespace mercury {
 
 namespace {
 
-constexpr float kLog2e = 1.4426950408889634f;
-constexpr int kProducerThreads = 32;
-constexpr int kSmallHeader = 512;  // ring barriers + per-warp partial sums in front of the stages
-
-template <typename T> struct Elem;
-template <> struct Elem<float> {
-    static __device__ __forceinline__ float ld(const float* p) { return *p; }
-    static constexpr uint32_t kNegInfWord = 0xff800000u;
-};
-template <> struct Elem<__nv_bfloat16> {
-    static __device__ __forceinline__ float ld(const __nv_bfloat16* p) {
-        return __uint_as_float(static_cast<uint32_t>(*reinterpret_cast<const unsigned short*>(p)) << 16);
-    }
-    static constexpr uint32_t kNegInfWord = 0xff80ff80u;
-};
-
-constexpr float kLn2 = 0.6931471805599453f;
-
-// packed bf16x2 max (one ALU op per two logits): NaN-free operand wins, like fmaxf
-__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
-    uint32_t r;
-    asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
-    return r;
-}
-
-// exp(x - m) summed as 2^(x*k - hi) with hi = fl(m*k): one FFMA + one MUFU per logit.  Every
-// term is off by the same factor 2^lo, lo = m*k - hi (exact, from an FMA); `log_fix` removes it
-// from log(sum) afterwards, so nothing is lost against computing (x - m) first.
-struct ExpScale {
-    float hi, lo;
-    __device__ __forceinline__ explicit ExpScale(float m) { hi = m * kLog2e; lo = fmaf(m, kLog2e, -hi); }
-    __device__ __forceinline__ float term(float x) const { return ex2_approx(fmaf(x, kLog2e, -hi)); }
-    __device__ __forceinline__ float log_fix() const { return lo * kLn2; }  // log(sum_true) = log(sum) - log_fix
-};
-
-// label handling shared by all layouts: returns true if the row contributes a loss.
-// Call it from ONE thread per row (it raises the status bit with an atomic).
-__device__ __forceinline__ bool label_ok(int64_t y, int64_t c, int64_t ignore_index, int32_t* status) {
-    if (y == ignore_index) return false;
-    if (y < 0 || y >= c) {
-        atomicOr(status, MERCURY_ST_BAD_LABEL);
-        return false;
-    }
-    return true;
-}
-__device__ __forceinline__ bool label_in_range(int64_t y, int64_t c, int64_t ignore_index) {
-    return y != ignore_index && y >= 0 && y < c;
-}
 
 // ------------------------------------------------------------------------------------------------
 // generic: one warp per row, scalar loads, two passes (second pass served by L1/L2)
@@ -171,148 +124,16 @@ __global__ void __launch_bounds__(256) score_warp_kernel(const T* __restrict__ l
 }
 
 // ------------------------------------------------------------------------------------------------
-// bulk-copy ring shared by the small-row and wide-row kernels
-template <int STAGES> struct Ring {
-    uint64_t full[STAGES];
-    uint64_t empty[STAGES];
-};
-
-template <int STAGES>
-__device__ __forceinline__ void ring_init(Ring<STAGES>* ring, int consumer_warps) {
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) {
-            mbar_init(&ring->full[s], 1);
-            mbar_init(&ring->empty[s], consumer_warps);
-        }
-        mbar_fence_init();
-    }
-    __syncthreads();
-}
-
-// small rows: tile = TR rows of logits + their labels per stage; consumers own rows.
-// CT > 0: compile-time class count (rows cached in registers); CT == 0: run-time class count.
+// small rows: the body lives in score_small.cuh (shared with the fused one-kernel step)
 template <typename T, int CT, int STAGES, int CONSUMERS>
 __global__ void __launch_bounds__(CONSUMERS + kProducerThreads, 3)
 score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels, int64_t n, int c_rt, int tile_rows,
                    int64_t ignore_index, float* __restrict__ scores, int32_t* status, double* __restrict__ tile_sums) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const int c = CT > 0 ? CT : c_rt;
-    Ring<STAGES>* ring = reinterpret_cast<Ring<STAGES>*>(smem);
-    const uint32_t logit_bytes = (uint32_t)tile_rows * c * sizeof(T);
-    const uint32_t logit_slot = (logit_bytes + 127u) & ~127u;
-    const uint32_t stage_bytes = logit_slot + (uint32_t)tile_rows * 8u;
-    double* tred = reinterpret_cast<double*>(smem + 128);  // [2][CONSUMERS / 32] per-warp score sums
-    unsigned char* stage0 = smem + kSmallHeader;
-    static_assert(sizeof(Ring<STAGES>) <= 128 && 128 + 2 * (CONSUMERS / 32) * 8 <= kSmallHeader, "header layout");
-    ring_init(ring, CONSUMERS / 32);
-    pdl_wait();                // (the previous step's draw kernel may still be reading the scores we overwrite)
-    pdl_launch_dependents();
-
-    const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    if (warp == 0) {
-        // ---- producer warp
-        int it = 0;
-        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-            const int s = it % STAGES, round = it / STAGES;
-            if (round > 0) mbar_wait(&ring->empty[s], (round - 1) & 1);
-            const int64_t row0 = tile * tile_rows;
-            const int rows = (int)min((int64_t)tile_rows, n - row0);
-            unsigned char* dst = stage0 + (size_t)s * stage_bytes;
-            const uint32_t lb = (uint32_t)rows * c * sizeof(T), yb = (uint32_t)rows * 8u;
-            if (((lb | yb) & 15u) == 0) {
-                if (lane == 0) {
-                    mbar_arrive_expect_tx(&ring->full[s], lb + yb);
-                    bulk_g2s(dst, logits + row0 * c, lb, &ring->full[s]);
-                    bulk_g2s(dst + logit_slot, labels + row0, yb, &ring->full[s]);
-                }
-            } else {  // ragged last tile: plain loads by the producer warp
-                const T* src = logits + row0 * c;
-                T* d = reinterpret_cast<T*>(dst);
-                for (int k = lane; k < rows * c; k += 32) d[k] = src[k];
-                int64_t* dy = reinterpret_cast<int64_t*>(dst + logit_slot);
-                for (int k = lane; k < rows; k += 32) dy[k] = labels[row0 + k];
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&ring->full[s]);
-            }
-            __syncwarp();
-        }
-    } else {
-        // ---- consumers
-        const int t = threadIdx.x - kProducerThreads;
-        int it = 0;
-        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-            const int s = it % STAGES, round = it / STAGES;
-            mbar_wait(&ring->full[s], round & 1);
-            const int64_t row0 = tile * tile_rows;
-            const int rows = (int)min((int64_t)tile_rows, n - row0);
-            const unsigned char* base = stage0 + (size_t)s * stage_bytes;
-            const T* tl = reinterpret_cast<const T*>(base);
-            const int64_t* ty = reinterpret_cast<const int64_t*>(base + logit_slot);
-            double tile_acc = 0.0;
-            for (int r = t; r < rows; r += CONSUMERS) {
-                const T* rp = tl + (size_t)r * c;
-                const int64_t y = ty[r];
-                float m = -INFINITY, l = 0.f, fix = 0.f;
-                if constexpr (CT > 0) {
-                    float x[CT > 0 ? CT : 1];
-                    if constexpr (sizeof(T) == 4 && (CT % 2) == 0) {
-#pragma unroll
-                        for (int j = 0; j < CT / 2; ++j) {
-                            const float2 p2 = reinterpret_cast<const float2*>(rp)[j];
-                            x[2 * j] = p2.x;
-                            x[2 * j + 1] = p2.y;
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < CT; ++j) x[j] = Elem<T>::ld(rp + j);
-                    }
-#pragma unroll
-                    for (int j = 0; j < CT; ++j) m = fmaxf(m, x[j]);
-                    const ExpScale es(m);
-                    float la = 0.f, lb = 0.f;
-#pragma unroll
-                    for (int j = 0; j + 1 < CT; j += 2) { la += es.term(x[j]); lb += es.term(x[j + 1]); }
-                    if (CT & 1) la += es.term(x[CT - 1]);
-                    l = la + lb;
-                    fix = es.log_fix();
-                } else {
-                    // rotate the start column by the row so that lanes hit different banks
-                    int j0 = r % c;
-                    int j = j0;
-                    for (int k = 0; k < c; ++k) {
-                        m = fmaxf(m, Elem<T>::ld(rp + j));
-                        if (++j == c) j = 0;
-                    }
-                    j = j0;
-                    for (int k = 0; k < c; ++k) {
-                        l += ex2_approx((Elem<T>::ld(rp + j) - m) * kLog2e);
-                        if (++j == c) j = 0;
-                    }
-                }
-                float out = 0.f;
-                if (label_ok(y, c, ignore_index, status)) out = (logf(l) - fix) - (Elem<T>::ld(rp + y) - m);
-                scores[row0 + r] = out;
-                tile_acc += (double)out;
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&ring->empty[s]);
-            if (tile_sums) {  // sum of this tile's scores, fixed order: feeds the pool statistics
-                tile_acc = warp_sum(tile_acc);
-                double* buf = tred + (it & 1) * (CONSUMERS / 32);
-                if (lane == 0) buf[(t >> 5)] = tile_acc;
-                asm volatile("bar.sync 2, %0;" ::"n"(CONSUMERS) : "memory");
-                if (t == 0) {
-                    double sum = 0.0;
-#pragma unroll
-                    for (int i = 0; i < CONSUMERS / 32; ++i) sum += buf[i];
-                    tile_sums[tile] = sum;
-                }
-            }
-        }
-    }
+    score_small_body<T, CT, STAGES, CONSUMERS, false, true>(smem, logits, labels, n, c_rt, tile_rows, ignore_index, scores, status,
+                                                            tile_sums);
 }
+
 
 // wide rows: one CTA per row, CHUNK-byte pieces through the ring, per-thread online softmax
 template <typename T, int STAGES, int CHUNK, int CONSUMERS>
@@ -445,21 +266,25 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
         constexpr int STAGES = 3, CONSUMERS = 256;
         // one row per consumer thread and tile (~12 KB per stage at 10 classes): three CTAs (27 warps) share an
         // SM and cover each other's stalls; measured best of {128..1024} rows x {1..8} CTAs/SM at 1M x 10
-        int tile_rows = row_bytes <= 40 ? 256 : row_bytes <= 88 ? 256 : row_bytes <= 184 ? 128 : 64;
-        int ctas_per_sm = 3;
-        if (const char* e = getenv("MERCURY_K1_TILE")) tile_rows = atoi(e);        // developer knobs
-        if (const char* e = getenv("MERCURY_K1_CTAS")) ctas_per_sm = atoi(e);
+        // developer knobs, read once and validated: rows per tile must divide the CDF chunk (the fused statistics
+        // sum whole tiles per chunk) and keep the ring inside shared memory
+        static const int knob_tile = env_knob("MERCURY_K1_TILE", 0, 32, 2048);
+        static const int knob_ctas = env_knob("MERCURY_K1_CTAS", 3, 1, 8);
+        int tile_rows = small_tile_rows(row_bytes);
+        if (knob_tile > 0 && (knob_tile & (knob_tile - 1)) == 0 && kCdfChunk % knob_tile == 0 &&
+            small_smem_bytes(STAGES, knob_tile, row_bytes) <= 200 * 1024)
+            tile_rows = knob_tile;
+        const int ctas_per_sm = knob_ctas;
         const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
         // every CTA gets the same number of tiles (the last ones one fewer at most): size the grid for that
         const int64_t slots = (int64_t)ctas_per_sm * kSMs;
         const int64_t per_cta = (ntiles + slots - 1) / slots;
         const int grid = (int)min_i64(ntiles, (ntiles + per_cta - 1) / per_cta);
-        const size_t logit_slot = ((size_t)tile_rows * row_bytes + 127) & ~(size_t)127;
-        const size_t smem = kSmallHeader + STAGES * (logit_slot + (size_t)tile_rows * 8);
+        const size_t smem = small_smem_bytes(STAGES, tile_rows, row_bytes);
         auto go = [&](auto kern) -> int {
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return cuda_fail(e, "score_small smem attribute");
-            e = launch_chain(chained, kern, dim3(grid), dim3(CONSUMERS + kProducerThreads), smem, st, logits, labels, n, (int)c, tile_rows,
+            int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem, "score_small smem attribute");
+            if (rc) return rc;
+            cudaError_t e = launch_chain(chained, kern, dim3(grid), dim3(CONSUMERS + kProducerThreads), smem, st, logits, labels, n, (int)c, tile_rows,
                              ignore_index, scores, status, part_sums);
             if (e != cudaSuccess) return cuda_fail(e, "score_small_kernel launch");
             if (per_out && part_sums) *per_out = tile_rows;
@@ -487,8 +312,8 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
         constexpr int STAGES = 4, CHUNK = 16384, CONSUMERS = 256;
         const size_t smem = 256 + (size_t)STAGES * CHUNK;
         auto kern = score_wide_kernel<T, STAGES, CHUNK, CONSUMERS>;
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return cuda_fail(e, "score_wide smem attribute");
+        const int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem, "score_wide smem attribute");
+        if (rc) return rc;
         const int grid = (int)min_i64(n, (int64_t)kSMs * 3);
         kern<<<grid, CONSUMERS + kProducerThreads, smem, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
         MB_CHECK_LAUNCH("score_wide_kernel");
