@@ -1413,18 +1413,34 @@ struct DrawArgs {
     int64_t* idx; float* nprob; float* seed; unsigned char* out_data; int64_t* out_labels; int64_t* out_index;
 };
 
+// barrier among the kDrawNT threads that work on a draw: the whole CTA in the stand-alone kernel, the 256 worker
+// threads (named barrier 1) inside the fused step, whose CTAs carry one more warp
+template <bool NAMED>
+__device__ __forceinline__ void draw_sync() {
+    if constexpr (NAMED) asm volatile("bar.sync 1, 256;" ::: "memory");
+    else __syncthreads();
+}
+
+struct DrawSmem {
+    ResolveSmem rs;
+    int wcnt[kDrawNT / 32];
+    int64_t chosen;
+};
+
+// One draw by kDrawNT threads: `chunk` < 0 -> find the chunk from the boundary values first.  cdf_s: kChunk floats of
+// shared memory.  `bits_known`: the exact running sum in front of `chunk` when the caller already has it.
+template <bool NAMED>
+__device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, double uj, int chunk, uint32_t bits_known, bool have_bits,
+                                             DrawSmem& ds, float* cdf_s);
+
 template <bool PEER>
 __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
-    __shared__ ResolveSmem rs;
+    __shared__ DrawSmem ds;
     __shared__ float cdf_s[kChunk];
-    __shared__ int wcnt[kDrawNT / 32];
-    __shared__ int64_t chosen;
     pdl_wait();
     pdl_launch_dependents();
     const int64_t j = blockIdx.x;
     double uj = a.u[j];
-    const float total = *a.total_ptr;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if constexpr (PEER) {
         __shared__ float sh_tot[kMaxShards];
         __shared__ double sh_u;
@@ -1462,6 +1478,17 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
         __syncthreads();
         uj = sh_u;
     }
+    draw_resolve<false>(a, j, uj, -1, 0u, false, ds, cdf_s);
+}
+
+template <bool NAMED>
+__device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, double uj, int chunk, uint32_t bits_known, bool have_bits,
+                                             DrawSmem& ds, float* cdf_s) {
+    ResolveSmem& rs = ds.rs;
+    int* wcnt = ds.wcnt;
+    int64_t& chosen = ds.chosen;
+    const float total = *a.total_ptr;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (uj < 0.0) {  // sharded pools: this draw belongs to another shard -> all-zero outputs (summed across ranks later)
         if (threadIdx.x == 0) {
             a.idx[j] = 0; a.nprob[j] = 0.f; a.seed[j] = 0.f;
@@ -1475,19 +1502,21 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
         return;
     }
     // (a) chunks whose last cdf value is < u
-    int cnt = 0;
-    for (int c = threadIdx.x; c < a.nchunks; c += kDrawNT) {
-        const float endv = __fdiv_rn(b2f(a.start_bits[c + 1]), total);
-        cnt += ((double)endv < uj) ? 1 : 0;
-    }
-    cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if (lane == 0) wcnt[warp] = cnt;
-    __syncthreads();
-    int chunk = 0;
+    if (chunk < 0) {
+        int cnt = 0;
+        for (int c = threadIdx.x; c < a.nchunks; c += kDrawNT) {
+            const float endv = __fdiv_rn(b2f(a.start_bits[c + 1]), total);
+            cnt += ((double)endv < uj) ? 1 : 0;
+        }
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0) wcnt[warp] = cnt;
+        draw_sync<NAMED>();
+        chunk = 0;
 #pragma unroll
-    for (int i = 0; i < kDrawNT / 32; ++i) chunk += wcnt[i];
-    if (chunk > a.nchunks - 1) chunk = a.nchunks - 1;
-    __syncthreads();
+        for (int i = 0; i < kDrawNT / 32; ++i) chunk += wcnt[i];
+        if (chunk > a.nchunks - 1) chunk = a.nchunks - 1;
+        draw_sync<NAMED>();
+    }
     // (b) the slot inside that chunk, sub-chunk by sub-chunk (64 candidates, 8 consecutive threads each).  Per round:
     //     every sub-chunk is reduced to its map for the current phase; warp 0 scans the 32 maps from the sub-chunk at
     //     which the exact sum is known, which gives the exact sum after every sub-chunk up to the one where the phase
@@ -1499,7 +1528,7 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     const int len = (int)min((int64_t)kChunk, a.n - start);
     uint32_t pb[kDrawIPT];
     load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
-    uint32_t bits = a.start_bits[chunk];
+    uint32_t bits = have_bits ? bits_known : a.start_bits[chunk];
     float* pv = cdf_s;                       // the chunk's probabilities, for the serial walks
     Pair* subm = rs.tot;                     // [32] one map per sub-chunk
     {
@@ -1520,7 +1549,7 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
             if ((lane & 7) + off < 8) m = compose(m, o);
         }
         if ((lane & 7) == 0) subm[threadIdx.x >> 3] = m;
-        __syncthreads();
+        draw_sync<NAMED>();
         if (warp == 0) {
             const Pair mine = lane >= cur ? subm[lane] : identity_pair();
             const Pair inc = warp_scan_pair(mine, lane);
@@ -1562,11 +1591,11 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
                 }
             }
         }
-        __syncthreads();
+        draw_sync<NAMED>();
         const bool done = rs.end_bits != 0u;
         const int val = rs.cross;
         const uint32_t nb = rs.next_bits;
-        __syncthreads();
+        draw_sync<NAMED>();
         if (done) {
             if (threadIdx.x == 0) chosen = start + val;
             break;
@@ -1574,7 +1603,7 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
         cur = val;
         bits = nb;
     }
-    __syncthreads();
+    draw_sync<NAMED>();
     // (d) payload row: everybody issues its first loads as soon as the slot is known; the scalar outputs ride along
     const int64_t pick = chosen;
     const bool copy = a.data && a.out_data;
