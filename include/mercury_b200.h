@@ -49,7 +49,8 @@ enum {
     MERCURY_ST_NONFINITE = 4,  /* multinomial: "probability entry = infinity or NaN"               */
     MERCURY_ST_ZERO_SUM = 8,   /* multinomial: "sum of probabilities <= 0"                         */
     MERCURY_ST_TOPK_TIES = 16, /* exponential race: more exact ties at the k-th key than buffered  */
-    MERCURY_ST_PEER_TIMEOUT = 32 /* peer exchange: a peer's word did not arrive within 4 s          */
+    MERCURY_ST_PEER_TIMEOUT = 32, /* peer exchange: a peer's word did not arrive within the bound   */
+    MERCURY_ST_INTERNAL = 64   /* a wait inside the one-kernel step ran into its 2 s bound (a bug)    */
 };
 
 /* layout of the 8-float statistics block written by mercury_pool_stats */
@@ -149,6 +150,17 @@ int mercury_gather_owned(const int64_t* idx, int64_t b, int64_t shard_lo, int64_
  * normal).  Guesses only choose which maps are precomputed, so any value must leave results
  * unchanged; the tests use it to force the mis-guess paths.  Process-global; not for production. */
 void mercury_test_set_guess_bias(double bias);
+
+/* Test hook, no counterpart in the reference: mercury_update_samples runs pools of small rows (<= 256 B of logits per
+ * candidate, <= 2 Mi candidates, <= 1024 draws, one EMA update) as ONE cooperative kernel, everything else as a chain
+ * of four kernels; both give the same bits.  mode 0 forces the chain, 1 the single kernel where it applies, -1 (default)
+ * follows the environment (MERCURY_FUSED=0 turns the single kernel off).  Process-global; not for production.
+ * mercury_debug_step_times copies to h_out128 (HOST, 128 values) what the last single-kernel step left in workspace
+ * `ws`: [0..8] %globaltimer stamps in ns -- start, CTA 0 scored, grid barrier passed, CTA 0 published its summaries,
+ * last CTA arrived (walker starts), walker loaded, walk done, draws published, CTA 0 done; [16..] clock64 << 4 | kind
+ * after each step of the walk (MERCURY_STEP_DBG=1).  It synchronises the device: a developer aid. */
+void mercury_test_set_fused(int mode);
+int mercury_debug_step_times(const void* ws, int64_t n, unsigned long long* h_out128);
 
 /* ---- sharded pools, totals-only exchange (north_star: "per-shard score totals and CDFs are exchanged
  * with NCCL allgather ... the global draw is resolved locally") ------------------------------------

@@ -15,7 +15,7 @@ ABI_VERSION = 2
 OK, ERR_ARG, ERR_CUDA, ERR_WORKSPACE = 0, -1, -2, -3
 F32, BF16 = 0, 1
 CDF_EXACT_SERIAL_F32, CDF_F64 = 0, 1
-ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES, ST_PEER_TIMEOUT = 1, 2, 4, 8, 16, 32
+ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES, ST_PEER_TIMEOUT, ST_INTERNAL = 1, 2, 4, 8, 16, 32, 64
 PEER_BOX_BYTES, PEER_HANDLE_BYTES = 4096, 64
 STAT_MEAN, STAT_EMA, STAT_SHIFT, STAT_TOTAL, STAT_CHAIN_TOTAL, STAT_COUNT = 0, 1, 2, 3, 4, 8
 STATIC_MAX_N = 1 << 22
@@ -60,6 +60,8 @@ SIGNATURES = {
     "mercury_gather_reweight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mercury_gather_owned": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mercury_test_set_guess_bias": (None, [c_f64]),
+    "mercury_test_set_fused": (None, [c_int]),
+    "mercury_debug_step_times": (c_int, [c_vp, c_i64, ctypes.POINTER(ctypes.c_ulonglong)]),
     "mercury_sum_scores": (c_int, [c_vp, c_i64, c_vp, c_vp, c_sz, c_vp]),
     "mercury_shard_select": (c_int, [c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp]),
     "mercury_score_head": (c_int, [c_vp, c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),

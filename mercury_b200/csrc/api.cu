@@ -125,6 +125,13 @@ extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, si
     int rc = check_ws(ws, ws_bytes, update_ws_bytes(a->n), "mercury_update_samples");
     if (rc) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (!scores) {  // small rows: the whole step is one persistent kernel
+        MB_CHECK_ARG(a->logits && a->labels && a->scores, "mercury_update_samples: logits / labels / scores are required");
+        MB_CHECK_ARG(a->c >= 1 && a->row_stride >= a->c, "mercury_update_samples: bad class count or row stride");
+        MB_CHECK_ARG(a->dtype == MERCURY_F32 || a->dtype == MERCURY_BF16, "mercury_update_samples: bad dtype");
+        rc = fused_step_launch(*a, ws, st);
+        if (rc <= 0) return rc;
+    }
     const double* part = nullptr;
     int per = 0;
     if (!scores) {

@@ -16,16 +16,20 @@
 //   4. `materialize` (or the fused draw kernel) rebuilds any chunk's exact prefix from its
 //      boundary value.
 // A wrong guess costs time, never correctness.
+#include <cooperative_groups.h>
 #include <math.h>
 
 #include <cstddef>
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <mutex>
+#include <utility>
 
 #include "chain.cuh"
 #include "common.cuh"
 #include "internal.cuh"
+#include "score_small.cuh"
 
 namespace mercury {
 
@@ -1646,9 +1650,12 @@ __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, doubl
     }
 }
 
+#include "step_fused.cuh"
+
 // workspace carving (all offsets 256-byte aligned)
 struct CdfWs {
     double* sums; double* approx; int* slotid; Summary* summaries; Pack* subs; uint32_t* start_bits; float* total;
+    StepCtrl* ctrl;  // whole-step layout only
     size_t bytes;
 };
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -1667,6 +1674,8 @@ inline CdfWs carve(void* ws, int64_t n, bool direct_subs = false, int compact_sl
     w.slotid = reinterpret_cast<int*>(p + off); off += align256(nchunks * 4);
     w.start_bits = reinterpret_cast<uint32_t*>(p + off); off += align256((nchunks + 1) * 4);
     w.total = reinterpret_cast<float*>(p + off); off += 256;
+    w.ctrl = nullptr;
+    if (direct_subs) { w.ctrl = reinterpret_cast<StepCtrl*>(p + off); off += align256(sizeof(StepCtrl)); }
     w.bytes = off;
     return w;
 }
@@ -1803,6 +1812,97 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
     return MERCURY_OK;
 }
 
+
+// ---- the whole step as one cooperative kernel (step_fused.cuh).  Returns 1 when the call does not fit that kernel (the
+// caller then runs the four-kernel chain), MERCURY_OK when it was launched, a negative error otherwise.
+int g_fused_mode = -1;  // test hook (mercury_test_set_fused): -1 = environment (MERCURY_FUSED, default on), 0 = off, 1 = on
+
+namespace {
+std::mutex g_fused_mu;
+std::map<std::pair<int, const void*>, int> g_fused_ctas;  // (device, kernel) -> co-resident CTAs per SM (0: cannot run)
+
+template <typename T, int CT>
+int fused_launch_typed(StepArgs& sa, int64_t want_ctas, cudaStream_t st) {
+    auto kern = fused_step_kernel<T, CT>;
+    const void* fn = reinterpret_cast<const void*>(kern);
+    int rc = ensure_dynamic_smem(fn, kStepSmemBytes, "fused_step_kernel smem attribute");
+    if (rc) return rc;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+    int per_sm;
+    {
+        std::lock_guard<std::mutex> lock(g_fused_mu);
+        auto it = g_fused_ctas.find(std::make_pair(dev, fn));
+        if (it == g_fused_ctas.end()) {
+            int occ = 0, coop = 0;
+            cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kStepThreads, kStepSmemBytes);
+            if (e == cudaSuccess) e = cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+            const int v = (e == cudaSuccess && coop && occ > 0) ? (occ > 3 ? 3 : occ) : 0;
+            it = g_fused_ctas.emplace(std::make_pair(dev, fn), v).first;
+        }
+        per_sm = it->second;
+    }
+    const int sms = device_sm_count();
+    if (per_sm <= 0 || sms <= 0) return 1;
+    static const int knob_per_sm = env_knob("MERCURY_STEP_CTAS", 3, 1, 3);   // developer knob: CTAs per SM
+    if (knob_per_sm < per_sm) per_sm = knob_per_sm;
+    const int grid = (int)min_i64((int64_t)per_sm * sms, want_ctas);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kStepThreads); cfg.dynamicSmemBytes = kStepSmemBytes; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, sa);
+    if (e != cudaSuccess) return cuda_fail(e, "fused_step_kernel launch");
+    return MERCURY_OK;
+}
+}  // namespace
+
+int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
+    static const int env_on = env_knob("MERCURY_FUSED", 1, 0, 1);
+    if (!(g_fused_mode < 0 ? env_on : g_fused_mode)) return 1;
+    if (a.scores_in || a.n_bounds != 0 || a.draw_only || a.peer_boxes || a.global_sums) return 1;
+    if (a.b > kStepMaxDraws || a.row_stride != a.c) return 1;
+    const int64_t elt = a.dtype == MERCURY_F32 ? 4 : 2, row_bytes = a.c * elt;
+    const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
+    if (row_bytes > 256 || nchunks > kStepMaxChunks) return 1;
+    if ((reinterpret_cast<uintptr_t>(a.logits) & 15) || (reinterpret_cast<uintptr_t>(a.labels) & 15)) return 1;
+    if (walk2_slots(nchunks) < 4) return 1;
+    const CdfWs w = carve(ws, a.n, true);
+    StepArgs sa{};
+    sa.logits = a.logits; sa.labels = a.labels; sa.n = a.n; sa.c = (int)a.c; sa.tile_rows = small_tile_rows(row_bytes);
+    sa.ignore_index = a.ignore_index; sa.scores = a.scores; sa.part = w.sums;
+    sa.ema_state = a.ema_state; sa.ema_first = a.ema_first; sa.ema_alpha = a.ema_alpha; sa.smooth_alpha = a.smooth_alpha; sa.stats = a.stats;
+    sa.nchunks = nchunks; sa.bias = g_guess_bias; sa.sums = w.summaries; sa.packs = reinterpret_cast<Pack2*>(w.subs);
+    sa.start_bits = w.start_bits; sa.total = w.total; sa.ctrl = w.ctrl; sa.status = a.status;
+    static const int dbg_flags = env_knob("MERCURY_STEP_DBG", 0, 0, 255);
+    sa.dbg_flags = dbg_flags;
+    if (small_smem_bytes(kStepStages, sa.tile_rows, row_bytes) > kStepSmemBytes) return 1;
+    DrawArgs& d = sa.d;
+    d.n_weight = a.n; d.idx_base = 0;
+    d.src = WeightSrc{a.scores, a.stats}; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total;
+    d.u = a.uniforms; d.b = a.b;
+    d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
+    d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
+    d.out_labels = a.out_labels; d.out_index = a.out_index;
+    const int64_t ntiles = (a.n + sa.tile_rows - 1) / sa.tile_rows;
+    const int64_t want = ntiles > a.b ? (ntiles > nchunks ? ntiles : nchunks) : (a.b > nchunks ? a.b : nchunks);
+    if (a.dtype == MERCURY_F32) {
+        if (a.c == 10) return fused_launch_typed<float, 10>(sa, want, st);
+        return fused_launch_typed<float, 0>(sa, want, st);
+    }
+    if (a.c == 10) return fused_launch_typed<__nv_bfloat16, 10>(sa, want, st);
+    return fused_launch_typed<__nv_bfloat16, 0>(sa, want, st);
+}
+
+// developer aid: the stamps the last fused step left in this workspace (16 phase times + 112 walk steps); synchronises
+int fused_step_times(const void* ws, int64_t n, unsigned long long* h_out128) {
+    const CdfWs w = carve(const_cast<void*>(ws), n, true);
+    cudaError_t e = cudaMemcpy(h_out128, w.ctrl->times, 128 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    return e == cudaSuccess ? MERCURY_OK : cuda_fail(e, "fused_step_times");
+}
+
 double* update_ws_part_sums(void* ws, int64_t n) { return carve(ws, n, true).sums; }
 
 }  // namespace mercury
@@ -1810,6 +1910,11 @@ double* update_ws_part_sums(void* ws, int64_t n) { return carve(ws, n, true).sum
 using namespace mercury;
 
 extern "C" void mercury_test_set_guess_bias(double bias) { g_guess_bias = bias; }
+extern "C" void mercury_test_set_fused(int mode) { g_fused_mode = mode; }
+extern "C" int mercury_debug_step_times(const void* ws, int64_t n, unsigned long long* h_out128) {
+    MB_CHECK_ARG(ws && n >= 1 && h_out128, "mercury_debug_step_times: bad arguments");
+    return fused_step_times(ws, n, h_out128);
+}
 
 extern "C" size_t mercury_pool_stats_workspace_bytes(int64_t n) { return cdf_ws_bytes(n); }
 

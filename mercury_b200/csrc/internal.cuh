@@ -21,6 +21,9 @@ int check_ws(void* ws, size_t have, size_t need, const char* who);
 size_t update_ws_bytes(int64_t n);
 double* update_ws_part_sums(void* ws, int64_t n);
 
+// the whole step as one cooperative kernel; 1 = not applicable to this call (run the kernel chain instead)
+int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st);
+
 int pool_stats_launch(const float* scores, int64_t n, const int64_t* h_bounds, int n_bounds, float* ema_state, int ema_first,
                       double ema_alpha, double smooth_alpha, float* stats, void* ws, cudaStream_t st, bool update_layout);
 

@@ -1,0 +1,794 @@
+// The whole step as ONE persistent cooperative kernel (included by cdf.cu, inside its anonymous namespace).
+//
+// Replaces the arithmetic of Trainer.update_samples (reference pytorch_collab.py:102-117) for pools of small rows
+// (<= 256 B of logits per candidate: the reference's 10-class head).  The four-kernel chain (score -> summarize ->
+// spine -> draw) spends most of its time between kernels and in a one-CTA serial walk; here the same work runs as
+// phases of one grid that stays resident:
+//   A  K1 (score_small_body): scores + the fp64 sum of every tile of scores;
+//      -- grid-wide barrier (cooperative groups) --
+//   B  every CTA: pool statistics (mean / EMA / shift / total, bit-identical in all CTAs), then for each of its chunks
+//      the 2-state map of the chunk in the guessed phase; a chunk in which the running sum may change binade also gets
+//      a Pack2: one map per 32-candidate sub-chunk for the guessed phase and the next, and the raw candidates of the
+//      sub-chunks in which the change should fall;
+//      -- every CTA arrives on a counter; the LAST one to arrive walks --
+//   C  the walker: loads all summaries + packs into shared memory (one round trip), walks the chain (chunk level as in
+//      spine_kernel; inside a pack the 64 sub-chunk increments are scanned by the warp, the first sub-chunk whose end
+//      leaves the phase is summed with the reference's own loop, 32 dependent fp32 adds), writes the exact boundary
+//      values, finds the chunk of every uniform and publishes (chunk, boundary value) per draw;
+//   D  every CTA: polls the word of its draws, rebuilds that chunk's prefix (draw_resolve) and gathers the row.
+// Results are bit-identical to the four-kernel chain (same statistics, same p, same chain); a contradicted guess falls
+// back to the same general code (serial_chunk).
+#pragma once
+// (cdf.cu includes <cooperative_groups.h> at global scope)
+namespace cg = cooperative_groups;
+
+constexpr int kStepNT = 256;                     // worker threads: warps 0..7 (K1's consumers); warp 8 is K1's producer
+constexpr int kStepThreads = kStepNT + kProducerThreads;
+constexpr int kStepStages = 3;
+constexpr int kStepMaxChunks = 1024;             // pools of up to 2 Mi candidates
+constexpr int kStepMaxDraws = 1024;
+constexpr int kStepMaxPacks = 64;                // flagged chunks that get a pack (beyond: the general code)
+constexpr int kStepMaxEvents = 192;
+constexpr size_t kStepSmemBytes = 70 * 1024;
+constexpr int kSub2 = 32, kSubs2 = kChunk / kSub2;
+constexpr int kRaw2 = 12;
+constexpr uint32_t kBadInc = kSatCap;            // "no plain increment known for this phase": forces a stop in the scan
+static_assert(kSubs2 == 64, "two sub-chunks per lane of the walking warp");
+
+struct __align__(128) Pack2 {
+    uint32_t e[kSubs2];            // guessed phase | kFlag (the change may fall here) | kTie0 | kTie1; kAnyPhase: all zero
+    uint2 q0[kSubs2];              // the sub-chunk's map in its guessed phase
+    uint2 q1[kSubs2];              // ... and in the phase above
+    uint8_t rawsub[16];            // sub-chunks whose candidates are in raw[] (0xff: unused)
+    uint32_t raw[kRaw2][kSub2];    // 16-byte aligned
+};
+static_assert(sizeof(Pack2) == 2944 && offsetof(Pack2, raw) % 16 == 0 && offsetof(Pack2, q0) % 16 == 0, "Pack2 layout");
+
+struct StepCtrl {
+    unsigned int nflag;            // pack slots handed out
+    unsigned int arrive;           // CTAs that published their summaries
+    unsigned int pad_[30];
+    unsigned long long times[16];  // developer aid: %globaltimer at the phase changes (CTA 0 and the walker)
+    unsigned long long evt[112];   // developer aid: clock64 after each of the walk's first steps (kind in the low 4 bits)
+    unsigned long long dinfo[kStepMaxDraws];  // per draw: 1 << 63 | chunk << 32 | boundary bits
+};
+constexpr unsigned long long kStepSpinNs = 2000000000ull;  // no wait may last this long: report instead of hanging the GPU
+
+struct StepArgs {
+    // K1
+    const void* logits; const int64_t* labels; int64_t n; int c; int tile_rows; int64_t ignore_index; float* scores;
+    double* part;                  // [ntiles] fp64 sums of the tiles' scores
+    // statistics
+    float* ema_state; int ema_first; double ema_alpha, smooth_alpha; float* stats;
+    // chain
+    int nchunks; double bias; Summary* sums; Pack2* packs; uint32_t* start_bits; float* total; StepCtrl* ctrl;
+    int32_t* status;
+    int dbg_flags;                 // developer aid (MERCURY_STEP_DBG): 1 = stamp the walk's steps
+    // draws
+    DrawArgs d;
+};
+
+__device__ __forceinline__ void wsync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ uint2 lds_u32x2(uint32_t saddr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ uint4 lds_u32x4(uint32_t saddr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// phase B: one chunk -> Summary (+ Pack2)
+struct Sum2Smem {
+    Pair wt[kStepNT / 32];
+    float wsum[kStepNT / 32];
+    int wnz[kStepNT / 32];
+    unsigned int wflag[kStepNT / 32];
+    double dred[2][kStepNT / 32];
+    double own[8];
+    int slot;
+};
+
+__device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const float (&raw)[8], double pre, double own, float shift,
+                                                 float total, Sum2Smem& sm) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t start = (int64_t)c * kChunk;
+    const int len = (int)min((int64_t)kChunk, a.n - start);
+    const double a_lo = (pre + (double)start * (double)shift) / (double)total;
+    const double a_hi = a_lo + (own + (double)len * (double)shift) / (double)total;
+    uint32_t pb[8];
+    {
+        const int base = threadIdx.x * 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) pb[k] = base + k < len ? f2b(__fdiv_rn(__fadd_rn(raw[k], shift), total)) : 0u;
+    }
+    uint32_t e;
+    const bool flagged = guess_span(a_lo, a_hi, a.bias, &e, chunk_margin(a.nchunks));  // block-uniform
+    // a flagged chunk claims a pack slot; the atomic's round trip hides behind the arithmetic below
+    unsigned int slot_u = 0xffffffffu;
+    if (flagged && threadIdx.x == 0) slot_u = atomicAdd(&a.ctrl->nflag, 1u);
+    Pair a0 = identity_pair();
+    int bad = 0;
+    bool nz = false;
+    float tsum = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float x = b2f(pb[k]);
+        if (!(x >= 0.f)) bad |= MERCURY_ST_NEGATIVE;
+        else if (isinf(x)) bad |= MERCURY_ST_NONFINITE;
+        nz |= pb[k] != 0u;
+        tsum += x;
+        a0 = compose(a0, addend_pair_fast(pb[k], e));
+    }
+    if (bad) atomicOr(a.status, bad);
+    const unsigned nzmask = __ballot_sync(0xffffffffu, nz);
+    if (__ballot_sync(0xffffffffu, a0.d0 != a0.d1) == 0u) {
+        a0.d0 = a0.d1 = sat(__reduce_add_sync(0xffffffffu, a0.d0));
+    } else {
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            Pair o0;
+            o0.d0 = __shfl_down_sync(0xffffffffu, a0.d0, off); o0.d1 = __shfl_down_sync(0xffffffffu, a0.d1, off);
+            if (lane + off < 32) a0 = compose(a0, o0);
+        }
+    }
+    float inc = tsum;  // inclusive scan of the thread sums (approximate: only feeds the sub-chunk guesses)
+    if (flagged) {
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const float o = __shfl_up_sync(0xffffffffu, inc, off);
+            if (lane >= off) inc += o;
+        }
+    }
+    wsync();  // (protects sm against the previous chunk's readers)
+    if (lane == 0) { sm.wt[warp] = a0; sm.wnz[warp] = nzmask != 0u; }
+    if (lane == 31) sm.wsum[warp] = inc;
+    if (threadIdx.x == 0) sm.slot = flagged ? (slot_u < (unsigned)kStepMaxPacks ? (int)slot_u : -2) : -1;
+    wsync();
+    const int slot = sm.slot;
+    if (threadIdx.x == 0) {
+        Pair t0 = identity_pair();
+        int any = 0;
+#pragma unroll
+        for (int i = 0; i < kStepNT / 32; ++i) { t0 = compose(t0, sm.wt[i]); any |= sm.wnz[i]; }
+        Summary s;
+        s.e = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u) | (flagged && slot < 0 ? kNoPack : 0u) | (t0.d0 != t0.d1 ? kTie0 : 0u);
+        s.q[0] = t0;
+        s.q[1] = Pair{kSatCap, kSatCap};
+        s.pad[0] = (uint32_t)slot; s.pad[1] = s.pad[2] = 0;
+        a.sums[c] = s;
+    }
+    if (slot < 0) return;
+    // ---- per sub-chunk: 4 consecutive threads = 32 candidates
+    float pre_f = 0.f;
+    for (int i = 0; i < warp; ++i) pre_f += sm.wsum[i];
+    const float t_lo = pre_f + inc - tsum, t_hi = pre_f + inc;
+    const int lead = lane & ~3;
+    const float s_lo = __shfl_sync(0xffffffffu, t_lo, lead), s_hi = __shfl_sync(0xffffffffu, t_hi, lead + 3);
+    const bool sub_nz = ((nzmask >> lead) & 0xfu) != 0u;
+    uint32_t es;
+    const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, a.bias, &es, sub_margin(a.nchunks)) && sub_nz;
+    Pair m0 = identity_pair(), m1 = identity_pair();
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        m0 = compose(m0, addend_pair_fast(pb[k], es));
+        m1 = compose(m1, addend_pair_fast(pb[k], es + 1u));
+    }
+#pragma unroll
+    for (int off = 1; off < 4; off <<= 1) {
+        Pair o0, o1;
+        o0.d0 = __shfl_down_sync(0xffffffffu, m0.d0, off, 4); o0.d1 = __shfl_down_sync(0xffffffffu, m0.d1, off, 4);
+        o1.d0 = __shfl_down_sync(0xffffffffu, m1.d0, off, 4); o1.d1 = __shfl_down_sync(0xffffffffu, m1.d1, off, 4);
+        if ((lane & 3) + off < 4) { m0 = compose(m0, o0); m1 = compose(m1, o1); }
+    }
+    Pack2* pk = a.packs + slot;
+    const int my_sub = threadIdx.x >> 2;
+    if ((lane & 3) == 0) {
+        pk->e[my_sub] = (sub_nz ? es : kAnyPhase) | (sub_flagged ? kFlag : 0u) | (m0.d0 != m0.d1 ? kTie0 : 0u) | (m1.d0 != m1.d1 ? kTie1 : 0u);
+        pk->q0[my_sub] = make_uint2(m0.d0, m0.d1);
+        pk->q1[my_sub] = make_uint2(m1.d0, m1.d1);
+    }
+    // which sub-chunks ship their raw candidates: the first kRaw2 flagged ones
+    const unsigned lead_flags = __ballot_sync(0xffffffffu, (lane & 3) == 0 && sub_flagged);  // bits 0,4,...,28
+    if (lane == 0) {
+        unsigned int eight = 0u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) eight |= ((lead_flags >> (4 * i)) & 1u) << i;
+        sm.wflag[warp] = eight;
+    }
+    wsync();
+    unsigned long long fmask = 0ull;
+#pragma unroll
+    for (int i = 0; i < kStepNT / 32; ++i) fmask |= (unsigned long long)sm.wflag[i] << (8 * i);
+    const int my_rank = __popcll(fmask & ((1ull << my_sub) - 1ull));
+    if (((fmask >> my_sub) & 1ull) && my_rank < kRaw2) {
+        uint4* dst = reinterpret_cast<uint4*>(&pk->raw[my_rank][(threadIdx.x & 3) * 8]);
+        dst[0] = make_uint4(pb[0], pb[1], pb[2], pb[3]);
+        dst[1] = make_uint4(pb[4], pb[5], pb[6], pb[7]);
+        if ((lane & 3) == 0) pk->rawsub[my_rank] = (uint8_t)my_sub;
+    }
+    if (threadIdx.x < 16 && (int)threadIdx.x >= min(__popcll(fmask), kRaw2)) pk->rawsub[threadIdx.x] = 0xff;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// phase C: the walk.  One warp walks, and it must stay CONVERGED: every statement below is executed by all 32 lanes
+// (stores of a warp-uniform value by every lane instead of `if (lane == 0)`), because a warp that has split pays
+// hundreds of cycles for every shuffle and vote.  What the rare general paths need lives in shared memory (WalkEnv), so
+// that the common path keeps its state in registers.
+struct WalkEnv {
+    WeightSrc src; int64_t n; float shift, totalw;
+    const unsigned long long* pc; const uint32_t* ce; const uint32_t* qd0; const uint32_t* qd1; const uint32_t* stopw;
+    const uint8_t* slot_of; uint32_t* sb; uint32_t* stage;
+    const Pack2* slots; Pack2* spare; const Pack2* packs_g; const Summary* sums; uint32_t* start_bits;
+};
+
+// the reference's loop over 32 consecutive candidates held in shared memory, run redundantly by every lane
+__device__ __forceinline__ uint32_t serial32(uint32_t b, uint32_t saddr) {
+    uint4 q[kSub2 / 4];
+#pragma unroll
+    for (int i = 0; i < kSub2 / 4; ++i) q[i] = lds_u32x4(saddr + 16u * i);
+    float s = b2f(b);
+#pragma unroll
+    for (int i = 0; i < kSub2 / 4; ++i) {
+        s = __fadd_rn(s, b2f(q[i].x));
+        s = __fadd_rn(s, b2f(q[i].y));
+        s = __fadd_rn(s, b2f(q[i].z));
+        s = __fadd_rn(s, b2f(q[i].w));
+    }
+    return f2b(s);
+}
+
+// candidates of sub-chunk f of chunk c that the pack does not carry: from the scores, into the stage line
+__device__ __noinline__ uint32_t stage_sub2(const WalkEnv* env, int c, int f, int lane) {
+    const int64_t i0 = (int64_t)c * kChunk + f * kSub2 + lane;
+    float shift, total;
+    shift = env->shift; total = env->totalw;
+    env->stage[lane] = i0 < env->n ? f2b(env->src.get(i0, shift, total)) : 0u;
+    __syncwarp();
+    return smem_u32(env->stage);
+}
+
+// serial pass over sub-chunk f of chunk c: raw candidates from the pack (shared memory, address P) if it carries them
+__device__ __forceinline__ uint32_t serial_sub2(const WalkEnv* env, uint32_t P, int c, int f, uint32_t b, int lane) {
+    const uint32_t rs = lds_u32(P + (uint32_t)offsetof(Pack2, rawsub) + 4u * (lane & 3));   // lane -> rawsub[(lane & 3) * 4 + ((lane >> 2) & 3)]
+    const uint32_t mine = (rs >> (8 * ((lane >> 2) & 3))) & 0xffu;
+    const unsigned hit = __ballot_sync(0xffffffffu, lane < 16 && mine == (uint32_t)f);
+    uint32_t saddr;
+    if (hit) {
+        const int l = __ffs(hit) - 1, r = (l & 3) * 4 + ((l >> 2) & 3);
+        saddr = P + (uint32_t)offsetof(Pack2, raw) + (uint32_t)r * (kSub2 * 4u);
+    } else {
+        saddr = stage_sub2(env, c, f, lane);
+    }
+    b = serial32(b, saddr);
+    __syncwarp();
+    return b;
+}
+
+// the increment of a sub-chunk while the running sum is in phase E, or kBadInc if no plain one is known (branch-free)
+__device__ __forceinline__ uint32_t sub_inc(uint32_t e, uint32_t d00, uint32_t d01, uint32_t d10, uint32_t d11, uint32_t E) {
+    const uint32_t g = e & kPhaseMask;
+    const uint32_t v0 = d00 == d01 ? d00 : kBadInc, v1 = d10 == d11 ? d10 : kBadInc;
+    const uint32_t r = g == E ? v0 : (g + 1u == E ? v1 : kBadInc);
+    return g == kAnyPhase ? 0u : r;
+}
+
+// a flagged chunk: the 64 sub-chunk increments for the current phase are scanned by the warp; the first sub-chunk whose
+// end would leave the phase (or that has no plain increment) is treated on its own -- a 2-state map if it only has exact
+// ties, else the serial loop -- and the scan resumes behind it in whatever phase the sum is then.  P: the pack's address
+// in SHARED memory.
+__device__ __forceinline__ uint32_t run_pack2(const WalkEnv* env, uint32_t P, int c, uint32_t b, int lane) {
+    const uint2 ee = lds_u32x2(P + (uint32_t)offsetof(Pack2, e) + 8u * lane);
+    const uint4 q0 = lds_u32x4(P + (uint32_t)offsetof(Pack2, q0) + 16u * lane);  // maps of sub-chunks 2*lane, 2*lane+1 in their guessed phase
+    const uint4 q1 = lds_u32x4(P + (uint32_t)offsetof(Pack2, q1) + 16u * lane);  // ... and in the phase above
+    uint32_t E = phase_of(b), S = b - (E << 23);
+    int k = 0;                                                       // first sub-chunk not yet applied
+    for (;;) {
+        const uint32_t w0 = 2 * lane >= k ? sub_inc(ee.x, q0.x, q0.y, q1.x, q1.y, E) : 0u;
+        const uint32_t w1 = 2 * lane + 1 >= k ? sub_inc(ee.y, q0.z, q0.w, q1.z, q1.w, E) : 0u;
+        uint32_t v = w0 + w1;                                        // (64 * 2^25 fits in 32 bits)
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, v, off);
+            if (lane >= off) v += o;
+        }
+        const uint32_t s_in = S + (v - (w0 + w1));                   // running sum before sub-chunk 2*lane
+        const uint32_t s_mid = s_in + w0, s_out = s_mid + w1;
+        const unsigned over0 = __ballot_sync(0xffffffffu, s_mid >= kPhaseLimit);
+        const unsigned over1 = __ballot_sync(0xffffffffu, s_out >= kPhaseLimit);
+        if ((over0 | over1) == 0u) { S = __shfl_sync(0xffffffffu, s_out, 31); break; }
+        const int f0 = over0 ? 2 * (__ffs(over0) - 1) : kSubs2, f1 = over1 ? 2 * (__ffs(over1) - 1) + 1 : kSubs2;
+        const int f = min(f0, f1);
+        const int fl = f >> 1;
+        const bool odd = f & 1;
+        const uint32_t Sf = __shfl_sync(0xffffffffu, odd ? s_mid : s_in, fl);
+        const uint32_t ef = __shfl_sync(0xffffffffu, odd ? ee.y : ee.x, fl);
+        const uint32_t qa = __shfl_sync(0xffffffffu, odd ? q0.z : q0.x, fl), qb = __shfl_sync(0xffffffffu, odd ? q0.w : q0.y, fl);
+        const uint32_t qc = __shfl_sync(0xffffffffu, odd ? q1.z : q1.x, fl), qd = __shfl_sync(0xffffffffu, odd ? q1.w : q1.y, fl);
+        const uint32_t g = ef & kPhaseMask;
+        // exact ties inside: the 2-state map, if the sum stays in the phase
+        const uint32_t mx = g == E ? qa : qc, my = g == E ? qb : qd;
+        const uint32_t Sn = Sf + ((Sf & 1u) ? my : mx);
+        const bool by_map = g != kAnyPhase && (g == E || g + 1u == E) && mx != my && Sn < kPhaseLimit;
+        if (by_map) S = Sn;
+        else {
+            b = serial_sub2(env, P, c, f, bits_of(E, Sf), lane);
+            E = phase_of(b); S = b - (E << 23);
+        }
+        k = f + 1;
+        if (k >= kSubs2) break;
+    }
+    return bits_of(E, S);
+}
+
+// a pack that is not among the prefetched ones: copied into the spare slot; returns its shared address
+__device__ __noinline__ uint32_t fetch_pack2(const WalkEnv* env, int slot_global, int lane) {
+    const uint4* g4 = reinterpret_cast<const uint4*>(env->packs_g + slot_global);
+    uint4* s4 = reinterpret_cast<uint4*>(env->spare);
+    for (int i = lane; i < (int)(sizeof(Pack2) / 16); i += 32) s4[i] = __ldcg(g4 + i);
+    __syncwarp();
+    return smem_u32(env->spare);
+}
+
+// one whole chunk summed the general way (serial_chunk of the kernel chain); only reached when a guess was contradicted
+__device__ __noinline__ uint32_t slow_chunk2(const WalkEnv* env, int c, uint32_t b, int lane) {
+    SpineCtx x;
+    x.src = env->src; x.n = env->n; x.shift = env->shift; x.totalw = env->totalw; x.lane = lane; x.dbg = nullptr; x.dbgt = nullptr;
+    x.prof_ = false; x.pacc = nullptr; x.stage = env->stage;
+    return serial_chunk<false>(x, c, b);
+}
+
+// chunks [c, c_end) the general way (no precompiled step, or its guard was contradicted); records their boundary values
+__device__ __noinline__ uint32_t walk_general2(const WalkEnv* env, int c, int c_end, uint32_t b, int lane) {
+    while (c < c_end) {
+        const uint32_t E = phase_of(b), S = b - (E << 23);
+        const uint32_t ec = env->ce[c], g = ec & kPhaseMask;
+        env->start_bits[c] = b; env->sb[c] = b;   // (every lane stores the same word)
+        if (ec & kFlag) {
+            const int sl = (int)env->slot_of[c] - 1;
+            const uint32_t P = sl >= 0 ? smem_u32(&env->slots[sl]) : fetch_pack2(env, (int)env->sums[c].pad[0], lane);
+            b = run_pack2(env, P, c, b, lane);
+            __syncwarp();
+            ++c;
+            continue;
+        }
+        if (g == kAnyPhase) { ++c; continue; }
+        if (g != E || (ec & kNoPack)) { b = slow_chunk2(env, c, b, lane); ++c; continue; }
+        if (ec & kTie0) {
+            const uint32_t Sn = apply(Pair{env->qd0[c], env->qd1[c]}, S);
+            if (Sn >= kPhaseLimit) b = slow_chunk2(env, c, b, lane); else b = bits_of(E, Sn);
+            ++c;
+            continue;
+        }
+        const int s = min(next_bit(env->stopw, c + 1), c_end);
+        const unsigned long long base = env->pc[c];
+        const unsigned long long Sn = (unsigned long long)S + (env->pc[s] - base);
+        int end = s;
+        if (Sn >= kPhaseLimit) {
+            int lo = c, hi = s;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if ((unsigned long long)S + (env->pc[mid] - base) >= kPhaseLimit) hi = mid; else lo = mid;
+            }
+            end = lo;
+        }
+        for (int k = c + 1 + lane; k < end; k += 32) {
+            const uint32_t v = bits_of(E, S + (uint32_t)(env->pc[k] - base));
+            env->start_bits[k] = v; env->sb[k] = v;
+        }
+        __syncwarp();
+        if (end == s) { b = bits_of(E, (uint32_t)Sn); c = s; continue; }
+        const uint32_t bf = bits_of(E, S + (uint32_t)(env->pc[end] - base));
+        env->start_bits[end] = bf; env->sb[end] = bf;
+        b = slow_chunk2(env, end, bf, lane);
+        c = end + 1;
+    }
+    return b;
+}
+
+__host__ __device__ inline size_t walk2_fixed_bytes(int nchunks) {
+    size_t b = (size_t)(nchunks + 1) * 8 + (size_t)nchunks * 13 + (size_t)((nchunks + 32) / 32) * 4 + (size_t)(nchunks + 1) * 4;
+    b = (b + 127) & ~(size_t)127;
+    return b + (size_t)kStageWords * 4 + (size_t)kStepMaxEvents * 20;
+}
+__host__ __device__ inline int walk2_slots(int nchunks) {
+    const long fit = ((long)kStepSmemBytes - (long)walk2_fixed_bytes(nchunks) - 256) / (long)sizeof(Pack2) - 1;
+    return (int)(fit > 16 ? 16 : fit);
+}
+
+struct WalkStatic {
+    WalkEnv env;
+    int nev, carry_ev;
+    unsigned long long wtot[kStepNT / 32];
+    unsigned long long carry_s;
+    int wcnt[kStepNT / 32];
+};
+
+// The walker (one CTA, 256 threads + named barrier 1).  Leaves the boundary values in global memory, and publishes the
+// chunk of every draw.
+__device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm, WalkStatic& ws, float stat_shift, float stat_total,
+                                            float stat_ema) {
+    const int nchunks = a.nchunks;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);
+    uint32_t* ce = reinterpret_cast<uint32_t*>(pc + nchunks + 1);
+    uint32_t* qd0 = ce + nchunks; uint32_t* qd1 = qd0 + nchunks;
+    uint32_t* stopw = qd1 + nchunks;
+    uint32_t* sb = stopw + (nchunks + 32) / 32;                        // [nchunks+1] boundary values
+    uint8_t* slot_of = reinterpret_cast<uint8_t*>(sb + nchunks + 1);
+    size_t off = (size_t)(nchunks + 1) * 8 + (size_t)nchunks * 13 + (size_t)((nchunks + 32) / 32) * 4 + (size_t)(nchunks + 1) * 4;
+    off = (off + 127) & ~(size_t)127;
+    const int max_slots = walk2_slots(nchunks);
+    Pack2* slots = reinterpret_cast<Pack2*>(sm + off);
+    Pack2* spare = slots + max_slots;
+    uint32_t* stage = reinterpret_cast<uint32_t*>(sm + off + (size_t)(max_slots + 1) * sizeof(Pack2));
+    uint4* evs = reinterpret_cast<uint4*>(stage + kStageWords);
+    uint32_t* evb = reinterpret_cast<uint32_t*>(evs + kStepMaxEvents);
+
+    // ---- everything in one round trip: the packs (first max_slots slots, whether used or not) and the summaries
+    if (tid == 0) {
+        ws.carry_s = 0ull; ws.carry_ev = 0;
+        WalkEnv& e = ws.env;
+        e.src = a.d.src; e.n = a.n; e.shift = stat_shift; e.totalw = stat_total;
+        e.pc = pc; e.ce = ce; e.qd0 = qd0; e.qd1 = qd1; e.stopw = stopw; e.slot_of = slot_of; e.sb = sb; e.stage = stage;
+        e.slots = slots; e.spare = spare; e.packs_g = a.packs; e.sums = a.sums; e.start_bits = a.start_bits;
+    }
+    {
+        constexpr int kPackVecs = (int)(sizeof(Pack2) / 16);
+        const uint4* g4 = reinterpret_cast<const uint4*>(a.packs);
+        uint4* s4 = reinterpret_cast<uint4*>(slots);
+        const int total_vecs = min(max_slots, kStepMaxPacks) * kPackVecs;
+        for (int i0 = tid; i0 < total_vecs; i0 += 8 * kStepNT) {
+            uint4 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const int i = i0 + k * kStepNT; if (i < total_vecs) v[k] = __ldcg(g4 + i); }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const int i = i0 + k * kStepNT; if (i < total_vecs) s4[i] = v[k]; }
+        }
+    }
+    wsync();
+    for (int c0 = 0; c0 < nchunks; c0 += kStepNT) {
+        const int c = c0 + tid;
+        unsigned long long inc = 0ull;
+        if (c < nchunks) {
+            const uint4 lo = __ldcg(reinterpret_cast<const uint4*>(a.sums + c));        // e, q0.d0, q0.d1, q1.d0
+            const uint32_t slot = __ldcg(reinterpret_cast<const uint32_t*>(a.sums + c) + 5);  // pad[0]
+            ce[c] = lo.x; qd0[c] = lo.y; qd1[c] = lo.z;
+            slot_of[c] = ((lo.x & kFlag) && (int)slot < max_slots) ? (uint8_t)(slot + 1) : 0;
+            inc = lo.y;
+        }
+        const unsigned long long mine = inc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        if (lane == 31) ws.wtot[warp] = inc;
+        wsync();
+        unsigned long long pre = ws.carry_s;
+        for (int i = 0; i < warp; ++i) pre += ws.wtot[i];
+        if (c < nchunks) pc[c] = pre + inc - mine;
+        wsync();
+        if (tid == kStepNT - 1) ws.carry_s = pre + inc;
+        wsync();
+    }
+    if (tid == 0) pc[nchunks] = ws.carry_s;
+    // stop mask: chunks that need individual treatment, or where the guess changes
+    for (int w0 = 0; w0 < (nchunks + 32) / 32; w0 += kStepNT / 32) {
+        const int c = (w0 + warp) * 32 + lane;
+        bool stop = false;
+        if (c < nchunks) {
+            const uint32_t e = ce[c], g = e & kPhaseMask;
+            stop = (e & (kFlag | kTie0 | kNoPack)) != 0u;
+            if (c > 0) { const uint32_t gp = ce[c - 1] & kPhaseMask; if (g != kAnyPhase && gp != kAnyPhase && g != gp) stop = true; }
+        }
+        if (c == nchunks) stop = true;  // sentinel
+        const unsigned bits = __ballot_sync(0xffffffffu, stop);
+        if (lane == 0 && w0 + warp < (nchunks + 32) / 32) stopw[w0 + warp] = bits;
+    }
+    wsync();
+    // precompiled chunk-level walk (as in spine_kernel)
+    for (int c0 = 0; c0 < nchunks; c0 += kStepNT) {
+        const int c = c0 + tid;
+        bool start = false;
+        if (c < nchunks) start = c == 0 || ((stopw[c >> 5] >> (c & 31)) & 1u) || (ce[c - 1] & (kFlag | kTie0 | kNoPack)) != 0u;
+        const unsigned bal = __ballot_sync(0xffffffffu, start);
+        if (lane == 0) ws.wcnt[warp] = __popc(bal);
+        wsync();
+        int idx = ws.carry_ev + __popc(bal & ((1u << lane) - 1u));
+        for (int i = 0; i < warp; ++i) idx += ws.wcnt[i];
+        if (start && idx < kStepMaxEvents) {
+            const uint32_t e = ce[c];
+            uint4 ev;
+            if (e & kFlag) ev = make_uint4(kEvPack, (uint32_t)c | ((uint32_t)(c + 1) << 16), 0u, 0u);
+            else if (e & kNoPack) ev = make_uint4(kEvSlow, (uint32_t)c | ((uint32_t)(c + 1) << 16), 0u, 0u);
+            else if (e & kTie0) ev = make_uint4(kEvMap | ((e & kPhaseMask) << 8), (uint32_t)c | ((uint32_t)(c + 1) << 16), qd0[c], qd1[c]);
+            else {
+                const int s = next_bit(stopw, c + 1);
+                uint32_t g = kAnyPhase;
+                for (int k = c; k < s && g == kAnyPhase; ++k) g = ce[k] & kPhaseMask;
+                const unsigned long long inc = pc[s] - pc[c];
+                ev = make_uint4(kEvAdd | (g << 8), (uint32_t)c | ((uint32_t)s << 16), (uint32_t)inc, (uint32_t)(inc >> 32));
+            }
+            evs[idx] = ev;
+        }
+        wsync();
+        if (tid == kStepNT - 1) ws.carry_ev = idx + (start ? 1 : 0);
+        wsync();
+    }
+    if (tid == 0) ws.nev = ws.carry_ev;
+    wsync();
+    const int nev = ws.nev;
+    const bool use_events = nev <= kStepMaxEvents;
+    if (tid == 32) a.ctrl->times[5] = global_ns();   // (a thread of another warp: the walking warp stays converged)
+
+    const int walk_warp = (a.dbg_flags >> 4) & 7;    // developer aid: which warp walks (default 0)
+    if (warp == walk_warp) {
+        const WalkEnv* env = &ws.env;
+        const bool stamp = a.dbg_flags & 1;
+        __syncwarp();
+        if (a.dbg_flags & 2) {   // developer aid: how fast does this warp run right now?
+            long long c0 = clock64();
+            uint32_t xx = (uint32_t)c0;
+#pragma unroll 1
+            for (int r = 0; r < 16; ++r) xx += __shfl_up_sync(0xffffffffu, xx, 1);
+            long long c1 = clock64();
+            float ff = __uint_as_float(xx & 0x3fffffffu);
+#pragma unroll
+            for (int r = 0; r < 64; ++r) ff = __fadd_rn(ff, 1.5f);
+            long long c2 = clock64();
+            a.ctrl->evt[104] = c1 - c0; a.ctrl->evt[105] = c2 - c1; a.ctrl->evt[108] = xx + __float_as_uint(ff);
+        }
+        uint32_t b = 0u;
+        if (!use_events) {
+            b = walk_general2(env, 0, nchunks, b, lane);
+        } else {
+            uint32_t E = 0u, S = 0u;
+            if (stamp) a.ctrl->evt[0] = (unsigned long long)clock64() << 4;
+            for (int i = 0; i < nev; ++i) {
+                const uint4 ev = evs[i];
+                if (stamp && i > 0 && i < 100) a.ctrl->evt[i] = ((unsigned long long)clock64() << 4) | (evs[i - 1].x & 0xfu);
+                const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
+                const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);
+                if (kind == kEvAdd) {
+                    const unsigned long long Sn = (unsigned long long)S + (((unsigned long long)ev.w << 32) | ev.z);
+                    if ((ph == E || ph == kAnyPhase) && Sn < kPhaseLimit) {
+                        evb[i] = bits_of(E, S);   // boundary values of [c, s): filled in by the whole CTA afterwards
+                        S = (uint32_t)Sn;
+                        continue;
+                    }
+                } else if (kind == kEvMap) {
+                    const uint32_t Sn = S + ((S & 1u) ? ev.w : ev.z);
+                    if (ph == E && Sn < kPhaseLimit) {
+                        a.start_bits[c] = bits_of(E, S); sb[c] = bits_of(E, S);
+                        S = Sn;
+                        continue;
+                    }
+                } else if (kind == kEvPack) {
+                    b = bits_of(E, S);
+                    a.start_bits[c] = b; sb[c] = b;
+                    const int sl = (int)slot_of[c] - 1;
+                    const uint32_t P = sl >= 0 ? smem_u32(&slots[sl]) : fetch_pack2(env, (int)a.sums[c].pad[0], lane);
+                    b = run_pack2(env, P, c, b, lane);
+                    __syncwarp();
+                    E = phase_of(b); S = b - (E << 23);
+                    continue;
+                }
+                // a contradicted guard, or a chunk without a shortcut: the general walk over this step's chunks
+                evs[i].x = kEvSlow;  // (so that the fill below skips it)
+                __syncwarp();
+                b = walk_general2(env, c, s, bits_of(E, S), lane);
+                E = phase_of(b); S = b - (E << 23);
+            }
+            b = bits_of(E, S);
+            if (stamp && nev < 100) a.ctrl->evt[nev] = ((unsigned long long)clock64() << 4) | (evs[nev - 1].x & 0xfu);
+        }
+        // (every lane writes the same words)
+        *a.ema_state = stat_ema;  // EMAverage.value for the next call (util.py:207-213)
+        a.start_bits[nchunks] = b; sb[nchunks] = b;
+        const float total = b2f(b);
+        *a.total = total;
+        a.stats[MERCURY_STAT_CHAIN_TOTAL] = total;
+        if (lane == 0) {
+            if (!(total > 0.f)) atomicOr(a.status, MERCURY_ST_ZERO_SUM);
+            else if (isinf(total)) atomicOr(a.status, MERCURY_ST_NONFINITE);
+            a.ctrl->times[6] = global_ns();
+            a.ctrl->times[12] = (unsigned long long)nev;
+        }
+    }
+    wsync();
+    // ---- boundary values inside the additive steps (whole CTA, one warp per step)
+    if (use_events) {
+        for (int i = warp; i < nev; i += kStepNT / 32) {
+            const uint4 ev = evs[i];
+            if ((ev.x & 0xffu) != kEvAdd) continue;
+            const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);
+            const uint32_t b0 = evb[i], E = phase_of(b0), S = b0 - (E << 23);
+            const unsigned long long base = pc[c];
+            for (int k = c + lane; k < s; k += 32) {
+                const uint32_t v = bits_of(E, S + (uint32_t)(pc[k] - base));
+                a.start_bits[k] = v; sb[k] = v;
+            }
+        }
+    }
+    __threadfence();
+    wsync();
+    // ---- the chunk of every draw: first chunk whose last cdf value is not below u (ATen's lower bound), then publish
+    const float total = b2f(sb[nchunks]);
+    for (int64_t j = tid; j < a.d.b; j += kStepNT) {
+        const double uj = a.d.u[j];
+        int lo = 0, hi = nchunks - 1;          // answer in [lo, hi]
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if ((double)__fdiv_rn(b2f(sb[mid + 1]), total) < uj) lo = mid + 1; else hi = mid;
+        }
+        st_relaxed_u64(&a.ctrl->dinfo[j], (1ull << 63) | ((unsigned long long)lo << 32) | sb[lo]);
+    }
+    if (tid == 0) a.ctrl->times[7] = global_ns();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+template <typename T, int CT>
+__global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ Sum2Smem s2;
+    __shared__ DrawSmem ds;
+    __shared__ WalkStatic wst;
+    __shared__ unsigned int ticket_s;
+    __shared__ unsigned long long dinfo_s;
+    cg::grid_group grid = cg::this_grid();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x == 0 && tid == 0) {
+        a.ctrl->nflag = 0u; a.ctrl->arrive = 0u;
+        a.ctrl->times[0] = global_ns();
+    }
+    if (blockIdx.x == 0) for (int64_t j = tid; j < a.d.b; j += kStepThreads) a.ctrl->dinfo[j] = 0ull;
+    // ---- A: scores + tile sums
+    score_small_body<T, CT, kStepStages, kStepNT, true, false>(smem, static_cast<const T*>(a.logits), a.labels, a.n, a.c, a.tile_rows,
+                                                               a.ignore_index, a.scores, a.status, a.part);
+    if (blockIdx.x == 0 && tid == 0) a.ctrl->times[1] = global_ns();
+    grid.sync();
+    if (warp == kStepNT / 32) return;  // the producer warp has nothing more to do (the barriers below are named, 256 threads)
+    if (blockIdx.x == 0 && tid == 0) a.ctrl->times[2] = global_ns();
+
+    // ---- B: statistics (pytorch_collab.py:109-112) and this CTA's chunks
+    const int nchunks = a.nchunks;
+    const int q = nchunks / (int)gridDim.x, r = nchunks % (int)gridDim.x;
+    const int c_first = (int)blockIdx.x * q + min((int)blockIdx.x, r), c_count = q + ((int)blockIdx.x < r ? 1 : 0);
+    const int per = a.tile_rows, npart = (int)((a.n + per - 1) / per), parts_per_chunk = kChunk / per;
+    float raw[8];
+    auto load_raw = [&](int c) {
+        const int64_t start = (int64_t)c * kChunk;
+        const int len = (int)min((int64_t)kChunk, a.n - start);
+        const int base = tid * 8;
+        const float* wp = a.scores + start + base;
+        if (base + 8 <= len && (reinterpret_cast<uintptr_t>(wp) & 15) == 0) {
+            const float4 v0 = __ldcg(reinterpret_cast<const float4*>(wp)), v1 = __ldcg(reinterpret_cast<const float4*>(wp) + 1);
+            raw[0] = v0.x; raw[1] = v0.y; raw[2] = v0.z; raw[3] = v0.w; raw[4] = v1.x; raw[5] = v1.y; raw[6] = v1.z; raw[7] = v1.w;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) raw[k] = base + k < len ? __ldcg(wp + k) : 0.f;
+        }
+    };
+    if (c_count > 0) load_raw(c_first);
+    const float ema_prev = *a.ema_state;
+    double tot = 0.0, pre = 0.0;
+    {
+        const int first_part = (int)((int64_t)(c_count > 0 ? c_first : 0) * kChunk / per);
+        constexpr int kInFlight = 16;
+        for (int i0 = tid; i0 < npart; i0 += kInFlight * kStepNT) {   // (same order of additions as summarize_kernel)
+            double v[kInFlight];
+#pragma unroll
+            for (int k = 0; k < kInFlight; ++k) { const int i = i0 + k * kStepNT; v[k] = i < npart ? __ldcg(a.part + i) : 0.0; }
+#pragma unroll
+            for (int k = 0; k < kInFlight; ++k) {
+                const int i = i0 + k * kStepNT;
+                tot += v[k];
+                if (i < first_part) pre += v[k];
+            }
+        }
+        tot = warp_sum(tot); pre = warp_sum(pre);
+        if (lane == 0) { s2.dred[0][warp] = tot; s2.dred[1][warp] = pre; }
+        // the sum of each of this CTA's chunks (one warp per chunk; more than 8 chunks per CTA: in rounds below)
+        if (warp < min(c_count, 8)) {
+            const int p0 = (c_first + warp) * parts_per_chunk;
+            double o = 0.0;
+            for (int i = p0 + lane; i < min(p0 + parts_per_chunk, npart); i += 32) o += __ldcg(a.part + i);
+            o = warp_sum(o);
+            if (lane == 0) s2.own[warp] = o;
+        }
+        wsync();
+        tot = pre = 0.0;
+#pragma unroll
+        for (int i = 0; i < kStepNT / 32; ++i) { tot += s2.dred[0][i]; pre += s2.dred[1][i]; }
+    }
+    const double n_stat = (double)a.n;
+    const float mean = (float)(tot / n_stat);
+    const float al = (float)a.ema_alpha, one_minus_a = (float)(1.0 - a.ema_alpha);
+    const float ema = a.ema_first ? mean : __fadd_rn(__fmul_rn(al, ema_prev), __fmul_rn(one_minus_a, mean));
+    const float shift = __fmul_rn((float)a.smooth_alpha, ema);
+    const float total = (float)(tot + n_stat * (double)shift);
+    if (blockIdx.x == 0 && tid == 0) {
+        a.ctrl->times[14] = global_ns();
+        a.stats[MERCURY_STAT_MEAN] = mean; a.stats[MERCURY_STAT_EMA] = ema;
+        a.stats[MERCURY_STAT_SHIFT] = shift; a.stats[MERCURY_STAT_TOTAL] = total;
+        a.stats[5] = a.stats[6] = a.stats[7] = 0.f;
+    }
+    for (int k = 0; k < c_count; ++k) {
+        double own;
+        if (k < 8) own = s2.own[k];
+        else {  // (only with very few CTAs for the chunk count: not the common case)
+            wsync();
+            if (warp == 0) {
+                const int p0 = (c_first + k) * parts_per_chunk;
+                double o = 0.0;
+                for (int i = p0 + lane; i < min(p0 + parts_per_chunk, npart); i += 32) o += __ldcg(a.part + i);
+                o = warp_sum(o);
+                if (lane == 0) s2.own[0] = o;
+            }
+            wsync();
+            own = s2.own[0];
+            wsync();
+        }
+        float cur[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) cur[i] = raw[i];
+        if (k + 1 < c_count) load_raw(c_first + k + 1);   // next chunk's scores travel while this one is reduced
+        summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2);
+        pre += own;
+    }
+    // ---- arrive; the last CTA to arrive walks
+    if (blockIdx.x == 0 && tid == 0) a.ctrl->times[15] = global_ns();
+    __threadfence();
+    wsync();
+    if (tid == 0) {
+        ticket_s = atomicAdd(&a.ctrl->arrive, 1u);
+        if (blockIdx.x == 0) a.ctrl->times[3] = global_ns();
+    }
+    wsync();
+    if (ticket_s == gridDim.x - 1) {
+        __threadfence();
+        if (tid == 0) a.ctrl->times[4] = global_ns();
+        walker_body(a, smem, wst, shift, total, ema);
+    }
+    // ---- D: draws
+    float* cdf_s = reinterpret_cast<float*>(smem);
+    for (int64_t j = blockIdx.x; j < a.d.b; j += gridDim.x) {
+        wsync();   // (the walker's shared memory, and the previous draw's, are free again)
+        if (tid == 0) {
+            unsigned long long v = ld_relaxed_u64(&a.ctrl->dinfo[j]);
+            if (!(v >> 63)) {
+                const unsigned long long t0 = global_ns();
+                for (unsigned int it = 0;; ++it) {
+                    v = ld_relaxed_u64(&a.ctrl->dinfo[j]);
+                    if (v >> 63) break;
+                    if ((it & 63u) == 63u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); break; }
+                }
+            }
+            __threadfence();
+            dinfo_s = v;
+        }
+        wsync();
+        const unsigned long long v = dinfo_s;
+        if (!(v >> 63)) return;  // timed out (reported): leave the outputs alone rather than write garbage
+        draw_resolve<true>(a.d, j, a.d.u[j], (int)((v >> 32) & 0x7fffffffu), (uint32_t)v, true, ds, cdf_s);
+    }
+    if (blockIdx.x == 0 && tid == 0) a.ctrl->times[8] = global_ns();
+}

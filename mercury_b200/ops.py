@@ -71,6 +71,8 @@ def check_status(status: torch.Tensor) -> None:
         raise RuntimeError("invalid multinomial distribution (sum of probabilities <= 0)")
     if bits & _lib.ST_PEER_TIMEOUT:
         raise RuntimeError("mercury_b200: a peer's exchange word did not arrive within 4 s (ranks out of step?)")
+    if bits & _lib.ST_INTERNAL:
+        raise RuntimeError("mercury_b200: a wait inside the one-kernel step hit its 2 s bound (internal error)")
     if bits & _lib.ST_TOPK_TIES:
         raise RuntimeError("mercury_b200: too many exactly tied keys at the k-th place of the exponential race")
 
@@ -411,6 +413,21 @@ def update_samples(logits: Optional[torch.Tensor], labels: Optional[torch.Tensor
     _lib.check(lib.mercury_update_samples(ctypes.byref(a), ws.data_ptr(), ws.numel(), _stream()))
     return UpdateResult(scores=scores, stats=stats, idx=idx, nprob=nprob, seed=seed, data=out_data, labels=out_labels,
                         index=out_index, status=status)
+
+
+def set_fused(mode: int) -> None:
+    """Test hook: 0 = always the four-kernel chain, 1 = the one-kernel step where it applies, -1 = environment."""
+    _lib.load().mercury_test_set_fused(int(mode))
+
+
+def step_times(n: int, device=None) -> list:
+    """Developer aid: the stamps the last one-kernel step on the current stream left behind (mercury_debug_step_times)."""
+    lib = _lib.load()
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    ws = workspace(dev, lib.mercury_update_samples_workspace_bytes(n, 0))
+    arr = (ctypes.c_ulonglong * 128)()
+    _lib.check(lib.mercury_debug_step_times(ws.data_ptr(), n, arr))
+    return list(arr)
 
 
 def sum_scores(scores: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:

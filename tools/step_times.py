@@ -1,0 +1,41 @@
+"""Phase timestamps of the one-kernel step (developer aid): [MERCURY_STEP_DBG=1] python tools/step_times.py [N] [B]
+Prints, per pool, microseconds since the kernel's start at: CTA 0 scored | grid barrier passed | CTA 0 had the statistics |
+CTA 0 published its summaries | last CTA arrived (walker starts) | walker loaded | walk done | draws published | CTA 0 done;
+with MERCURY_STEP_DBG=1 also the cycles of each step of the walk."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from mercury_b200 import ops  # noqa: E402
+
+dev = torch.device("cuda", 0)
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+b = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+c = 10
+g = torch.Generator(device=dev).manual_seed(100)
+pools = [((torch.randn(n, c, generator=g, device=dev) * 2), torch.randint(0, c, (n,), generator=g, device=dev)) for _ in range(7)]
+payload = torch.rand(n, 3, 32, 32, device=dev, generator=g)
+index = torch.arange(n, device=dev)
+u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(3)).to(dev)
+ema = torch.zeros(1, device=dev)
+out = {}
+ops.set_fused(1)
+order = [("scored", 1), ("barrier", 2), ("stats", 14), ("summarized", 15), ("published", 3), ("walker", 4), ("loaded", 5),
+         ("walked", 6), ("draws_out", 7), ("cta0_done", 8)]
+for i in range(10):
+    r = ops.update_samples(*pools[i % 7], u, ema, i == 0, data=payload, index=index, out=out)
+    out.update({k: v for k, v in r.items() if v is not None})
+    torch.cuda.synchronize()
+    t = ops.step_times(n)
+    if i >= 5:
+        print("  ".join(f"{nm}={(t[k] - t[0]) / 1e3:6.2f}" for nm, k in order))
+ops.check_status(r.status)
+if int(os.environ.get("MERCURY_STEP_DBG", "0")) & 1:
+    nev = t[12]
+    ev = t[16:16 + nev + 1]
+    print("walk steps (cycles : kind of the step, 0 add 1 map 3 pack 4 slow):")
+    print(" ".join(f"{(ev[i] >> 4) - (ev[i - 1] >> 4)}:{ev[i] & 15}" for i in range(1, len(ev))))
+if int(os.environ.get("MERCURY_STEP_DBG", "0")) & 2:
+    print("micro (cycles): 16 dependent SHFL loop iterations", t[16 + 104], "| 64 unrolled dependent FADD", t[16 + 105])
