@@ -1415,6 +1415,7 @@ struct DrawArgs {
     const double* u; int64_t b;
     const unsigned char* data; int64_t row_bytes; const int64_t* labels; const int64_t* index;
     int64_t* idx; float* nprob; float* seed; unsigned char* out_data; int64_t* out_labels; int64_t* out_index;
+    unsigned long long* dbg;   // developer aid: when set, CTA 0 stamps %globaltimer after the chunk's scores arrived and after the slot is known
 };
 
 // barrier among the kDrawNT threads that work on a draw: the whole CTA in the stand-alone kernel, the 256 worker
@@ -1540,6 +1541,7 @@ __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, doubl
 #pragma unroll
         for (int k = 0; k < kDrawIPT; ++k) pv[base + k] = b2f(pb[k]);
     }
+    if (a.dbg && blockIdx.x == 0 && threadIdx.x == 64) a.dbg[0] = global_ns();
     int cur = 0;                             // the exact sum `bits` is the one before sub-chunk `cur`
     for (;;) {                               // (block-uniform control flow: decisions travel through rs)
         const uint32_t E = phase_of(bits), S = bits - (E << 23);
@@ -1609,6 +1611,7 @@ __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, doubl
     }
     draw_sync<NAMED>();
     // (d) payload row: everybody issues its first loads as soon as the slot is known; the scalar outputs ride along
+    if (a.dbg && blockIdx.x == 0 && threadIdx.x == 64) a.dbg[1] = global_ns();
     const int64_t pick = chosen;
     const bool copy = a.data && a.out_data;
     const unsigned char* srow = copy ? a.data + pick * a.row_bytes : nullptr;
@@ -1886,6 +1889,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
     d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
     d.out_labels = a.out_labels; d.out_index = a.out_index;
+    d.dbg = (dbg_flags & 4) ? &w.ctrl->evt[107] : nullptr;
     const int64_t ntiles = (a.n + sa.tile_rows - 1) / sa.tile_rows;
     const int64_t want = ntiles > a.b ? (ntiles > nchunks ? ntiles : nchunks) : (a.b > nchunks ? a.b : nchunks);
     if (a.dtype == MERCURY_F32) {

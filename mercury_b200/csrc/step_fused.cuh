@@ -32,6 +32,7 @@ constexpr int kStepMaxEvents = 192;
 constexpr size_t kStepSmemBytes = 70 * 1024;
 constexpr int kSub2 = 32, kSubs2 = kChunk / kSub2;
 constexpr int kRaw2 = 12;
+constexpr int kHeadMax = 1024;                   // candidates at the head of the pool summed serially during phase B
 constexpr uint32_t kBadInc = kSatCap;            // "no plain increment known for this phase": forces a stop in the scan
 static_assert(kSubs2 == 64, "two sub-chunks per lane of the walking warp");
 
@@ -41,13 +42,23 @@ struct __align__(128) Pack2 {
     uint2 q1[kSubs2];              // ... and in the phase above
     uint8_t rawsub[16];            // sub-chunks whose candidates are in raw[] (0xff: unused)
     uint32_t raw[kRaw2][kSub2];    // 16-byte aligned
+    // inclusive prefix sums of the sub-chunks' plain increments while the running sum is in phase e_lo (psA) or e_lo + 1
+    // (psB); a sub-chunk without a plain increment for that phase counts kBadInc, which pushes every later entry beyond
+    // 2^24 (so it reads as "leaves the phase here")
+    uint32_t psA[kSubs2], psB[kSubs2];
+    uint32_t e_lo;                 // the chunk's low guess
+    uint32_t pad_[31];
 };
-static_assert(sizeof(Pack2) == 2944 && offsetof(Pack2, raw) % 16 == 0 && offsetof(Pack2, q0) % 16 == 0, "Pack2 layout");
+static_assert(sizeof(Pack2) == 3584 && offsetof(Pack2, raw) % 16 == 0 && offsetof(Pack2, q0) % 16 == 0 && offsetof(Pack2, psA) % 16 == 0,
+              "Pack2 layout");
 
 struct StepCtrl {
     unsigned int nflag;            // pack slots handed out
     unsigned int arrive;           // CTAs that published their summaries
-    unsigned int pad_[30];
+    unsigned int head_k;           // sub-chunks at the head of chunk 0 already summed serially (by CTA 0's spare warp) ...
+    unsigned int head_bits;        // ... and the exact running sum behind them
+    unsigned int head_want;        // what head_k will be once that warp is done (0: no head)
+    unsigned int pad_[27];
     unsigned long long times[16];  // developer aid: %globaltimer at the phase changes (CTA 0 and the walker)
     unsigned long long evt[112];   // developer aid: clock64 after each of the walk's first steps (kind in the low 4 bits)
     unsigned long long dinfo[kStepMaxDraws];  // per draw: 1 << 63 | chunk << 32 | boundary bits
@@ -94,6 +105,14 @@ __device__ __forceinline__ uint4 lds_u32x4(uint32_t saddr) {
     return v;
 }
 
+// the increment of a sub-chunk while the running sum is in phase E, or kBadInc if no plain one is known (branch-free)
+__device__ __forceinline__ uint32_t sub_inc(uint32_t e, uint32_t d00, uint32_t d01, uint32_t d10, uint32_t d11, uint32_t E) {
+    const uint32_t g = e & kPhaseMask;
+    const uint32_t v0 = d00 == d01 ? d00 : kBadInc, v1 = d10 == d11 ? d10 : kBadInc;
+    const uint32_t r = g == E ? v0 : (g + 1u == E ? v1 : kBadInc);
+    return g == kAnyPhase ? 0u : r;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // phase B: one chunk -> Summary (+ Pack2)
 struct Sum2Smem {
@@ -104,6 +123,8 @@ struct Sum2Smem {
     double dred[2][kStepNT / 32];
     double own[8];
     int slot;
+    uint32_t sub_e[kSubs2]; uint2 sub_q0[kSubs2], sub_q1[kSubs2];
+    float bc_shift, bc_total;
 };
 
 __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const float (&raw)[8], double pre, double own, float shift,
@@ -111,31 +132,48 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t start = (int64_t)c * kChunk;
     const int len = (int)min((int64_t)kChunk, a.n - start);
-    const double a_lo = (pre + (double)start * (double)shift) / (double)total;
-    const double a_hi = a_lo + (own + (double)len * (double)shift) / (double)total;
+    const double inv_total = 1.0 / (double)total;   // (the approximate running totals only feed the guesses)
+    const double a_lo = (pre + (double)start * (double)shift) * inv_total;
+    const double a_hi = a_lo + (own + (double)len * (double)shift) * inv_total;
     uint32_t pb[8];
     {
         const int base = threadIdx.x * 8;
 #pragma unroll
         for (int k = 0; k < 8; ++k) pb[k] = base + k < len ? f2b(__fdiv_rn(__fadd_rn(raw[k], shift), total)) : 0u;
     }
+#define MB_BSTAMP(i) do { if ((a.dbg_flags & 4) && c == 0 && threadIdx.x == 64) a.ctrl->evt[100 + (i)] = global_ns(); } while (0)
+    MB_BSTAMP(0);
     uint32_t e;
     const bool flagged = guess_span(a_lo, a_hi, a.bias, &e, chunk_margin(a.nchunks));  // block-uniform
     // a flagged chunk claims a pack slot; the atomic's round trip hides behind the arithmetic below
     unsigned int slot_u = 0xffffffffu;
     if (flagged && threadIdx.x == 0) slot_u = atomicAdd(&a.ctrl->nflag, 1u);
-    Pair a0 = identity_pair();
+    Pair a0;
     int bad = 0;
     bool nz = false;
     float tsum = 0.f;
+    {
+        // without exact ties every addend is a plain increment and the thread's map is their sum (the usual case);
+        // only a thread that meets a tie composes the 2-state maps
+        uint32_t plain = 0u;
+        bool tie = false;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const float x = b2f(pb[k]);
-        if (!(x >= 0.f)) bad |= MERCURY_ST_NEGATIVE;
-        else if (isinf(x)) bad |= MERCURY_ST_NONFINITE;
-        nz |= pb[k] != 0u;
-        tsum += x;
-        a0 = compose(a0, addend_pair_fast(pb[k], e));
+        for (int k = 0; k < 8; ++k) {
+            const float x = b2f(pb[k]);
+            if (!(x >= 0.f)) bad |= MERCURY_ST_NEGATIVE;
+            else if (isinf(x)) bad |= MERCURY_ST_NONFINITE;
+            nz |= pb[k] != 0u;
+            tsum += x;
+            const Pair q = addend_pair_fast(pb[k], e);
+            tie |= q.d0 != q.d1;
+            plain += q.d0;                                 // (8 * 2^25 fits)
+        }
+        a0.d0 = a0.d1 = sat(plain);
+        if (tie) {
+            a0 = identity_pair();
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a0 = compose(a0, addend_pair_fast(pb[k], e));
+        }
     }
     if (bad) atomicOr(a.status, bad);
     const unsigned nzmask = __ballot_sync(0xffffffffu, nz);
@@ -157,6 +195,7 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
             if (lane >= off) inc += o;
         }
     }
+    MB_BSTAMP(1);
     wsync();  // (protects sm against the previous chunk's readers)
     if (lane == 0) { sm.wt[warp] = a0; sm.wnz[warp] = nzmask != 0u; }
     if (lane == 31) sm.wsum[warp] = inc;
@@ -176,6 +215,7 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         a.sums[c] = s;
     }
     if (slot < 0) return;
+    MB_BSTAMP(2);
     // ---- per sub-chunk: 4 consecutive threads = 32 candidates
     float pre_f = 0.f;
     for (int i = 0; i < warp; ++i) pre_f += sm.wsum[i];
@@ -185,11 +225,25 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
     const bool sub_nz = ((nzmask >> lead) & 0xfu) != 0u;
     uint32_t es;
     const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, a.bias, &es, sub_margin(a.nchunks)) && sub_nz;
-    Pair m0 = identity_pair(), m1 = identity_pair();
+    Pair m0, m1;
+    {
+        uint32_t p0 = 0u, p1 = 0u;
+        bool tie = false;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        m0 = compose(m0, addend_pair_fast(pb[k], es));
-        m1 = compose(m1, addend_pair_fast(pb[k], es + 1u));
+        for (int k = 0; k < 8; ++k) {
+            const Pair x0 = addend_pair_fast(pb[k], es), x1 = addend_pair_fast(pb[k], es + 1u);
+            tie |= (x0.d0 != x0.d1) | (x1.d0 != x1.d1);
+            p0 += x0.d0; p1 += x1.d0;
+        }
+        m0.d0 = m0.d1 = sat(p0); m1.d0 = m1.d1 = sat(p1);
+        if (tie) {
+            m0 = identity_pair(); m1 = identity_pair();
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                m0 = compose(m0, addend_pair_fast(pb[k], es));
+                m1 = compose(m1, addend_pair_fast(pb[k], es + 1u));
+            }
+        }
     }
 #pragma unroll
     for (int off = 1; off < 4; off <<= 1) {
@@ -198,12 +252,16 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         o1.d0 = __shfl_down_sync(0xffffffffu, m1.d0, off, 4); o1.d1 = __shfl_down_sync(0xffffffffu, m1.d1, off, 4);
         if ((lane & 3) + off < 4) { m0 = compose(m0, o0); m1 = compose(m1, o1); }
     }
+    MB_BSTAMP(3);
     Pack2* pk = a.packs + slot;
     const int my_sub = threadIdx.x >> 2;
     if ((lane & 3) == 0) {
         pk->e[my_sub] = (sub_nz ? es : kAnyPhase) | (sub_flagged ? kFlag : 0u) | (m0.d0 != m0.d1 ? kTie0 : 0u) | (m1.d0 != m1.d1 ? kTie1 : 0u);
         pk->q0[my_sub] = make_uint2(m0.d0, m0.d1);
         pk->q1[my_sub] = make_uint2(m1.d0, m1.d1);
+        sm.sub_e[my_sub] = sub_nz ? es : kAnyPhase;
+        sm.sub_q0[my_sub] = make_uint2(m0.d0, m0.d1);
+        sm.sub_q1[my_sub] = make_uint2(m1.d0, m1.d1);
     }
     // which sub-chunks ship their raw candidates: the first kRaw2 flagged ones
     const unsigned lead_flags = __ballot_sync(0xffffffffu, (lane & 3) == 0 && sub_flagged);  // bits 0,4,...,28
@@ -225,6 +283,22 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         if ((lane & 3) == 0) pk->rawsub[my_rank] = (uint8_t)my_sub;
     }
     if (threadIdx.x < 16 && (int)threadIdx.x >= min(__popcll(fmask), kRaw2)) pk->rawsub[threadIdx.x] = 0xff;
+    if (warp == 0) {   // prefix sums of the 64 plain increments for the chunk's guessed phase and the next (2 per lane)
+        const uint32_t e0 = sm.sub_e[2 * lane], e1 = sm.sub_e[2 * lane + 1];
+        const uint2 a0q = sm.sub_q0[2 * lane], a1q = sm.sub_q0[2 * lane + 1], b0q = sm.sub_q1[2 * lane], b1q = sm.sub_q1[2 * lane + 1];
+        const uint32_t A0 = sub_inc(e0, a0q.x, a0q.y, b0q.x, b0q.y, e), A1 = sub_inc(e1, a1q.x, a1q.y, b1q.x, b1q.y, e);
+        const uint32_t B0 = sub_inc(e0, a0q.x, a0q.y, b0q.x, b0q.y, e + 1u), B1 = sub_inc(e1, a1q.x, a1q.y, b1q.x, b1q.y, e + 1u);
+        uint32_t va = A0 + A1, vb = B0 + B1;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t oa = __shfl_up_sync(0xffffffffu, va, off), ob = __shfl_up_sync(0xffffffffu, vb, off);
+            if (lane >= off) { va += oa; vb += ob; }
+        }
+        reinterpret_cast<uint2*>(pk->psA)[lane] = make_uint2(va - A1, va);
+        reinterpret_cast<uint2*>(pk->psB)[lane] = make_uint2(vb - B1, vb);
+        if (lane == 0) pk->e_lo = e;
+    }
+    MB_BSTAMP(4);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -237,6 +311,8 @@ struct WalkEnv {
     const unsigned long long* pc; const uint32_t* ce; const uint32_t* qd0; const uint32_t* qd1; const uint32_t* stopw;
     const uint8_t* slot_of; uint32_t* sb; uint32_t* stage;
     const Pack2* slots; Pack2* spare; const Pack2* packs_g; const Summary* sums; uint32_t* start_bits;
+    int head_k; uint32_t head_bits;   // chunk 0: the first head_k sub-chunks are already summed, the sum is head_bits
+    unsigned int cnt_iter, cnt_serial, cnt_map;   // developer aid
 };
 
 // the reference's loop over 32 consecutive candidates held in shared memory, run redundantly by every lane
@@ -267,6 +343,7 @@ __device__ __noinline__ uint32_t stage_sub2(const WalkEnv* env, int c, int f, in
 
 // serial pass over sub-chunk f of chunk c: raw candidates from the pack (shared memory, address P) if it carries them
 __device__ __forceinline__ uint32_t serial_sub2(const WalkEnv* env, uint32_t P, int c, int f, uint32_t b, int lane) {
+    const_cast<WalkEnv*>(env)->cnt_serial = env->cnt_serial + 1u;
     const uint32_t rs = lds_u32(P + (uint32_t)offsetof(Pack2, rawsub) + 4u * (lane & 3));   // lane -> rawsub[(lane & 3) * 4 + ((lane >> 2) & 3)]
     const uint32_t mine = (rs >> (8 * ((lane >> 2) & 3))) & 0xffu;
     const unsigned hit = __ballot_sync(0xffffffffu, lane < 16 && mine == (uint32_t)f);
@@ -282,37 +359,67 @@ __device__ __forceinline__ uint32_t serial_sub2(const WalkEnv* env, uint32_t P, 
     return b;
 }
 
-// the increment of a sub-chunk while the running sum is in phase E, or kBadInc if no plain one is known (branch-free)
-__device__ __forceinline__ uint32_t sub_inc(uint32_t e, uint32_t d00, uint32_t d01, uint32_t d10, uint32_t d11, uint32_t E) {
-    const uint32_t g = e & kPhaseMask;
-    const uint32_t v0 = d00 == d01 ? d00 : kBadInc, v1 = d10 == d11 ? d10 : kBadInc;
-    const uint32_t r = g == E ? v0 : (g + 1u == E ? v1 : kBadInc);
-    return g == kAnyPhase ? 0u : r;
-}
-
-// a flagged chunk: the 64 sub-chunk increments for the current phase are scanned by the warp; the first sub-chunk whose
-// end would leave the phase (or that has no plain increment) is treated on its own -- a 2-state map if it only has exact
-// ties, else the serial loop -- and the scan resumes behind it in whatever phase the sum is then.  P: the pack's address
-// in SHARED memory.
-__device__ __forceinline__ uint32_t run_pack2(const WalkEnv* env, uint32_t P, int c, uint32_t b, int lane) {
+// a flagged chunk, from sub-chunk k0 on (b: the exact sum in front of it).  P: the pack's address in SHARED memory.
+// Expected case (the sum is in the chunk's guessed phase and changes phase once): the pack's prefix sums locate the
+// sub-chunk whose end leaves the phase, that sub-chunk is summed with the reference's own loop (32 dependent fp32 adds),
+// and the prefix sums for the next phase cross the rest.  Anything else: the general loop below -- the 64 increments
+// for the current phase are scanned by the warp, the first sub-chunk that leaves the phase (or has no plain increment)
+// is treated on its own (a 2-state map if it only has exact ties, else the serial loop), and the scan resumes behind it.
+__device__ __forceinline__ uint32_t run_pack2(const WalkEnv* env, uint32_t P, int c, uint32_t b, int lane, int k0) {
+    uint32_t E = phase_of(b), S = b - (E << 23);
+    int k = k0;                                                      // first sub-chunk not yet applied
+    const uint32_t e_lo = lds_u32(P + (uint32_t)offsetof(Pack2, e_lo));
+    if (E == e_lo) {
+        const uint2 pa = lds_u32x2(P + (uint32_t)offsetof(Pack2, psA) + 8u * lane);
+        const uint32_t base = k0 > 0 ? lds_u32(P + (uint32_t)offsetof(Pack2, psA) + 4u * (k0 - 1)) : 0u;
+        const uint32_t s_mid = S + (pa.x - base), s_out = S + (pa.y - base);   // (meaningful for sub-chunks >= k0)
+        const unsigned over0 = __ballot_sync(0xffffffffu, 2 * lane >= k0 && s_mid >= kPhaseLimit);
+        const unsigned over1 = __ballot_sync(0xffffffffu, 2 * lane + 1 >= k0 && s_out >= kPhaseLimit);
+        if ((over0 | over1) == 0u) return bits_of(E, __shfl_sync(0xffffffffu, s_out, 31));
+        const int f0 = over0 ? 2 * (__ffs(over0) - 1) : kSubs2, f1 = over1 ? 2 * (__ffs(over1) - 1) + 1 : kSubs2;
+        const int f = min(f0, f1), fl = f >> 1;
+        // the sum in front of sub-chunk f
+        const uint32_t prev_out = __shfl_sync(0xffffffffu, s_out, fl > 0 ? fl - 1 : 0), this_mid = __shfl_sync(0xffffffffu, s_mid, fl);
+        const uint32_t Sf = f == k0 ? S : ((f & 1) ? this_mid : prev_out);
+        const uint32_t ef = lds_u32(P + (uint32_t)offsetof(Pack2, e) + 4u * f);
+        const uint2 qa = lds_u32x2(P + (uint32_t)offsetof(Pack2, q0) + 8u * f), qb = lds_u32x2(P + (uint32_t)offsetof(Pack2, q1) + 8u * f);
+        const uint32_t rest_lo = lds_u32(P + (uint32_t)offsetof(Pack2, psB) + 4u * f), rest_hi = lds_u32(P + (uint32_t)offsetof(Pack2, psB) + 4u * 63);
+        const uint32_t g = ef & kPhaseMask;
+        const uint32_t mx = g == E ? qa.x : qb.x, my = g == E ? qa.y : qb.y;
+        const uint32_t Sn = Sf + ((Sf & 1u) ? my : mx);
+        const bool by_map = g != kAnyPhase && (g == E || g + 1u == E) && mx != my && Sn < kPhaseLimit;
+        k = f + 1;
+        if (by_map) S = Sn;   // (exact ties inside, the sum stays in the phase: on with the general loop)
+        else {
+            b = serial_sub2(env, P, c, f, bits_of(E, Sf), lane);
+            E = phase_of(b); S = b - (E << 23);
+            const uint32_t Se = S + (rest_hi - rest_lo);
+            if (E == e_lo + 1u && Se < kPhaseLimit) return bits_of(E, Se);
+        }
+        if (k >= kSubs2) return bits_of(E, S);
+    }
     const uint2 ee = lds_u32x2(P + (uint32_t)offsetof(Pack2, e) + 8u * lane);
     const uint4 q0 = lds_u32x4(P + (uint32_t)offsetof(Pack2, q0) + 16u * lane);  // maps of sub-chunks 2*lane, 2*lane+1 in their guessed phase
     const uint4 q1 = lds_u32x4(P + (uint32_t)offsetof(Pack2, q1) + 16u * lane);  // ... and in the phase above
-    uint32_t E = phase_of(b), S = b - (E << 23);
-    int k = 0;                                                       // first sub-chunk not yet applied
+    bool rescan = true;
+    uint32_t s_in = 0u, s_mid = 0u, s_out = 0u;
     for (;;) {
-        const uint32_t w0 = 2 * lane >= k ? sub_inc(ee.x, q0.x, q0.y, q1.x, q1.y, E) : 0u;
-        const uint32_t w1 = 2 * lane + 1 >= k ? sub_inc(ee.y, q0.z, q0.w, q1.z, q1.w, E) : 0u;
-        uint32_t v = w0 + w1;                                        // (64 * 2^25 fits in 32 bits)
+        if (rescan) {
+            const_cast<WalkEnv*>(env)->cnt_iter = env->cnt_iter + 1u;
+            const uint32_t w0 = 2 * lane >= k ? sub_inc(ee.x, q0.x, q0.y, q1.x, q1.y, E) : 0u;
+            const uint32_t w1 = 2 * lane + 1 >= k ? sub_inc(ee.y, q0.z, q0.w, q1.z, q1.w, E) : 0u;
+            uint32_t v = w0 + w1;                                    // (64 * 2^25 fits in 32 bits)
 #pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, v, off);
-            if (lane >= off) v += o;
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, v, off);
+                if (lane >= off) v += o;
+            }
+            s_in = S + (v - (w0 + w1));                              // running sum before sub-chunk 2*lane
+            s_mid = s_in + w0; s_out = s_mid + w1;
         }
-        const uint32_t s_in = S + (v - (w0 + w1));                   // running sum before sub-chunk 2*lane
-        const uint32_t s_mid = s_in + w0, s_out = s_mid + w1;
-        const unsigned over0 = __ballot_sync(0xffffffffu, s_mid >= kPhaseLimit);
-        const unsigned over1 = __ballot_sync(0xffffffffu, s_out >= kPhaseLimit);
+        // (sub-chunks before k were applied already: they never count as leaving the phase)
+        const unsigned over0 = __ballot_sync(0xffffffffu, 2 * lane >= k && s_mid >= kPhaseLimit);
+        const unsigned over1 = __ballot_sync(0xffffffffu, 2 * lane + 1 >= k && s_out >= kPhaseLimit);
         if ((over0 | over1) == 0u) { S = __shfl_sync(0xffffffffu, s_out, 31); break; }
         const int f0 = over0 ? 2 * (__ffs(over0) - 1) : kSubs2, f1 = over1 ? 2 * (__ffs(over1) - 1) + 1 : kSubs2;
         const int f = min(f0, f1);
@@ -327,10 +434,18 @@ __device__ __forceinline__ uint32_t run_pack2(const WalkEnv* env, uint32_t P, in
         const uint32_t mx = g == E ? qa : qc, my = g == E ? qb : qd;
         const uint32_t Sn = Sf + ((Sf & 1u) ? my : mx);
         const bool by_map = g != kAnyPhase && (g == E || g + 1u == E) && mx != my && Sn < kPhaseLimit;
-        if (by_map) S = Sn;
-        else {
+        if (by_map) {
+            // same phase: every running sum behind f moves by (what f really added) - (the kBadInc it was counted as);
+            // no new scan (unsigned wrap-around is fine: only entries behind f are looked at again)
+            const_cast<WalkEnv*>(env)->cnt_map = env->cnt_map + 1u;
+            const uint32_t adj = (Sn - Sf) - kBadInc;
+            S = Sn;
+            s_in += adj; s_mid += adj; s_out += adj;
+            rescan = false;
+        } else {
             b = serial_sub2(env, P, c, f, bits_of(E, Sf), lane);
             E = phase_of(b); S = b - (E << 23);
+            rescan = true;
         }
         k = f + 1;
         if (k >= kSubs2) break;
@@ -364,7 +479,8 @@ __device__ __noinline__ uint32_t walk_general2(const WalkEnv* env, int c, int c_
         if (ec & kFlag) {
             const int sl = (int)env->slot_of[c] - 1;
             const uint32_t P = sl >= 0 ? smem_u32(&env->slots[sl]) : fetch_pack2(env, (int)env->sums[c].pad[0], lane);
-            b = run_pack2(env, P, c, b, lane);
+            const bool head = c == 0 && env->head_k > 0;
+            b = run_pack2(env, P, c, head ? env->head_bits : b, lane, head ? env->head_k : 0);
             __syncwarp();
             ++c;
             continue;
@@ -449,6 +565,25 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
         e.src = a.d.src; e.n = a.n; e.shift = stat_shift; e.totalw = stat_total;
         e.pc = pc; e.ce = ce; e.qd0 = qd0; e.qd1 = qd1; e.stopw = stopw; e.slot_of = slot_of; e.sb = sb; e.stage = stage;
         e.slots = slots; e.spare = spare; e.packs_g = a.packs; e.sums = a.sums; e.start_bits = a.start_bits;
+        e.head_k = 0; e.head_bits = 0u;
+        const unsigned int want = __ldcg(&a.ctrl->head_want);
+        if (want) {   // the head of the pool is being summed by CTA 0's spare warp: normally long done by now
+            const unsigned long long t0 = global_ns();
+            unsigned int got;
+            do {
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(got) : "l"(&a.ctrl->head_k) : "memory");
+            } while (got != want && global_ns() - t0 < 20000ull);   // (20 us: then walk chunk 0 from its start, the general way)
+            if (got == want) { __threadfence(); e.head_k = (int)want; e.head_bits = __ldcg(&a.ctrl->head_bits); }
+        }
+        e.cnt_iter = e.cnt_serial = e.cnt_map = 0u;
+        a.ctrl->times[13] = (unsigned long long)e.head_k;
+    }
+    // (the first round of summaries is requested before the packs, so that both travel together)
+    uint4 sum_lo = make_uint4(0u, 0u, 0u, 0u);
+    uint32_t sum_slot = 0u;
+    if (tid < nchunks) {
+        sum_lo = __ldcg(reinterpret_cast<const uint4*>(a.sums + tid));                  // e, q0.d0, q0.d1, q1.d0
+        sum_slot = __ldcg(reinterpret_cast<const uint32_t*>(a.sums + tid) + 5);         // pad[0]
     }
     {
         constexpr int kPackVecs = (int)(sizeof(Pack2) / 16);
@@ -468,8 +603,8 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
         const int c = c0 + tid;
         unsigned long long inc = 0ull;
         if (c < nchunks) {
-            const uint4 lo = __ldcg(reinterpret_cast<const uint4*>(a.sums + c));        // e, q0.d0, q0.d1, q1.d0
-            const uint32_t slot = __ldcg(reinterpret_cast<const uint32_t*>(a.sums + c) + 5);  // pad[0]
+            const uint4 lo = c0 == 0 ? sum_lo : __ldcg(reinterpret_cast<const uint4*>(a.sums + c));
+            const uint32_t slot = c0 == 0 ? sum_slot : __ldcg(reinterpret_cast<const uint32_t*>(a.sums + c) + 5);
             ce[c] = lo.x; qd0[c] = lo.y; qd1[c] = lo.z;
             slot_of[c] = ((lo.x & kFlag) && (int)slot < max_slots) ? (uint8_t)(slot + 1) : 0;
             inc = lo.y;
@@ -561,10 +696,12 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
             b = walk_general2(env, 0, nchunks, b, lane);
         } else {
             uint32_t E = 0u, S = 0u;
-            if (stamp) a.ctrl->evt[0] = (unsigned long long)clock64() << 4;
+            if (stamp) a.ctrl->evt[0] = (unsigned long long)clock64() << 16;
             for (int i = 0; i < nev; ++i) {
                 const uint4 ev = evs[i];
-                if (stamp && i > 0 && i < 100) a.ctrl->evt[i] = ((unsigned long long)clock64() << 4) | (evs[i - 1].x & 0xfu);
+                if (stamp && i > 0 && i < 100)
+                    a.ctrl->evt[i] = ((unsigned long long)clock64() << 16) | (env->cnt_iter << 12) | ((env->cnt_serial & 15u) << 8) | ((env->cnt_map & 15u) << 4) | (evs[i - 1].x & 0xfu);
+                if (stamp) { ws.env.cnt_iter = 0u; ws.env.cnt_serial = 0u; ws.env.cnt_map = 0u; }
                 const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
                 const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);
                 if (kind == kEvAdd) {
@@ -586,7 +723,8 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
                     a.start_bits[c] = b; sb[c] = b;
                     const int sl = (int)slot_of[c] - 1;
                     const uint32_t P = sl >= 0 ? smem_u32(&slots[sl]) : fetch_pack2(env, (int)a.sums[c].pad[0], lane);
-                    b = run_pack2(env, P, c, b, lane);
+                    const bool head = c == 0 && env->head_k > 0;
+                    b = run_pack2(env, P, c, head ? env->head_bits : b, lane, head ? env->head_k : 0);
                     __syncwarp();
                     E = phase_of(b); S = b - (E << 23);
                     continue;
@@ -598,7 +736,8 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
                 E = phase_of(b); S = b - (E << 23);
             }
             b = bits_of(E, S);
-            if (stamp && nev < 100) a.ctrl->evt[nev] = ((unsigned long long)clock64() << 4) | (evs[nev - 1].x & 0xfu);
+            if (stamp && nev < 100)
+                a.ctrl->evt[nev] = ((unsigned long long)clock64() << 16) | (env->cnt_iter << 12) | ((env->cnt_serial & 15u) << 8) | ((env->cnt_map & 15u) << 4) | (evs[nev - 1].x & 0xfu);
         }
         // (every lane writes the same words)
         *a.ema_state = stat_ema;  // EMAverage.value for the next call (util.py:207-213)
@@ -656,7 +795,8 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     cg::grid_group grid = cg::this_grid();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (blockIdx.x == 0 && tid == 0) {
-        a.ctrl->nflag = 0u; a.ctrl->arrive = 0u;
+        a.ctrl->nflag = 0u; a.ctrl->arrive = 0u; a.ctrl->head_k = 0u; a.ctrl->head_bits = 0u;
+        a.ctrl->head_want = (unsigned int)((min(kHeadMax, (int)min((int64_t)kChunk, a.n)) & ~(kSub2 - 1)) / kSub2);
         a.ctrl->times[0] = global_ns();
     }
     if (blockIdx.x == 0) for (int64_t j = tid; j < a.d.b; j += kStepThreads) a.ctrl->dinfo[j] = 0ull;
@@ -665,13 +805,56 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
                                                                a.ignore_index, a.scores, a.status, a.part);
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[1] = global_ns();
     grid.sync();
-    if (warp == kStepNT / 32) return;  // the producer warp has nothing more to do (the barriers below are named, 256 threads)
+    if (warp == kStepNT / 32) {
+        // The producer warp has nothing more to do -- except in CTA 0, where it sums the head of the pool serially (the
+        // reference's own loop) while the other warps build the summaries: the running sum changes binade about ten times
+        // in the first thousand candidates, which would otherwise cost the walk one serial pass each.
+        if (blockIdx.x != 0) return;
+        asm volatile("bar.sync 3, %0;" ::"n"(kStepThreads) : "memory");   // the workers have put shift / total into s2
+        const int len0 = (int)min((int64_t)kChunk, a.n);
+        const int H = min(kHeadMax, len0) & ~(kSub2 - 1);
+        if (H > 0) {
+            const float shift = s2.bc_shift, total = s2.bc_total;
+            uint32_t* hp = reinterpret_cast<uint32_t*>(smem);
+            // all loads first (8 x 16 bytes per lane in flight), then the arithmetic
+            const bool vec = (reinterpret_cast<uintptr_t>(a.scores) & 15) == 0;
+            float4 hv[kHeadMax / 128];
+#pragma unroll
+            for (int r = 0; r < kHeadMax / 128; ++r) {
+                const int i = (r * 32 + lane) * 4;
+                if (i < H) {
+                    if (vec) hv[r] = __ldcg(reinterpret_cast<const float4*>(a.scores + i));
+                    else hv[r] = make_float4(__ldcg(a.scores + i), __ldcg(a.scores + i + 1), __ldcg(a.scores + i + 2), __ldcg(a.scores + i + 3));
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < kHeadMax / 128; ++r) {
+                const int i = (r * 32 + lane) * 4;
+                if (i < H)
+                    *reinterpret_cast<uint4*>(hp + i) = make_uint4(f2b(__fdiv_rn(__fadd_rn(hv[r].x, shift), total)), f2b(__fdiv_rn(__fadd_rn(hv[r].y, shift), total)),
+                                                                   f2b(__fdiv_rn(__fadd_rn(hv[r].z, shift), total)), f2b(__fdiv_rn(__fadd_rn(hv[r].w, shift), total)));
+            }
+            __syncwarp();
+            uint32_t hb = 0u;
+            const uint32_t haddr = smem_u32(hp);
+            for (int blk = 0; blk < H / kSub2; ++blk) hb = serial32(hb, haddr + (uint32_t)blk * (kSub2 * 4u));
+            a.ctrl->head_bits = hb;                                               // (every lane stores the same words)
+            __threadfence();
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(&a.ctrl->head_k), "r"((unsigned int)(H / kSub2)) : "memory");
+            if (lane == 0) a.ctrl->times[9] = global_ns();
+        }
+        asm volatile("bar.sync 4, %0;" ::"n"(kStepThreads) : "memory");   // (the shared memory it used is free once this passes)
+        return;
+    }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[2] = global_ns();
 
     // ---- B: statistics (pytorch_collab.py:109-112) and this CTA's chunks
     const int nchunks = a.nchunks;
     const int q = nchunks / (int)gridDim.x, r = nchunks % (int)gridDim.x;
-    const int c_first = (int)blockIdx.x * q + min((int)blockIdx.x, r), c_count = q + ((int)blockIdx.x < r ? 1 : 0);
+    // contiguous blocks of chunks, the r larger blocks at the END of the pool: the expensive chunks (those in which the running
+    // sum changes binade, crowded at the head of the pool) then sit alone in their CTA
+    const int big0 = (int)gridDim.x - r;
+    const int c_first = (int)blockIdx.x * q + max(0, (int)blockIdx.x - big0), c_count = q + ((int)blockIdx.x >= big0 ? 1 : 0);
     const int per = a.tile_rows, npart = (int)((a.n + per - 1) / per), parts_per_chunk = kChunk / per;
     float raw[8];
     auto load_raw = [&](int c) {
@@ -690,6 +873,12 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     if (c_count > 0) load_raw(c_first);
     const float ema_prev = *a.ema_state;
     double tot = 0.0, pre = 0.0;
+    double own_part[2] = {0.0, 0.0};   // this warp's chunk: its (at most 64) tile sums, two per lane, requested up front
+    if (warp < min(c_count, 8)) {
+        const int p0 = (c_first + warp) * parts_per_chunk;
+        if (lane < parts_per_chunk && p0 + lane < npart) own_part[0] = __ldcg(a.part + p0 + lane);
+        if (lane + 32 < parts_per_chunk && p0 + lane + 32 < npart) own_part[1] = __ldcg(a.part + p0 + lane + 32);
+    }
     {
         const int first_part = (int)((int64_t)(c_count > 0 ? c_first : 0) * kChunk / per);
         constexpr int kInFlight = 16;
@@ -708,10 +897,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         if (lane == 0) { s2.dred[0][warp] = tot; s2.dred[1][warp] = pre; }
         // the sum of each of this CTA's chunks (one warp per chunk; more than 8 chunks per CTA: in rounds below)
         if (warp < min(c_count, 8)) {
-            const int p0 = (c_first + warp) * parts_per_chunk;
-            double o = 0.0;
-            for (int i = p0 + lane; i < min(p0 + parts_per_chunk, npart); i += 32) o += __ldcg(a.part + i);
-            o = warp_sum(o);
+            const double o = warp_sum(own_part[0] + own_part[1]);
             if (lane == 0) s2.own[warp] = o;
         }
         wsync();
@@ -725,6 +911,10 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     const float ema = a.ema_first ? mean : __fadd_rn(__fmul_rn(al, ema_prev), __fmul_rn(one_minus_a, mean));
     const float shift = __fmul_rn((float)a.smooth_alpha, ema);
     const float total = (float)(tot + n_stat * (double)shift);
+    if (blockIdx.x == 0) {   // CTA 0's spare warp needs shift / total for the head of the pool
+        if (tid == 0) { s2.bc_shift = shift; s2.bc_total = total; }
+        asm volatile("bar.sync 3, %0;" ::"n"(kStepThreads) : "memory");
+    }
     if (blockIdx.x == 0 && tid == 0) {
         a.ctrl->times[14] = global_ns();
         a.stats[MERCURY_STAT_MEAN] = mean; a.stats[MERCURY_STAT_EMA] = ema;
@@ -763,7 +953,12 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         if (blockIdx.x == 0) a.ctrl->times[3] = global_ns();
     }
     wsync();
-    if (ticket_s == gridDim.x - 1) {
+    const bool walker = ticket_s == gridDim.x - 1;
+    if (blockIdx.x == 0) {   // CTA 0's spare warp may still be summing the head of the pool out of the dynamic shared memory:
+        if (walker) asm volatile("bar.sync 4, %0;" ::"n"(kStepThreads) : "memory");     // the walker needs that memory -> wait
+        else asm volatile("bar.arrive 4, %0;" ::"n"(kStepThreads) : "memory");          // everybody else just lets it finish
+    }
+    if (walker) {
         __threadfence();
         if (tid == 0) a.ctrl->times[4] = global_ns();
         walker_body(a, smem, wst, shift, total, ema);
@@ -787,6 +982,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         }
         wsync();
         const unsigned long long v = dinfo_s;
+        if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 64) a.ctrl->evt[106] = global_ns();
         if (!(v >> 63)) return;  // timed out (reported): leave the outputs alone rather than write garbage
         draw_resolve<true>(a.d, j, a.d.u[j], (int)((v >> 32) & 0x7fffffffu), (uint32_t)v, true, ds, cdf_s);
     }

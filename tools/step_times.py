@@ -22,7 +22,7 @@ u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(3
 ema = torch.zeros(1, device=dev)
 out = {}
 ops.set_fused(1)
-order = [("scored", 1), ("barrier", 2), ("stats", 14), ("summarized", 15), ("published", 3), ("walker", 4), ("loaded", 5),
+order = [("scored", 1), ("barrier", 2), ("stats", 14), ("summarized", 15), ("head", 9), ("published", 3), ("walker", 4), ("loaded", 5),
          ("walked", 6), ("draws_out", 7), ("cta0_done", 8)]
 for i in range(10):
     r = ops.update_samples(*pools[i % 7], u, ema, i == 0, data=payload, index=index, out=out)
@@ -35,7 +35,12 @@ ops.check_status(r.status)
 if int(os.environ.get("MERCURY_STEP_DBG", "0")) & 1:
     nev = t[12]
     ev = t[16:16 + nev + 1]
-    print("walk steps (cycles : kind of the step, 0 add 1 map 3 pack 4 slow):")
-    print(" ".join(f"{(ev[i] >> 4) - (ev[i - 1] >> 4)}:{ev[i] & 15}" for i in range(1, len(ev))))
+    print("walk steps (cycles : kind of the step, 0 add 1 map 3 pack 4 slow [general-loop scans / serial sub-chunks / tie maps]); head_k =", t[13])
+    print(" ".join(f"{(ev[i] >> 16) - (ev[i - 1] >> 16)}:{ev[i] & 15}" + (f"[{(ev[i] >> 12) & 15}/{(ev[i] >> 8) & 15}/{(ev[i] >> 4) & 15}]" if ev[i] & 15 == 3 else "")
+                   for i in range(1, len(ev))))
 if int(os.environ.get("MERCURY_STEP_DBG", "0")) & 2:
     print("micro (cycles): 16 dependent SHFL loop iterations", t[16 + 104], "| 64 unrolled dependent FADD", t[16 + 105])
+if int(os.environ.get("MERCURY_STEP_DBG", "0")) & 4:
+    e = t[16 + 100:16 + 110]
+    print("CTA 0, chunk 0 (us since start): p ready %.2f | thread maps %.2f | summary written %.2f | sub-chunk maps %.2f | pack written %.2f" % tuple((x - t[0]) / 1e3 for x in e[:5]))
+    print("CTA 0 draw (us since start): word seen %.2f | chunk loaded %.2f | slot known %.2f | done %.2f" % tuple((x - t[0]) / 1e3 for x in (e[6], e[7], e[8], t[8])))
