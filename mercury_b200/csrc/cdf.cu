@@ -1891,7 +1891,9 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     d.out_labels = a.out_labels; d.out_index = a.out_index;
     d.dbg = (dbg_flags & 4) ? &w.ctrl->evt[107] : nullptr;
     const int64_t ntiles = (a.n + sa.tile_rows - 1) / sa.tile_rows;
-    const int64_t want = ntiles > a.b ? (ntiles > nchunks ? ntiles : nchunks) : (a.b > nchunks ? a.b : nchunks);
+    // CTAs wanted: one per tile of scores, per chunk (+ the walker, which owns none) or per draw, whichever is largest
+    int64_t want = ntiles > a.b ? ntiles : a.b;
+    if (want < nchunks + 1) want = nchunks + 1;
     if (a.dtype == MERCURY_F32) {
         if (a.c == 10) return fused_launch_typed<float, 10>(sa, want, st);
         return fused_launch_typed<float, 0>(sa, want, st);

@@ -10,7 +10,7 @@
 //      the 2-state map of the chunk in the guessed phase; a chunk in which the running sum may change binade also gets
 //      a Pack2: one map per 32-candidate sub-chunk for the guessed phase and the next, and the raw candidates of the
 //      sub-chunks in which the change should fall;
-//      -- every CTA arrives on a counter; the LAST one to arrive walks --
+//      -- the last CTA is the walker: it owns no chunks and polls the summaries (tagged with the launch's start time) --
 //   C  the walker: loads all summaries + packs into shared memory (one round trip), walks the chain (chunk level as in
 //      spine_kernel; inside a pack the 64 sub-chunk increments are scanned by the warp, the first sub-chunk whose end
 //      leaves the phase is summed with the reference's own loop, 32 dependent fp32 adds), writes the exact boundary
@@ -54,11 +54,11 @@ static_assert(sizeof(Pack2) == 3584 && offsetof(Pack2, raw) % 16 == 0 && offseto
 
 struct StepCtrl {
     unsigned int nflag;            // pack slots handed out
-    unsigned int arrive;           // CTAs that published their summaries
-    unsigned int head_k;           // sub-chunks at the head of chunk 0 already summed serially (by CTA 0's spare warp) ...
-    unsigned int head_bits;        // ... and the exact running sum behind them
-    unsigned int head_want;        // what head_k will be once that warp is done (0: no head)
+    unsigned int arrive_unused;
+    unsigned int packs_done;       // packs written (the walker waits for min(nflag, kStepMaxPacks))
     unsigned int pad_[27];
+    unsigned long long epoch;      // this launch's tag (%globaltimer at its start): a summary is valid once it carries it
+
     unsigned long long times[16];  // developer aid: %globaltimer at the phase changes (CTA 0 and the walker)
     unsigned long long evt[112];   // developer aid: clock64 after each of the walk's first steps (kind in the low 4 bits)
     unsigned long long dinfo[kStepMaxDraws];  // per draw: 1 << 63 | chunk << 32 | boundary bits
@@ -113,6 +113,31 @@ __device__ __forceinline__ uint32_t sub_inc(uint32_t e, uint32_t d00, uint32_t d
     return g == kAnyPhase ? 0u : r;
 }
 
+// Sum of the plain increments of 8 addends while the running sum is in phase E, and whether any of them is an exact tie
+// (then the sum is meaningless and the caller composes the 2-state maps instead).  p / ulp is p times a power of two,
+// exact in fp32, and away from ties the increment is that number rounded to nearest: 7 instructions per addend.
+__device__ __forceinline__ void plain_incs8(const uint32_t (&pb)[8], uint32_t E, uint32_t& sum, bool& tie) {
+    sum = 0u;
+    tie = false;
+    if (E < kFastPhaseMin) {   // (running sums below 2^-104: the scale is not a normal float; the integer version decides)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const Pair q = addend_pair_fast(pb[k], E);
+            tie |= q.d0 != q.d1;
+            sum += q.d0;
+        }
+        return;
+    }
+    const float scale = b2f((276u - E) << 23);             // 2^(149 - E)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float t = fminf(b2f(pb[k]) * scale, 33554432.f);   // capped at 2^25 (inf and NaN land there too)
+        const float r = rintf(t);
+        sum += (uint32_t)r;                                 // (8 * 2^25 fits)
+        tie |= fabsf(r - t) == 0.5f;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // phase B: one chunk -> Summary (+ Pack2)
 struct Sum2Smem {
@@ -124,11 +149,12 @@ struct Sum2Smem {
     double own[8];
     int slot;
     uint32_t sub_e[kSubs2]; uint2 sub_q0[kSubs2], sub_q1[kSubs2];
-    float bc_shift, bc_total;
 };
 
+// epoch: this launch's tag.  The summary carries it in both of its 16-byte halves (each written by one vector store), which
+// is how the walker knows that a summary it reads is this launch's: no fence, no counter.
 __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const float (&raw)[8], double pre, double own, float shift,
-                                                 float total, Sum2Smem& sm) {
+                                                 float total, Sum2Smem& sm, unsigned long long epoch) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t start = (int64_t)c * kChunk;
     const int len = (int)min((int64_t)kChunk, a.n - start);
@@ -155,8 +181,6 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
     {
         // without exact ties every addend is a plain increment and the thread's map is their sum (the usual case);
         // only a thread that meets a tie composes the 2-state maps
-        uint32_t plain = 0u;
-        bool tie = false;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const float x = b2f(pb[k]);
@@ -164,12 +188,12 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
             else if (isinf(x)) bad |= MERCURY_ST_NONFINITE;
             nz |= pb[k] != 0u;
             tsum += x;
-            const Pair q = addend_pair_fast(pb[k], e);
-            tie |= q.d0 != q.d1;
-            plain += q.d0;                                 // (8 * 2^25 fits)
         }
+        uint32_t plain;
+        bool tie;
+        plain_incs8(pb, e, plain, tie);
         a0.d0 = a0.d1 = sat(plain);
-        if (tie) {
+        if (tie || bad) {
             a0 = identity_pair();
 #pragma unroll
             for (int k = 0; k < 8; ++k) a0 = compose(a0, addend_pair_fast(pb[k], e));
@@ -209,10 +233,10 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         for (int i = 0; i < kStepNT / 32; ++i) { t0 = compose(t0, sm.wt[i]); any |= sm.wnz[i]; }
         Summary s;
         s.e = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u) | (flagged && slot < 0 ? kNoPack : 0u) | (t0.d0 != t0.d1 ? kTie0 : 0u);
-        s.q[0] = t0;
-        s.q[1] = Pair{kSatCap, kSatCap};
-        s.pad[0] = (uint32_t)slot; s.pad[1] = s.pad[2] = 0;
-        a.sums[c] = s;
+        uint4* dst = reinterpret_cast<uint4*>(a.sums + c);
+        // {e, q0.d0, q0.d1, tag lo} {tag hi, slot, 0, 0}: Summary's q[1] and pad[1..] are not used on this path
+        dst[0] = make_uint4(s.e, t0.d0, t0.d1, (uint32_t)epoch);
+        dst[1] = make_uint4((uint32_t)(epoch >> 32), (uint32_t)slot, 0u, 0u);
     }
     if (slot < 0) return;
     MB_BSTAMP(2);
@@ -227,14 +251,11 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
     const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, a.bias, &es, sub_margin(a.nchunks)) && sub_nz;
     Pair m0, m1;
     {
-        uint32_t p0 = 0u, p1 = 0u;
-        bool tie = false;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const Pair x0 = addend_pair_fast(pb[k], es), x1 = addend_pair_fast(pb[k], es + 1u);
-            tie |= (x0.d0 != x0.d1) | (x1.d0 != x1.d1);
-            p0 += x0.d0; p1 += x1.d0;
-        }
+        uint32_t p0, p1;
+        bool tie0, tie1;
+        plain_incs8(pb, es, p0, tie0);
+        plain_incs8(pb, es + 1u, p1, tie1);
+        const bool tie = tie0 | tie1 | (bad != 0);
         m0.d0 = m0.d1 = sat(p0); m1.d0 = m1.d1 = sat(p1);
         if (tie) {
             m0 = identity_pair(); m1 = identity_pair();
@@ -299,6 +320,9 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         if (lane == 0) pk->e_lo = e;
     }
     MB_BSTAMP(4);
+    // the pack is complete: tell the walker
+    wsync();
+    if (threadIdx.x == 0) { __threadfence(); atomicAdd(&a.ctrl->packs_done, 1u); }   // (release: cumulative over the barrier)
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -531,16 +555,16 @@ __host__ __device__ inline int walk2_slots(int nchunks) {
 
 struct WalkStatic {
     WalkEnv env;
-    int nev, carry_ev;
-    unsigned long long wtot[kStepNT / 32];
-    unsigned long long carry_s;
-    int wcnt[kStepNT / 32];
+    int npacks;
+    bool packs_early;
+    unsigned long long wtot[kStepMaxChunks / kStepNT][kStepNT / 32];
+    int wcnt[kStepMaxChunks / kStepNT][kStepNT / 32];
 };
 
 // The walker (one CTA, 256 threads + named barrier 1).  Leaves the boundary values in global memory, and publishes the
 // chunk of every draw.
 __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm, WalkStatic& ws, float stat_shift, float stat_total,
-                                            float stat_ema) {
+                                            float stat_ema, unsigned long long epoch) {
     const int nchunks = a.nchunks;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(sm);
@@ -558,38 +582,63 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
     uint4* evs = reinterpret_cast<uint4*>(stage + kStageWords);
     uint32_t* evb = reinterpret_cast<uint32_t*>(evs + kStepMaxEvents);
 
-    // ---- everything in one round trip: the packs (first max_slots slots, whether used or not) and the summaries
+    // ---- the summaries (the packs follow once the steps are compiled: they are still being written)
     if (tid == 0) {
-        ws.carry_s = 0ull; ws.carry_ev = 0;
-        WalkEnv& e = ws.env;
+        WalkEnv& e = ws.env;   // (head_k / head_bits were filled in by the warp that summed the head of the pool)
         e.src = a.d.src; e.n = a.n; e.shift = stat_shift; e.totalw = stat_total;
         e.pc = pc; e.ce = ce; e.qd0 = qd0; e.qd1 = qd1; e.stopw = stopw; e.slot_of = slot_of; e.sb = sb; e.stage = stage;
         e.slots = slots; e.spare = spare; e.packs_g = a.packs; e.sums = a.sums; e.start_bits = a.start_bits;
-        e.head_k = 0; e.head_bits = 0u;
-        const unsigned int want = __ldcg(&a.ctrl->head_want);
-        if (want) {   // the head of the pool is being summed by CTA 0's spare warp: normally long done by now
-            const unsigned long long t0 = global_ns();
-            unsigned int got;
-            do {
-                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(got) : "l"(&a.ctrl->head_k) : "memory");
-            } while (got != want && global_ns() - t0 < 20000ull);   // (20 us: then walk chunk 0 from its start, the general way)
-            if (got == want) { __threadfence(); e.head_k = (int)want; e.head_bits = __ldcg(&a.ctrl->head_bits); }
-        }
         e.cnt_iter = e.cnt_serial = e.cnt_map = 0u;
         a.ctrl->times[13] = (unsigned long long)e.head_k;
     }
-    // (the first round of summaries is requested before the packs, so that both travel together)
-    uint4 sum_lo = make_uint4(0u, 0u, 0u, 0u);
-    uint32_t sum_slot = 0u;
-    if (tid < nchunks) {
-        sum_lo = __ldcg(reinterpret_cast<const uint4*>(a.sums + tid));                  // e, q0.d0, q0.d1, q1.d0
-        sum_slot = __ldcg(reinterpret_cast<const uint32_t*>(a.sums + tid) + 5);         // pad[0]
-    }
+    // All rounds of 256 chunks are handled together, so that every stage below needs ONE barrier: loads, prefix sums of the
+    // chunk increments, the stop mask, the precompiled steps.
+    constexpr int kR = kStepMaxChunks / kStepNT;
+    const int nr = (nchunks + kStepNT - 1) / kStepNT;
+    uint4 lo[kR];
+    uint32_t sl[kR];
     {
+        // every thread polls its own summaries until they carry this launch's tag (the workers write them with two 16-byte
+        // stores, the tag in both: whatever is read with the tag is complete)
+        const uint32_t tag_lo = (uint32_t)epoch, tag_hi = (uint32_t)(epoch >> 32);
+        const unsigned long long t0 = global_ns();
+        bool ok[kR];
+#pragma unroll
+        for (int r = 0; r < kR; ++r) { ok[r] = !(r < nr && r * kStepNT + tid < nchunks); lo[r] = make_uint4(0u, 0u, 0u, 0u); sl[r] = 0u; }
+        for (unsigned int it = 0;; ++it) {
+            bool all = true;
+#pragma unroll
+            for (int r = 0; r < kR; ++r) {
+                if (!ok[r]) {
+                    const uint32_t* src = reinterpret_cast<const uint32_t*>(a.sums + (r * kStepNT + tid));
+                    uint4 v; uint2 h;
+                    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src) : "memory");
+                    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0,%1}, [%2];" : "=r"(h.x), "=r"(h.y) : "l"(src + 4) : "memory");
+                    if (v.w == tag_lo && h.x == tag_hi) { lo[r] = v; sl[r] = h.y; ok[r] = true; } else all = false;
+                }
+            }
+            if (all) break;
+            if ((it & 15u) == 15u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); break; }
+        }
+    }
+    // the packs: all slots are handed out by now (a flagged chunk claims its slot before it writes its summary, and every
+    // summary has been seen); if the packs are all written already they are fetched now, else once the steps are compiled
+    wsync();
+    if (tid == 0) {
+        const unsigned int nflag = __ldcg(&a.ctrl->nflag);
+        const unsigned int want = nflag < (unsigned)kStepMaxPacks ? nflag : (unsigned)kStepMaxPacks;
+        unsigned int got;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(got) : "l"(&a.ctrl->packs_done) : "memory");
+        ws.npacks = (int)want;
+        ws.packs_early = got >= want;
+        if (got >= want) __threadfence();
+    }
+    wsync();
+    auto load_packs = [&]() {
         constexpr int kPackVecs = (int)(sizeof(Pack2) / 16);
         const uint4* g4 = reinterpret_cast<const uint4*>(a.packs);
         uint4* s4 = reinterpret_cast<uint4*>(slots);
-        const int total_vecs = min(max_slots, kStepMaxPacks) * kPackVecs;
+        const int total_vecs = min(max_slots, ws.npacks) * kPackVecs;
         for (int i0 = tid; i0 < total_vecs; i0 += 8 * kStepNT) {
             uint4 v[8];
 #pragma unroll
@@ -597,17 +646,19 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
 #pragma unroll
             for (int k = 0; k < 8; ++k) { const int i = i0 + k * kStepNT; if (i < total_vecs) s4[i] = v[k]; }
         }
-    }
-    wsync();
-    for (int c0 = 0; c0 < nchunks; c0 += kStepNT) {
-        const int c = c0 + tid;
+    };
+    const bool packs_early = ws.packs_early;
+    if (packs_early) load_packs();
+    unsigned long long excl[kR];   // this chunk's increment prefix inside its warp (exclusive)
+#pragma unroll
+    for (int r = 0; r < kR; ++r) {
+        if (r >= nr) break;
+        const int c = r * kStepNT + tid;
         unsigned long long inc = 0ull;
         if (c < nchunks) {
-            const uint4 lo = c0 == 0 ? sum_lo : __ldcg(reinterpret_cast<const uint4*>(a.sums + c));
-            const uint32_t slot = c0 == 0 ? sum_slot : __ldcg(reinterpret_cast<const uint32_t*>(a.sums + c) + 5);
-            ce[c] = lo.x; qd0[c] = lo.y; qd1[c] = lo.z;
-            slot_of[c] = ((lo.x & kFlag) && (int)slot < max_slots) ? (uint8_t)(slot + 1) : 0;
-            inc = lo.y;
+            ce[c] = lo[r].x; qd0[c] = lo[r].y; qd1[c] = lo[r].z;
+            slot_of[c] = ((lo[r].x & kFlag) && (int)sl[r] < max_slots) ? (uint8_t)(sl[r] + 1) : 0;
+            inc = lo[r].y;
         }
         const unsigned long long mine = inc;
 #pragma unroll
@@ -615,16 +666,27 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
             const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
             if (lane >= o) inc += v;
         }
-        if (lane == 31) ws.wtot[warp] = inc;
-        wsync();
-        unsigned long long pre = ws.carry_s;
-        for (int i = 0; i < warp; ++i) pre += ws.wtot[i];
-        if (c < nchunks) pc[c] = pre + inc - mine;
-        wsync();
-        if (tid == kStepNT - 1) ws.carry_s = pre + inc;
-        wsync();
+        if (lane == 31) ws.wtot[r][warp] = inc;
+        excl[r] = inc - mine;
     }
-    if (tid == 0) pc[nchunks] = ws.carry_s;
+    wsync();
+    {
+        unsigned long long running = 0ull;
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+            if (r >= nr) break;
+            const int c = r * kStepNT + tid;
+            unsigned long long pre = running;
+#pragma unroll
+            for (int i = 0; i < kStepNT / 32; ++i) {
+                const unsigned long long t = ws.wtot[r][i];
+                if (i < warp) pre += t;
+                running += t;
+            }
+            if (c < nchunks) pc[c] = pre + excl[r];
+        }
+        if (tid == 0) pc[nchunks] = running;
+    }
     // stop mask: chunks that need individual treatment, or where the guess changes
     for (int w0 = 0; w0 < (nchunks + 32) / 32; w0 += kStepNT / 32) {
         const int c = (w0 + warp) * 32 + lane;
@@ -639,16 +701,33 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
         if (lane == 0 && w0 + warp < (nchunks + 32) / 32) stopw[w0 + warp] = bits;
     }
     wsync();
-    // precompiled chunk-level walk (as in spine_kernel)
-    for (int c0 = 0; c0 < nchunks; c0 += kStepNT) {
-        const int c = c0 + tid;
+    // precompiled chunk-level walk (as in spine_kernel): a step starts at chunk 0, at every stop, and behind every chunk
+    // that is a step of its own
+    unsigned bal[kR];
+#pragma unroll
+    for (int r = 0; r < kR; ++r) {
+        bal[r] = 0u;
+        if (r >= nr) break;
+        const int c = r * kStepNT + tid;
         bool start = false;
         if (c < nchunks) start = c == 0 || ((stopw[c >> 5] >> (c & 31)) & 1u) || (ce[c - 1] & (kFlag | kTie0 | kNoPack)) != 0u;
-        const unsigned bal = __ballot_sync(0xffffffffu, start);
-        if (lane == 0) ws.wcnt[warp] = __popc(bal);
-        wsync();
-        int idx = ws.carry_ev + __popc(bal & ((1u << lane) - 1u));
-        for (int i = 0; i < warp; ++i) idx += ws.wcnt[i];
+        bal[r] = __ballot_sync(0xffffffffu, start);
+        if (lane == 0) ws.wcnt[r][warp] = __popc(bal[r]);
+    }
+    wsync();
+    int nev_all = 0;
+#pragma unroll
+    for (int r = 0; r < kR; ++r) {
+        if (r >= nr) break;
+        const int c = r * kStepNT + tid;
+        int idx = nev_all + __popc(bal[r] & ((1u << lane) - 1u));
+#pragma unroll
+        for (int i = 0; i < kStepNT / 32; ++i) {
+            const int t = ws.wcnt[r][i];
+            if (i < warp) idx += t;
+            nev_all += t;
+        }
+        const bool start = (bal[r] >> lane) & 1u;
         if (start && idx < kStepMaxEvents) {
             const uint32_t e = ce[c];
             uint4 ev;
@@ -656,21 +735,33 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
             else if (e & kNoPack) ev = make_uint4(kEvSlow, (uint32_t)c | ((uint32_t)(c + 1) << 16), 0u, 0u);
             else if (e & kTie0) ev = make_uint4(kEvMap | ((e & kPhaseMask) << 8), (uint32_t)c | ((uint32_t)(c + 1) << 16), qd0[c], qd1[c]);
             else {
-                const int s = next_bit(stopw, c + 1);
+                const int s2 = next_bit(stopw, c + 1);
                 uint32_t g = kAnyPhase;
-                for (int k = c; k < s && g == kAnyPhase; ++k) g = ce[k] & kPhaseMask;
-                const unsigned long long inc = pc[s] - pc[c];
-                ev = make_uint4(kEvAdd | (g << 8), (uint32_t)c | ((uint32_t)s << 16), (uint32_t)inc, (uint32_t)(inc >> 32));
+                for (int k = c; k < s2 && g == kAnyPhase; ++k) g = ce[k] & kPhaseMask;
+                const unsigned long long inc = pc[s2] - pc[c];
+                ev = make_uint4(kEvAdd | (g << 8), (uint32_t)c | ((uint32_t)s2 << 16), (uint32_t)inc, (uint32_t)(inc >> 32));
             }
             evs[idx] = ev;
         }
-        wsync();
-        if (tid == kStepNT - 1) ws.carry_ev = idx + (start ? 1 : 0);
-        wsync();
     }
-    if (tid == 0) ws.nev = ws.carry_ev;
+    if (!packs_early) {
+        if (tid == 0) {   // wait until every pack is written
+            const unsigned int want = (unsigned int)ws.npacks;
+            unsigned int got;
+            const unsigned long long t0 = global_ns();
+            for (unsigned int it = 0;; ++it) {
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(got) : "l"(&a.ctrl->packs_done) : "memory");
+                if (got >= want) break;
+                if ((it & 63u) == 63u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); break; }
+            }
+            __threadfence();
+        }
+        wsync();
+        load_packs();
+    }
+    if (tid == 64) a.ctrl->times[10] = global_ns();
     wsync();
-    const int nev = ws.nev;
+    const int nev = nev_all;
     const bool use_events = nev <= kStepMaxEvents;
     if (tid == 32) a.ctrl->times[5] = global_ns();   // (a thread of another warp: the walking warp stays converged)
 
@@ -790,14 +881,14 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     __shared__ Sum2Smem s2;
     __shared__ DrawSmem ds;
     __shared__ WalkStatic wst;
-    __shared__ unsigned int ticket_s;
     __shared__ unsigned long long dinfo_s;
     cg::grid_group grid = cg::this_grid();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (blockIdx.x == 0 && tid == 0) {
-        a.ctrl->nflag = 0u; a.ctrl->arrive = 0u; a.ctrl->head_k = 0u; a.ctrl->head_bits = 0u;
-        a.ctrl->head_want = (unsigned int)((min(kHeadMax, (int)min((int64_t)kChunk, a.n)) & ~(kSub2 - 1)) / kSub2);
-        a.ctrl->times[0] = global_ns();
+        const unsigned long long now = global_ns();
+        a.ctrl->nflag = 0u; a.ctrl->packs_done = 0u;
+        a.ctrl->epoch = now;                       // this launch's tag (read by everybody behind the grid barrier)
+        a.ctrl->times[0] = now;
     }
     if (blockIdx.x == 0) for (int64_t j = tid; j < a.d.b; j += kStepThreads) a.ctrl->dinfo[j] = 0ull;
     // ---- A: scores + tile sums
@@ -805,56 +896,22 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
                                                                a.ignore_index, a.scores, a.status, a.part);
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[1] = global_ns();
     grid.sync();
-    if (warp == kStepNT / 32) {
-        // The producer warp has nothing more to do -- except in CTA 0, where it sums the head of the pool serially (the
-        // reference's own loop) while the other warps build the summaries: the running sum changes binade about ten times
-        // in the first thousand candidates, which would otherwise cost the walk one serial pass each.
-        if (blockIdx.x != 0) return;
-        asm volatile("bar.sync 3, %0;" ::"n"(kStepThreads) : "memory");   // the workers have put shift / total into s2
-        const int len0 = (int)min((int64_t)kChunk, a.n);
-        const int H = min(kHeadMax, len0) & ~(kSub2 - 1);
-        if (H > 0) {
-            const float shift = s2.bc_shift, total = s2.bc_total;
-            uint32_t* hp = reinterpret_cast<uint32_t*>(smem);
-            // all loads first (8 x 16 bytes per lane in flight), then the arithmetic
-            const bool vec = (reinterpret_cast<uintptr_t>(a.scores) & 15) == 0;
-            float4 hv[kHeadMax / 128];
-#pragma unroll
-            for (int r = 0; r < kHeadMax / 128; ++r) {
-                const int i = (r * 32 + lane) * 4;
-                if (i < H) {
-                    if (vec) hv[r] = __ldcg(reinterpret_cast<const float4*>(a.scores + i));
-                    else hv[r] = make_float4(__ldcg(a.scores + i), __ldcg(a.scores + i + 1), __ldcg(a.scores + i + 2), __ldcg(a.scores + i + 3));
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < kHeadMax / 128; ++r) {
-                const int i = (r * 32 + lane) * 4;
-                if (i < H)
-                    *reinterpret_cast<uint4*>(hp + i) = make_uint4(f2b(__fdiv_rn(__fadd_rn(hv[r].x, shift), total)), f2b(__fdiv_rn(__fadd_rn(hv[r].y, shift), total)),
-                                                                   f2b(__fdiv_rn(__fadd_rn(hv[r].z, shift), total)), f2b(__fdiv_rn(__fadd_rn(hv[r].w, shift), total)));
-            }
-            __syncwarp();
-            uint32_t hb = 0u;
-            const uint32_t haddr = smem_u32(hp);
-            for (int blk = 0; blk < H / kSub2; ++blk) hb = serial32(hb, haddr + (uint32_t)blk * (kSub2 * 4u));
-            a.ctrl->head_bits = hb;                                               // (every lane stores the same words)
-            __threadfence();
-            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(&a.ctrl->head_k), "r"((unsigned int)(H / kSub2)) : "memory");
-            if (lane == 0) a.ctrl->times[9] = global_ns();
-        }
-        asm volatile("bar.sync 4, %0;" ::"n"(kStepThreads) : "memory");   // (the shared memory it used is free once this passes)
-        return;
-    }
+    if (warp == kStepNT / 32) return;  // the producer warp has nothing more to do (the barriers below are named, 256 threads)
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[2] = global_ns();
 
-    // ---- B: statistics (pytorch_collab.py:109-112) and this CTA's chunks
+    const unsigned long long epoch = __ldcg(&a.ctrl->epoch);
+    // ---- B: statistics (pytorch_collab.py:109-112), then: the last CTA is the walker and owns no chunks (with a single
+    // CTA it is its own worker); the others each take a contiguous block of chunks
     const int nchunks = a.nchunks;
-    const int q = nchunks / (int)gridDim.x, r = nchunks % (int)gridDim.x;
-    // contiguous blocks of chunks, the r larger blocks at the END of the pool: the expensive chunks (those in which the running
-    // sum changes binade, crowded at the head of the pool) then sit alone in their CTA
-    const int big0 = (int)gridDim.x - r;
-    const int c_first = (int)blockIdx.x * q + max(0, (int)blockIdx.x - big0), c_count = q + ((int)blockIdx.x >= big0 ? 1 : 0);
+    const bool walker = blockIdx.x == gridDim.x - 1;
+    const int nworkers = gridDim.x > 1 ? (int)gridDim.x - 1 : 1;
+    const bool worker = !walker || gridDim.x == 1;
+    const int q = nchunks / nworkers, r = nchunks % nworkers;
+    // (the r larger blocks at the END of the pool: the expensive chunks -- those in which the running sum changes binade,
+    // crowded at the head of the pool -- then sit alone in their CTA)
+    const int big0 = nworkers - r;
+    const int c_first = worker ? (int)blockIdx.x * q + max(0, (int)blockIdx.x - big0) : 0;
+    const int c_count = worker ? q + ((int)blockIdx.x >= big0 ? 1 : 0) : 0;
     const int per = a.tile_rows, npart = (int)((a.n + per - 1) / per), parts_per_chunk = kChunk / per;
     float raw[8];
     auto load_raw = [&](int c) {
@@ -871,6 +928,9 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         }
     };
     if (c_count > 0) load_raw(c_first);
+    // the walker sums the head of the pool serially while the workers build their summaries (warp 1 below): its scores
+    const int len0 = (int)min((int64_t)kChunk, a.n);
+    const int H = min(kHeadMax, len0) & ~(kSub2 - 1);
     const float ema_prev = *a.ema_state;
     double tot = 0.0, pre = 0.0;
     double own_part[2] = {0.0, 0.0};   // this warp's chunk: its (at most 64) tile sums, two per lane, requested up front
@@ -895,7 +955,6 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         }
         tot = warp_sum(tot); pre = warp_sum(pre);
         if (lane == 0) { s2.dred[0][warp] = tot; s2.dred[1][warp] = pre; }
-        // the sum of each of this CTA's chunks (one warp per chunk; more than 8 chunks per CTA: in rounds below)
         if (warp < min(c_count, 8)) {
             const double o = warp_sum(own_part[0] + own_part[1]);
             if (lane == 0) s2.own[warp] = o;
@@ -911,10 +970,6 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     const float ema = a.ema_first ? mean : __fadd_rn(__fmul_rn(al, ema_prev), __fmul_rn(one_minus_a, mean));
     const float shift = __fmul_rn((float)a.smooth_alpha, ema);
     const float total = (float)(tot + n_stat * (double)shift);
-    if (blockIdx.x == 0) {   // CTA 0's spare warp needs shift / total for the head of the pool
-        if (tid == 0) { s2.bc_shift = shift; s2.bc_total = total; }
-        asm volatile("bar.sync 3, %0;" ::"n"(kStepThreads) : "memory");
-    }
     if (blockIdx.x == 0 && tid == 0) {
         a.ctrl->times[14] = global_ns();
         a.stats[MERCURY_STAT_MEAN] = mean; a.stats[MERCURY_STAT_EMA] = ema;
@@ -941,27 +996,46 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
 #pragma unroll
         for (int i = 0; i < 8; ++i) cur[i] = raw[i];
         if (k + 1 < c_count) load_raw(c_first + k + 1);   // next chunk's scores travel while this one is reduced
-        summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2);
+        summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2, epoch);
         pre += own;
     }
-    // ---- arrive; the last CTA to arrive walks
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[15] = global_ns();
-    __threadfence();
-    wsync();
-    if (tid == 0) {
-        ticket_s = atomicAdd(&a.ctrl->arrive, 1u);
-        if (blockIdx.x == 0) a.ctrl->times[3] = global_ns();
-    }
-    wsync();
-    const bool walker = ticket_s == gridDim.x - 1;
-    if (blockIdx.x == 0) {   // CTA 0's spare warp may still be summing the head of the pool out of the dynamic shared memory:
-        if (walker) asm volatile("bar.sync 4, %0;" ::"n"(kStepThreads) : "memory");     // the walker needs that memory -> wait
-        else asm volatile("bar.arrive 4, %0;" ::"n"(kStepThreads) : "memory");          // everybody else just lets it finish
-    }
+    if (blockIdx.x == 0 && tid == 0) a.ctrl->times[3] = global_ns();
     if (walker) {
-        __threadfence();
+        // ---- C: the head of the pool (warp 1: the reference's own loop over the first candidates, in which the running sum
+        // changes binade about ten times), the wait for the workers' summaries (thread 0), then the walk
+        if (warp == 1) {
+            uint32_t hb = 0u;
+            if (H > 0) {
+                // all loads first (8 x 16 bytes per lane in flight), then the arithmetic
+                float4 hv[kHeadMax / 128];
+                const bool vec = (reinterpret_cast<uintptr_t>(a.scores) & 15) == 0;
+#pragma unroll
+                for (int rr = 0; rr < kHeadMax / 128; ++rr) {
+                    const int i = (rr * 32 + lane) * 4;
+                    if (i < H) {
+                        if (vec) hv[rr] = __ldcg(reinterpret_cast<const float4*>(a.scores + i));
+                        else hv[rr] = make_float4(__ldcg(a.scores + i), __ldcg(a.scores + i + 1), __ldcg(a.scores + i + 2), __ldcg(a.scores + i + 3));
+                    }
+                }
+                uint32_t* hp = reinterpret_cast<uint32_t*>(smem) + (kStepSmemBytes / 4 - kHeadMax);   // (the stage / event area: unused until the walk)
+#pragma unroll
+                for (int rr = 0; rr < kHeadMax / 128; ++rr) {
+                    const int i = (rr * 32 + lane) * 4;
+                    if (i < H)
+                        *reinterpret_cast<uint4*>(hp + i) = make_uint4(f2b(__fdiv_rn(__fadd_rn(hv[rr].x, shift), total)), f2b(__fdiv_rn(__fadd_rn(hv[rr].y, shift), total)),
+                                                                       f2b(__fdiv_rn(__fadd_rn(hv[rr].z, shift), total)), f2b(__fdiv_rn(__fadd_rn(hv[rr].w, shift), total)));
+                }
+                __syncwarp();
+                const uint32_t haddr = smem_u32(hp);
+                for (int blk = 0; blk < H / kSub2; ++blk) hb = serial32(hb, haddr + (uint32_t)blk * (kSub2 * 4u));
+            }
+            wst.env.head_k = H / kSub2; wst.env.head_bits = hb;   // (every lane stores the same words)
+            if (lane == 0) a.ctrl->times[9] = global_ns();
+        }
         if (tid == 0) a.ctrl->times[4] = global_ns();
-        walker_body(a, smem, wst, shift, total, ema);
+        wsync();
+        walker_body(a, smem, wst, shift, total, ema, epoch);
     }
     // ---- D: draws
     float* cdf_s = reinterpret_cast<float*>(smem);

@@ -50,5 +50,35 @@ def timed(uni, label):
     print(f"{label}: {a.elapsed_time(z) / 420 * 1e3:.2f} us")
 
 
+def timed_one_graph(uni, label):
+    """All seven pools' steps in ONE graph: what is left of the per-launch gap between consecutive steps."""
+    out, status = {}, ops.new_status(dev)
+
+    def step(i):
+        r = ops.update_samples(*pools[i % 7], uni, ema, False, data=payload, index=index, out=out, status=status)
+        out.update({k: v for k, v in r.items() if k != "status" and v is not None})
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(3):
+            step(i)
+    torch.cuda.synchronize()
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr, stream=side):
+        for i in range(7):
+            step(i)
+    gr.replay()
+    torch.cuda.synchronize()
+    a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(60):
+        gr.replay()
+    z.record()
+    torch.cuda.synchronize()
+    print(f"{label}: {a.elapsed_time(z) / 420 * 1e3:.2f} us")
+
+
 timed(u, "step")
 timed(u0, "step without draws")
+timed_one_graph(u, "step, seven steps per graph")
