@@ -1849,7 +1849,7 @@ int fused_launch_typed(StepArgs& sa, int64_t want_ctas, cudaStream_t st) {
     if (per_sm <= 0 || sms <= 0) return 1;
     static const int knob_per_sm = env_knob("MERCURY_STEP_CTAS", 3, 1, 3);   // developer knob: CTAs per SM
     if (knob_per_sm < per_sm) per_sm = knob_per_sm;
-    const int grid = (int)min_i64((int64_t)per_sm * sms, want_ctas);
+    const int grid = (int)min_i64(min_i64((int64_t)per_sm * sms, want_ctas), kStepMaxCtas);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kStepThreads); cfg.dynamicSmemBytes = kStepSmemBytes; cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -1891,6 +1891,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     d.out_labels = a.out_labels; d.out_index = a.out_index;
     d.dbg = (dbg_flags & 4) ? &w.ctrl->evt[107] : nullptr;
     const int64_t ntiles = (a.n + sa.tile_rows - 1) / sa.tile_rows;
+    sa.ntiles = (int)ntiles;
     // CTAs wanted: one per tile of scores, per chunk (+ the walker, which owns none) or per draw, whichever is largest
     int64_t want = ntiles > a.b ? ntiles : a.b;
     if (want < nchunks + 1) want = nchunks + 1;

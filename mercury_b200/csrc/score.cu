@@ -131,7 +131,7 @@ score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ lab
                    int64_t ignore_index, float* __restrict__ scores, int32_t* status, double* __restrict__ tile_sums) {
     extern __shared__ __align__(128) unsigned char smem[];
     score_small_body<T, CT, STAGES, CONSUMERS, false, true>(smem, logits, labels, n, c_rt, tile_rows, ignore_index, scores, status,
-                                                            tile_sums);
+                                                            tile_sums, blockIdx.x, (n + tile_rows - 1) / tile_rows, gridDim.x, nullptr);
 }
 
 

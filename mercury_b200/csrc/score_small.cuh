@@ -81,11 +81,14 @@ __device__ __forceinline__ void ring_init(Ring<STAGES>* ring, int consumer_warps
 // PRODUCER_LAST: the producer warp is the CTA's last warp and the consumers are threads 0..CONSUMERS-1 (the fused step
 // wants its worker threads numbered from zero); otherwise warp 0 produces and the consumers follow it.
 // PDL: first kernel of a programmatic-dependent-launch chain (the stand-alone kernel).
+// This CTA scores tiles tile_begin, tile_begin + tile_step, ... < tile_end.  cta_sum_out (optional): the fp64 sum of this
+// CTA's tile sums, added in the order the tiles were taken (needs tile_sums).
 // Every thread of the CTA must call this; it returns when the CTA's tiles are done (no barrier at the end).
 template <typename T, int CT, int STAGES, int CONSUMERS, bool PRODUCER_LAST, bool PDL>
 __device__ __forceinline__ void score_small_body(unsigned char* smem, const T* __restrict__ logits, const int64_t* __restrict__ labels,
                                                  int64_t n, int c_rt, int tile_rows, int64_t ignore_index, float* __restrict__ scores,
-                                                 int32_t* status, double* __restrict__ tile_sums) {
+                                                 int32_t* status, double* __restrict__ tile_sums, int64_t tile_begin, int64_t tile_end,
+                                                 int64_t tile_step, double* __restrict__ cta_sum_out) {
     const int c = CT > 0 ? CT : c_rt;
     Ring<STAGES>* ring = reinterpret_cast<Ring<STAGES>*>(smem);
     const uint32_t logit_bytes = (uint32_t)tile_rows * c * sizeof(T);
@@ -100,14 +103,13 @@ __device__ __forceinline__ void score_small_body(unsigned char* smem, const T* _
         pdl_launch_dependents();
     }
 
-    const int64_t ntiles = (n + tile_rows - 1) / tile_rows;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool producer = PRODUCER_LAST ? warp == CONSUMERS / 32 : warp == 0;
 
     if (producer) {
         // ---- producer warp
         int it = 0;
-        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        for (int64_t tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
             const int s = it % STAGES, round = it / STAGES;
             if (round > 0) mbar_wait(&ring->empty[s], (round - 1) & 1);
             const int64_t row0 = tile * tile_rows;
@@ -134,8 +136,9 @@ __device__ __forceinline__ void score_small_body(unsigned char* smem, const T* _
     } else {
         // ---- consumers
         const int t = PRODUCER_LAST ? (int)threadIdx.x : (int)threadIdx.x - kProducerThreads;
+        double cta_acc = 0.0;
         int it = 0;
-        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        for (int64_t tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
             const int s = it % STAGES, round = it / STAGES;
             mbar_wait(&ring->full[s], round & 1);
             const int64_t row0 = tile * tile_rows;
@@ -201,9 +204,11 @@ __device__ __forceinline__ void score_small_body(unsigned char* smem, const T* _
 #pragma unroll
                     for (int i = 0; i < CONSUMERS / 32; ++i) sum += buf[i];
                     tile_sums[tile] = sum;
+                    cta_acc += sum;
                 }
             }
         }
+        if (cta_sum_out && t == 0) *cta_sum_out = cta_acc;
     }
 }
 

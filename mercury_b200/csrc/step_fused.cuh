@@ -27,6 +27,7 @@ constexpr int kStepThreads = kStepNT + kProducerThreads;
 constexpr int kStepStages = 3;
 constexpr int kStepMaxChunks = 1024;             // pools of up to 2 Mi candidates
 constexpr int kStepMaxDraws = 1024;
+constexpr int kStepMaxCtas = 1024;
 constexpr int kStepMaxPacks = 64;                // flagged chunks that get a pack (beyond: the general code)
 constexpr int kStepMaxEvents = 192;
 constexpr size_t kStepSmemBytes = 70 * 1024;
@@ -62,12 +63,13 @@ struct StepCtrl {
     unsigned long long times[16];  // developer aid: %globaltimer at the phase changes (CTA 0 and the walker)
     unsigned long long evt[112];   // developer aid: clock64 after each of the walk's first steps (kind in the low 4 bits)
     unsigned long long dinfo[kStepMaxDraws];  // per draw: 1 << 63 | chunk << 32 | boundary bits
+    double cta_part[kStepMaxCtas];            // per CTA: the fp64 sum of the scores it computed (its tiles are contiguous)
 };
 constexpr unsigned long long kStepSpinNs = 2000000000ull;  // no wait may last this long: report instead of hanging the GPU
 
 struct StepArgs {
     // K1
-    const void* logits; const int64_t* labels; int64_t n; int c; int tile_rows; int64_t ignore_index; float* scores;
+    const void* logits; const int64_t* labels; int64_t n; int c; int tile_rows; int ntiles; int64_t ignore_index; float* scores;
     double* part;                  // [ntiles] fp64 sums of the tiles' scores
     // statistics
     float* ema_state; int ema_first; double ema_alpha, smooth_alpha; float* stats;
@@ -892,8 +894,15 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     }
     if (blockIdx.x == 0) for (int64_t j = tid; j < a.d.b; j += kStepThreads) a.ctrl->dinfo[j] = 0ull;
     // ---- A: scores + tile sums
-    score_small_body<T, CT, kStepStages, kStepNT, true, false>(smem, static_cast<const T*>(a.logits), a.labels, a.n, a.c, a.tile_rows,
-                                                               a.ignore_index, a.scores, a.status, a.part);
+    // (contiguous tiles per CTA, so that one partial sum per CTA gives the pool statistics and the running totals in front
+    // of the chunks: 2 loads per thread behind the barrier instead of every CTA re-reading every tile's sum)
+    {
+        const unsigned int ntiles = (unsigned int)a.ntiles;   // (<= 2^16)
+        const int64_t tb = ntiles * blockIdx.x / gridDim.x, te = ntiles * (blockIdx.x + 1u) / gridDim.x;
+        score_small_body<T, CT, kStepStages, kStepNT, true, false>(smem, static_cast<const T*>(a.logits), a.labels, a.n, a.c, a.tile_rows,
+                                                                   a.ignore_index, a.scores, a.status, a.part, tb, te, 1,
+                                                                   &a.ctrl->cta_part[blockIdx.x]);
+    }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[1] = global_ns();
     grid.sync();
     if (warp == kStepNT / 32) return;  // the producer warp has nothing more to do (the barriers below are named, 256 threads)
@@ -912,7 +921,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     const int big0 = nworkers - r;
     const int c_first = worker ? (int)blockIdx.x * q + max(0, (int)blockIdx.x - big0) : 0;
     const int c_count = worker ? q + ((int)blockIdx.x >= big0 ? 1 : 0) : 0;
-    const int per = a.tile_rows, npart = (int)((a.n + per - 1) / per), parts_per_chunk = kChunk / per;
+    const int per = a.tile_rows, npart = a.ntiles, parts_per_chunk = kChunk / per;
     float raw[8];
     auto load_raw = [&](int c) {
         const int64_t start = (int64_t)c * kChunk;
@@ -940,19 +949,23 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         if (lane + 32 < parts_per_chunk && p0 + lane + 32 < npart) own_part[1] = __ldcg(a.part + p0 + lane + 32);
     }
     {
-        const int first_part = (int)((int64_t)(c_count > 0 ? c_first : 0) * kChunk / per);
-        constexpr int kInFlight = 16;
-        for (int i0 = tid; i0 < npart; i0 += kInFlight * kStepNT) {   // (same order of additions as summarize_kernel)
-            double v[kInFlight];
-#pragma unroll
-            for (int k = 0; k < kInFlight; ++k) { const int i = i0 + k * kStepNT; v[k] = i < npart ? __ldcg(a.part + i) : 0.0; }
-#pragma unroll
-            for (int k = 0; k < kInFlight; ++k) {
-                const int i = i0 + k * kStepNT;
-                tot += v[k];
-                if (i < first_part) pre += v[k];
-            }
+        // the CTA whose tiles straddle the start of this CTA's first chunk: the partial sums of the CTAs in front of it
+        // count whole, its own tiles in front of the chunk one by one (warp 7)
+        // (32-bit arithmetic: at most 2^16 tiles and 2^10 CTAs; 64-bit divisions are long instruction sequences)
+        const unsigned int G = gridDim.x, T = (unsigned int)npart;
+        const unsigned int t0 = min((unsigned int)(c_first * parts_per_chunk), T);
+        unsigned int bstar = T > 0u ? t0 * G / T : 0u;
+        while (bstar < G && T * (bstar + 1u) / G <= t0) ++bstar;
+        while (bstar > 0u && T * bstar / G > t0) --bstar;
+        double straddle = 0.0;
+        if (warp == kStepNT / 32 - 1 && c_count > 0 && bstar < G)
+            for (unsigned int i = T * bstar / G + lane; i < t0; i += 32) straddle += __ldcg(a.part + i);
+        for (int b = tid; b < (int)G; b += kStepNT) {   // (fixed order: every CTA gets the same bits)
+            const double v = __ldcg(&a.ctrl->cta_part[b]);
+            tot += v;
+            if ((unsigned int)b < bstar) pre += v;
         }
+        if (warp == kStepNT / 32 - 1) pre += straddle;
         tot = warp_sum(tot); pre = warp_sum(pre);
         if (lane == 0) { s2.dred[0][warp] = tot; s2.dred[1][warp] = pre; }
         if (warp < min(c_count, 8)) {

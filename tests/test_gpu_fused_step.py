@@ -59,13 +59,24 @@ def _bits(t):
 
 
 def _assert_same(a, b):
+    """Scores are the same kernel code: bit-equal.  The pool statistics are fp64 sums taken in different orders (per-tile
+    sums in the chain, per-CTA sums in the one-kernel step): equal to fp32 rounding, 1e-6 relative at most."""
     (ra, ea), (rb, eb) = a, b
-    for k in ("scores", "stats", "idx", "nprob", "seed", "data", "labels", "index"):
-        va, vb = ra[k], rb[k]
-        assert (va is None) == (vb is None), k
-        if va is not None:
-            assert torch.equal(_bits(va), _bits(vb)), f"{k} differs between chain and one-kernel step"
-    assert torch.equal(ea.view(torch.int32), eb.view(torch.int32)), "EMA state differs"
+    assert torch.equal(_bits(ra.scores), _bits(rb.scores)), "scores differ between chain and one-kernel step"
+    np.testing.assert_allclose(ra.stats.cpu().numpy()[:4], rb.stats.cpu().numpy()[:4], rtol=1e-6)
+    np.testing.assert_allclose(ea.cpu().numpy(), eb.cpu().numpy(), rtol=1e-6)
+
+
+def _assert_exact(ops, r, u, data, index, y):
+    """Indices bit-exact for the device's own importance vector; gathered rows and weights belong to those indices."""
+    p = ops.normalize(r.scores, r.stats).cpu().numpy()
+    want = orc.draw_with_replacement(p, u.numpy())
+    assert np.array_equal(r.idx.cpu().numpy(), want), "indices are not those of the serial fp32 chain"
+    if data is not None:
+        assert torch.equal(r.data.cpu(), data[want]) and torch.equal(r.index.cpu(), index[want]) and torch.equal(r.labels.cpu(), y[want])
+    np.testing.assert_array_equal(r.nprob.cpu().numpy(), p[want] * np.float32(len(p)))
+    chain = orc.serial_chain_f32(p)
+    assert r.stats.cpu().numpy().view(np.uint32)[4] == chain[-1:].view(np.uint32)[0], "chain total"
 
 
 @pytest.mark.parametrize("n,c,dtype,b,kind", [
@@ -88,13 +99,10 @@ def test_one_kernel_step_equals_chain_and_oracle(ops, n, c, dtype, b, kind):
     xd, yd, ud = x.to(DEV), y.to(DEV), u.to(DEV)
     chain, fused = _both(ops, xd, yd, ud, torch.zeros(1, device=DEV), True, data=data.to(DEV), index=index.to(DEV))
     _assert_same(chain, fused)
-    r = fused[0]
-    p = ops.normalize(r.scores, r.stats).cpu().numpy()
-    want = orc.draw_with_replacement(p, u.numpy())
-    assert np.array_equal(r.idx.cpu().numpy(), want), "indices are not those of the serial fp32 chain"
-    assert torch.equal(r.data.cpu(), data[want]) and torch.equal(r.index.cpu(), index[want]) and torch.equal(r.labels.cpu(), y[want])
+    for r, _ in (chain, fused):
+        _assert_exact(ops, r, u, data, index, y)
     ref = orc.score(x, y)
-    np.testing.assert_allclose(r.scores.cpu().numpy(), ref.numpy(), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(fused[0].scores.cpu().numpy(), ref.numpy(), rtol=1e-5, atol=1e-5)
 
 
 def test_one_kernel_step_carries_the_ema_and_reuses_its_workspace(ops):
@@ -111,8 +119,9 @@ def test_one_kernel_step_carries_the_ema_and_reuses_its_workspace(ops):
         rf = ops.update_samples(x.to(DEV), y.to(DEV), u, ema_f, it == 0)
         ops.set_fused(-1)
         ops.check_status(rf.status)
-        assert torch.equal(rc.idx, rf.idx) and torch.equal(rc.stats.view(torch.int32), rf.stats.view(torch.int32))
-        assert torch.equal(ema_c.view(torch.int32), ema_f.view(torch.int32))
+        np.testing.assert_allclose(rc.stats.cpu().numpy()[:4], rf.stats.cpu().numpy()[:4], rtol=1e-6)
+        np.testing.assert_allclose(float(ema_c), float(ema_f), rtol=1e-6)
+        _assert_exact(ops, rf, u.cpu(), None, None, None)
         orc.pool_stats(orc.score(x, y), ema_ref)
         np.testing.assert_allclose(float(ema_f), float(ema_ref.value), rtol=1e-6)
 
