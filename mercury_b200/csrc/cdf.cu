@@ -378,7 +378,7 @@ static_assert(sizeof(Pack) == 3072 && offsetof(Pack, raw) % 16 == 0 && offsetof(
 //              neither increment keeps the sum inside its phase.  y low byte = raw slot in the pack (0xff: fetch it)
 //   kEvPack  : (chunk level) a flagged chunk: y = shared-memory slot of its pack (0xffffffff: fetch it)
 //   kEvSlow  : (chunk level) a chunk that needs the general code
-enum EvKind : uint32_t { kEvAdd = 0, kEvMap = 1, kEvSerial = 2, kEvPack = 3, kEvSlow = 4 };
+enum EvKind : uint32_t { kEvAdd = 0, kEvMap = 1, kEvSerial = 2, kEvPack = 3, kEvSlow = 4, kEvEnd = 5, kEvNone = 6 };  // (kEvEnd / kEvNone: step_fused.cuh)
 
 double g_guess_bias = 1.0;  // test hook (mercury_test_set_guess_bias): scales every guess
 
@@ -1870,6 +1870,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     const int64_t elt = a.dtype == MERCURY_F32 ? 4 : 2, row_bytes = a.c * elt;
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
     if (row_bytes > 256 || nchunks > kStepMaxChunks) return 1;
+    if (g_fused_mode < 0 && nchunks > kStepBestChunks) return 1;   // (forced on by the test hook it takes all it can)
     if ((reinterpret_cast<uintptr_t>(a.logits) & 15) || (reinterpret_cast<uintptr_t>(a.labels) & 15)) return 1;
     if (walk2_slots(nchunks) < 4) return 1;
     const CdfWs w = carve(ws, a.n, true);
@@ -1907,6 +1908,13 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
 int fused_step_times(const void* ws, int64_t n, unsigned long long* h_out128) {
     const CdfWs w = carve(const_cast<void*>(ws), n, true);
     cudaError_t e = cudaMemcpy(h_out128, w.ctrl->times, 128 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && getenv("MERCURY_STEP_DUMP_K1")) {   // developer aid: per-CTA scoring times to stderr
+        static unsigned int h[kStepMaxCtas];
+        e = cudaMemcpy(h, w.ctrl->k1_end, sizeof(h), cudaMemcpyDeviceToHost);
+        const unsigned int t0 = (unsigned int)h_out128[0];
+        for (int i = 0; i < 444 && e == cudaSuccess; ++i) fprintf(stderr, "%d:%.2f ", i, (double)(h[i] - t0) / 1e3);
+        fprintf(stderr, "\n");
+    }
     return e == cudaSuccess ? MERCURY_OK : cuda_fail(e, "fused_step_times");
 }
 

@@ -25,7 +25,8 @@ namespace cg = cooperative_groups;
 constexpr int kStepNT = 256;                     // worker threads: warps 0..7 (K1's consumers); warp 8 is K1's producer
 constexpr int kStepThreads = kStepNT + kProducerThreads;
 constexpr int kStepStages = 3;
-constexpr int kStepMaxChunks = 1024;             // pools of up to 2 Mi candidates
+constexpr int kStepMaxChunks = 1024;             // pools of up to 2 Mi candidates (shared-memory layout)
+constexpr int kStepBestChunks = 768;             // ... taken by default up to 1.5 Mi (measured: the kernel chain is faster beyond)
 constexpr int kStepMaxDraws = 1024;
 constexpr int kStepMaxCtas = 1024;
 constexpr int kStepMaxPacks = 64;                // flagged chunks that get a pack (beyond: the general code)
@@ -63,7 +64,10 @@ struct StepCtrl {
     unsigned long long times[16];  // developer aid: %globaltimer at the phase changes (CTA 0 and the walker)
     unsigned long long evt[112];   // developer aid: clock64 after each of the walk's first steps (kind in the low 4 bits)
     unsigned long long dinfo[kStepMaxDraws];  // per draw: 1 << 63 | chunk << 32 | boundary bits
+    unsigned long long dinfo2[kStepMaxDraws]; // per draw: 1 << 63 | bits of the chain's total (each word is valid on its own:
+                                              // no fence between the walker's results and these words is needed)
     double cta_part[kStepMaxCtas];            // per CTA: the fp64 sum of the scores it computed (its tiles are contiguous)
+    unsigned int k1_end[kStepMaxCtas];        // developer aid (MERCURY_STEP_DBG & 4): ns from the start until each CTA had scored
 };
 constexpr unsigned long long kStepSpinNs = 2000000000ull;  // no wait may last this long: report instead of hanging the GPU
 
@@ -156,7 +160,7 @@ struct Sum2Smem {
 // epoch: this launch's tag.  The summary carries it in both of its 16-byte halves (each written by one vector store), which
 // is how the walker knows that a summary it reads is this launch's: no fence, no counter.
 __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const float (&raw)[8], double pre, double own, float shift,
-                                                 float total, Sum2Smem& sm, unsigned long long epoch) {
+                                                 float total, Sum2Smem& sm, unsigned long long epoch, bool first) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t start = (int64_t)c * kChunk;
     const int len = (int)min((int64_t)kChunk, a.n - start);
@@ -173,10 +177,13 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
     MB_BSTAMP(0);
     uint32_t e;
     const bool flagged = guess_span(a_lo, a_hi, a.bias, &e, chunk_margin(a.nchunks));  // block-uniform
+    // the usual flagged chunk meets ONE change of binade: its sub-chunks are then all summarised for the chunk's guessed
+    // phase and the next, whatever their own position (the head of the pool, with many changes, guesses per sub-chunk)
+    const bool two_phase = flagged && phase_of(f2b((float)(a_hi * a.bias * (1.0 + chunk_margin(a.nchunks))))) == e + 1u;
     // a flagged chunk claims a pack slot; the atomic's round trip hides behind the arithmetic below
     unsigned int slot_u = 0xffffffffu;
     if (flagged && threadIdx.x == 0) slot_u = atomicAdd(&a.ctrl->nflag, 1u);
-    Pair a0;
+    Pair th0, th1;   // this thread's 8 addends as a map, in phase e (and e + 1: two-phase chunks only)
     int bad = 0;
     bool nz = false;
     float tsum = 0.f;
@@ -194,15 +201,26 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         uint32_t plain;
         bool tie;
         plain_incs8(pb, e, plain, tie);
-        a0.d0 = a0.d1 = sat(plain);
+        th0.d0 = th0.d1 = sat(plain);
         if (tie || bad) {
-            a0 = identity_pair();
+            th0 = identity_pair();
 #pragma unroll
-            for (int k = 0; k < 8; ++k) a0 = compose(a0, addend_pair_fast(pb[k], e));
+            for (int k = 0; k < 8; ++k) th0 = compose(th0, addend_pair_fast(pb[k], e));
+        }
+        th1 = th0;
+        if (two_phase) {
+            plain_incs8(pb, e + 1u, plain, tie);
+            th1.d0 = th1.d1 = sat(plain);
+            if (tie || bad) {
+                th1 = identity_pair();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) th1 = compose(th1, addend_pair_fast(pb[k], e + 1u));
+            }
         }
     }
     if (bad) atomicOr(a.status, bad);
     const unsigned nzmask = __ballot_sync(0xffffffffu, nz);
+    Pair a0 = th0;
     if (__ballot_sync(0xffffffffu, a0.d0 != a0.d1) == 0u) {
         a0.d0 = a0.d1 = sat(__reduce_add_sync(0xffffffffu, a0.d0));
     } else {
@@ -222,23 +240,32 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         }
     }
     MB_BSTAMP(1);
-    wsync();  // (protects sm against the previous chunk's readers)
+    if (!first) wsync();  // (protects sm against the previous chunk's readers)
     if (lane == 0) { sm.wt[warp] = a0; sm.wnz[warp] = nzmask != 0u; }
     if (lane == 31) sm.wsum[warp] = inc;
     if (threadIdx.x == 0) sm.slot = flagged ? (slot_u < (unsigned)kStepMaxPacks ? (int)slot_u : -2) : -1;
     wsync();
     const int slot = sm.slot;
-    if (threadIdx.x == 0) {
-        Pair t0 = identity_pair();
-        int any = 0;
+    if (warp == 0) {   // the chunk's map: the 8 warp maps in order (lanes 0..7), one integer reduction unless there are ties
+        Pair t0 = lane < kStepNT / 32 ? sm.wt[lane] : identity_pair();
+        const unsigned any = __ballot_sync(0xffffffffu, lane < kStepNT / 32 && sm.wnz[lane] != 0);
+        if (__ballot_sync(0xffffffffu, t0.d0 != t0.d1) == 0u) {
+            t0.d0 = t0.d1 = sat(__reduce_add_sync(0xffffffffu, t0.d0));
+        } else {
 #pragma unroll
-        for (int i = 0; i < kStepNT / 32; ++i) { t0 = compose(t0, sm.wt[i]); any |= sm.wnz[i]; }
-        Summary s;
-        s.e = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u) | (flagged && slot < 0 ? kNoPack : 0u) | (t0.d0 != t0.d1 ? kTie0 : 0u);
-        uint4* dst = reinterpret_cast<uint4*>(a.sums + c);
-        // {e, q0.d0, q0.d1, tag lo} {tag hi, slot, 0, 0}: Summary's q[1] and pad[1..] are not used on this path
-        dst[0] = make_uint4(s.e, t0.d0, t0.d1, (uint32_t)epoch);
-        dst[1] = make_uint4((uint32_t)(epoch >> 32), (uint32_t)slot, 0u, 0u);
+            for (int off = 1; off < kStepNT / 32; off <<= 1) {
+                Pair o0;
+                o0.d0 = __shfl_down_sync(0xffffffffu, t0.d0, off); o0.d1 = __shfl_down_sync(0xffffffffu, t0.d1, off);
+                if (lane + off < kStepNT / 32) t0 = compose(t0, o0);
+            }
+        }
+        if (lane == 0) {
+            const uint32_t se = (any ? e : kAnyPhase) | (slot >= 0 ? kFlag : 0u) | (flagged && slot < 0 ? kNoPack : 0u) | (t0.d0 != t0.d1 ? kTie0 : 0u);
+            uint4* dst = reinterpret_cast<uint4*>(a.sums + c);
+            // {e, q0.d0, q0.d1, tag lo} {tag hi, slot, 0, 0}: Summary's q[1] and pad[1..] are not used on this path
+            dst[0] = make_uint4(se, t0.d0, t0.d1, (uint32_t)epoch);
+            dst[1] = make_uint4((uint32_t)(epoch >> 32), (uint32_t)slot, 0u, 0u);
+        }
     }
     if (slot < 0) return;
     MB_BSTAMP(2);
@@ -251,8 +278,9 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
     const bool sub_nz = ((nzmask >> lead) & 0xfu) != 0u;
     uint32_t es;
     const bool sub_flagged = guess_span(a_lo + (double)s_lo, a_lo + (double)s_hi, a.bias, &es, sub_margin(a.nchunks)) && sub_nz;
-    Pair m0, m1;
-    {
+    if (two_phase) es = e;
+    Pair m0 = th0, m1 = th1;
+    if (!two_phase) {
         uint32_t p0, p1;
         bool tie0, tie1;
         plain_incs8(pb, es, p0, tie0);
@@ -268,18 +296,28 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
             }
         }
     }
+    if (__ballot_sync(0xffffffffu, (m0.d0 != m0.d1) | (m1.d0 != m1.d1)) == 0u) {   // no ties in this warp: plain sums
+        uint32_t v0 = m0.d0, v1 = m1.d0;
 #pragma unroll
-    for (int off = 1; off < 4; off <<= 1) {
-        Pair o0, o1;
-        o0.d0 = __shfl_down_sync(0xffffffffu, m0.d0, off, 4); o0.d1 = __shfl_down_sync(0xffffffffu, m0.d1, off, 4);
-        o1.d0 = __shfl_down_sync(0xffffffffu, m1.d0, off, 4); o1.d1 = __shfl_down_sync(0xffffffffu, m1.d1, off, 4);
-        if ((lane & 3) + off < 4) { m0 = compose(m0, o0); m1 = compose(m1, o1); }
+        for (int off = 1; off < 4; off <<= 1) {
+            v0 += __shfl_down_sync(0xffffffffu, v0, off, 4);
+            v1 += __shfl_down_sync(0xffffffffu, v1, off, 4);
+        }
+        m0.d0 = m0.d1 = sat(v0); m1.d0 = m1.d1 = sat(v1);   // (meaningful in the leader lanes)
+    } else {
+#pragma unroll
+        for (int off = 1; off < 4; off <<= 1) {
+            Pair o0, o1;
+            o0.d0 = __shfl_down_sync(0xffffffffu, m0.d0, off, 4); o0.d1 = __shfl_down_sync(0xffffffffu, m0.d1, off, 4);
+            o1.d0 = __shfl_down_sync(0xffffffffu, m1.d0, off, 4); o1.d1 = __shfl_down_sync(0xffffffffu, m1.d1, off, 4);
+            if ((lane & 3) + off < 4) { m0 = compose(m0, o0); m1 = compose(m1, o1); }
+        }
     }
     MB_BSTAMP(3);
     Pack2* pk = a.packs + slot;
     const int my_sub = threadIdx.x >> 2;
     if ((lane & 3) == 0) {
-        pk->e[my_sub] = (sub_nz ? es : kAnyPhase) | (sub_flagged ? kFlag : 0u) | (m0.d0 != m0.d1 ? kTie0 : 0u) | (m1.d0 != m1.d1 ? kTie1 : 0u);
+        // (the word is completed below, once the raw slots are known: bits 10..13 = raw slot + 1)
         pk->q0[my_sub] = make_uint2(m0.d0, m0.d1);
         pk->q1[my_sub] = make_uint2(m1.d0, m1.d1);
         sm.sub_e[my_sub] = sub_nz ? es : kAnyPhase;
@@ -304,6 +342,11 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
         dst[0] = make_uint4(pb[0], pb[1], pb[2], pb[3]);
         dst[1] = make_uint4(pb[4], pb[5], pb[6], pb[7]);
         if ((lane & 3) == 0) pk->rawsub[my_rank] = (uint8_t)my_sub;
+    }
+    if ((lane & 3) == 0) {
+        const uint32_t raw_slot = (((fmask >> my_sub) & 1ull) && my_rank < kRaw2) ? (uint32_t)(my_rank + 1) : 0u;
+        pk->e[my_sub] = (sub_nz ? es : kAnyPhase) | (sub_flagged ? kFlag : 0u) | (m0.d0 != m0.d1 ? kTie0 : 0u) | (m1.d0 != m1.d1 ? kTie1 : 0u) |
+                        (raw_slot << 10);
     }
     if (threadIdx.x < 16 && (int)threadIdx.x >= min(__popcll(fmask), kRaw2)) pk->rawsub[threadIdx.x] = 0xff;
     if (warp == 0) {   // prefix sums of the 64 plain increments for the chunk's guessed phase and the next (2 per lane)
@@ -367,19 +410,11 @@ __device__ __noinline__ uint32_t stage_sub2(const WalkEnv* env, int c, int f, in
     return smem_u32(env->stage);
 }
 
-// serial pass over sub-chunk f of chunk c: raw candidates from the pack (shared memory, address P) if it carries them
-__device__ __forceinline__ uint32_t serial_sub2(const WalkEnv* env, uint32_t P, int c, int f, uint32_t b, int lane) {
-    const_cast<WalkEnv*>(env)->cnt_serial = env->cnt_serial + 1u;
-    const uint32_t rs = lds_u32(P + (uint32_t)offsetof(Pack2, rawsub) + 4u * (lane & 3));   // lane -> rawsub[(lane & 3) * 4 + ((lane >> 2) & 3)]
-    const uint32_t mine = (rs >> (8 * ((lane >> 2) & 3))) & 0xffu;
-    const unsigned hit = __ballot_sync(0xffffffffu, lane < 16 && mine == (uint32_t)f);
-    uint32_t saddr;
-    if (hit) {
-        const int l = __ffs(hit) - 1, r = (l & 3) * 4 + ((l >> 2) & 3);
-        saddr = P + (uint32_t)offsetof(Pack2, raw) + (uint32_t)r * (kSub2 * 4u);
-    } else {
-        saddr = stage_sub2(env, c, f, lane);
-    }
+// serial pass over sub-chunk f of chunk c (ef: its word in the pack): raw candidates from the pack (shared memory, address
+// P) if it carries them
+__device__ __forceinline__ uint32_t serial_sub2(const WalkEnv* env, uint32_t P, int c, int f, uint32_t ef, uint32_t b, int lane) {
+    const uint32_t r1 = (ef >> 10) & 15u;   // raw slot + 1
+    const uint32_t saddr = r1 ? P + (uint32_t)offsetof(Pack2, raw) + (r1 - 1u) * (kSub2 * 4u) : stage_sub2(env, c, f, lane);
     b = serial32(b, saddr);
     __syncwarp();
     return b;
@@ -417,7 +452,7 @@ __device__ __forceinline__ uint32_t run_pack2(const WalkEnv* env, uint32_t P, in
         k = f + 1;
         if (by_map) S = Sn;   // (exact ties inside, the sum stays in the phase: on with the general loop)
         else {
-            b = serial_sub2(env, P, c, f, bits_of(E, Sf), lane);
+            b = serial_sub2(env, P, c, f, ef, bits_of(E, Sf), lane);
             E = phase_of(b); S = b - (E << 23);
             const uint32_t Se = S + (rest_hi - rest_lo);
             if (E == e_lo + 1u && Se < kPhaseLimit) return bits_of(E, Se);
@@ -431,7 +466,6 @@ __device__ __forceinline__ uint32_t run_pack2(const WalkEnv* env, uint32_t P, in
     uint32_t s_in = 0u, s_mid = 0u, s_out = 0u;
     for (;;) {
         if (rescan) {
-            const_cast<WalkEnv*>(env)->cnt_iter = env->cnt_iter + 1u;
             const uint32_t w0 = 2 * lane >= k ? sub_inc(ee.x, q0.x, q0.y, q1.x, q1.y, E) : 0u;
             const uint32_t w1 = 2 * lane + 1 >= k ? sub_inc(ee.y, q0.z, q0.w, q1.z, q1.w, E) : 0u;
             uint32_t v = w0 + w1;                                    // (64 * 2^25 fits in 32 bits)
@@ -463,13 +497,12 @@ __device__ __forceinline__ uint32_t run_pack2(const WalkEnv* env, uint32_t P, in
         if (by_map) {
             // same phase: every running sum behind f moves by (what f really added) - (the kBadInc it was counted as);
             // no new scan (unsigned wrap-around is fine: only entries behind f are looked at again)
-            const_cast<WalkEnv*>(env)->cnt_map = env->cnt_map + 1u;
             const uint32_t adj = (Sn - Sf) - kBadInc;
             S = Sn;
             s_in += adj; s_mid += adj; s_out += adj;
             rescan = false;
         } else {
-            b = serial_sub2(env, P, c, f, bits_of(E, Sf), lane);
+            b = serial_sub2(env, P, c, f, ef, bits_of(E, Sf), lane);
             E = phase_of(b); S = b - (E << 23);
             rescan = true;
         }
@@ -626,6 +659,7 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
     // the packs: all slots are handed out by now (a flagged chunk claims its slot before it writes its summary, and every
     // summary has been seen); if the packs are all written already they are fetched now, else once the steps are compiled
     wsync();
+    if (tid == 64) a.ctrl->times[4] = global_ns();
     if (tid == 0) {
         const unsigned int nflag = __ldcg(&a.ctrl->nflag);
         const unsigned int want = nflag < (unsigned)kStepMaxPacks ? nflag : (unsigned)kStepMaxPacks;
@@ -696,28 +730,53 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
         if (c < nchunks) {
             const uint32_t e = ce[c], g = e & kPhaseMask;
             stop = (e & (kFlag | kTie0 | kNoPack)) != 0u;
-            if (c > 0) { const uint32_t gp = ce[c - 1] & kPhaseMask; if (g != kAnyPhase && gp != kAnyPhase && g != gp) stop = true; }
+            if (c > 0) {   // (a change of the guess right behind a chunk of its own needs no stop: a run starts there anyway)
+                const uint32_t ep = ce[c - 1], gp = ep & kPhaseMask;
+                if (g != kAnyPhase && gp != kAnyPhase && g != gp && !(ep & (kFlag | kTie0 | kNoPack))) stop = true;
+            }
         }
         if (c == nchunks) stop = true;  // sentinel
         const unsigned bits = __ballot_sync(0xffffffffu, stop);
         if (lane == 0 && w0 + warp < (nchunks + 32) / 32) stopw[w0 + warp] = bits;
     }
     wsync();
-    // precompiled chunk-level walk (as in spine_kernel): a step starts at chunk 0, at every stop, and behind every chunk
-    // that is a step of its own
+    // The walk, precompiled: one step per stop s (and one for the end of the pool).  A step is the additive run of plain
+    // chunks in front of s -- one guarded addition of prefix sums -- followed by what chunk s itself needs: its pack, its
+    // 2-state map, the general code, or nothing (s only marks a change of the guessed phase).
     unsigned bal[kR];
 #pragma unroll
     for (int r = 0; r < kR; ++r) {
         bal[r] = 0u;
         if (r >= nr) break;
         const int c = r * kStepNT + tid;
-        bool start = false;
-        if (c < nchunks) start = c == 0 || ((stopw[c >> 5] >> (c & 31)) & 1u) || (ce[c - 1] & (kFlag | kTie0 | kNoPack)) != 0u;
-        bal[r] = __ballot_sync(0xffffffffu, start);
+        const bool stop = c < nchunks && ((stopw[c >> 5] >> (c & 31)) & 1u);
+        bal[r] = __ballot_sync(0xffffffffu, stop);
         if (lane == 0) ws.wcnt[r][warp] = __popc(bal[r]);
     }
     wsync();
     int nev_all = 0;
+    auto make_step = [&](int s2) -> uint4 {
+        // the run in front of s2 starts behind the previous stop if that was a chunk of its own, else at it
+        int p = s2 - 1, run_start = 0;
+        {
+            int w = p >> 5;
+            uint32_t m = p >= 0 ? stopw[w] & (0xffffffffu >> (31 - (p & 31))) : 0u;
+            while (p >= 0 && m == 0u && w > 0) m = stopw[--w];
+            if (p >= 0 && m != 0u) {
+                const int q = (w << 5) + 31 - __clz(m);
+                run_start = (ce[q] & (kFlag | kTie0 | kNoPack)) ? q + 1 : q;
+            }
+        }
+        uint32_t g = kAnyPhase;
+        for (int k = run_start; k < s2 && g == kAnyPhase; ++k) g = ce[k] & kPhaseMask;
+        const unsigned long long inc = pc[s2] - pc[run_start];
+        uint32_t kind = kEvEnd;
+        if (s2 < nchunks) {
+            const uint32_t e = ce[s2];
+            kind = (e & kFlag) ? kEvPack : (e & kNoPack) ? kEvSlow : (e & kTie0) ? kEvMap : kEvNone;
+        }
+        return make_uint4(kind | (g << 8), (uint32_t)run_start | ((uint32_t)s2 << 16), (uint32_t)inc, (uint32_t)(inc >> 32));
+    };
 #pragma unroll
     for (int r = 0; r < kR; ++r) {
         if (r >= nr) break;
@@ -729,23 +788,10 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
             if (i < warp) idx += t;
             nev_all += t;
         }
-        const bool start = (bal[r] >> lane) & 1u;
-        if (start && idx < kStepMaxEvents) {
-            const uint32_t e = ce[c];
-            uint4 ev;
-            if (e & kFlag) ev = make_uint4(kEvPack, (uint32_t)c | ((uint32_t)(c + 1) << 16), 0u, 0u);
-            else if (e & kNoPack) ev = make_uint4(kEvSlow, (uint32_t)c | ((uint32_t)(c + 1) << 16), 0u, 0u);
-            else if (e & kTie0) ev = make_uint4(kEvMap | ((e & kPhaseMask) << 8), (uint32_t)c | ((uint32_t)(c + 1) << 16), qd0[c], qd1[c]);
-            else {
-                const int s2 = next_bit(stopw, c + 1);
-                uint32_t g = kAnyPhase;
-                for (int k = c; k < s2 && g == kAnyPhase; ++k) g = ce[k] & kPhaseMask;
-                const unsigned long long inc = pc[s2] - pc[c];
-                ev = make_uint4(kEvAdd | (g << 8), (uint32_t)c | ((uint32_t)s2 << 16), (uint32_t)inc, (uint32_t)(inc >> 32));
-            }
-            evs[idx] = ev;
-        }
+        if (((bal[r] >> lane) & 1u) && idx < kStepMaxEvents) evs[idx] = make_step(c);
     }
+    if (tid == 0 && nev_all < kStepMaxEvents) evs[nev_all] = make_step(nchunks);   // the end of the pool
+    nev_all += 1;
     if (!packs_early) {
         if (tid == 0) {   // wait until every pack is written
             const unsigned int want = (unsigned int)ws.npacks;
@@ -792,45 +838,47 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
             if (stamp) a.ctrl->evt[0] = (unsigned long long)clock64() << 16;
             for (int i = 0; i < nev; ++i) {
                 const uint4 ev = evs[i];
-                if (stamp && i > 0 && i < 100)
-                    a.ctrl->evt[i] = ((unsigned long long)clock64() << 16) | (env->cnt_iter << 12) | ((env->cnt_serial & 15u) << 8) | ((env->cnt_map & 15u) << 4) | (evs[i - 1].x & 0xfu);
-                if (stamp) { ws.env.cnt_iter = 0u; ws.env.cnt_serial = 0u; ws.env.cnt_map = 0u; }
+                if (stamp && i > 0 && i < 100) a.ctrl->evt[i] = ((unsigned long long)clock64() << 16) | (evs[i - 1].x & 0xfu);
                 const uint32_t kind = ev.x & 0xffu, ph = (ev.x >> 8) & kPhaseMask;
-                const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);
-                if (kind == kEvAdd) {
+                const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);   // the run [c, s), then chunk s
+                if (s > c) {
                     const unsigned long long Sn = (unsigned long long)S + (((unsigned long long)ev.w << 32) | ev.z);
                     if ((ph == E || ph == kAnyPhase) && Sn < kPhaseLimit) {
                         evb[i] = bits_of(E, S);   // boundary values of [c, s): filled in by the whole CTA afterwards
                         S = (uint32_t)Sn;
-                        continue;
+                    } else {   // a contradicted guard: the general walk over the run (it records the boundary values itself)
+                        evs[i].x = ev.x | 0x80u;
+                        __syncwarp();
+                        b = walk_general2(env, c, s, bits_of(E, S), lane);
+                        E = phase_of(b); S = b - (E << 23);
                     }
-                } else if (kind == kEvMap) {
-                    const uint32_t Sn = S + ((S & 1u) ? ev.w : ev.z);
-                    if (ph == E && Sn < kPhaseLimit) {
-                        a.start_bits[c] = bits_of(E, S); sb[c] = bits_of(E, S);
-                        S = Sn;
-                        continue;
-                    }
-                } else if (kind == kEvPack) {
+                }
+                if (kind == kEvPack) {
                     b = bits_of(E, S);
-                    a.start_bits[c] = b; sb[c] = b;
-                    const int sl = (int)slot_of[c] - 1;
-                    const uint32_t P = sl >= 0 ? smem_u32(&slots[sl]) : fetch_pack2(env, (int)a.sums[c].pad[0], lane);
-                    const bool head = c == 0 && env->head_k > 0;
-                    b = run_pack2(env, P, c, head ? env->head_bits : b, lane, head ? env->head_k : 0);
+                    a.start_bits[s] = b; sb[s] = b;
+                    const int sl = (int)slot_of[s] - 1;
+                    const uint32_t P = sl >= 0 ? smem_u32(&slots[sl]) : fetch_pack2(env, (int)a.sums[s].pad[0], lane);
+                    const bool head = s == 0 && env->head_k > 0;
+                    b = run_pack2(env, P, s, head ? env->head_bits : b, lane, head ? env->head_k : 0);
                     __syncwarp();
                     E = phase_of(b); S = b - (E << 23);
-                    continue;
+                } else if (kind == kEvMap) {
+                    const uint32_t d0 = qd0[s], d1 = qd1[s];
+                    const uint32_t Sn = S + ((S & 1u) ? d1 : d0);
+                    if ((ce[s] & kPhaseMask) == E && Sn < kPhaseLimit) {
+                        a.start_bits[s] = bits_of(E, S); sb[s] = bits_of(E, S);
+                        S = Sn;
+                    } else {
+                        b = walk_general2(env, s, s + 1, bits_of(E, S), lane);
+                        E = phase_of(b); S = b - (E << 23);
+                    }
+                } else if (kind == kEvSlow) {
+                    b = walk_general2(env, s, s + 1, bits_of(E, S), lane);
+                    E = phase_of(b); S = b - (E << 23);
                 }
-                // a contradicted guard, or a chunk without a shortcut: the general walk over this step's chunks
-                evs[i].x = kEvSlow;  // (so that the fill below skips it)
-                __syncwarp();
-                b = walk_general2(env, c, s, bits_of(E, S), lane);
-                E = phase_of(b); S = b - (E << 23);
             }
             b = bits_of(E, S);
-            if (stamp && nev < 100)
-                a.ctrl->evt[nev] = ((unsigned long long)clock64() << 16) | (env->cnt_iter << 12) | ((env->cnt_serial & 15u) << 8) | ((env->cnt_map & 15u) << 4) | (evs[nev - 1].x & 0xfu);
+            if (stamp && nev < 100) a.ctrl->evt[nev] = ((unsigned long long)clock64() << 16) | (evs[nev - 1].x & 0xfu);
         }
         // (every lane writes the same words)
         *a.ema_state = stat_ema;  // EMAverage.value for the next call (util.py:207-213)
@@ -850,8 +898,9 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
     if (use_events) {
         for (int i = warp; i < nev; i += kStepNT / 32) {
             const uint4 ev = evs[i];
-            if ((ev.x & 0xffu) != kEvAdd) continue;
+            if (ev.x & 0x80u) continue;   // (that run was walked the general way)
             const int c = (int)(ev.y & 0xffffu), s = (int)(ev.y >> 16);
+            if (s <= c) continue;
             const uint32_t b0 = evb[i], E = phase_of(b0), S = b0 - (E << 23);
             const unsigned long long base = pc[c];
             for (int k = c + lane; k < s; k += 32) {
@@ -860,7 +909,6 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
             }
         }
     }
-    __threadfence();
     wsync();
     // ---- the chunk of every draw: first chunk whose last cdf value is not below u (ATen's lower bound), then publish
     const float total = b2f(sb[nchunks]);
@@ -872,8 +920,21 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
             if ((double)__fdiv_rn(b2f(sb[mid + 1]), total) < uj) lo = mid + 1; else hi = mid;
         }
         st_relaxed_u64(&a.ctrl->dinfo[j], (1ull << 63) | ((unsigned long long)lo << 32) | sb[lo]);
+        st_relaxed_u64(&a.ctrl->dinfo2[j], (1ull << 63) | f2b(total));
     }
     if (tid == 0) a.ctrl->times[7] = global_ns();
+}
+
+// Tiles of scores per CTA: contiguous ranges, the CTAs of the first third of the grid a little longer ones than those of
+// the last third.  With three CTAs per SM the grid comes up in three waves; the last wave starts about a microsecond
+// later (measured), and an even split would leave everybody waiting for it at the grid barrier.  A static rule, so the
+// sums come out the same in every run.  first tile of CTA b = T * W(b) / W(G), W = cumulative weight.
+__device__ __forceinline__ unsigned int tile_weight_prefix(unsigned int b, unsigned int G) {
+    const unsigned int g1 = G / 3u, g2 = 2u * G / 3u;   // weights 53 : 50 : 47
+    return 53u * min(b, g1) + 50u * (min(b, g2) - min(b, g1)) + 47u * (b - min(b, g2));
+}
+__device__ __forceinline__ unsigned int tile_begin(unsigned int b, unsigned int G, unsigned int T) {
+    return (unsigned int)((unsigned long long)T * tile_weight_prefix(b, G) / tile_weight_prefix(G, G));
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -890,20 +951,26 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         const unsigned long long now = global_ns();
         a.ctrl->nflag = 0u; a.ctrl->packs_done = 0u;
         a.ctrl->epoch = now;                       // this launch's tag (read by everybody behind the grid barrier)
+        a.ctrl->times[11] = 0ull;
         a.ctrl->times[0] = now;
     }
-    if (blockIdx.x == 0) for (int64_t j = tid; j < a.d.b; j += kStepThreads) a.ctrl->dinfo[j] = 0ull;
+    if (blockIdx.x == 0) for (int64_t j = tid; j < a.d.b; j += kStepThreads) { a.ctrl->dinfo[j] = 0ull; a.ctrl->dinfo2[j] = 0ull; }
     // ---- A: scores + tile sums
     // (contiguous tiles per CTA, so that one partial sum per CTA gives the pool statistics and the running totals in front
     // of the chunks: 2 loads per thread behind the barrier instead of every CTA re-reading every tile's sum)
     {
         const unsigned int ntiles = (unsigned int)a.ntiles;   // (<= 2^16)
-        const int64_t tb = ntiles * blockIdx.x / gridDim.x, te = ntiles * (blockIdx.x + 1u) / gridDim.x;
+        int64_t tb = tile_begin(blockIdx.x, gridDim.x, ntiles), te = tile_begin(blockIdx.x + 1u, gridDim.x, ntiles), ts = 1;
         score_small_body<T, CT, kStepStages, kStepNT, true, false>(smem, static_cast<const T*>(a.logits), a.labels, a.n, a.c, a.tile_rows,
-                                                                   a.ignore_index, a.scores, a.status, a.part, tb, te, 1,
+                                                                   a.ignore_index, a.scores, a.status, a.part, tb, te, ts,
                                                                    &a.ctrl->cta_part[blockIdx.x]);
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[1] = global_ns();
+    if ((a.dbg_flags & 4) && tid == 0) {   // developer aid: when the LAST CTA had scored, and when each one had
+        const unsigned long long now = global_ns();
+        atomicMax(&a.ctrl->times[11], now);
+        a.ctrl->k1_end[blockIdx.x] = (unsigned int)now;
+    }
     grid.sync();
     if (warp == kStepNT / 32) return;  // the producer warp has nothing more to do (the barriers below are named, 256 threads)
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[2] = global_ns();
@@ -954,12 +1021,14 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         // (32-bit arithmetic: at most 2^16 tiles and 2^10 CTAs; 64-bit divisions are long instruction sequences)
         const unsigned int G = gridDim.x, T = (unsigned int)npart;
         const unsigned int t0 = min((unsigned int)(c_first * parts_per_chunk), T);
-        unsigned int bstar = T > 0u ? t0 * G / T : 0u;
-        while (bstar < G && T * (bstar + 1u) / G <= t0) ++bstar;
-        while (bstar > 0u && T * bstar / G > t0) --bstar;
+        unsigned int bstar = T > 0u ? t0 * G / T : 0u;   // (a first guess; the weights move it by a few CTAs at most)
+        bstar = min(bstar, G - 1u);
+        while (bstar + 1u < G && tile_begin(bstar + 1u, G, T) <= t0) ++bstar;
+        while (bstar > 0u && tile_begin(bstar, G, T) > t0) --bstar;
+        if (t0 >= T) bstar = G;   // (nothing in front of a chunk that starts behind the last tile -- cannot happen)
         double straddle = 0.0;
         if (warp == kStepNT / 32 - 1 && c_count > 0 && bstar < G)
-            for (unsigned int i = T * bstar / G + lane; i < t0; i += 32) straddle += __ldcg(a.part + i);
+            for (unsigned int i = tile_begin(bstar, G, T) + lane; i < t0; i += 32) straddle += __ldcg(a.part + i);
         for (int b = tid; b < (int)G; b += kStepNT) {   // (fixed order: every CTA gets the same bits)
             const double v = __ldcg(&a.ctrl->cta_part[b]);
             tot += v;
@@ -1009,7 +1078,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
 #pragma unroll
         for (int i = 0; i < 8; ++i) cur[i] = raw[i];
         if (k + 1 < c_count) load_raw(c_first + k + 1);   // next chunk's scores travel while this one is reduced
-        summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2, epoch);
+        summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2, epoch, k == 0);
         pre += own;
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[15] = global_ns();
@@ -1046,32 +1115,38 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
             wst.env.head_k = H / kSub2; wst.env.head_bits = hb;   // (every lane stores the same words)
             if (lane == 0) a.ctrl->times[9] = global_ns();
         }
-        if (tid == 0) a.ctrl->times[4] = global_ns();
         wsync();
         walker_body(a, smem, wst, shift, total, ema, epoch);
     }
-    // ---- D: draws
+    // ---- D: draws.  What a draw needs from the walker comes in its two words; the pool statistics are in registers
+    // already (every CTA computed the same bits), so draw_resolve reads both from shared memory instead of global memory.
     float* cdf_s = reinterpret_cast<float*>(smem);
+    __shared__ float dstats[MERCURY_STAT_COUNT];
+    __shared__ float dtotal;
+    DrawArgs da = a.d;
+    da.src.stats = dstats;
+    da.total_ptr = &dtotal;
     for (int64_t j = blockIdx.x; j < a.d.b; j += gridDim.x) {
         wsync();   // (the walker's shared memory, and the previous draw's, are free again)
         if (tid == 0) {
-            unsigned long long v = ld_relaxed_u64(&a.ctrl->dinfo[j]);
-            if (!(v >> 63)) {
-                const unsigned long long t0 = global_ns();
-                for (unsigned int it = 0;; ++it) {
-                    v = ld_relaxed_u64(&a.ctrl->dinfo[j]);
-                    if (v >> 63) break;
-                    if ((it & 63u) == 63u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); break; }
-                }
+            unsigned long long v, w;
+            const unsigned long long t0 = global_ns();
+            for (unsigned int it = 0;; ++it) {
+                v = ld_relaxed_u64(&a.ctrl->dinfo[j]);
+                w = ld_relaxed_u64(&a.ctrl->dinfo2[j]);
+                if ((v & w) >> 63) break;
+                if ((it & 63u) == 63u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); v = 0ull; break; }
             }
-            __threadfence();
             dinfo_s = v;
+            dtotal = b2f((uint32_t)w);
+            dstats[MERCURY_STAT_SHIFT] = shift; dstats[MERCURY_STAT_TOTAL] = total;
         }
+        const double uj = a.d.u[j];
         wsync();
         const unsigned long long v = dinfo_s;
         if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 64) a.ctrl->evt[106] = global_ns();
         if (!(v >> 63)) return;  // timed out (reported): leave the outputs alone rather than write garbage
-        draw_resolve<true>(a.d, j, a.d.u[j], (int)((v >> 32) & 0x7fffffffu), (uint32_t)v, true, ds, cdf_s);
+        draw_resolve<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), (uint32_t)v, true, ds, cdf_s);
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[8] = global_ns();
 }

@@ -10,8 +10,9 @@ from mercury_b200 import ops  # noqa: E402
 
 dev = torch.device("cuda", 0)
 n, c, b = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000, 10, 128
+NP = 7 if n * 48 >= (40 << 20) else min(64, -(-(320 << 20) // (n * 48)))   # >= 300 MB of pools in rotation
 g = torch.Generator(device=dev).manual_seed(100)
-pools = [((torch.randn(n, c, generator=g, device=dev) * 2), torch.randint(0, c, (n,), generator=g, device=dev)) for _ in range(7)]
+pools = [((torch.randn(n, c, generator=g, device=dev) * 2), torch.randint(0, c, (n,), generator=g, device=dev)) for _ in range(NP)]
 payload = torch.rand(n, 3, 32, 32, device=dev, generator=g)
 index = torch.arange(n, device=dev)
 u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(3)).to(dev)
@@ -23,7 +24,7 @@ def timed(uni, label):
     out, status = {}, ops.new_status(dev)
 
     def step(i):
-        r = ops.update_samples(*pools[i % 7], uni, ema, False, data=payload, index=index, out=out, status=status)
+        r = ops.update_samples(*pools[i % NP], uni, ema, False, data=payload, index=index, out=out, status=status)
         out.update({k: v for k, v in r.items() if k != "status" and v is not None})
 
     side = torch.cuda.Stream()
@@ -33,7 +34,7 @@ def timed(uni, label):
             step(i)
     torch.cuda.synchronize()
     graphs = []
-    for i in range(7):
+    for i in range(NP):
         gr = torch.cuda.CUDAGraph()
         with torch.cuda.graph(gr, stream=side):
             step(i)
@@ -44,7 +45,7 @@ def timed(uni, label):
     a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for i in range(420):
-        graphs[i % 7].replay()
+        graphs[i % NP].replay()
     z.record()
     torch.cuda.synchronize()
     print(f"{label}: {a.elapsed_time(z) / 420 * 1e3:.2f} us")
@@ -55,7 +56,7 @@ def timed_one_graph(uni, label):
     out, status = {}, ops.new_status(dev)
 
     def step(i):
-        r = ops.update_samples(*pools[i % 7], uni, ema, False, data=payload, index=index, out=out, status=status)
+        r = ops.update_samples(*pools[i % NP], uni, ema, False, data=payload, index=index, out=out, status=status)
         out.update({k: v for k, v in r.items() if k != "status" and v is not None})
 
     side = torch.cuda.Stream()
@@ -66,19 +67,20 @@ def timed_one_graph(uni, label):
     torch.cuda.synchronize()
     gr = torch.cuda.CUDAGraph()
     with torch.cuda.graph(gr, stream=side):
-        for i in range(7):
+        for i in range(NP):
             step(i)
     gr.replay()
     torch.cuda.synchronize()
     a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for i in range(60):
+    reps = max(4, 420 // NP)
+    for i in range(reps):
         gr.replay()
     z.record()
     torch.cuda.synchronize()
-    print(f"{label}: {a.elapsed_time(z) / 420 * 1e3:.2f} us")
+    print(f"{label}: {a.elapsed_time(z) / (reps * NP) * 1e3:.2f} us")
 
 
 timed(u, "step")
 timed(u0, "step without draws")
-timed_one_graph(u, "step, seven steps per graph")
+timed_one_graph(u, f"step, {NP} steps per graph")

@@ -22,7 +22,7 @@ u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(3
 ema = torch.zeros(1, device=dev)
 out = {}
 ops.set_fused(1)
-order = [("scored", 1), ("barrier", 2), ("stats", 14), ("summarized", 15), ("head", 9), ("published", 3), ("walker", 4), ("packs_in", 10), ("loaded", 5),
+order = [("scored", 1), ("all_scored", 11), ("barrier", 2), ("stats", 14), ("summarized", 15), ("head", 9), ("published", 3), ("summaries_seen", 4), ("packs_in", 10), ("loaded", 5),
          ("walked", 6), ("draws_out", 7), ("cta0_done", 8)]
 for i in range(10):
     r = ops.update_samples(*pools[i % 7], u, ema, i == 0, data=payload, index=index, out=out)
