@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define MERCURY_ABI_VERSION 2
+#define MERCURY_ABI_VERSION 3
 
 enum { MERCURY_OK = 0, MERCURY_ERR_ARG = -1, MERCURY_ERR_CUDA = -2, MERCURY_ERR_WORKSPACE = -3 };
 
@@ -248,6 +248,11 @@ typedef struct mercury_update_args {
     double* sums_all;                 /* out fp64 [n_shards]: every shard's sum of scores                      */
     float* totals_all;                /* out fp32 [n_shards]: every shard's chain total                        */
     double* local_uniforms;           /* out fp64 [b]: position inside this shard's CDF, or -1 (not mine)      */
+    /* how the cumulative distribution is accumulated (ABI 3): MERCURY_CDF_EXACT_SERIAL_F32 (0, the default: indices     */
+    /* bit-identical to torch.multinomial on the CPU for the same p and uniforms) or MERCURY_CDF_F64: cdf_i = float(fp64  */
+    /* running total / fp64 total) -- deterministic and without the serial walk, a draw from the same distribution but   */
+    /* not the same indices.  MERCURY_CDF_F64 excludes global_sums and peer_boxes.                                       */
+    int cdf_mode;
 } mercury_update_args;
 
 size_t mercury_update_samples_workspace_bytes(int64_t n, int64_t b);

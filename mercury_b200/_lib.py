@@ -10,7 +10,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(HERE, "libmercury_b200.so")
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 OK, ERR_ARG, ERR_CUDA, ERR_WORKSPACE = 0, -1, -2, -3
 F32, BF16 = 0, 1
@@ -40,6 +40,7 @@ class UpdateArgs(ctypes.Structure):
         ("global_sums", c_vp), ("n_global_sums", c_int), ("n_global", c_i64), ("index_base", c_i64), ("draw_only", c_int),
         ("peer_boxes", c_vp), ("n_shards", c_int), ("shard_rank", c_int), ("sums_all", c_vp), ("totals_all", c_vp),
         ("local_uniforms", c_vp),
+        ("cdf_mode", c_int),
     ]
 
 

@@ -101,6 +101,10 @@ extern "C" int mercury_update_samples(const mercury_update_args* a, void* ws, si
                  "mercury_update_samples: sharded call needs n_global_sums >= 1, n_global >= n and no pool-size list");
     MB_CHECK_ARG(!a->global_sums || a->n <= ((int64_t)8192 * 2048), "mercury_update_samples: shard too large");
     MB_CHECK_ARG(!a->draw_only || a->scores_in, "mercury_update_samples: draw_only needs scores_in");
+    MB_CHECK_ARG(a->cdf_mode == MERCURY_CDF_EXACT_SERIAL_F32 || a->cdf_mode == MERCURY_CDF_F64, "mercury_update_samples: unknown cdf_mode %d",
+                 a->cdf_mode);
+    MB_CHECK_ARG(a->cdf_mode == MERCURY_CDF_EXACT_SERIAL_F32 || (!a->global_sums && !a->peer_boxes),
+                 "mercury_update_samples: MERCURY_CDF_F64 excludes global_sums and peer_boxes");
     if (a->peer_boxes) {
         MB_CHECK_ARG(!a->global_sums && !a->draw_only && a->n_bounds == 0,
                      "mercury_update_samples: peer_boxes excludes global_sums, draw_only and a pool-size list");

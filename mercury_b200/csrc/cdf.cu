@@ -1415,8 +1415,53 @@ struct DrawArgs {
     const double* u; int64_t b;
     const unsigned char* data; int64_t row_bytes; const int64_t* labels; const int64_t* index;
     int64_t* idx; float* nprob; float* seed; unsigned char* out_data; int64_t* out_labels; int64_t* out_index;
+    const double* approx;      // fp64 mode: running total of p in front of every chunk, [nchunks + 1]
     unsigned long long* dbg;   // developer aid: when set, CTA 0 stamps %globaltimer after the chunk's scores arrived and after the slot is known
 };
+
+// (d) of a draw: the payload row of candidate `pick` -> output row j, plus the scalar outputs.  Everybody issues its first
+// loads at once; the scalar outputs ride along.
+__device__ __forceinline__ void draw_gather(const DrawArgs& a, int64_t j, int64_t pick) {
+    if (a.dbg && blockIdx.x == 0 && threadIdx.x == 64) a.dbg[1] = global_ns();
+    const bool copy = a.data && a.out_data;
+    const unsigned char* srow = copy ? a.data + pick * a.row_bytes : nullptr;
+    unsigned char* drow = copy ? a.out_data + j * a.row_bytes : nullptr;
+    const bool vec = copy && ((reinterpret_cast<uintptr_t>(srow) | reinterpret_cast<uintptr_t>(drow) | (uintptr_t)a.row_bytes) & 15) == 0;
+    const int64_t nvec = vec ? (a.row_bytes >> 4) : 0;
+    constexpr int kAhead = 4;
+    uint4 v[kAhead];
+#pragma unroll
+    for (int k = 0; k < kAhead; ++k) {
+        const int64_t i = threadIdx.x + (int64_t)k * kDrawNT;
+        if (i < nvec) v[k] = ldg_stream(reinterpret_cast<const uint4*>(srow) + i);
+    }
+    if (threadIdx.x == 0) {
+        // all loads first (a store in between would order them one latency after the other)
+        const bool want_l = a.labels && a.out_labels, want_i = a.index && a.out_index;
+        const int64_t lab = want_l ? a.labels[pick] : 0, ind = want_i ? a.index[pick] : 0;
+        float shift, tot2;
+        a.src.prepare(shift, tot2);
+        const float p = a.src.get(pick, shift, tot2);
+        // pytorch_collab.py:116: losses_pros[idx] * N ; :137,:145: grad = (1/B) / probs
+        const float np_ = __fmul_rn(p, (float)a.n_weight);
+        a.idx[j] = a.idx_base + pick;
+        a.nprob[j] = np_;
+        a.seed[j] = __fdiv_rn(__fdiv_rn(1.f, (float)a.b), np_);
+        if (want_l) a.out_labels[j] = lab;
+        if (want_i) a.out_index[j] = ind;
+    }
+    if (vec) {
+#pragma unroll
+        for (int k = 0; k < kAhead; ++k) {
+            const int64_t i = threadIdx.x + (int64_t)k * kDrawNT;
+            if (i < nvec) reinterpret_cast<uint4*>(drow)[i] = v[k];
+        }
+        for (int64_t i = threadIdx.x + (int64_t)kAhead * kDrawNT; i < nvec; i += kDrawNT)
+            reinterpret_cast<uint4*>(drow)[i] = reinterpret_cast<const uint4*>(srow)[i];
+    } else if (copy) {
+        for (int64_t i = threadIdx.x; i < a.row_bytes; i += kDrawNT) drow[i] = srow[i];
+    }
+}
 
 // barrier among the kDrawNT threads that work on a draw: the whole CTA in the stand-alone kernel, the 256 worker
 // threads (named barrier 1) inside the fused step, whose CTAs carry one more warp
@@ -1430,6 +1475,7 @@ struct DrawSmem {
     ResolveSmem rs;
     int wcnt[kDrawNT / 32];
     int64_t chosen;
+    double dwt[kDrawNT / 32];
 };
 
 // One draw by kDrawNT threads: `chunk` < 0 -> find the chunk from the boundary values first.  cdf_s: kChunk floats of
@@ -1610,47 +1656,98 @@ __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, doubl
         bits = nb;
     }
     draw_sync<NAMED>();
-    // (d) payload row: everybody issues its first loads as soon as the slot is known; the scalar outputs ride along
-    if (a.dbg && blockIdx.x == 0 && threadIdx.x == 64) a.dbg[1] = global_ns();
-    const int64_t pick = chosen;
-    const bool copy = a.data && a.out_data;
-    const unsigned char* srow = copy ? a.data + pick * a.row_bytes : nullptr;
-    unsigned char* drow = copy ? a.out_data + j * a.row_bytes : nullptr;
-    const bool vec = copy && ((reinterpret_cast<uintptr_t>(srow) | reinterpret_cast<uintptr_t>(drow) | (uintptr_t)a.row_bytes) & 15) == 0;
-    const int64_t nvec = vec ? (a.row_bytes >> 4) : 0;
-    constexpr int kAhead = 4;
-    uint4 v[kAhead];
+    draw_gather(a, j, chosen);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// fp64 mode of the whole step (MERCURY_CDF_F64): cdf_i = float(fp64 running total of p / fp64 total), searched as ATen
+// searches.  Deterministic, no serial walk -- and not index-identical to torch.multinomial (3.5 % of the
+// draws agree at a million candidates); for callers that want a draw from the same distribution, not the same stream.
+__global__ void __launch_bounds__(256) psum_kernel(WeightSrc src, int64_t n, double* __restrict__ sums, int32_t* status) {
+    __shared__ double red[8];
+    pdl_wait();
+    pdl_launch_dependents();
+    float shift, total;
+    src.prepare(shift, total);
+    const int64_t start = (int64_t)blockIdx.x * kChunk;
+    const int len = (int)min((int64_t)kChunk, n - start);
+    double acc = 0.0;
+    int bad = 0;
+    for (int i = threadIdx.x; i < len; i += 256) {
+        const float x = src.get(start + i, shift, total);
+        if (!(x >= 0.f)) bad |= MERCURY_ST_NEGATIVE;
+        else if (isinf(x)) bad |= MERCURY_ST_NONFINITE;
+        acc += (double)x;
+    }
+    if (bad) atomicOr(status, bad);
+    const double t = block_sum<256>(acc, red);
+    if (threadIdx.x == 0) sums[blockIdx.x] = t;
+}
+
+// One fp64 draw by kDrawNT threads.  chunk < 0: find it from a.approx first; else run0 is the running total in front of it.
+template <bool NAMED>
+__device__ __forceinline__ void draw_resolve_f64(const DrawArgs& a, int64_t j, double uj, int chunk, double run0, double total64,
+                                                 DrawSmem& ds) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (chunk < 0) {
+        int cnt = 0;
+        for (int c = threadIdx.x; c < a.nchunks; c += kDrawNT) cnt += ((double)(float)(a.approx[c + 1] / total64) < uj) ? 1 : 0;
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0) ds.wcnt[warp] = cnt;
+        draw_sync<NAMED>();
+        chunk = 0;
 #pragma unroll
-    for (int k = 0; k < kAhead; ++k) {
-        const int64_t i = threadIdx.x + (int64_t)k * kDrawNT;
-        if (i < nvec) v[k] = ldg_stream(reinterpret_cast<const uint4*>(srow) + i);
+        for (int i = 0; i < kDrawNT / 32; ++i) chunk += ds.wcnt[i];
+        if (chunk > a.nchunks - 1) chunk = a.nchunks - 1;
+        run0 = a.approx[chunk];
+        draw_sync<NAMED>();
     }
-    if (threadIdx.x == 0) {
-        // all loads first (a store in between would order them one latency after the other)
-        const bool want_l = a.labels && a.out_labels, want_i = a.index && a.out_index;
-        const int64_t lab = want_l ? a.labels[pick] : 0, ind = want_i ? a.index[pick] : 0;
-        float shift, tot2;
-        a.src.prepare(shift, tot2);
-        const float p = a.src.get(pick, shift, tot2);
-        // pytorch_collab.py:116: losses_pros[idx] * N ; :137,:145: grad = (1/B) / probs
-        const float np_ = __fmul_rn(p, (float)a.n_weight);
-        a.idx[j] = a.idx_base + pick;
-        a.nprob[j] = np_;
-        a.seed[j] = __fdiv_rn(__fdiv_rn(1.f, (float)a.b), np_);
-        if (want_l) a.out_labels[j] = lab;
-        if (want_i) a.out_index[j] = ind;
-    }
-    if (vec) {
+    const int64_t start = (int64_t)chunk * kChunk;
+    const int len = (int)min((int64_t)kChunk, a.n - start);
+    uint32_t pb[kDrawIPT];
+    load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
+    double loc[kDrawIPT];
+    double t = 0.0;
 #pragma unroll
-        for (int k = 0; k < kAhead; ++k) {
-            const int64_t i = threadIdx.x + (int64_t)k * kDrawNT;
-            if (i < nvec) reinterpret_cast<uint4*>(drow)[i] = v[k];
-        }
-        for (int64_t i = threadIdx.x + (int64_t)kAhead * kDrawNT; i < nvec; i += kDrawNT)
-            reinterpret_cast<uint4*>(drow)[i] = reinterpret_cast<const uint4*>(srow)[i];
-    } else if (copy) {
-        for (int64_t i = threadIdx.x; i < a.row_bytes; i += kDrawNT) drow[i] = srow[i];
+    for (int k = 0; k < kDrawIPT; ++k) { t += (double)b2f(pb[k]); loc[k] = t; }
+    double inc = t;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const double o = __shfl_up_sync(0xffffffffu, inc, off);
+        if (lane >= off) inc += o;
     }
+    if (lane == 31) ds.dwt[warp] = inc;
+    draw_sync<NAMED>();
+    double pre = run0 + (inc - t);
+    for (int i = 0; i < warp; ++i) pre += ds.dwt[i];
+    // the slot: how many candidates of the chunk lie below u (the cdf never decreases)
+    const int base = threadIdx.x * kDrawIPT;
+    int below = 0;
+#pragma unroll
+    for (int k = 0; k < kDrawIPT; ++k)
+        if (base + k < len && (double)(float)((pre + loc[k]) / total64) < uj) ++below;
+    below = __reduce_add_sync(0xffffffffu, below);
+    if (lane == 0) ds.wcnt[warp] = below;
+    draw_sync<NAMED>();
+    int slot = 0;
+#pragma unroll
+    for (int i = 0; i < kDrawNT / 32; ++i) slot += ds.wcnt[i];
+    if (slot > len - 1) slot = len - 1;
+    draw_sync<NAMED>();
+    draw_gather(a, j, start + slot);
+}
+
+__global__ void __launch_bounds__(kDrawNT) draw_f64_kernel(DrawArgs a, float* chain_total_out, int32_t* status) {
+    __shared__ DrawSmem ds;
+    pdl_wait();
+    pdl_launch_dependents();
+    const double total64 = a.approx[a.nchunks];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (chain_total_out) *chain_total_out = (float)total64;
+        if (!(total64 > 0.0)) atomicOr(status, MERCURY_ST_ZERO_SUM);
+        else if (isinf((float)total64)) atomicOr(status, MERCURY_ST_NONFINITE);
+    }
+    draw_resolve_f64<false>(a, blockIdx.x, a.u[blockIdx.x], -1, 0.0, total64, ds);
 }
 
 #include "step_fused.cuh"
@@ -1779,6 +1876,31 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
     WeightSrc src{scores, a.stats};
     int rc = MERCURY_OK;
+    if (a.cdf_mode == MERCURY_CDF_F64) {
+        // statistics -> fp64 chunk sums of p -> their scan -> one CTA per draw (no serial walk)
+        if (!a.draw_only) {
+            rc = pool_stats_launch(scores, a.n, a.h_bounds, a.n_bounds, a.ema_state, a.ema_first, a.ema_alpha, a.smooth_alpha, a.stats,
+                                   ws, st, true);
+            if (rc) return rc;
+            cudaError_t e = launch_chain(false, psum_kernel, dim3(nchunks), dim3(256), 0, st, src, a.n, w.sums, a.status);
+            if (e != cudaSuccess) return cuda_fail(e, "psum_kernel launch");
+            prefix_finalize_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, w.approx, w.slotid, 1.0, 0);
+            MB_CHECK_LAUNCH("prefix_finalize_kernel");
+        }
+        if (a.b > 0) {
+            DrawArgs d{};
+            d.n_weight = a.n; d.idx_base = 0;
+            d.src = src; d.n = a.n; d.nchunks = nchunks; d.start_bits = w.start_bits; d.total_ptr = w.total; d.approx = w.approx;
+            d.u = a.uniforms; d.b = a.b;
+            d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
+            d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
+            d.out_labels = a.out_labels; d.out_index = a.out_index;
+            cudaError_t e = launch_chain(false, draw_f64_kernel, dim3((unsigned)a.b), dim3(kDrawNT), 0, st, d,
+                                         a.stats + MERCURY_STAT_CHAIN_TOTAL, a.status);
+            if (e != cudaSuccess) return cuda_fail(e, "draw_f64_kernel launch");
+        }
+        return MERCURY_OK;
+    }
     if (a.draw_only) {
         // boundaries, total and statistics are those a previous call on this workspace left behind
     } else if (a.n_bounds == 0 && nchunks <= kFusedMaxChunks) {
@@ -1866,6 +1988,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     static const int env_on = env_knob("MERCURY_FUSED", 1, 0, 1);
     if (!(g_fused_mode < 0 ? env_on : g_fused_mode)) return 1;
     if (a.scores_in || a.n_bounds != 0 || a.draw_only || a.peer_boxes || a.global_sums) return 1;
+    if (a.cdf_mode != MERCURY_CDF_EXACT_SERIAL_F32) return 1;
     if (a.b > kStepMaxDraws || a.row_stride != a.c) return 1;
     const int64_t elt = a.dtype == MERCURY_F32 ? 4 : 2, row_bytes = a.c * elt;
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);

@@ -330,12 +330,14 @@ def update_samples(logits: Optional[torch.Tensor], labels: Optional[torch.Tensor
                    scores_in: Optional[torch.Tensor] = None, bounds: Optional[Sequence[int]] = None,
                    ignore_index: int = -100, status: Optional[torch.Tensor] = None, out: Optional[dict] = None,
                    global_sums: Optional[torch.Tensor] = None, n_global: Optional[int] = None, index_base: int = 0,
-                   draw_only: bool = False, peer: Optional[dict] = None) -> UpdateResult:
+                   draw_only: bool = False, peer: Optional[dict] = None, cdf_mode: str = "exact") -> UpdateResult:
     """Score -> statistics -> exact CDF -> B draws -> gather + weights + seed, in one C-ABI call.
 
     The arithmetic of Trainer.update_samples (pytorch_collab.py:102-117) on an assembled pool.
     ``uniforms`` are the fp64 numbers torch.multinomial would draw.  ``out`` may carry
     preallocated result tensors (keys as in the result) to keep the call allocation-free.
+    ``cdf_mode="exact"`` (default): indices bit-identical to ``torch.multinomial`` on the CPU for the same p and
+    uniforms; ``"f64"``: fp64 running totals, no serial walk -- the same distribution, not the same indices.
     """
     lib = _lib.load()
     _cuda(uniforms, "uniforms", torch.float64)
@@ -402,6 +404,7 @@ def update_samples(logits: Optional[torch.Tensor], labels: Optional[torch.Tensor
         a.global_sums, a.n_global_sums = global_sums.data_ptr(), global_sums.numel()
         a.n_global, a.index_base = int(n_global), int(index_base)
     a.draw_only = int(bool(draw_only))
+    a.cdf_mode = {"exact": _lib.CDF_EXACT_SERIAL_F32, "f64": _lib.CDF_F64}[cdf_mode]
     if peer is not None:  # the whole sharded step in this one call (sharded.ShardedPool, mode "totals", exchange "peer")
         boxes = _cuda(peer["boxes"], "peer boxes", torch.int64)
         a.peer_boxes, a.n_shards, a.shard_rank = boxes.data_ptr(), boxes.numel(), int(peer["rank"])

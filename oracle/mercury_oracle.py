@@ -126,6 +126,15 @@ def draw_with_replacement(p, u) -> np.ndarray:
     return lower_bound(serial_cdf_f32(p), u)
 
 
+def draw_with_replacement_f64(p, u) -> np.ndarray:
+    """The non-exact "fp64" mode of the draw (no counterpart in the reference, which always takes
+    torch.multinomial's serial fp32 sum, pytorch_collab.py:114): running totals in fp64, each
+    divided by the fp64 total and rounded to fp32, searched as ATen searches."""
+    run = np.cumsum(np.asarray(p, dtype=np.float32).astype(np.float64))
+    cdf = (run / run[-1]).astype(np.float32)
+    return lower_bound(cdf, u)
+
+
 def uniforms_like_multinomial(n: int, generator: torch.Generator) -> torch.Tensor:
     """The fp64 uniforms ``torch.multinomial`` consumes from a CPU generator."""
     return torch.rand(n, dtype=torch.float64, generator=generator)

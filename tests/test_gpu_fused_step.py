@@ -178,3 +178,45 @@ def test_one_kernel_step_in_a_cuda_graph(ops):
         ops.check_status(out["status"])
     finally:
         ops.set_fused(-1)
+
+
+# ------------------------------------------------------------------------------------- the fp64 (non-exact) mode
+@pytest.mark.parametrize("n,c,dtype,b", [(320, 10, torch.float32, 32), (50000, 10, torch.float32, 128), (1000000, 10, torch.float32, 256),
+                                         (20000, 1000, torch.bfloat16, 256)])
+def test_fp64_mode_matches_an_fp64_cdf_search(ops, n, c, dtype, b):
+    """cdf_mode="f64": the indices are those of an fp64 running total searched as ATen searches.  The device adds in a
+    tree, NumPy serially: the totals can differ in their last fp64 bits, which moves a draw only when its uniform sits
+    within an fp32 rounding of a cdf value -- such a draw may land on the neighbouring candidate, nothing else may differ."""
+    x, y = _pool(n, c, dtype, seed=21)
+    g = torch.Generator().manual_seed(4)
+    u = torch.rand(b, dtype=torch.float64, generator=g)
+    u[0], u[-1] = 0.0, 1.0 - 2.0 ** -53
+    data = torch.rand(n, 6, generator=g)
+    r = ops.update_samples(x.to(DEV), y.to(DEV), u.to(DEV), torch.zeros(1, device=DEV), True, data=data.to(DEV), cdf_mode="f64")
+    ops.check_status(r.status)
+    p = ops.normalize(r.scores, r.stats).cpu().numpy()
+    want = orc.draw_with_replacement_f64(p, u.numpy())
+    got = r.idx.cpu().numpy()
+    off = np.abs(got - want)
+    assert off.max() <= 1 and (off == 0).mean() >= 0.99, (off.max(), (off == 0).mean())
+    assert torch.equal(r.data.cpu(), data[got]) and torch.equal(r.labels.cpu(), y[got])
+    np.testing.assert_array_equal(r.nprob.cpu().numpy(), p[got] * np.float32(n))
+    # the same statistics as the exact mode (one code path), and mostly different indices for large pools
+    e = ops.update_samples(x.to(DEV), y.to(DEV), u.to(DEV), torch.zeros(1, device=DEV), True, cdf_mode="exact")
+    np.testing.assert_allclose(e.stats.cpu().numpy()[:4], r.stats.cpu().numpy()[:4], rtol=1e-6)
+    np.testing.assert_allclose(float(r.stats[4]), 1.0, rtol=1e-5)
+
+
+def test_fp64_mode_chi_squared(ops):
+    from scipy import stats as sps
+
+    n, draws, bins = 4096, 1 << 18, 64
+    x, y = _pool(n, 10, torch.float32, seed=31)
+    u = torch.rand(draws, dtype=torch.float64, generator=torch.Generator().manual_seed(5))
+    r = ops.update_samples(x.to(DEV), y.to(DEV), u.to(DEV), torch.zeros(1, device=DEV), True, cdf_mode="f64")
+    ops.check_status(r.status)
+    p = ops.normalize(r.scores, r.stats).cpu().double().numpy()
+    obs = np.bincount(r.idx.cpu().numpy() // (n // bins), minlength=bins)
+    exp = p.reshape(bins, -1).sum(1) * draws
+    chi2 = ((obs - exp) ** 2 / exp).sum()
+    assert sps.chi2.sf(chi2, bins - 1) > 1e-4, f"chi2={chi2}"

@@ -250,3 +250,15 @@ def test_c_oracle_head_and_two_level_draw_agree_with_the_python_oracle(golden_di
     st, idx = c_oracle.two_level_draw(shards, u)
     assert st == 0
     assert np.array_equal(idx, orc.sharded_draw_two_level(shards, u))
+
+
+def test_fp64_draw_restatement_is_a_valid_inverse_cdf():
+    """draw_with_replacement_f64: lower bound of an fp64 running total (the non-exact mode): agrees with the exact
+    serial-fp32 draw on small pools and stays within a few candidates of it on a large one."""
+    g = torch.Generator().manual_seed(2)
+    for n in (17, 320, 200000):
+        w = torch.rand(n, generator=g) + 0.01
+        p = (w / w.sum()).numpy()
+        u = torch.rand(256, dtype=torch.float64, generator=g).numpy()
+        a, b = orc.draw_with_replacement(p, u), orc.draw_with_replacement_f64(p, u)
+        assert np.abs(a - b).max() <= (0 if n <= 320 else 8)
