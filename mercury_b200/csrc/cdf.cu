@@ -1988,7 +1988,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     static const int env_on = env_knob("MERCURY_FUSED", 1, 0, 1);
     if (!(g_fused_mode < 0 ? env_on : g_fused_mode)) return 1;
     if (a.scores_in || a.n_bounds != 0 || a.draw_only || a.peer_boxes || a.global_sums) return 1;
-    if (a.cdf_mode != MERCURY_CDF_EXACT_SERIAL_F32) return 1;
+
     if (a.b > kStepMaxDraws || a.row_stride != a.c) return 1;
     const int64_t elt = a.dtype == MERCURY_F32 ? 4 : 2, row_bytes = a.c * elt;
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
@@ -2003,6 +2003,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     sa.ema_state = a.ema_state; sa.ema_first = a.ema_first; sa.ema_alpha = a.ema_alpha; sa.smooth_alpha = a.smooth_alpha; sa.stats = a.stats;
     sa.nchunks = nchunks; sa.bias = g_guess_bias; sa.sums = w.summaries; sa.packs = reinterpret_cast<Pack2*>(w.subs);
     sa.start_bits = w.start_bits; sa.total = w.total; sa.ctrl = w.ctrl; sa.status = a.status;
+    sa.cdf_mode = a.cdf_mode; sa.approx = w.approx;
     static const int dbg_flags = env_knob("MERCURY_STEP_DBG", 0, 0, 255);
     sa.dbg_flags = dbg_flags;
     if (small_smem_bytes(kStepStages, sa.tile_rows, row_bytes) > kStepSmemBytes) return 1;
@@ -2013,6 +2014,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     d.data = static_cast<const unsigned char*>(a.data); d.row_bytes = a.row_bytes; d.labels = a.labels; d.index = a.index;
     d.idx = a.idx; d.nprob = a.nprob; d.seed = a.seed; d.out_data = static_cast<unsigned char*>(a.out_data);
     d.out_labels = a.out_labels; d.out_index = a.out_index;
+    d.approx = w.approx;
     d.dbg = (dbg_flags & 4) ? &w.ctrl->evt[107] : nullptr;
     const int64_t ntiles = (a.n + sa.tile_rows - 1) / sa.tile_rows;
     sa.ntiles = (int)ntiles;

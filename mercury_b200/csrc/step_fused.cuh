@@ -67,6 +67,8 @@ struct StepCtrl {
     unsigned long long dinfo2[kStepMaxDraws]; // per draw: 1 << 63 | bits of the chain's total (each word is valid on its own:
                                               // no fence between the walker's results and these words is needed)
     double cta_part[kStepMaxCtas];            // per CTA: the fp64 sum of the scores it computed (its tiles are contiguous)
+    double dapprox[kStepMaxDraws];            // fp64 mode, per draw: the running total of p in front of its chunk ...
+    double dtotal[kStepMaxDraws];             // ... and the total (written before dinfo[j], a fence in between)
     unsigned int k1_end[kStepMaxCtas];        // developer aid (MERCURY_STEP_DBG & 4): ns from the start until each CTA had scored
 };
 constexpr unsigned long long kStepSpinNs = 2000000000ull;  // no wait may last this long: report instead of hanging the GPU
@@ -81,6 +83,8 @@ struct StepArgs {
     int nchunks; double bias; Summary* sums; Pack2* packs; uint32_t* start_bits; float* total; StepCtrl* ctrl;
     int32_t* status;
     int dbg_flags;                 // developer aid (MERCURY_STEP_DBG): 1 = stamp the walk's steps
+    int cdf_mode;                  // MERCURY_CDF_EXACT_SERIAL_F32 or MERCURY_CDF_F64 (no walk: fp64 chunk sums and their scan)
+    double* approx;                // fp64 mode: [nchunks + 1] running total of p in front of every chunk
     // draws
     DrawArgs d;
 };
@@ -370,6 +374,36 @@ __device__ __forceinline__ void summarize2_chunk(const StepArgs& a, int c, const
     if (threadIdx.x == 0) { __threadfence(); atomicAdd(&a.ctrl->packs_done, 1u); }   // (release: cumulative over the barrier)
 }
 
+// fp64 mode, phase B: the chunk's fp64 sum of p, as one 16-byte record {sum, launch tag} where its Summary would be
+__device__ __forceinline__ void sum_f64_chunk(const StepArgs& a, int c, const float (&raw)[8], float shift, float total, Sum2Smem& sm,
+                                              unsigned long long epoch, bool first) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t start = (int64_t)c * kChunk;
+    const int len = (int)min((int64_t)kChunk, a.n - start);
+    const int base = threadIdx.x * 8;
+    double acc = 0.0;
+    int bad = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float x = base + k < len ? __fdiv_rn(__fadd_rn(raw[k], shift), total) : 0.f;
+        if (!(x >= 0.f)) bad |= MERCURY_ST_NEGATIVE;
+        else if (isinf(x)) bad |= MERCURY_ST_NONFINITE;
+        acc += (double)x;
+    }
+    if (bad) atomicOr(a.status, bad);
+    acc = warp_sum(acc);
+    if (!first) wsync();
+    if (lane == 0) sm.dred[0][warp] = acc;
+    wsync();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int i = 0; i < kStepNT / 32; ++i) t += sm.dred[0][i];
+        const unsigned long long bits = (unsigned long long)__double_as_longlong(t);
+        *reinterpret_cast<uint4*>(a.sums + c) = make_uint4((uint32_t)bits, (uint32_t)(bits >> 32), (uint32_t)epoch, (uint32_t)(epoch >> 32));
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // phase C: the walk.  One warp walks, and it must stay CONVERGED: every statement below is executed by all 32 lanes
 // (stores of a warp-uniform value by every lane instead of `if (lane == 0)`), because a warp that has split pays
@@ -595,6 +629,92 @@ struct WalkStatic {
     unsigned long long wtot[kStepMaxChunks / kStepNT][kStepNT / 32];
     int wcnt[kStepMaxChunks / kStepNT][kStepNT / 32];
 };
+
+// fp64 mode, phase C (the walker CTA): scan of the chunk sums, the chunk of every draw, publish.  No serial part.
+__device__ __forceinline__ void walker_f64_body(const StepArgs& a, unsigned char* sm, WalkStatic& ws, float stat_ema, unsigned long long epoch) {
+    const int nchunks = a.nchunks;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double* ap = reinterpret_cast<double*>(sm);   // [nchunks + 1]
+    constexpr int kR = kStepMaxChunks / kStepNT;
+    const int nr = (nchunks + kStepNT - 1) / kStepNT;
+    double v[kR], excl[kR];
+    {
+        const uint32_t tag_lo = (uint32_t)epoch, tag_hi = (uint32_t)(epoch >> 32);
+        const unsigned long long t0 = global_ns();
+        bool ok[kR];
+#pragma unroll
+        for (int r = 0; r < kR; ++r) { ok[r] = !(r < nr && r * kStepNT + tid < nchunks); v[r] = 0.0; }
+        for (unsigned int it = 0;; ++it) {
+            bool all = true;
+#pragma unroll
+            for (int r = 0; r < kR; ++r) {
+                if (!ok[r]) {
+                    uint4 q;
+                    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
+                                 : "l"(a.sums + (r * kStepNT + tid)) : "memory");
+                    if (q.z == tag_lo && q.w == tag_hi) { v[r] = __longlong_as_double((long long)(((unsigned long long)q.y << 32) | q.x)); ok[r] = true; }
+                    else all = false;
+                }
+            }
+            if (all) break;
+            if ((it & 15u) == 15u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); break; }
+        }
+    }
+    double* dw = reinterpret_cast<double*>(&ws.wtot[0][0]);   // [kR][8] warp totals
+#pragma unroll
+    for (int r = 0; r < kR; ++r) {
+        if (r >= nr) break;
+        double inc = v[r];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const double t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) dw[r * (kStepNT / 32) + warp] = inc;
+        excl[r] = inc - v[r];
+    }
+    wsync();
+    {
+        double running = 0.0;
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+            if (r >= nr) break;
+            const int c = r * kStepNT + tid;
+            double pre = running;
+#pragma unroll
+            for (int i = 0; i < kStepNT / 32; ++i) {
+                const double t = dw[r * (kStepNT / 32) + i];
+                if (i < warp) pre += t;
+                running += t;
+            }
+            if (c < nchunks) { ap[c] = pre + excl[r]; a.approx[c] = pre + excl[r]; }
+        }
+        if (tid == 0) {
+            ap[nchunks] = running; a.approx[nchunks] = running;
+            *a.ema_state = stat_ema;
+            a.stats[MERCURY_STAT_CHAIN_TOTAL] = (float)running;
+            if (!(running > 0.0)) atomicOr(a.status, MERCURY_ST_ZERO_SUM);
+            else if (isinf((float)running)) atomicOr(a.status, MERCURY_ST_NONFINITE);
+            a.ctrl->times[6] = global_ns();
+        }
+    }
+    wsync();
+    const double total64 = ap[nchunks];
+    for (int64_t j = tid; j < a.d.b; j += kStepNT) {
+        const double uj = a.d.u[j];
+        int lo = 0, hi = nchunks - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if ((double)(float)(ap[mid + 1] / total64) < uj) lo = mid + 1; else hi = mid;
+        }
+        a.ctrl->dapprox[j] = ap[lo];
+        a.ctrl->dtotal[j] = total64;
+        __threadfence();
+        st_relaxed_u64(&a.ctrl->dinfo[j], (1ull << 63) | ((unsigned long long)lo << 32));
+        st_relaxed_u64(&a.ctrl->dinfo2[j], 1ull << 63);
+    }
+    if (tid == 0) a.ctrl->times[7] = global_ns();
+}
 
 // The walker (one CTA, 256 threads + named barrier 1).  Leaves the boundary values in global memory, and publishes the
 // chunk of every draw.
@@ -976,6 +1096,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[2] = global_ns();
 
     const unsigned long long epoch = __ldcg(&a.ctrl->epoch);
+    const bool f64 = a.cdf_mode == MERCURY_CDF_F64;   // (no walk: fp64 chunk sums, their scan, one CTA per draw)
     // ---- B: statistics (pytorch_collab.py:109-112), then: the last CTA is the walker and owns no chunks (with a single
     // CTA it is its own worker); the others each take a contiguous block of chunks
     const int nchunks = a.nchunks;
@@ -1078,7 +1199,8 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
 #pragma unroll
         for (int i = 0; i < 8; ++i) cur[i] = raw[i];
         if (k + 1 < c_count) load_raw(c_first + k + 1);   // next chunk's scores travel while this one is reduced
-        summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2, epoch, k == 0);
+        if (f64) sum_f64_chunk(a, c_first + k, cur, shift, total, s2, epoch, k == 0);
+        else summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2, epoch, k == 0);
         pre += own;
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[15] = global_ns();
@@ -1086,7 +1208,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     if (walker) {
         // ---- C: the head of the pool (warp 1: the reference's own loop over the first candidates, in which the running sum
         // changes binade about ten times), the wait for the workers' summaries (thread 0), then the walk
-        if (warp == 1) {
+        if (warp == 1 && !f64) {
             uint32_t hb = 0u;
             if (H > 0) {
                 // all loads first (8 x 16 bytes per lane in flight), then the arithmetic
@@ -1116,13 +1238,15 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
             if (lane == 0) a.ctrl->times[9] = global_ns();
         }
         wsync();
-        walker_body(a, smem, wst, shift, total, ema, epoch);
+        if (f64) walker_f64_body(a, smem, wst, ema, epoch);
+        else walker_body(a, smem, wst, shift, total, ema, epoch);
     }
     // ---- D: draws.  What a draw needs from the walker comes in its two words; the pool statistics are in registers
     // already (every CTA computed the same bits), so draw_resolve reads both from shared memory instead of global memory.
     float* cdf_s = reinterpret_cast<float*>(smem);
     __shared__ float dstats[MERCURY_STAT_COUNT];
     __shared__ float dtotal;
+    __shared__ double drun0, dtot64;
     DrawArgs da = a.d;
     da.src.stats = dstats;
     da.total_ptr = &dtotal;
@@ -1139,6 +1263,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
             }
             dinfo_s = v;
             dtotal = b2f((uint32_t)w);
+            if (f64 && (v >> 63)) { __threadfence(); drun0 = __ldcg(&a.ctrl->dapprox[j]); dtot64 = __ldcg(&a.ctrl->dtotal[j]); }
             dstats[MERCURY_STAT_SHIFT] = shift; dstats[MERCURY_STAT_TOTAL] = total;
         }
         const double uj = a.d.u[j];
@@ -1146,7 +1271,8 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         const unsigned long long v = dinfo_s;
         if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 64) a.ctrl->evt[106] = global_ns();
         if (!(v >> 63)) return;  // timed out (reported): leave the outputs alone rather than write garbage
-        draw_resolve<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), (uint32_t)v, true, ds, cdf_s);
+        if (f64) draw_resolve_f64<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), drun0, dtot64, ds);
+        else draw_resolve<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), (uint32_t)v, true, ds, cdf_s);
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[8] = global_ns();
 }

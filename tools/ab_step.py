@@ -6,6 +6,8 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 
+MODE = os.environ.get("CDF", "exact")   # or f64
+
 from mercury_b200 import ops  # noqa: E402
 
 dev = torch.device("cuda", 0)
@@ -24,7 +26,7 @@ def timed(uni, label):
     out, status = {}, ops.new_status(dev)
 
     def step(i):
-        r = ops.update_samples(*pools[i % NP], uni, ema, False, data=payload, index=index, out=out, status=status)
+        r = ops.update_samples(*pools[i % NP], uni, ema, False, data=payload, index=index, out=out, status=status, cdf_mode=MODE)
         out.update({k: v for k, v in r.items() if k != "status" and v is not None})
 
     side = torch.cuda.Stream()
@@ -56,7 +58,7 @@ def timed_one_graph(uni, label):
     out, status = {}, ops.new_status(dev)
 
     def step(i):
-        r = ops.update_samples(*pools[i % NP], uni, ema, False, data=payload, index=index, out=out, status=status)
+        r = ops.update_samples(*pools[i % NP], uni, ema, False, data=payload, index=index, out=out, status=status, cdf_mode=MODE)
         out.update({k: v for k, v in r.items() if k != "status" and v is not None})
 
     side = torch.cuda.Stream()
