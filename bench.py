@@ -197,21 +197,75 @@ def library_baseline(pools, payload, index, u, b, steps=20):
             "what": "stock ATen CUDA ops, eager, same pools (results not reproducible against the CPU reference)"}
 
 
+def auto_pools(wl, pools_arg):
+    """>= 300 MB of distinct pools in rotation (> 126 MB L2); a pool of tens of GB is its own L2 flush."""
+    s = 4 if wl["dtype"] == "f32" else 2
+    pool_bytes = wl["n"] * (wl["c"] * s + 8)
+    return pools_arg or (1 if pool_bytes >= (16 << 30) else max(2, min(8, -(-(300 << 20) // pool_bytes))))
+
+
+def make_config(args, wl, world, exchange=None):
+    """The `config` object of the JSON line: the same for both arms (--impl ours / reference) of one command."""
+    s = 4 if wl["dtype"] == "f32" else 2
+    pool_bytes = wl["n"] * (wl["c"] * s + 8)
+    npools = auto_pools(wl, args.pools)
+    rotated = npools * pool_bytes
+    l2 = (f"{npools} distinct pools rotated ({rotated >> 20} MiB > 126 MiB L2)" if rotated > (126 << 20) else
+          f"{npools} distinct pools rotated ({rotated >> 20} MiB: they FIT the 126 MiB L2 -- a latency-bound workload, not an HBM number)")
+    row_bytes = 4 * (wl["payload"][0] * wl["payload"][1] * wl["payload"][2]) if wl["payload"] else 0
+    return {"workload": args.workload, "note": wl["note"], "candidates_per_gpu": wl["n"], "classes": wl["c"], "draws": wl["b"],
+            "payload_row_bytes": row_bytes, "l2": l2,
+            "cdf": "exact serial-fp32 (bit-identical to torch.multinomial on CPU)",
+            "launch": (f"CUDA graph replay, one graph of {npools} steps (one per pool)" if args.graph else "eager launches"),
+            "multi_gpu": None if world == 1 else MULTI_GPU_NOTE[args.shard_mode],
+            "exchange": None if world == 1 else EXCHANGE_NOTE[exchange or (args.exchange if args.shard_mode == "totals" else "nccl")]}
+
+
 def run_reference(args, wl):
+    """The reference arm: the reference's own CPU arithmetic (oracle port on torch CPU ops: the reference is pure
+    Python over torch, and its modules do not import under this torch) on all host threads.  W warm-up + K timed
+    steps; a step is one pass over one pool (a row slice for the widest shapes); with N GPUs named, the N shards are
+    processed one after the other by the one host (same rate)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warm = args.steps, args.warmup
-    base = cpu_baseline(wl, budget_s=max(5.0, min(60.0, 2.0 * steps)))
+    from oracle import mercury_oracle as orc
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.set_num_threads(os.cpu_count() or 1)
+    n, c, b = wl["n"], wl["c"], wl["b"]
+    rows = n
+    while rows * c > 64_000_000 and rows > 4096:   # bound one pass to a few seconds
+        rows //= 2
+    g = torch.Generator().manual_seed(0)
+    dt = torch.float32 if wl["dtype"] == "f32" else torch.bfloat16
+    x = (torch.randn(rows, c, generator=g) * 2).to(dt)
+    y = torch.randint(0, c, (rows,), generator=g)
+    gen = torch.Generator().manual_seed(3)
+
+    def one():
+        r = orc.update_samples_flat(x, y, b, orc.EMAverage(), generator=gen)
+        orc.reweighted_loss(torch.ones(b), r["nprob"])
+
+    for _ in range(max(1, args.warmup)):
+        one()
+    steps = max(1, args.steps)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    el = time.perf_counter() - t0
+    value = rows * steps / el
+    base = {"value": value, "unit": "candidates/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{steps} passes over {rows} x {c} {wl['dtype']} candidates, B={b} "
+                      f"({'full pool' if rows == n else 'row slice of the pool, rate per candidate'}), {el:.1f} s; "
+                      f"with {world} GPU(s) named the shards would be processed one after the other at this rate"}
     line = {
-        "impl": "reference", "metric": "importance-scored+sampled candidates/sec", "value": base["value"], "unit": "candidates/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": 1e3 * wl["n"] / base["value"],
+        "impl": "reference", "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n / value,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
-        "config": {"workload": args.workload, "note": wl["note"], "candidates_per_gpu": wl["n"], "classes": wl["c"],
-                   "draws": wl["b"], "payload_row_bytes": 4 * (wl["payload"][0] * wl["payload"][1] * wl["payload"][2]) if wl["payload"] else 0,
-                   "cdf": "torch.multinomial on CPU (serial fp32)", "launch": "torch CPU ops, all host threads"},
+        "config": make_config(args, wl, world),
         "cpu_baseline": base,
-        "e2e": {"value": base["value"], "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "e2e": {"value": value, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
@@ -219,8 +273,10 @@ def run_reference(args, wl):
 
 MULTI_GPU_NOTE = {
     "totals": "pool sharded by rank; every rank builds the exact chain of its own shard; one fp64 sum and one fp32 chain total "
-              "per rank are exchanged; two-level draw (shard by totals, then position) by the owning rank",
-    "scores": "pool sharded by rank; NCCL all-gather of scores; replicated exact CDF of the whole pool; rows gathered by their owner",
+              "per rank are exchanged; two-level draw (shard by totals, then position) by the owning rank; the drawn rows "
+              "stay on their owner in the timed step (other ranks hold zero rows): the batch is NOT assembled",
+    "scores": "pool sharded by rank; NCCL all-gather of scores; replicated exact CDF of the whole pool; rows gathered by their owner "
+              "(other ranks hold zero rows: the batch is NOT assembled)",
 }
 
 
@@ -228,6 +284,428 @@ EXCHANGE_NOTE = {
     "peer": "in-kernel stores into the peers' exchange boxes (CUDA IPC over NVLink/NVSwitch), no collective in the step",
     "nccl": "NCCL all-gather",
 }
+
+
+def timed_steps(step, npools, steps, warmup, use_graph, barrier, dist=None, dev=None):
+    """W warm-up steps, then EXACTLY `steps` timed steps between two barriers, CUDA events on the launching stream, max
+    over ranks.  With graphs: one graph holding one step per pool, replayed steps // npools times, plus a graph with the
+    remaining steps % npools steps.  Returns (ms per step, replay callable for extra untimed steps)."""
+    for i in range(max(3, warmup)):
+        step(i)
+    barrier()
+    full = rest = None
+    nrest = steps % npools
+    if use_graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            step(0)  # allocates this stream's workspace outside capture
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        full = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(full, stream=side):
+            for i in range(npools):
+                step(i)
+        if nrest:
+            rest = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(rest, stream=side):
+                for i in range(nrest):
+                    step(i)
+            rest.replay()
+        full.replay()
+        torch.cuda.synchronize()
+
+    def run(nsteps):
+        if full is None:
+            for i in range(nsteps):
+                step(i)
+            return
+        for _ in range(nsteps // npools):
+            full.replay()
+        if nsteps % npools:
+            if nsteps % npools == nrest and rest is not None:
+                rest.replay()
+            else:
+                for i in range(nsteps % npools):
+                    step(i)
+
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    run(steps)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / steps
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+    return ms, run
+
+
+def step_launches(ops, wl, world, exchange, shard_mode, fast=False):
+    """Kernels of ours per step and rank.  One GPU, small rows: the whole step is ONE cooperative kernel (fused_step_kernel)
+    up to 1.5 Mi candidates; else the chain score -> summarize -> spine -> draw (4).  fp64 mode outside the one-kernel
+    step: score, chunk sums, statistics, chunk sums of p, scan, draw (6)."""
+    s = 4 if wl["dtype"] == "f32" else 2
+    one_kernel = wl["c"] * s <= 256 and wl["n"] <= 768 * 2048 and wl["b"] <= 1024
+    if world == 1:
+        return 1 if one_kernel else (6 if fast else 4)
+    return 4 if exchange == "peer" else 6 if shard_mode == "scores" else 7
+
+
+def bench_single(ops, wl, dev, args, npools, steps, warmup, payload_ok=True, rank=0):
+    """One workload on one GPU: the exact step, the fp64 step, K1 alone.  Returns a dict of measurements and the live
+    tensors the caller may reuse (pools, payload, index, u)."""
+    n, c, b = wl["n"], wl["c"], wl["b"]
+    s = 4 if wl["dtype"] == "f32" else 2
+    row_bytes = 0
+    payload = None
+    if wl["payload"] and payload_ok:
+        payload = torch.rand((n,) + wl["payload"], device=dev, generator=torch.Generator(device=dev).manual_seed(2))
+        row_bytes = payload[0].numel() * 4
+    index = torch.arange(n, device=dev) + rank * n
+    pools = [make_pool(wl, dev, seed=100 * rank + i) for i in range(npools)]
+    gen = torch.Generator().manual_seed(3)
+    u_host = torch.rand(b, dtype=torch.float64, generator=gen).pin_memory()
+    u = u_host.to(dev)
+    ema = torch.zeros(1, device=dev)
+    status = ops.new_status(dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+
+    def make_step(mode, out):
+        def step(i):
+            lg, lb = pools[i % npools]
+            r = ops.update_samples(lg, lb, u, ema, False, data=payload, index=index, out=out, status=status, cdf_mode=mode)
+            out.update({k: v for k, v in r.items() if k in ("scores", "stats", "idx", "nprob", "seed", "data", "labels", "index")})
+            return r
+        return step
+
+    out = {}
+    step = make_step("exact", out)
+    ms, run = timed_steps(step, npools, steps, warmup, args.graph, barrier)
+    ops.check_status(status)
+    idx_exact = []
+    for i in range(min(npools, 4)):   # indices of the exact mode on the first pools (for the fp64 mode's agreement figure)
+        step(i)
+        idx_exact.append(out["idx"].clone())
+    out_f = {}
+    step_f = make_step("f64", out_f)
+    ms_f, _ = timed_steps(step_f, npools, steps, warmup, args.graph, barrier)
+    ops.check_status(status)
+    agree = []
+    for i in range(min(npools, 4)):
+        step_f(i)
+        agree.append(float((out_f["idx"] == idx_exact[i]).float().mean()))
+    # ---- K1 (score) alone, one launch per pool in a graph, timed on its launching stream
+    sc = torch.empty(n, dtype=torch.float32, device=dev)
+    st = ops.new_status(dev)
+    kstream = torch.cuda.Stream()
+    kstream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(kstream):
+        for i in range(3):
+            ops.score(*pools[i % npools], status=st, out=sc)
+    torch.cuda.synchronize()
+    reps = max(2, -(-max(steps, 10) // npools))
+    kg = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(kg, stream=kstream):
+        for i in range(npools):
+            ops.score(*pools[i], status=st, out=sc)
+    with torch.cuda.stream(kstream):
+        kg.replay()
+        a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(kstream)
+        for _ in range(reps):
+            kg.replay()
+        z.record(kstream)
+    torch.cuda.synchronize()
+    k1_ms = a.elapsed_time(z) / (reps * npools)
+    peak, peak_src = peak_hbm()
+    step_bytes = algorithmic_bytes(n, c, s, b, row_bytes)
+    k1_bytes = n * (c * s + 8 + 4)
+    res = {
+        "ms_per_step": ms, "value": n / (ms * 1e-3),
+        "step_bytes": step_bytes, "step_gbs": step_bytes / (ms * 1e-3) / 1e9, "step_frac": step_bytes / (ms * 1e-3) / 1e9 / peak,
+        "fast": {"ms_per_step": ms_f, "value": n / (ms_f * 1e-3), "frac": step_bytes / (ms_f * 1e-3) / 1e9 / peak,
+                 "index_agreement_vs_exact": sum(agree) / len(agree),
+                 "what": "cdf_mode='f64': fp64 running totals, no serial walk; same distribution, not the same indices"},
+        "k1_ms": k1_ms, "k1_bytes": k1_bytes, "k1_gbs": k1_bytes / (k1_ms * 1e-3) / 1e9, "k1_frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / peak,
+        "peak": peak, "peak_src": peak_src, "row_bytes": row_bytes,
+    }
+    live = {"pools": pools, "payload": payload, "index": index, "u": u, "u_host": u_host, "run": run, "status": status}
+    return res, live
+
+
+def e2e_single(ops, wl, dev, live, args, n, c, s, b):
+    """The same step through the public API with HOST buffers (pinned): logits, labels and uniforms copied in, idx / weights /
+    seed / statistics copied out, every step, all inside the timed region.  Pools above 8 GB: a 64 Ki-row slice (the copy
+    dominates and is linear in the rows), rate per candidate."""
+    pools, payload, index, u_host = live["pools"], live["payload"], live["index"], live["u_host"]
+    pool_bytes = n * (c * s + 8)
+    e2e_rows = n if pool_bytes <= (8 << 30) else 1 << 16
+    lg0, lb0 = pools[0][0][:e2e_rows], pools[0][1][:e2e_rows]
+    e2e_payload = payload[:e2e_rows] if payload is not None else None
+    e2e_index = index[:e2e_rows]
+    h_logits = torch.empty(lg0.shape, dtype=lg0.dtype).pin_memory()
+    h_labels = torch.empty(lb0.shape, dtype=lb0.dtype).pin_memory()
+    h_logits.copy_(lg0)
+    h_labels.copy_(lb0)
+    d_logits, d_labels, d_u = torch.empty_like(lg0), torch.empty_like(lb0), torch.empty_like(live["u"])
+    h_idx = torch.empty(b, dtype=torch.int64).pin_memory()
+    h_np = torch.empty(b, dtype=torch.float32).pin_memory()
+    h_seed = torch.empty(b, dtype=torch.float32).pin_memory()
+    h_stats = torch.empty(8, dtype=torch.float32).pin_memory()
+    ema2 = torch.zeros(1, device=dev)
+    e2e_out = {}
+
+    def e2e_step(first=False):
+        d_logits.copy_(h_logits, non_blocking=True)
+        d_labels.copy_(h_labels, non_blocking=True)
+        d_u.copy_(u_host, non_blocking=True)
+        rr = ops.update_samples(d_logits, d_labels, d_u, ema2, first, data=e2e_payload, index=e2e_index, out=e2e_out)
+        e2e_out.update({k: v for k, v in rr.items() if v is not None})
+        h_idx.copy_(rr["idx"], non_blocking=True)
+        h_np.copy_(rr["nprob"], non_blocking=True)
+        h_seed.copy_(rr["seed"], non_blocking=True)
+        h_stats.copy_(rr["stats"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller reads the result every step
+
+    for i in range(3):
+        e2e_step(first=(i == 0))
+    torch.cuda.synchronize()
+    e2e_steps = max(5, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    return {"value": e2e_rows / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": e2e_rows * (c * s + 8) + b * 8,
+            "d2h_bytes_per_step": b * (8 + 4 + 4) + 32, "ms_per_step": e2e_ms, "steps": e2e_steps, "rows_per_step": e2e_rows}
+
+
+def main_single(args, wl, dev):
+    from mercury_b200 import ops
+
+    n, c, b = wl["n"], wl["c"], wl["b"]
+    s = 4 if wl["dtype"] == "f32" else 2
+    npools = auto_pools(wl, args.pools)
+    with ClockSampler(dev.index or 0) as clocks:
+        res, live = bench_single(ops, wl, dev, args, npools, args.steps, args.warmup)
+        # keep the clocks sampled over a region long enough for nvidia-smi to see it (~0.6 s)
+        live["run"](max(npools, min(20000, int(600.0 / max(res["ms_per_step"], 1e-3)))))
+        torch.cuda.synchronize()
+    ops.check_status(live["status"])
+    e2e = e2e_single(ops, wl, dev, live, args, n, c, s, b)
+    launches = step_launches(ops, wl, 1, None, None)
+    one_kernel = launches == 1
+    traffic = k1_traffic(args.workload)
+    line = {
+        "metric": "importance-scored+sampled candidates/sec", "value": res["value"], "unit": "candidates/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
+        "config": make_config(args, wl, 1),
+        # the headline fraction: the WHOLE step (SURVEY 8d), which for small rows is one kernel launch
+        "roofline": {"kernel": "whole step: " + ("fused_step_kernel (score + statistics + exact CDF + draws + gather, one cooperative launch)"
+                                                 if one_kernel else "score -> summarize -> spine -> draw (4 launches; K1 dominates)"),
+                     "bound": "hbm", "achieved": res["step_gbs"], "peak": res["peak"], "unit": "GB/s", "frac": res["step_frac"],
+                     "traffic": None if one_kernel else traffic, "peak_source": res["peak_src"], "ms_per_launch": res["ms_per_step"],
+                     "algorithmic_bytes_per_launch": res["step_bytes"]},
+        "k1_roofline": {"kernel": "K1 score (mercury_score) timed alone", "bound": "hbm", "achieved": res["k1_gbs"], "peak": res["peak"],
+                        "unit": "GB/s", "frac": res["k1_frac"], "traffic": traffic, "ms_per_launch": res["k1_ms"],
+                        "algorithmic_bytes_per_launch": res["k1_bytes"]},
+        "fast_mode": res["fast"],
+        "e2e": e2e,
+        "gpu_launches": launches * args.steps,
+        "clocks": clocks.summary(),
+    }
+    if n * c * 4 <= (32 << 30):   # (ATen upcasts the logits: needs N*C*4 bytes of scratch)
+        line["library_baseline"] = library_baseline(live["pools"], live["payload"], live["index"], live["u"], b)
+    del live
+    torch.cuda.empty_cache()
+    # ---- the bandwidth-bound workloads (BASELINE configs[2] and the configs[4] row shape), 2 pools each: a few seconds
+    if args.workload == "cfg2" and not args.no_other_workloads:
+        others = {}
+        for name in ("cfg3", "cfg5"):
+            w2 = dict(WORKLOADS[name])
+            try:
+                with ClockSampler(dev.index or 0) as ck:
+                    r2, l2 = bench_single(ops, w2, dev, args, 2, 6, 3, payload_ok=False)
+                    l2["run"](max(2, min(400, int(400.0 / max(r2["ms_per_step"], 1e-3)))))
+                    torch.cuda.synchronize()
+                others[name] = {"note": w2["note"], "ms_per_step": r2["ms_per_step"], "value": r2["value"],
+                                "step_roofline": {"algorithmic_bytes": r2["step_bytes"], "achieved_gbs": r2["step_gbs"], "frac": r2["step_frac"]},
+                                "k1_roofline": {"ms_per_launch": r2["k1_ms"], "frac": r2["k1_frac"]},
+                                "fast_mode": {k: r2["fast"][k] for k in ("ms_per_step", "frac", "index_agreement_vs_exact")},
+                                "pools": 2, "steps": 6, "clocks": ck.summary()}
+                del l2
+            except Exception as e:  # noqa: BLE001
+                others[name] = {"error": str(e)[:200]}
+            torch.cuda.empty_cache()
+        line["other_workloads"] = others
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(wl)
+    print(json.dumps(line))
+
+
+def parity_check(ops, sp, pools, payload, index, u, n, world, rank, dist, dev, mode):
+    """Before the timed region: this step's draw against the oracle, on the job's own scores.  Every rank's shard of
+    scores is gathered once; rank 0 recomputes the draw on the CPU (oracle.sharded_draw_two_level for the totals mode,
+    the flat serial-fp32 draw for the scores mode) and compares the indices, which the ranks assemble by a SUM
+    all-reduce (a draw is non-zero on its owner only)."""
+    import numpy as np
+
+    from oracle import mercury_oracle as orc
+
+    lg, lb = pools[0]
+    out = {}
+    r = sp.update_samples(lg, lb, u, data=payload, index=index, out=out)
+    torch.cuda.synchronize()
+    idx = r["idx"].clone()
+    if mode == "totals":
+        dist.all_reduce(idx, op=dist.ReduceOp.SUM)   # (other ranks hold zeros)
+    scores = [torch.empty(n, dtype=torch.float32, device=dev) for _ in range(world)]
+    dist.all_gather(scores, r["scores"].contiguous())
+    ok = None
+    if rank == 0:
+        st = r["stats"].cpu().numpy()
+        sh = [((x.cpu().numpy() + np.float32(st[2])).astype(np.float32) / np.float32(st[3])).astype(np.float32) for x in scores]
+        if mode == "totals":
+            want = orc.sharded_draw_two_level(sh, u.cpu().numpy())
+        else:
+            want = orc.draw_with_replacement(np.concatenate(sh), u.cpu().numpy())
+        ok = bool(np.array_equal(idx.cpu().numpy(), want))
+    return {"mode": "two-level (oracle.sharded_draw_two_level)" if mode == "totals" else "flat (serial fp32 chain over the gathered scores)",
+            "idx_equal": ok, "ranks": world, "draws": int(u.numel())}
+
+
+def main_multi(args, wl, dev, world, rank):
+    import torch.distributed as dist
+
+    dist.init_process_group("nccl", device_id=dev)
+    from mercury_b200 import ops
+    from mercury_b200.sharded import ShardedPool
+
+    n, c, b = wl["n"], wl["c"], wl["b"]
+    s = 4 if wl["dtype"] == "f32" else 2
+    npools = auto_pools(wl, args.pools)
+    row_bytes = 0
+    payload = None
+    if wl["payload"]:
+        payload = torch.rand((n,) + wl["payload"], device=dev, generator=torch.Generator(device=dev).manual_seed(2))
+        row_bytes = payload[0].numel() * 4
+    index = torch.arange(n, device=dev) + rank * n
+    pools = [make_pool(wl, dev, seed=100 * rank + i) for i in range(npools)]
+    u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(3)).to(dev)
+    out = {}
+    exchange = args.exchange if args.shard_mode == "totals" else "nccl"
+    if exchange == "peer":
+        # peer mapping is a set-up step that a box may refuse (no IPC between these GPUs): agree on it across ranks
+        try:
+            sp = ShardedPool(n_local=n, device=dev, mode="totals", exchange="peer")
+            ok = 1
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] rank {rank}: peer exchange unavailable ({e}); using NCCL", file=sys.stderr)
+            ok = 0
+        t = torch.tensor([ok], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        if int(t) == 0:
+            exchange = "nccl"
+    if exchange == "nccl":
+        sp = ShardedPool(n_local=n, device=dev, mode=args.shard_mode)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(i):
+        lg, lb = pools[i % npools]
+        return sp.update_samples(lg, lb, u, data=payload, index=index, out=out)
+
+    pc = parity_check(ops, sp, pools, payload, index, u, n, world, rank, dist, dev, args.shard_mode)
+    use_graph = args.graph and os.environ.get("MERCURY_BENCH_GRAPH_NCCL", "1") == "1"
+    with ClockSampler(dev.index or 0) as clocks:
+        ms, run = timed_steps(step, npools, args.steps, args.warmup, use_graph, barrier, dist, dev)
+        extra = max(npools, min(20000, int(600.0 / max(ms, 1e-3))))   # (the SAME number of steps on every rank)
+        run(extra)
+        torch.cuda.synchronize()
+    r = step(0)
+    torch.cuda.synchronize()
+    ops.check_status(r["status"])
+    if r.get("xstatus") is not None:
+        ops.check_status(r["xstatus"])
+    peak, peak_src = peak_hbm()
+    step_bytes = algorithmic_bytes(n, c, s, b, row_bytes)
+    # ---- end to end with host buffers: every rank copies its shard's logits, labels and the uniforms in, results out
+    pool_bytes = n * (c * s + 8)
+    e2e_rows = n if pool_bytes <= (8 << 30) else 1 << 16
+    e2e = None
+    if e2e_rows == n:
+        lg0, lb0 = pools[0]
+        h_logits = torch.empty(lg0.shape, dtype=lg0.dtype).pin_memory()
+        h_labels = torch.empty(lb0.shape, dtype=lb0.dtype).pin_memory()
+        h_logits.copy_(lg0)
+        h_labels.copy_(lb0)
+        u_host = u.cpu().pin_memory()
+        d_logits, d_labels, d_u = torch.empty_like(lg0), torch.empty_like(lb0), torch.empty_like(u)
+        h_idx = torch.empty(b, dtype=torch.int64).pin_memory()
+        h_np = torch.empty(b, dtype=torch.float32).pin_memory()
+        h_seed = torch.empty(b, dtype=torch.float32).pin_memory()
+        h_stats = torch.empty(8, dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            d_logits.copy_(h_logits, non_blocking=True)
+            d_labels.copy_(h_labels, non_blocking=True)
+            d_u.copy_(u_host, non_blocking=True)
+            rr = sp.update_samples(d_logits, d_labels, d_u, data=payload, index=index, out=out)
+            h_idx.copy_(rr["idx"], non_blocking=True)
+            h_np.copy_(rr["nprob"], non_blocking=True)
+            h_seed.copy_(rr["seed"], non_blocking=True)
+            h_stats.copy_(rr["stats"], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        for i in range(3):
+            e2e_step()
+        barrier()
+        e2e_steps = max(5, min(args.steps, 20))
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            e2e_step()
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        t = torch.tensor([e2e_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t)
+        e2e = {"value": n * world / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": world * (n * (c * s + 8) + b * 8),
+               "d2h_bytes_per_step": world * (b * (8 + 4 + 4) + 32), "ms_per_step": e2e_ms, "steps": e2e_steps, "rows_per_step": n * world}
+    else:
+        e2e = {"value": None, "unit": "candidates/s", "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
+               "note": "pool above 8 GB per GPU: the host path of this shape is timed on one GPU (row slice); not repeated per rank"}
+    if rank == 0:
+        value = n * world / (ms * 1e-3)
+        line = {
+            "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
+            "config": make_config(args, wl, world, exchange),
+            "roofline": {"kernel": "whole step per GPU: score -> summarize -> spine -> draw on the rank's shard, exchanges inside",
+                         "bound": "hbm", "achieved": step_bytes / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": step_bytes / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "ms_per_launch": ms,
+                         "algorithmic_bytes_per_launch": step_bytes},
+            "parity_check": pc,
+            "e2e": e2e,
+            "gpu_launches": step_launches(ops, wl, world, exchange, args.shard_mode) * world * args.steps,
+            "clocks": clocks.summary(),
+        }
+        print(json.dumps(line))
+    # Graphs that captured NCCL work keep the communicator busy at teardown (destroy_process_group was seen to block):
+    # agree that everybody is done, then leave without the collective teardown.
+    dist.barrier()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
 
 
 def main():
@@ -243,6 +721,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pools", type=int, default=0, help="distinct pools rotated to defeat L2 (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-workloads", action="store_true", help="N=1, cfg2: skip the short cfg3 / cfg5 blocks")
     ap.add_argument("--shard-mode", choices=["totals", "scores"], default=os.environ.get("MERCURY_SHARD_MODE", "totals"),
                     help="N>1 only: 'totals' = shard-local exact chains, only per-shard sums/totals exchanged, two-level draw; "
                          "'scores' = all-gather the scores and replicate the flat pool's exact CDF on every rank")
@@ -264,253 +743,10 @@ def main():
         raise SystemExit("bench.py needs a GPU (there is no CPU path); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist = None
     if world > 1:
-        import torch.distributed as dist
-
-        dist.init_process_group("nccl", device_id=dev)
-
-    from mercury_b200 import ops
-
-    n, c, b = wl["n"], wl["c"], wl["b"]
-    s = 4 if wl["dtype"] == "f32" else 2
-    row_bytes = 0
-    payload = None
-    if wl["payload"]:
-        payload = torch.rand((n,) + wl["payload"], device=dev, generator=torch.Generator(device=dev).manual_seed(2))
-        row_bytes = payload[0].numel() * 4
-    index = torch.arange(n, device=dev) + rank * n
-    pool_bytes = n * (c * s + 8)
-    # >= 300 MB in rotation (> 126 MB L2); a pool of tens of GB is its own L2 flush
-    npools = args.pools or (1 if pool_bytes >= (16 << 30) else max(2, min(8, -(-(300 << 20) // pool_bytes))))
-    pools = [make_pool(wl, dev, seed=100 * rank + i) for i in range(npools)]
-    gen = torch.Generator().manual_seed(3)
-    u_host = torch.rand(b, dtype=torch.float64, generator=gen).pin_memory()
-    u = u_host.to(dev)
-    ema = torch.zeros(1, device=dev)
-    out = {}  # result buffers reused across steps: no allocation inside the timed region
-
-    if world > 1:
-        from mercury_b200.sharded import ShardedPool
-
-        exchange = args.exchange if args.shard_mode == "totals" else "nccl"
-        if exchange == "peer":
-            # peer mapping is a set-up step that a box may refuse (no IPC between these GPUs): agree on it across ranks
-            try:
-                sp = ShardedPool(n_local=n, device=dev, mode="totals", exchange="peer")
-                ok = 1
-            except Exception as e:  # noqa: BLE001
-                print(f"[bench] rank {rank}: peer exchange unavailable ({e}); using NCCL", file=sys.stderr)
-                ok = 0
-            t = torch.tensor([ok], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MIN)
-            if int(t) == 0:
-                exchange = "nccl"
-        if exchange == "nccl":
-            sp = ShardedPool(n_local=n, device=dev, mode=args.shard_mode)
-
-    status = ops.new_status(dev)
-
-    def step(i, first=False):
-        lg, lb = pools[i % npools]
-        if world > 1:
-            return sp.update_samples(lg, lb, u, data=payload, index=index, out=out)
-        r = ops.update_samples(lg, lb, u, ema, first, data=payload, index=index, out=out, status=status)
-        out.update({k: v for k, v in r.items() if k in ("scores", "stats", "idx", "nprob", "seed", "data", "labels", "index")})
-        return r
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for i in range(max(3, args.warmup)):
-        r = step(i, first=(i == 0))
-    barrier()
-    # One CUDA graph per pool (the pools differ only in their pointers): the step is replayed with
-    # no host work between its kernels.  Multi-rank steps capture their NCCL all-gather in the graph
-    # as well (MERCURY_BENCH_GRAPH_NCCL=0 keeps them eager).
-    graphs = None
-    if args.graph and (world == 1 or os.environ.get("MERCURY_BENCH_GRAPH_NCCL", "1") == "1"):
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            step(0)  # allocates this stream's workspace outside capture
-        torch.cuda.current_stream().wait_stream(side)
-        torch.cuda.synchronize()
-        graphs = []
-        for i in range(npools):
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g, stream=side):
-                step(i)
-            graphs.append(g)
-        for g in graphs:
-            g.replay()
-        torch.cuda.synchronize()
-
-    def run(i):
-        if graphs is not None:
-            graphs[i % npools].replay()
-        else:
-            step(i)
-
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
-        barrier()
-        e0.record()
-        for i in range(args.steps):
-            run(i)
-        e1.record()
-        barrier()
-        ms = e0.elapsed_time(e1) / args.steps
-        if dist is not None:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t)
-        # keep the clocks sampled over a region long enough for nvidia-smi to see it (~0.6 s; the
-        # SAME number of steps on every rank: a step contains a collective)
-        for i in range(max(1, min(20000, int(600.0 / max(ms, 1e-3))))):
-            run(i)
-        torch.cuda.synchronize()
-    ops.check_status(r["status"])
-    total_candidates = n * world
-    value = total_candidates / (ms * 1e-3)
-
-    # ---- dominant kernel (K1 score) timed alone on its launching stream.  The launches are
-    # captured into one graph (one launch per rotating pool) so that the events bracket GPU
-    # time, not the Python/ctypes launch rate.
-    sc = torch.empty(n, dtype=torch.float32, device=dev)
-    st = ops.new_status(dev)
-    kstream = torch.cuda.Stream()
-    kstream.wait_stream(torch.cuda.current_stream())
-    with torch.cuda.stream(kstream):
-        for i in range(3):
-            ops.score(*pools[i % npools], status=st, out=sc)
-    torch.cuda.synchronize()
-    reps = max(2, -(-max(args.steps, 10) // npools))
-    if world == 1 or os.environ.get("MERCURY_BENCH_GRAPH_NCCL", "1") == "1":
-        kg = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(kg, stream=kstream):
-            for i in range(npools):
-                ops.score(*pools[i], status=st, out=sc)
-        with torch.cuda.stream(kstream):
-            kg.replay()
-            a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(kstream)
-            for _ in range(reps):
-                kg.replay()
-            z.record(kstream)
+        main_multi(args, wl, dev, world, rank)
     else:
-        # multi-rank: no graph capture beside NCCL's watchdog; stall the stream so that the launches queue up
-        with torch.cuda.stream(kstream):
-            torch.cuda._sleep(int(4e6))
-            a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(kstream)
-            for _ in range(reps):
-                for i in range(npools):
-                    ops.score(*pools[i], status=st, out=sc)
-            z.record(kstream)
-    torch.cuda.synchronize()
-    k1_ms = a.elapsed_time(z) / (reps * npools)
-    peak, peak_src = peak_hbm()
-    k1_bytes = n * (c * s + 8 + 4)
-    k1_gbs = k1_bytes / (k1_ms * 1e-3) / 1e9
-    step_bytes = algorithmic_bytes(n, c, s, b, row_bytes)
-
-    # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
-    e2e_rows = n
-    if pool_bytes > (8 << 30) and world > 1:
-        raise SystemExit("bench.py: workloads with pools above 8 GB per GPU are single-GPU runs (their host path is timed on a slice)")
-    if pool_bytes > (8 << 30):
-        # a pool that does not fit pinned host memory comfortably: time the host path on a 64 Ki-row slice and
-        # report the rate per candidate (the copy dominates and is linear in the rows)
-        e2e_rows = 1 << 16
-    lg0, lb0 = pools[0][0][:e2e_rows], pools[0][1][:e2e_rows]
-    e2e_payload = payload[:e2e_rows] if payload is not None else None
-    e2e_index = index[:e2e_rows]
-    h_logits = torch.empty(lg0.shape, dtype=lg0.dtype).pin_memory()
-    h_labels = torch.empty(lb0.shape, dtype=lb0.dtype).pin_memory()
-    h_logits.copy_(lg0)
-    h_labels.copy_(lb0)
-    d_logits, d_labels, d_u = torch.empty_like(lg0), torch.empty_like(lb0), torch.empty_like(u)
-    h_idx = torch.empty(b, dtype=torch.int64).pin_memory()
-    h_np = torch.empty(b, dtype=torch.float32).pin_memory()
-    h_seed = torch.empty(b, dtype=torch.float32).pin_memory()
-    h_stats = torch.empty(8, dtype=torch.float32).pin_memory()
-    ema2 = torch.zeros(1, device=dev)
-    e2e_out = out if e2e_rows == n else {}
-
-    def e2e_step(first=False):
-        d_logits.copy_(h_logits, non_blocking=True)
-        d_labels.copy_(h_labels, non_blocking=True)
-        d_u.copy_(u_host, non_blocking=True)
-        if world > 1:
-            rr = sp.update_samples(d_logits, d_labels, d_u, data=payload, index=index, out=out)
-        else:
-            rr = ops.update_samples(d_logits, d_labels, d_u, ema2, first, data=e2e_payload, index=e2e_index, out=e2e_out)
-        h_idx.copy_(rr["idx"], non_blocking=True)
-        h_np.copy_(rr["nprob"], non_blocking=True)
-        h_seed.copy_(rr["seed"], non_blocking=True)
-        h_stats.copy_(rr["stats"], non_blocking=True)
-        torch.cuda.current_stream().synchronize()  # the caller reads the result every step
-
-    for i in range(3):
-        e2e_step(first=(i == 0))
-    barrier()
-    e2e_steps = max(5, min(args.steps, 20))
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        e2e_step()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
-    if dist is not None:
-        t = torch.tensor([e2e_ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t)
-    h2d = world * (e2e_rows * (c * s + 8) + b * 8)   # whole job: every rank copies its shard's logits, labels and the uniforms in
-    d2h = world * (b * (8 + 4 + 4) + 32)      # ... and idx / N*p / seed / stats out
-
-    if rank == 0:
-        # our kernels per step and rank: score, summarize (statistics folded in), spine, draw; sharded: + chunk sums, gather_owned
-        # totals: score, chunk sums, sum(+exchange), summarize, spine, select(+exchange), draw; scores: + gather_owned
-        # totals over peer memory: score, summarize (+ exchange of the shard sums), spine (+ publishes the chain total),
-        # draw (+ shard selection): the same four launches as on one GPU
-        per_rank = 4 if (world == 1 or exchange == "peer") else 6 if args.shard_mode == "scores" else 7
-        launches_per_step = per_rank * world
-        line = {
-            "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
-            "config": {"workload": args.workload, "note": wl["note"], "candidates_per_gpu": n, "classes": c, "draws": b,
-                       "payload_row_bytes": row_bytes, "l2": f"{npools} distinct pools rotated ({npools * pool_bytes >> 20} MiB > 126 MiB L2)",
-                       "cdf": "exact serial-fp32 (bit-identical to torch.multinomial on CPU)",
-                       "launch": "CUDA graph replay, one graph per pool" if graphs is not None else "eager launches",
-                       "multi_gpu": None if world == 1 else MULTI_GPU_NOTE[args.shard_mode],
-                       "exchange": None if world == 1 else EXCHANGE_NOTE[exchange]},
-            "step_roofline": {"algorithmic_bytes": step_bytes, "achieved_gbs": step_bytes / (ms * 1e-3) / 1e9,
-                              "frac": step_bytes / (ms * 1e-3) / 1e9 / peak},
-            "roofline": {"kernel": "K1 score (mercury_score)", "bound": "hbm", "achieved": k1_gbs, "peak": peak, "unit": "GB/s",
-                         "frac": k1_gbs / peak, "traffic": k1_traffic(args.workload) if world == 1 else None, "peak_source": peak_src, "ms_per_launch": k1_ms,
-                         "algorithmic_bytes_per_launch": k1_bytes},
-            "e2e": {"value": e2e_rows * world / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps,
-                    "rows_per_step": e2e_rows * world},
-            "gpu_launches": launches_per_step * args.steps,
-            "clocks": clocks.summary(),
-        }
-        if world == 1 and n * c * 4 <= (32 << 30):   # (ATen upcasts the logits: needs N*C*4 bytes of scratch)
-            line["library_baseline"] = library_baseline(pools, payload, index, u, b)
-        if not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(wl)
-        print(json.dumps(line))
-    if dist is not None:
-        # Graphs that captured NCCL work keep the communicator busy at teardown (destroy_process_group
-        # was seen to block): agree that everybody is done, then leave without the collective teardown.
-        dist.barrier()
-        torch.cuda.synchronize()
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(0)
+        main_single(args, wl, dev)
 
 
 if __name__ == "__main__":
