@@ -329,6 +329,7 @@ def timed_steps(step, npools, steps, warmup, use_graph, barrier, dist=None, dev=
                 for i in range(nsteps % npools):
                     step(i)
 
+    run(max(npools, (max(3, warmup) // npools + 1) * npools))   # warm-up through the same path as the timed steps
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
