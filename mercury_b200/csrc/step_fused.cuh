@@ -83,6 +83,8 @@ struct StepArgs {
     int nchunks; double bias; Summary* sums; Pack2* packs; uint32_t* start_bits; float* total; StepCtrl* ctrl;
     int32_t* status;
     int dbg_flags;                 // developer aid (MERCURY_STEP_DBG): 1 = stamp the walk's steps
+    // sharded pool, exchanges inside the kernel (peers != nullptr; see mercury_peer_create): this launch covers one shard
+    PeerBox* const* peers; int nshards, rank; int64_t n_global; double* sums_all; float* totals_all; double* local_u;
     int cdf_mode;                  // MERCURY_CDF_EXACT_SERIAL_F32 or MERCURY_CDF_F64 (no walk: fp64 chunk sums and their scan)
     double* approx;                // fp64 mode: [nchunks + 1] running total of p in front of every chunk
     // draws
@@ -1030,10 +1032,53 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
         }
     }
     wsync();
+    // ---- sharded pool: every rank's chain total, exchanged through the peers' boxes (one CTA waits here, not every draw)
+    if (a.peers) {
+        float* sh_cdf = reinterpret_cast<float*>(evs);   // [nshards] (the steps are not needed any more)
+        PeerBox* const mine = a.peers[a.rank];
+        const unsigned int tag = mine->seq_total + 1u;
+        if (tid < a.nshards) {
+            peer_store(&a.peers[tid]->total[tag & 1u][a.rank], ((unsigned long long)sb[nchunks] << 32) | tag);
+            unsigned long long w;
+            if (!peer_wait(&mine->total[tag & 1u][tid], tag, w, &mine->dead)) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
+            sh_cdf[tid] = __uint_as_float((unsigned int)(w >> 32));
+            a.totals_all[tid] = sh_cdf[tid];
+        }
+        wsync();
+        if (tid == 0) {   // serial fp32 CDF over the shard totals (shard_select_kernel's arithmetic); step counters for the next call
+            mine->seq_total = tag; mine->seq_sum = mine->seq_sum + 1u;
+            float cs = 0.f;
+            for (int k = 0; k < a.nshards; ++k) cs = __fadd_rn(cs, sh_cdf[k]);
+            float run = 0.f;
+            for (int k = 0; k < a.nshards; ++k) { run = __fadd_rn(run, sh_cdf[k]); sh_cdf[k] = __fdiv_rn(run, cs); }
+        }
+        wsync();
+    }
     // ---- the chunk of every draw: first chunk whose last cdf value is not below u (ATen's lower bound), then publish
     const float total = b2f(sb[nchunks]);
     for (int64_t j = tid; j < a.d.b; j += kStepNT) {
-        const double uj = a.d.u[j];
+        double uj = a.d.u[j];
+        if (a.peers) {   // which shard the uniform falls in, and where inside that shard's own CDF (-1: another rank's draw)
+            const float* sh_cdf = reinterpret_cast<const float*>(evs);
+            int k = 0;
+            while (k < a.nshards - 1 && (double)sh_cdf[k] < uj) ++k;
+            double lu = -1.0;
+            if (k == a.rank) {
+                const double lo_c = k > 0 ? (double)sh_cdf[k - 1] : 0.0, hi_c = (double)sh_cdf[k];
+                lu = hi_c > lo_c ? (uj - lo_c) / (hi_c - lo_c) : 0.0;
+                if (lu < 0.0) lu = 0.0;
+                if (lu >= 1.0) lu = 0.99999999999999989;
+            }
+            a.local_u[j] = lu;
+            if (lu < 0.0) {
+                __threadfence();
+                st_relaxed_u64(&a.ctrl->dinfo[j], (1ull << 63) | (1ull << 62));
+                st_relaxed_u64(&a.ctrl->dinfo2[j], (1ull << 63) | f2b(total));
+                continue;
+            }
+            uj = lu;
+            __threadfence();   // (the draw's CTA reads local_u[j] behind its word)
+        }
         int lo = 0, hi = nchunks - 1;          // answer in [lo, hi]
         while (lo < hi) {
             const int mid = (lo + hi) >> 1;
@@ -1167,7 +1212,30 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
 #pragma unroll
         for (int i = 0; i < kStepNT / 32; ++i) { tot += s2.dred[0][i]; pre += s2.dred[1][i]; }
     }
-    const double n_stat = (double)a.n;
+    double n_stat = (double)a.n;
+    if (a.peers) {   // sharded pool: the statistics are those of the WHOLE pool -- CTA 0 pushes this shard's sum, every CTA waits for all
+        __shared__ double gs[kMaxShards];
+        PeerBox* const my_box = a.peers[a.rank];
+        const unsigned int sum_tag = my_box->seq_sum + 1u;   // (the walker advances seq_sum once the step's sums are in)
+        const int par = sum_tag & 1u;
+        if (tid < a.nshards) {
+            if (blockIdx.x == 0) {
+                const unsigned long long bits = (unsigned long long)__double_as_longlong(tot);
+                peer_store(&a.peers[tid]->sum_hi[par][a.rank], (bits >> 32 << 32) | sum_tag);
+                peer_store(&a.peers[tid]->sum_lo[par][a.rank], (bits << 32) | sum_tag);
+            }
+            unsigned long long hi, lo;
+            const bool ok = peer_wait(&my_box->sum_hi[par][tid], sum_tag, hi, &my_box->dead) &
+                            peer_wait(&my_box->sum_lo[par][tid], sum_tag, lo, &my_box->dead);
+            if (!ok) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
+            gs[tid] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
+            if (blockIdx.x == 0) a.sums_all[tid] = gs[tid];
+        }
+        wsync();
+        tot = 0.0;
+        for (int i = 0; i < a.nshards; ++i) tot += gs[i];   // (same order on every rank and in every CTA)
+        n_stat = (double)a.n_global;
+    }
     const float mean = (float)(tot / n_stat);
     const float al = (float)a.ema_alpha, one_minus_a = (float)(1.0 - a.ema_alpha);
     const float ema = a.ema_first ? mean : __fadd_rn(__fmul_rn(al, ema_prev), __fmul_rn(one_minus_a, mean));
@@ -1261,14 +1329,16 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
                 if ((v & w) >> 63) break;
                 if ((it & 63u) == 63u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); v = 0ull; break; }
             }
+            if (a.peers) __threadfence();
             dinfo_s = v;
             dtotal = b2f((uint32_t)w);
             if (f64 && (v >> 63)) { __threadfence(); drun0 = __ldcg(&a.ctrl->dapprox[j]); dtot64 = __ldcg(&a.ctrl->dtotal[j]); }
             dstats[MERCURY_STAT_SHIFT] = shift; dstats[MERCURY_STAT_TOTAL] = total;
         }
-        const double uj = a.d.u[j];
+        double uj = a.d.u[j];
         wsync();
         const unsigned long long v = dinfo_s;
+        if (a.peers && (v >> 63)) uj = ((v >> 62) & 1ull) ? -1.0 : __ldcg(&a.local_u[j]);   // (written in front of the word, fenced)
         if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 64) a.ctrl->evt[106] = global_ns();
         if (!(v >> 63)) return;  // timed out (reported): leave the outputs alone rather than write garbage
         if (f64) draw_resolve_f64<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), drun0, dtot64, ds);

@@ -46,8 +46,10 @@ def _worker(rank, world, port, n, c, b, ret):
     pools = {"nccl": ShardedPool(nl, dev, mode="totals", exchange="nccl"),
              "peer": ShardedPool(nl, dev, mode="totals", exchange="peer"),                  # one C call per step
              "peer_staged": ShardedPool(nl, dev, mode="totals", exchange="peer", fused=False)}  # one call per stage
+    pools["peer_one_kernel"] = pools["peer"]   # the same pool, the whole sharded step as ONE kernel (test hook: off by default)
     outs = {}
     for x, sp in pools.items():
+        ops.set_fused(1 if x == "peer_one_kernel" else -1)
         steps = []
         for step in range(3):
             r = sp.update_samples((logits[sl] + step).to(dev), labels[sl].to(dev), u.to(dev), data=data[sl].to(dev), assemble=True)
@@ -74,6 +76,8 @@ def test_peer_exchange_two_gpus_matches_nccl_and_oracle():
         for k in ("idx", "nprob", "seed", "data", "labels"):
             assert torch.equal(ret[0]["peer"][step][k], ret[0]["nccl"][step][k]), (step, k)   # peer == NCCL exchange
             assert torch.equal(ret[0]["peer_staged"][step][k], ret[0]["nccl"][step][k]), (step, k)
+            if k != "nprob" and k != "seed":   # (its pool statistics are summed per CTA, not per tile: equal to 1e-6, see test_gpu_fused_step)
+                assert torch.equal(ret[0]["peer_one_kernel"][step][k], ret[0]["nccl"][step][k]), (step, k)
             assert torch.equal(ret[0]["peer"][step][k], ret[1]["peer"][step][k]), (step, k)   # assembled on both ranks
         st = ret[0]["peer"][step]["stats"]
         assert torch.equal(st[:4], ret[1]["peer"][step]["stats"][:4]) and torch.equal(st[:4], ret[0]["nccl"][step]["stats"][:4])
