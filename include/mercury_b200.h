@@ -212,6 +212,17 @@ int mercury_score_head(const void* features, int dtype, int64_t n, int64_t d, in
                        const float* weight, const float* bias, int64_t c, const int64_t* labels,
                        int64_t ignore_index, float* scores, int32_t* status, void* stream);
 
+/* The same for WIDE heads, on the tensor cores (the reference's Bottleneck ResNets end in
+ * nn.Linear(512 * expansion, num_classes) = 2048 -> C, pytorch_model.py:39-64, 78, 94-96): features [n, d] bf16 and
+ * weight [c, d] bf16 (nn.Linear.weight cast once), both with d contiguous, row strides in elements (multiples of 8),
+ * 16-byte aligned; bias fp32 [c] or NULL; 1 <= c <= 4096.  TMA-staged operands, tcgen05.mma with fp32 accumulators in
+ * tensor memory, online log-sum-exp in the epilogue: the [n, c] logits are never written.  Products are bf16 x bf16 in
+ * fp32: scores agree with F.cross_entropy(F.linear(features.float(), weight.float(), bias), labels) to rtol/atol 2e-5.
+ * Labels as in mercury_score. */
+int mercury_score_head_wide(const void* features, int64_t n, int64_t d, int64_t row_stride, const void* weight,
+                            int64_t weight_stride, const float* bias, int64_t c, const int64_t* labels,
+                            int64_t ignore_index, float* scores, int32_t* status, void* stream);
+
 /* ---- the whole step ---------------------------------------------------------------------------
  * replaces Trainer.update_samples' arithmetic (pytorch_collab.py:102-117) on an assembled pool:
  * score -> stats -> exact CDF -> b draws from caller-supplied uniforms -> gather + weights + seed.

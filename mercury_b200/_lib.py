@@ -66,6 +66,7 @@ SIGNATURES = {
     "mercury_sum_scores": (c_int, [c_vp, c_i64, c_vp, c_vp, c_sz, c_vp]),
     "mercury_shard_select": (c_int, [c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp]),
     "mercury_score_head": (c_int, [c_vp, c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),
+    "mercury_score_head_wide": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "mercury_peer_create": (c_int, [c_vp, c_vp]),
     "mercury_peer_open": (c_int, [c_vp, c_vp]),
     "mercury_peer_close": (c_int, [c_vp]),

@@ -113,10 +113,13 @@ def score_head(features: torch.Tensor, weight: torch.Tensor, bias: Optional[torc
     reduction='none')`` without materialising the logits (pytorch_model.py:96 + pytorch_collab.py:102).
     features [N, D] fp32/bf16 with D a multiple of 128, weight fp32 [C, D] with C <= 16 (the reference's 512 -> 10 head)."""
     _cuda(features, "features")
-    _cuda(weight, "weight", torch.float32)
+    _cuda(weight, "weight")
     _cuda(labels, "labels", torch.int64)
     if features.dim() != 2 or weight.dim() != 2 or weight.shape[1] != features.shape[1] or labels.shape != features.shape[:1]:
         raise RuntimeError("mercury_b200.score_head: expected features [N, D], weight [C, D] and labels [N]")
+    if weight.shape[0] > 16 or weight.dtype == torch.bfloat16:
+        return score_head_wide(features, weight, bias, labels, ignore_index, status, out)
+    _cuda(weight, "weight", torch.float32)
     if features.stride(1) != 1:
         features = features.contiguous()
     weight = weight.contiguous()
@@ -131,6 +134,38 @@ def score_head(features: torch.Tensor, weight: torch.Tensor, bias: Optional[torc
     _lib.check(_lib.load().mercury_score_head(features.data_ptr(), _dtype_code(features), n, d, features.stride(0) if n > 1 else d,
                                               weight.data_ptr(), _ptr(bias), weight.shape[0], labels.data_ptr(), ignore_index,
                                               out.data_ptr(), status.data_ptr(), _stream()))
+    return out
+
+
+def score_head_wide(features: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], labels: torch.Tensor,
+                    ignore_index: int = -100, status: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """The wide head on the tensor cores (tcgen05): bf16 features [N, D] x bf16 weight [C, D]^T + bias, cross-entropy in the
+    epilogue, logits never written (pytorch_model.py:94-96 for the Bottleneck ResNets' 2048 -> C head, then
+    pytorch_collab.py:102).  fp32 inputs are cast to bf16 (a parameter / activation cast, as autocast would do)."""
+    _cuda(features, "features")
+    _cuda(weight, "weight")
+    _cuda(labels, "labels", torch.int64)
+    if features.dtype != torch.bfloat16:
+        features = features.to(torch.bfloat16)
+    if weight.dtype != torch.bfloat16:
+        weight = weight.to(torch.bfloat16)
+    if features.stride(1) != 1 or features.stride(0) % 8 or features.data_ptr() % 16:
+        features = features.contiguous()
+    if weight.stride(1) != 1 or weight.stride(0) % 8 or weight.data_ptr() % 16:
+        weight = weight.contiguous()
+    n, d = features.shape
+    if d % 8:
+        raise RuntimeError("mercury_b200.score_head_wide: the feature width must be a multiple of 8")
+    if bias is not None:
+        bias = _cuda(bias, "bias").float().contiguous()
+    labels = labels.contiguous()
+    if status is None:
+        status = new_status(features.device)
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=features.device)
+    _lib.check(_lib.load().mercury_score_head_wide(features.data_ptr(), n, d, features.stride(0) if n > 1 else d, weight.data_ptr(),
+                                                   weight.stride(0) if weight.shape[0] > 1 else d, _ptr(bias), weight.shape[0],
+                                                   labels.data_ptr(), ignore_index, out.data_ptr(), status.data_ptr(), _stream()))
     return out
 
 
