@@ -50,7 +50,8 @@ enum {
     MERCURY_ST_ZERO_SUM = 8,   /* multinomial: "sum of probabilities <= 0"                         */
     MERCURY_ST_TOPK_TIES = 16, /* exponential race: more exact ties at the k-th key than buffered  */
     MERCURY_ST_PEER_TIMEOUT = 32, /* peer exchange: a peer's word did not arrive within the bound   */
-    MERCURY_ST_INTERNAL = 64   /* a wait inside the one-kernel step ran into its 2 s bound (a bug)    */
+    MERCURY_ST_INTERNAL = 64,  /* a wait inside the one-kernel step ran into its 2 s bound (a bug)    */
+    MERCURY_ST_GROUP_COUNT = 128 /* group-masked draw: the group has not the member count the host gave */
 };
 
 /* layout of the 8-float statistics block written by mercury_pool_stats */
@@ -124,6 +125,19 @@ int mercury_sample_with_replacement(const float* cdf, int64_t n, const double* u
 size_t mercury_sample_topk_workspace_bytes(int64_t n, int64_t k);
 int mercury_sample_topk(const float* weights, int64_t n, const double* uniforms, int64_t k,
                         int64_t* idx, int32_t* status, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- group-masked draws ------------------------------------------------------------------------
+ * replaces Groupwise_Sampler.__iter__'s body (util.py:140-157): mask = (tags == group); imp = importance[mask];
+ * imp + np.mean(imp); / np.sum; torch.multinomial(torch.Tensor(imp), 1, replacement) and the nonzero() that maps the
+ * winner back -- without compacting anything.  importance fp32 [n], tags int32 [n]; `count` = members of the group
+ * (the host knows it: it wrote the tags; a mismatch sets MERCURY_ST_GROUP_COUNT).  p = (imp + mean) / sum in float64,
+ * rounded once to fp32; member m (in position order) races with uniform m of its draw: uniforms fp64 [ndraws * count].
+ * k == 1: ndraws independent single draws (idx int64 [ndraws], dataset positions); k > 1 (ndraws == 1): the k largest
+ * keys in descending order (draw without replacement).  p_out fp32 [n] (optional): p at the members, 0 elsewhere. */
+size_t mercury_groupwise_draw_workspace_bytes(int64_t n, int64_t ndraws);
+int mercury_groupwise_draw(const float* importance, const int32_t* tags, int32_t group, int64_t n, int64_t count,
+                           const double* uniforms, int64_t ndraws, int64_t k, int64_t* idx, float* p_out,
+                           int32_t* status, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- K3: gather the drawn candidates + importance weights + backward seed ----------------------
  * replaces losses_pros[idx] * N, cat(datas)[idx], cat(labels)[idx], cat(index)[idx]

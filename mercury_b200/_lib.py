@@ -15,7 +15,7 @@ ABI_VERSION = 3
 OK, ERR_ARG, ERR_CUDA, ERR_WORKSPACE = 0, -1, -2, -3
 F32, BF16 = 0, 1
 CDF_EXACT_SERIAL_F32, CDF_F64 = 0, 1
-ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES, ST_PEER_TIMEOUT, ST_INTERNAL = 1, 2, 4, 8, 16, 32, 64
+ST_BAD_LABEL, ST_NEGATIVE, ST_NONFINITE, ST_ZERO_SUM, ST_TOPK_TIES, ST_PEER_TIMEOUT, ST_INTERNAL, ST_GROUP_COUNT = 1, 2, 4, 8, 16, 32, 64, 128
 PEER_BOX_BYTES, PEER_HANDLE_BYTES = 4096, 64
 STAT_MEAN, STAT_EMA, STAT_SHIFT, STAT_TOTAL, STAT_CHAIN_TOTAL, STAT_COUNT = 0, 1, 2, 3, 4, 8
 STATIC_MAX_N = 1 << 22
@@ -58,6 +58,8 @@ SIGNATURES = {
     "mercury_sample_with_replacement": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp]),
     "mercury_sample_topk_workspace_bytes": (c_sz, [c_i64, c_i64]),
     "mercury_sample_topk": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "mercury_groupwise_draw_workspace_bytes": (c_sz, [c_i64, c_i64]),
+    "mercury_groupwise_draw": (c_int, [c_vp, c_vp, ctypes.c_int32, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "mercury_gather_reweight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mercury_gather_owned": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mercury_test_set_guess_bias": (None, [c_f64]),

@@ -157,6 +157,154 @@ __global__ void __launch_bounds__(1024) sort_kernel(const SelState* __restrict__
     for (int i = threadIdx.x; i < k; i += 1024) idx[i] = (int64_t)(0xffffffffu - (uint32_t)(s[i] & 0xffffffffull));
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Group-masked draws (Groupwise_Sampler.__iter__, reference util.py:140-157): the members of the current group are the
+// positions whose tag equals `group`; p = (imp + mean(imp)) / sum(...) over the members in float64, rounded once to
+// fp32 (util.py:144-150: numpy float64, then torch.Tensor); the m-th member (in position order) races with the m-th
+// uniform of the draw, exactly the stream torch.multinomial consumes on the compacted vector.  No compaction happens:
+// a count + scan gives every member its rank, non-members never enter the race.
+constexpr int kGwChunk = 2048;
+struct GwState { double mean, denom; unsigned int count; unsigned int pad; };
+
+__global__ void __launch_bounds__(256) gw_count_kernel(const float* __restrict__ imp, const int32_t* __restrict__ tags, int32_t group,
+                                                       int64_t n, unsigned int* __restrict__ cnt, double* __restrict__ sum) {
+    __shared__ double rs[8];
+    __shared__ unsigned int rc[8];
+    const int64_t start = (int64_t)blockIdx.x * kGwChunk;
+    unsigned int c = 0;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < kGwChunk && start + i < n; i += 256)
+        if (tags[start + i] == group) { ++c; s += (double)imp[start + i]; }
+    s = warp_sum(s);
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0) { rs[threadIdx.x >> 5] = s; rc[threadIdx.x >> 5] = c; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        unsigned int k = 0;
+        for (int i = 0; i < 8; ++i) { t += rs[i]; k += rc[i]; }
+        cnt[blockIdx.x] = k; sum[blockIdx.x] = t;
+    }
+}
+
+// exclusive prefix of the chunk counts (in place), the group's mean and normaliser
+__global__ void __launch_bounds__(1024) gw_scan_kernel(unsigned int* __restrict__ cnt, const double* __restrict__ sum, int nchunks,
+                                                       unsigned int expect_count, GwState* st, int32_t* status) {
+    __shared__ unsigned int wtot[32];
+    __shared__ double dsum[32];
+    __shared__ unsigned int carry;
+    if (threadIdx.x == 0) carry = 0u;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double acc = 0.0;
+    for (int c0 = 0; c0 < nchunks; c0 += 1024) {
+        const int c = c0 + threadIdx.x;
+        const unsigned int v = c < nchunks ? cnt[c] : 0u;
+        if (c < nchunks) acc += sum[c];
+        unsigned int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+        if (lane == 31) wtot[warp] = inc;
+        __syncthreads();
+        unsigned int pre = carry;
+        for (int i = 0; i < warp; ++i) pre += wtot[i];
+        if (c < nchunks) cnt[c] = pre + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = pre + inc;
+        __syncthreads();
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) dsum[warp] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < 32; ++i) t += dsum[i];
+        const unsigned int count = carry;
+        const double mean = count ? t / (double)count : 0.0;
+        st->mean = mean; st->denom = t + (double)count * mean; st->count = count;   // sum(imp + mean) over the members
+        if (count != expect_count) atomicOr(status, MERCURY_ST_GROUP_COUNT);
+        if (!(st->denom > 0.0)) atomicOr(status, MERCURY_ST_ZERO_SUM);
+    }
+}
+
+// the race.  grid (chunks, draws).  RACE1: every draw is a single draw -> block maximum of (key bits << 32 | ~position)
+// into best[draw]; else (one draw, k > 1): keys + first histogram for the radix select above (non-members: key 0).
+template <bool RACE1>
+__global__ void __launch_bounds__(256) gw_race_kernel(const float* __restrict__ imp, const int32_t* __restrict__ tags, int32_t group,
+                                                      int64_t n, const unsigned int* __restrict__ base, const GwState* __restrict__ st,
+                                                      const double* __restrict__ u, unsigned long long* __restrict__ best,
+                                                      float* __restrict__ keys, uint32_t* __restrict__ hist, float* __restrict__ p_out) {
+    __shared__ unsigned int wtot[8];
+    __shared__ unsigned long long wbest[8];
+    __shared__ uint32_t sh[RACE1 ? 1 : kBins];
+    if (!RACE1) { for (int i = threadIdx.x; i < kBins; i += 256) sh[i] = 0; }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t start = (int64_t)blockIdx.x * kGwChunk + (int64_t)threadIdx.x * 8;
+    const double mean = st->mean, denom = st->denom;
+    const unsigned int count = st->count;
+    bool mem[8];
+    unsigned int local = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { mem[k] = start + k < n && tags[start + k] == group; local += mem[k]; }
+    unsigned int inc = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) wtot[warp] = inc;
+    __syncthreads();
+    unsigned int rank = base[blockIdx.x] + inc - local;
+    for (int i = 0; i < warp; ++i) rank += wtot[i];
+    const double* ud = u + (size_t)blockIdx.y * count;
+    unsigned long long mine = 0ull;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        float key = 0.f;
+        if (mem[k]) {
+            const float p = (float)(((double)imp[start + k] + mean) / denom);
+            const float q = (float)(-log1p(-ud[rank]));
+            key = __fdiv_rn(p, q);
+            ++rank;
+            if (p_out && blockIdx.y == 0) p_out[start + k] = p;
+            const unsigned long long comp = ((unsigned long long)__float_as_uint(key) << 32) | (0xffffffffu - (uint32_t)(start + k));
+            mine = comp > mine ? comp : mine;
+        } else if (p_out && blockIdx.y == 0 && start + k < n) p_out[start + k] = 0.f;
+        if (!RACE1 && start + k < n) { keys[start + k] = key; atomicAdd(&sh[__float_as_uint(key) >> 20], 1u); }
+    }
+    if (RACE1) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, mine, o); mine = t > mine ? t : mine; }
+        if (lane == 0) wbest[warp] = mine;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long b = 0ull;
+            for (int i = 0; i < 8; ++i) b = wbest[i] > b ? wbest[i] : b;
+            if (b) atomicMax(&best[blockIdx.y], b);
+        }
+    } else {
+        __syncthreads();
+        for (int i = threadIdx.x; i < kBins; i += 256)
+            if (sh[i]) atomicAdd(&hist[i], sh[i]);
+    }
+}
+
+__global__ void gw_decode_kernel(const unsigned long long* __restrict__ best, int64_t ndraws, int64_t* __restrict__ idx) {
+    const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (j < ndraws) idx[j] = (int64_t)(0xffffffffu - (uint32_t)best[j]);
+}
+
+struct GwWs { unsigned int* cnt; double* sum; GwState* st; unsigned long long* best; size_t topk_off; size_t bytes; };
+inline GwWs gw_carve(void* ws, int64_t n, int64_t ndraws) {
+    unsigned char* p = static_cast<unsigned char*>(ws);
+    const size_t nch = (size_t)((n + kGwChunk - 1) / kGwChunk);
+    GwWs w; size_t off = 0;
+    w.cnt = reinterpret_cast<unsigned int*>(p + off); off += al256(nch * 4);
+    w.sum = reinterpret_cast<double*>(p + off); off += al256(nch * 8);
+    w.st = reinterpret_cast<GwState*>(p + off); off += 256;
+    w.best = reinterpret_cast<unsigned long long*>(p + off); off += al256((size_t)(ndraws < 1 ? 1 : ndraws) * 8);
+    w.topk_off = off; off += carve(nullptr, n).bytes;
+    w.bytes = off;
+    return w;
+}
+
 }  // namespace
 }  // namespace mercury
 
@@ -195,6 +343,58 @@ extern "C" int mercury_sample_topk(const float* weights, int64_t n, const double
     collect_kernel<<<grid, 256, 0, st>>>(w.keys, n, w.st, w.cand, status);
     MB_CHECK_LAUNCH("collect_kernel");
     sort_kernel<<<1, 1024, 0, st>>>(w.st, w.cand, k, idx);
+    MB_CHECK_LAUNCH("sort_kernel");
+    return MERCURY_OK;
+}
+
+extern "C" size_t mercury_groupwise_draw_workspace_bytes(int64_t n, int64_t ndraws) { return gw_carve(nullptr, n, ndraws).bytes; }
+
+extern "C" int mercury_groupwise_draw(const float* importance, const int32_t* tags, int32_t group, int64_t n, int64_t count,
+                                      const double* uniforms, int64_t ndraws, int64_t k, int64_t* idx, float* p_out,
+                                      int32_t* status, void* ws, size_t ws_bytes, void* stream) {
+    MB_CHECK_ARG(n >= 1 && n <= ((int64_t)1 << 24), "mercury_groupwise_draw: 1 <= n <= 2^24");
+    MB_CHECK_ARG(count >= 1 && count <= n, "mercury_groupwise_draw: the group must have between 1 and n members");
+    MB_CHECK_ARG(ndraws >= 1 && k >= 1 && (k == 1 || ndraws == 1), "mercury_groupwise_draw: either single draws (k == 1) or one draw of k");
+    MB_CHECK_ARG(k <= count, "cannot sample n_sample > prob_dist.size(-1) samples without replacement");
+    MB_CHECK_ARG(k <= kMaxK, "mercury_groupwise_draw: k (%lld) exceeds %d", (long long)k, kMaxK);
+    MB_CHECK_ARG(ndraws <= 65535, "mercury_groupwise_draw: at most 65535 draws per call");
+    MB_CHECK_ARG(importance && tags && uniforms && idx && status, "mercury_groupwise_draw: null pointer");
+    const GwWs w = gw_carve(ws, n, ndraws);
+    int rc = check_ws(ws, ws_bytes, w.bytes, "mercury_groupwise_draw");
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nch = (int)((n + kGwChunk - 1) / kGwChunk);
+    gw_count_kernel<<<nch, 256, 0, st>>>(importance, tags, group, n, w.cnt, w.sum);
+    MB_CHECK_LAUNCH("gw_count_kernel");
+    gw_scan_kernel<<<1, 1024, 0, st>>>(w.cnt, w.sum, nch, (unsigned int)count, w.st, status);
+    MB_CHECK_LAUNCH("gw_scan_kernel");
+    if (k == 1) {
+        cudaError_t e = cudaMemsetAsync(w.best, 0, (size_t)ndraws * 8, st);
+        if (e != cudaSuccess) return cuda_fail(e, "mercury_groupwise_draw: memset");
+        gw_race_kernel<true><<<dim3(nch, (unsigned)ndraws), 256, 0, st>>>(importance, tags, group, n, w.cnt, w.st, uniforms, w.best, nullptr,
+                                                                          nullptr, p_out);
+        MB_CHECK_LAUNCH("gw_race_kernel");
+        gw_decode_kernel<<<(unsigned)((ndraws + 255) / 256), 256, 0, st>>>(w.best, ndraws, idx);
+        MB_CHECK_LAUNCH("gw_decode_kernel");
+        return MERCURY_OK;
+    }
+    const TopkWs t = carve(static_cast<unsigned char*>(ws) + w.topk_off, n);
+    cudaError_t e = cudaMemsetAsync(t.hist, 0, al256(kBins * 4) + 256, st);
+    if (e != cudaSuccess) return cuda_fail(e, "mercury_groupwise_draw: memset");
+    gw_race_kernel<false><<<dim3(nch, 1), 256, 0, st>>>(importance, tags, group, n, w.cnt, w.st, uniforms, nullptr, t.keys, t.hist, p_out);
+    MB_CHECK_LAUNCH("gw_race_kernel");
+    const int grid = (int)min_i64((n + 255) / 256, (int64_t)kSMs * 4);
+    for (int pass = 0; pass < 3; ++pass) {
+        if (pass > 0) {
+            hist_kernel<<<grid, 256, 0, st>>>(t.keys, n, pass, t.st, t.hist);
+            MB_CHECK_LAUNCH("hist_kernel");
+        }
+        select_kernel<<<1, 1024, 0, st>>>(pass, (uint32_t)k, t.st, t.hist);
+        MB_CHECK_LAUNCH("select_kernel");
+    }
+    collect_kernel<<<grid, 256, 0, st>>>(t.keys, n, t.st, t.cand, status);
+    MB_CHECK_LAUNCH("collect_kernel");
+    sort_kernel<<<1, 1024, 0, st>>>(t.st, t.cand, k, idx);
     MB_CHECK_LAUNCH("sort_kernel");
     return MERCURY_OK;
 }

@@ -73,6 +73,8 @@ def check_status(status: torch.Tensor) -> None:
         raise RuntimeError("mercury_b200: a peer's exchange word did not arrive within 4 s (ranks out of step?)")
     if bits & _lib.ST_INTERNAL:
         raise RuntimeError("mercury_b200: a wait inside the one-kernel step hit its 2 s bound (internal error)")
+    if bits & _lib.ST_GROUP_COUNT:
+        raise RuntimeError("mercury_b200: the group does not have the member count the host passed (tags changed behind the sampler?)")
     if bits & _lib.ST_TOPK_TIES:
         raise RuntimeError("mercury_b200: too many exactly tied keys at the k-th place of the exponential race")
 
@@ -286,6 +288,29 @@ def multinomial(p: torch.Tensor, num_samples: int, replacement: bool = False, *,
     if check:
         check_status(status)
     return idx
+
+
+def groupwise_draw(importance: torch.Tensor, tags: torch.Tensor, group: int, count: int, uniforms: torch.Tensor, ndraws: int = 1,
+                   k: int = 1, want_p: bool = False, status: Optional[torch.Tensor] = None):
+    """Draws from the current group of a Groupwise_Sampler (util.py:140-157) without compacting it: ``ndraws`` single draws
+    (k == 1; draw j races the group's members, in position order, with uniforms[j*count:(j+1)*count]) or one draw of k
+    without replacement.  Returns dataset positions int64 [ndraws or k] (and p fp32 [n], 0 outside the group, if want_p)."""
+    _cuda(importance, "importance", torch.float32)
+    _cuda(tags, "tags", torch.int32)
+    _cuda(uniforms, "uniforms", torch.float64)
+    n = importance.numel()
+    if uniforms.numel() < ndraws * count:
+        raise RuntimeError("mercury_b200.groupwise_draw: one uniform per member and draw is required")
+    lib = _lib.load()
+    if status is None:
+        status = new_status(importance.device)
+    idx = torch.empty(ndraws if k == 1 else k, dtype=torch.int64, device=importance.device)
+    p = torch.empty(n, dtype=torch.float32, device=importance.device) if want_p else None
+    ws = workspace(importance.device, lib.mercury_groupwise_draw_workspace_bytes(n, ndraws))
+    _lib.check(lib.mercury_groupwise_draw(importance.contiguous().data_ptr(), tags.contiguous().data_ptr(), int(group), n, int(count),
+                                          uniforms.contiguous().data_ptr(), int(ndraws), int(k), idx.data_ptr(), _ptr(p),
+                                          status.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
+    return (idx, p) if want_p else idx
 
 
 # ----------------------------------------------------------------------------------------- K3

@@ -10,6 +10,7 @@ from __future__ import annotations
 
 from typing import Optional, Sequence
 
+import numpy as np
 import torch
 
 from . import _lib, ops
@@ -101,23 +102,32 @@ class ImportanceSampler:
 class Groupwise_Sampler(torch.utils.data.Sampler):
     """util.py:94-160 with the importance array, the group tags and the draws on the device.
 
-    ``update_importance`` scores a slice of the dataset with the fused CE kernel and stores the
-    losses; ``__iter__`` smooths the current group's losses with their mean (util.py:146),
-    normalises (:147) and draws one index per step by the exponential race (:150, n_sample = 1),
-    consuming ``n_group`` fp64 uniforms from the CPU generator per draw like torch.multinomial.
+    ``update_importance`` scores a slice of the dataset with the fused CE kernel and stores the losses (no device->host
+    copy; util.py:132 syncs).  ``__iter__`` draws by the exponential race over the current group (util.py:144-151:
+    ``imp + mean(imp)``, normalise in float64, ``torch.multinomial(.., 1, replacement)``) with ONE kernel sequence per
+    block of draws and no compaction: mercury_groupwise_draw ranks the members in place.  Each single draw consumes
+    ``n_group`` fp64 uniforms from the CPU generator, exactly as torch.multinomial does in the reference.
+
+    ``prefetch`` single draws are raced per device round trip.  The reference re-reads the importance array before every
+    yield; here a change made by ``update_importance`` takes effect at the next block, so ``prefetch=1`` (the default)
+    is the reference's timing and larger values trade that for ``prefetch`` times fewer synchronisations.
     """
 
-    def __init__(self, dataset, replacement: bool = True, device="cuda", generator: Optional[torch.Generator] = None):
+    def __init__(self, dataset, replacement: bool = True, device="cuda", generator: Optional[torch.Generator] = None,
+                 prefetch: int = 1):
         self.dataset = dataset
         self.replacement = replacement
         self.device = torch.device(device)
         n = len(dataset)
         self.group_indicator = torch.zeros(n, dtype=torch.int32, device=self.device)
+        self._tags_host = np.zeros(n, dtype=np.int32)   # mirror of the tags: the host wrote them, so it knows the group sizes
         self.importance = torch.ones(n, dtype=torch.float32, device=self.device)
         self.cur_sample_index = 0
         self.group_index = 0
         self.last_update_iteration = -1
         self.generator = generator
+        self.prefetch = max(1, int(prefetch))
+        self.status = ops.new_status(self.device)
         self.num_samples = n  # the reference's __len__ reads this (undefined there, util.py:159-160)
 
     def update_importance(self, iteration, update_batchsize, model, device=None):
@@ -133,30 +143,38 @@ class Groupwise_Sampler(torch.utils.data.Sampler):
             output = model(data)
         ops.score(output, label, out=self.importance[start:end])  # no device->host copy (util.py:132 syncs)
         self.group_indicator[start:end] = self.group_index
+        self._tags_host[start:end] = self.group_index
         self.cur_sample_index = 0 if end == len(self.dataset) else end
 
-    def group_probabilities(self):
-        """(member positions, p) of the current group: p = (imp + mean(imp)) / sum(...) (util.py:144-147)."""
-        members = torch.nonzero(self.group_indicator == self.group_index).flatten()
-        imp = self.importance[members].contiguous()
-        state = torch.zeros(1, dtype=torch.float32, device=self.device)
-        stats = ops.pool_stats(imp, state, True, smooth_alpha=1.0)  # first update: ema == mean, shift == mean
-        return members, ops.normalize(imp, stats)
+    def group_size(self) -> int:
+        return int((self._tags_host == self.group_index).sum())
 
-    def draw(self, k: int = 1) -> torch.Tensor:
-        """k dataset positions from the current group in one race (k > 1: without replacement)."""
-        members, p = self.group_probabilities()
-        idx = ops.multinomial(p, k, replacement=False if k > 1 else self.replacement, generator=self.generator)
-        return members[idx]
+    def group_probabilities(self):
+        """p of the current group at the members' own positions (0 elsewhere): (imp + mean(imp)) / sum(...) (util.py:144-147)."""
+        count = self.group_size()
+        u = torch.full((count,), 0.5, dtype=torch.float64, device=self.device)
+        _, p = ops.groupwise_draw(self.importance, self.group_indicator, self.group_index, count, u, want_p=True, status=self.status)
+        return p
+
+    def draw(self, k: int = 1, ndraws: int = 1) -> torch.Tensor:
+        """Dataset positions from the current group: ``ndraws`` single draws (k == 1), or one race for k positions without
+        replacement (k > 1).  Uniforms: ``count`` per draw from the CPU generator, like torch.multinomial."""
+        count = self.group_size()
+        if count == 0:
+            raise RuntimeError("Groupwise_Sampler: the current group is empty (call update_importance first)")
+        u = torch.rand(ndraws * count, dtype=torch.float64, generator=self.generator).to(self.device, non_blocking=True)
+        return ops.groupwise_draw(self.importance, self.group_indicator, self.group_index, count, u, ndraws=ndraws, k=k,
+                                  status=self.status)
 
     def __iter__(self):
         counter = 0
-        while True:
-            for i in self.draw(1).tolist():
+        total = len(self.dataset)
+        while counter < total:
+            block = min(self.prefetch, total - counter)
+            for i in self.draw(1, block).tolist():   # one synchronisation per block of draws
                 yield i
                 counter += 1
-                if counter >= len(self.dataset):
-                    return
+        ops.check_status(self.status)
 
     def __len__(self):
         return self.num_samples

@@ -296,3 +296,40 @@ def test_peer_exchange_world1_equals_collective_path(fused):
             ops.check_status(rp["status"])
     finally:
         p.peer.close()
+
+
+@pytest.mark.parametrize("n,groups", [(192, 3), (50000, 4), (1000000, 7)])
+def test_groupwise_draw_kernel_matches_the_restated_reference(n, groups):
+    """mercury_groupwise_draw against the restatement of util.py:140-157 (oracle.groupwise_probabilities + the exponential
+    race on the compacted group): probabilities to one fp32 rounding, single draws and a without-replacement draw equal
+    index for index (ties in the race aside, which the inputs here do not produce)."""
+    from mercury_b200 import ops
+
+    g = torch.Generator().manual_seed(n)
+    imp = (torch.rand(n, generator=g) * 3 + 1e-3).float()
+    tags = torch.randint(1, groups + 1, (n,), generator=g).to(torch.int32)
+    group = 2
+    members = np.nonzero(tags.numpy() == group)[0]
+    count = len(members)
+    p_ref = orc.groupwise_probabilities(imp.numpy()[members].astype(np.float64)).numpy()
+    ndraws = 5
+    u = torch.rand(ndraws * count, dtype=torch.float64, generator=g)
+    st = ops.new_status(DEV)
+    idx, p = ops.groupwise_draw(imp.to(DEV), tags.to(DEV), group, count, u.to(DEV), ndraws=ndraws, want_p=True, status=st)
+    ops.check_status(st)
+    p = p.cpu().numpy()
+    assert np.all(p[tags.numpy() != group] == 0)
+    np.testing.assert_allclose(p[members], p_ref, rtol=2e-7)
+    for j in range(ndraws):
+        keys = orc.exp_race_keys(torch.from_numpy(p[members]), u[j * count:(j + 1) * count].numpy())
+        assert int(idx[j]) == int(members[int(torch.argmax(keys))])
+    k = 16
+    idxk = ops.groupwise_draw(imp.to(DEV), tags.to(DEV), group, count, u[:count].to(DEV), k=k, status=st)
+    ops.check_status(st)
+    keys = orc.exp_race_keys(torch.from_numpy(p[members]), u[:count].numpy())
+    want = members[torch.topk(keys, k).indices.numpy()]
+    assert np.array_equal(idxk.cpu().numpy(), want)
+    # a wrong member count is reported, not silently used
+    ops.groupwise_draw(imp.to(DEV), tags.to(DEV), group, count - 1, u.to(DEV), status=st)
+    with pytest.raises(RuntimeError, match="member count"):
+        ops.check_status(st)
