@@ -56,6 +56,9 @@ class Trainer(object):
         self._pool = None      # ResidentPool: preallocated, written in place (no torch.cat, pytorch_collab.py:108,116-117)
         self._grad_bucket = None
         self.overlap_sampling = True   # run update_samples on a side stream beside average_gradients
+        self.graph_sampling = False    # replay the fused sampling call from a CUDA graph (static pool, static uniforms)
+        self._graph = None
+        self._u_dev = None
         self._side = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" and torch.cuda.is_available() else None
 
     # ---- pool feeder (pytorch_collab.py:74-82, with next(it) for Python 3)
@@ -103,13 +106,45 @@ class Trainer(object):
                 pool.append(idx, data, label, output)
         logits, labels, datas, index = pool.tensors()
         bounds = pool.growing_bounds()
-        u = torch.rand(len(bounds) * B, dtype=torch.float64)[(len(bounds) - 1) * B:].to(self.device, non_blocking=True)
-        if self._head is not None:   # the pool holds scores
-            r = self.ops.update_samples(None, labels, u, ema_loss.state, ema_loss.first_update, ema_alpha=ema_loss.alpha,
-                                        smooth_alpha=alpha, data=datas, index=index, bounds=bounds, scores_in=logits)
+        u = torch.rand(len(bounds) * B, dtype=torch.float64)[(len(bounds) - 1) * B:]
+        if self._u_dev is None or self._u_dev.numel() != u.numel():
+            self._u_dev = torch.empty(u.numel(), dtype=torch.float64, device=self.device)
+            self._graph = None
+        self._u_dev.copy_(u, non_blocking=True)
+        u = self._u_dev
+
+        def call(first, out=None):
+            kw = {} if out is None else {"out": out}
+            if self._head is not None:   # the pool holds scores
+                return self.ops.update_samples(None, labels, u, ema_loss.state, first, ema_alpha=ema_loss.alpha, smooth_alpha=alpha,
+                                               data=datas, index=index, bounds=bounds, scores_in=logits, **kw)
+            return self.ops.update_samples(logits, labels, u, ema_loss.state, first, ema_alpha=ema_loss.alpha, smooth_alpha=alpha,
+                                           data=datas, index=index, bounds=bounds, **kw)
+
+        graphable = self.graph_sampling and self.device.type == "cuda" and not ema_loss.first_update
+        if graphable and self._graph is not None and self._graph[1] is ema_loss.state:
+            self._graph[0].replay()          # the pool, the uniforms and the EMA state are the captured tensors, refilled in place
+            r = self._graph[2]
+        elif graphable and self.last is not None:
+            # capture on the stream this call runs on (the pool tensors are static: ResidentPool writes them in place)
+            out = {k: self.last[k] for k in ("scores", "stats", "idx", "nprob", "seed", "data", "labels", "index") if self.last[k] is not None}
+            out["status"] = self.last["status"]
+            cur = torch.cuda.current_stream()
+            cap = torch.cuda.Stream(device=self.device)
+            cap.wait_stream(cur)
+            with torch.cuda.stream(cap):
+                call(False, out)             # allocates this stream's workspace outside the capture
+            cur.wait_stream(cap)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            saved = ema_loss.state.clone()
+            with torch.cuda.graph(g, stream=cap):
+                r = call(False, out)
+            ema_loss.state.copy_(saved)      # (the warm-up call above advanced the EMA once: undo, then take this step's update)
+            g.replay()
+            self._graph = (g, ema_loss.state, r)
         else:
-            r = self.ops.update_samples(logits, labels, u, ema_loss.state, ema_loss.first_update, ema_alpha=ema_loss.alpha,
-                                        smooth_alpha=alpha, data=datas, index=index, bounds=bounds)
+            r = call(ema_loss.first_update)
         ema_loss.first_update = False
         self.last = r
         return r.nprob, r.data, r.labels, r.index, r.stats[_lib.STAT_MEAN]
@@ -124,7 +159,7 @@ class Trainer(object):
             output = self.net(i_data)
             losses = F.cross_entropy(output, i_label, reduction="none")      # :133 training side, stock
             loss = reweighted_mean(losses, seed)                             # :137,:145
-            self.optimizer.zero_grad()
+            self._zero_grads()
             loss.backward()                                                  # :148
             self.should_compute_importance = True
             if self.overlap_sampling and self.device.type == "cuda":
@@ -155,18 +190,40 @@ class Trainer(object):
             self.epoch = epoch
             self.train(max_steps=max_steps)
 
+    def _setup_grad_bucket(self):
+        """One persistent flat buffer whose slices ARE the ``.grad`` tensors: the reference flattens the gradients into a
+        fresh vector, all-reduces it and unflattens it every step (pytorch_collab.py:236-249, util.py:23-63); here backward
+        writes into the bucket directly and the collective works on it in place -- no copy in, no copy out."""
+        params = [p for p in self.net.parameters() if p.requires_grad]
+        total = sum(p.numel() for p in params)
+        self._grad_bucket = torch.zeros(total, dtype=params[0].dtype, device=params[0].device)
+        off = 0
+        for p in params:
+            p.grad = self._grad_bucket[off:off + p.numel()].view_as(p)
+            off += p.numel()
+
+    def _zero_grads(self):
+        if self.world_size > 1 and self._grad_bucket is None:
+            self._setup_grad_bucket()
+        if self._grad_bucket is not None:
+            self._grad_bucket.zero_()            # (optimizer.zero_grad() would drop the views)
+        else:
+            self.optimizer.zero_grad()
+
     def average_gradients(self):
-        """pytorch_collab.py:236-249: one all-reduce of a persistent flat bucket, then divide."""
+        """pytorch_collab.py:236-249 as ONE in-place collective on the persistent bucket: ncclAllReduce(AVG) (gloo has no AVG:
+        SUM, then one division)."""
         if self.world_size == 1:
             return
-        grads = [p.grad for p in self.net.parameters() if p.grad is not None]
-        total = sum(g.numel() for g in grads)
-        if self._grad_bucket is None or self._grad_bucket.numel() != total:
-            self._grad_bucket = torch.empty(total, dtype=grads[0].dtype, device=grads[0].device)
-        torch._foreach_copy_(list(self._grad_bucket.split([g.numel() for g in grads])), [g.reshape(-1) for g in grads])
-        dist.all_reduce(self._grad_bucket, op=dist.ReduceOp.SUM)
-        self._grad_bucket /= self.world_size
-        torch._foreach_copy_([g.reshape(-1) for g in grads], list(self._grad_bucket.split([g.numel() for g in grads])))
+        if self._grad_bucket is None:           # called outside train(): adopt the existing gradients once
+            grads = [p.grad for p in self.net.parameters() if p.grad is not None]
+            self._setup_grad_bucket()
+            torch._foreach_copy_([p.grad for p in self.net.parameters() if p.requires_grad], grads)
+        if dist.get_backend() == "nccl":
+            dist.all_reduce(self._grad_bucket, op=dist.ReduceOp.AVG)
+        else:
+            dist.all_reduce(self._grad_bucket, op=dist.ReduceOp.SUM)
+            self._grad_bucket /= self.world_size
 
     def evaluate(self):
         """pytorch_collab.py:201-234 reduced to the test split: (mean loss, accuracy)."""

@@ -45,22 +45,39 @@ def load_cifar10(split_num: int = 1, n_train: int = 50000, n_test: int = 10000, 
     return train_loader, presam_loader, test_loader
 
 
+def partition_hetero(targets: np.ndarray, n_nets: int, alpha: float, rng=np.random, num_classes: int = 10, min_size_required: int = 10):
+    """The reference's Dirichlet partitioner, cifar10/data_loader.py:138-161 ("hetero"), restated: per class, shuffle its
+    indices, draw Dirichlet(alpha) proportions over the workers, zero the share of every worker that already holds its
+    N / n_nets ("Balance", :150-151), split; repeat the whole assignment until the smallest shard has at least 10 samples
+    (:144); finally shuffle every shard.  ``rng``: the module ``numpy.random`` (the reference uses the global generator it
+    seeds at pytorch_collab.py:280) or a RandomState -- same calls in the same order, so the same seed gives the same map."""
+    targets = np.asarray(targets)
+    N = targets.shape[0]
+    min_size = 0
+    idx_batch = [[] for _ in range(n_nets)]
+    while min_size < min_size_required:
+        idx_batch = [[] for _ in range(n_nets)]
+        for k in range(num_classes):
+            idx_k = np.where(targets == k)[0]
+            rng.shuffle(idx_k)
+            proportions = rng.dirichlet(np.repeat(alpha, n_nets))
+            proportions = np.array([p * (len(idx_j) < N / n_nets) for p, idx_j in zip(proportions, idx_batch)])
+            proportions = proportions / proportions.sum()
+            cuts = (np.cumsum(proportions) * len(idx_k)).astype(int)[:-1]
+            idx_batch = [idx_j + idx.tolist() for idx_j, idx in zip(idx_batch, np.split(idx_k, cuts))]
+            min_size = min(len(idx_j) for idx_j in idx_batch)
+    for j in range(n_nets):
+        rng.shuffle(idx_batch[j])
+    return {j: idx_batch[j] for j in range(n_nets)}
+
+
 def load_cifar10_noniid(split_num: int, alpha: float, n_train: int = 50000, n_test: int = 10000, seed: int = 0,
                         batch_size: int = 32):
-    """exp_dataset.py:9-20: (presam_loaders[list], train_global, test_global) with a Dirichlet(alpha)
-    class-skewed split across workers (cifar10/data_loader.py:138-161), on synthetic data."""
+    """exp_dataset.py:9-20: (presam_loaders[list], train_global, test_global) with the Dirichlet(alpha) class-skewed split
+    across workers of cifar10/data_loader.py:138-161 (``partition_hetero``), on synthetic data."""
     assert split_num > 1
     train = SyntheticCIFAR10(n_train, seed)
     test = SyntheticCIFAR10(n_test, seed + 1)
-    rng = np.random.RandomState(seed)
-    targets = train.targets.numpy()
-    shards = [[] for _ in range(split_num)]
-    for k in range(10):
-        idx_k = np.where(targets == k)[0]
-        rng.shuffle(idx_k)
-        props = rng.dirichlet(np.repeat(alpha, split_num))
-        cuts = (np.cumsum(props) * len(idx_k)).astype(int)[:-1]
-        for s, part in zip(shards, np.split(idx_k, cuts)):
-            s.extend(part.tolist())
-    presam = [DataLoader(Subset(train, s), batch_size=batch_size, shuffle=True) for s in shards]
+    shards = partition_hetero(train.targets.numpy(), split_num, alpha, np.random.RandomState(seed))
+    presam = [DataLoader(Subset(train, shards[j]), batch_size=batch_size, shuffle=True) for j in range(split_num)]
     return presam, DataLoader(train, batch_size=batch_size, shuffle=True), DataLoader(test, batch_size=batch_size)

@@ -248,9 +248,31 @@ def ref_head(seed, n=64):
                 label=label.numpy(), logits=out.numpy(), scores=scores.numpy(), seed=np.int64(seed))
 
 
+def ref_partition(seed, n=6000, n_nets=4, alpha=0.5):
+    """The reference's own Dirichlet ("hetero") partitioner, cifar10/data_loader.py:126-161, run on synthetic labels: its
+    data loader (which would download CIFAR-10) is replaced from outside, the partitioning code runs unmodified."""
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+    from cifar10 import data_loader as dl
+
+    rng = np.random.RandomState(seed)
+    y = rng.randint(0, 10, size=n).astype(np.int64)
+    dl.load_cifar10_data = lambda datadir: (np.zeros((n, 1), dtype=np.uint8), y, np.zeros((1, 1), dtype=np.uint8), y[:1])
+    np.random.seed(seed)   # (the reference seeds the global generator, pytorch_collab.py:22, 280)
+    _, _, _, _, net_map, counts = dl.partition_data("cifar10", "", "hetero", n_nets, alpha)
+    out = dict(labels=y, seed=np.int64(seed), n_nets=np.int64(n_nets), alpha=np.float64(alpha))
+    for j in range(n_nets):
+        out[f"shard{j}"] = np.asarray(net_map[j], dtype=np.int64)
+    return out
+
+
 def main():
     _install_stubs()
     torch.set_num_threads(1)
+    if len(sys.argv) > 1 and sys.argv[1] == "partition":   # only the fixture added in round 2
+        np.savez_compressed(os.path.join(HERE, "ref_partition.npz"), **ref_partition(900))
+        print("ref_partition.npz", os.path.getsize(os.path.join(HERE, "ref_partition.npz")))
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "head":   # only the fixture added after the others were committed
         np.savez_compressed(os.path.join(HERE, "ref_head.npz"), **ref_head(800))
         print("ref_head.npz", os.path.getsize(os.path.join(HERE, "ref_head.npz")))
@@ -261,6 +283,7 @@ def main():
     np.savez_compressed(os.path.join(HERE, "ref_update_samples_resnet18.npz"), **ref_update_samples("resnet18", 128, 600))
     np.savez_compressed(os.path.join(HERE, "ref_groupwise.npz"), **ref_groupwise(700))
     np.savez_compressed(os.path.join(HERE, "ref_head.npz"), **ref_head(800))
+    np.savez_compressed(os.path.join(HERE, "ref_partition.npz"), **ref_partition(900))
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))
