@@ -131,16 +131,16 @@ class Trainer(object):
             out["status"] = self.last["status"]
             cur = torch.cuda.current_stream()
             cap = torch.cuda.Stream(device=self.device)
+            saved = ema_loss.state.clone()
             cap.wait_stream(cur)
             with torch.cuda.stream(cap):
                 call(False, out)             # allocates this stream's workspace outside the capture
             cur.wait_stream(cap)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
-            saved = ema_loss.state.clone()
             with torch.cuda.graph(g, stream=cap):
                 r = call(False, out)
-            ema_loss.state.copy_(saved)      # (the warm-up call above advanced the EMA once: undo, then take this step's update)
+            ema_loss.state.copy_(saved)      # (the warm-up call above advanced the EMA: undo, then take this step's update)
             g.replay()
             self._graph = (g, ema_loss.state, r)
         else:

@@ -209,13 +209,14 @@ def test_graphed_update_equals_eager_calls():
     ops.check_status(g.status)
 
 
-def test_two_level_sharded_draw_matches_its_oracle():
-    """Mode "totals" (north-star literal): three shards emulated one after the other on one GPU --
+@pytest.mark.parametrize("G,n_local,b", [(3, 40000, 200), (8, 6250, 128)])   # (8 x 6250: BASELINE configs[3], the 50k pool over 8 workers)
+def test_two_level_sharded_draw_matches_its_oracle(G, n_local, b):
+    """Mode "totals" (north-star literal): the shards emulated one after the other on one GPU --
     the kernels are the ones ShardedPool(mode="totals") calls, the exchanges are plain concatenations."""
     from mercury_b200 import _lib, ops
 
     gen = torch.Generator().manual_seed(21)
-    G, n_local, c, b = 3, 40000, 10, 200
+    c = 10
     N = G * n_local
     logits = [(torch.randn(n_local, c, generator=gen) * 2).to(DEV) for _ in range(G)]
     labels = [torch.randint(0, c, (n_local,), generator=gen).to(DEV) for _ in range(G)]
