@@ -122,16 +122,21 @@ class Trainer(object):
                                            data=datas, index=index, bounds=bounds, **kw)
 
         graphable = self.graph_sampling and self.device.type == "cuda" and not ema_loss.first_update
-        if graphable and self._graph is not None and self._graph[1] is ema_loss.state:
-            self._graph[0].replay()          # the pool, the uniforms and the EMA state are the captured tensors, refilled in place
-            r = self._graph[2]
+        if graphable and self._graph is not None:
+            # the pool, the uniforms and the EMA slot are the captured tensors, refilled in place (the slot is the trainer's own,
+            # so the graph survives the reference's per-epoch EMAverage, pytorch_collab.py:121)
+            g, slot, r = self._graph
+            slot.copy_(ema_loss.state)
+            g.replay()
+            ema_loss.state.copy_(slot)
         elif graphable and self.last is not None:
             # capture on the stream this call runs on (the pool tensors are static: ResidentPool writes them in place)
             out = {k: self.last[k] for k in ("scores", "stats", "idx", "nprob", "seed", "data", "labels", "index") if self.last[k] is not None}
             out["status"] = self.last["status"]
             cur = torch.cuda.current_stream()
             cap = torch.cuda.Stream(device=self.device)
-            saved = ema_loss.state.clone()
+            slot = ema_loss.state.clone()
+            user_state, ema_loss.state = ema_loss.state, slot
             cap.wait_stream(cur)
             with torch.cuda.stream(cap):
                 call(False, out)             # allocates this stream's workspace outside the capture
@@ -140,9 +145,11 @@ class Trainer(object):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=cap):
                 r = call(False, out)
-            ema_loss.state.copy_(saved)      # (the warm-up call above advanced the EMA: undo, then take this step's update)
+            ema_loss.state = user_state
+            slot.copy_(user_state)           # (the warm-up call above advanced the slot: reset it, then take this step's update)
             g.replay()
-            self._graph = (g, ema_loss.state, r)
+            user_state.copy_(slot)
+            self._graph = (g, slot, r)
         else:
             r = call(ema_loss.first_update)
         ema_loss.first_update = False

@@ -57,6 +57,7 @@ def _worker(rank, world, port, n, c, b, ret):
                 ops.check_status(r["xstatus"])
             ops.check_status(r["status"])
             steps.append({k: r[k].cpu() for k in ("idx", "nprob", "seed", "data", "labels", "stats")})
+            steps[-1]["scores"] = sp.local_scores.cpu()      # this rank's shard of the scores, as K1 wrote them
         outs[x] = steps
     ret[rank] = outs
     dist.barrier()
@@ -79,7 +80,12 @@ def test_peer_exchange_two_gpus_matches_nccl_and_oracle():
             assert torch.equal(ret[0]["peer"][step][k], ret[1]["peer"][step][k]), (step, k)   # assembled on both ranks
         st = ret[0]["peer"][step]["stats"]
         assert torch.equal(st[:4], ret[1]["peer"][step]["stats"][:4]) and torch.equal(st[:4], ret[0]["nccl"][step]["stats"][:4])
-        losses = orc.score(logits + step, labels)
+        ref_losses = orc.score(logits + step, labels)
+        for x in ("peer", "peer_one_kernel"):
+            dev_scores = torch.cat([ret[0][x][step]["scores"], ret[1][x][step]["scores"]])
+            np.testing.assert_allclose(dev_scores.numpy(), ref_losses.numpy(), rtol=1e-5, atol=1e-6)
+        # (the draws are checked on the device's own scores: one ulp in a score can move a draw that sits on a CDF step)
+        losses = torch.cat([ret[0]["peer"][step]["scores"], ret[1]["peer"][step]["scores"]])
         p = ((losses.numpy() + np.float32(st[2])).astype(np.float32) / np.float32(st[3])).astype(np.float32)
         want = orc.sharded_draw_two_level([p[:n // 2], p[n // 2:]], u.numpy())
         assert np.array_equal(ret[0]["peer"][step]["idx"].numpy(), want)
@@ -88,6 +94,7 @@ def test_peer_exchange_two_gpus_matches_nccl_and_oracle():
         # the oracle on ITS OWN probabilities
         s1 = ret[0]["peer_one_kernel"][step]["stats"]
         np.testing.assert_allclose(s1[:4].numpy(), st[:4].numpy(), rtol=1e-6)
+        losses = torch.cat([ret[0]["peer_one_kernel"][step]["scores"], ret[1]["peer_one_kernel"][step]["scores"]])
         p1 = ((losses.numpy() + np.float32(s1[2])).astype(np.float32) / np.float32(s1[3])).astype(np.float32)
         want1 = orc.sharded_draw_two_level([p1[:n // 2], p1[n // 2:]], u.numpy())
         assert np.array_equal(ret[0]["peer_one_kernel"][step]["idx"].numpy(), want1)
