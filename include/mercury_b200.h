@@ -10,7 +10,23 @@
  * Conventions
  *  - every pointer is a DEVICE pointer unless its name starts with h_;
  *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*), performs no
- *    allocation, no host synchronisation and keeps no global state;
+ *    allocation, no host synchronisation and keeps no global state -- with these exceptions, each
+ *    stated again at its declaration:
+ *      * mercury_peer_create / _open / _close / _destroy are set-up calls: they allocate (cudaMalloc),
+ *        clear and synchronise the device once; the per-step calls that use the boxes do not;
+ *      * mercury_cdf_static works in a static device array shared by the process (one per device) and
+ *        caches that array's address per device under a mutex on first use;
+ *      * per device and kernel, the first launch of a kernel that needs more than 48 KB of dynamic shared
+ *        memory (or a cooperative launch) sets the function attribute / queries occupancy once and
+ *        remembers it in a mutex-protected table (host memory, no device allocation);
+ *      * process-wide knobs read ONCE from the environment at first use and then fixed: MERCURY_PDL
+ *        (0 = no programmatic dependent launch), MERCURY_K1_TILE / MERCURY_K1_CTAS (tile rows / grid of
+ *        the small-row scoring kernel; validated, bad values are ignored), MERCURY_FUSED (-1 never,
+ *        0 automatic, 1 always: the one-kernel step), MERCURY_STEP_CTAS, MERCURY_STEP_DBG and
+ *        MERCURY_SPINE_DEBUG (development), MERCURY_PEER_WAIT_MS (bound of one peer wait);
+ *      * mercury_test_set_guess_bias / mercury_test_set_fused / mercury_debug_step_times are TEST HOOKS:
+ *        process-global atomics read at launch time, there so the parity tests can force the rare paths
+ *        (mis-guessed binades, the fallback chain); a production caller never calls them;
  *  - scratch memory is supplied by the caller (`ws`, sized by the matching *_workspace_bytes);
  *    workspaces must be 256-byte aligned; a workspace may be reused by the next call on the
  *    same stream without clearing it;
@@ -150,6 +166,10 @@ int mercury_gather_reweight(const float* p, const int64_t* idx, int64_t b, int64
                             const int64_t* index, void* out_data, int64_t* out_labels,
                             int64_t* out_index, float* nprob, float* seed, void* stream);
 
+/* torch.mean(torch.div(losses, probs)) of pytorch_collab.py:137,145 as sum_j losses_j * seed_j (seed from the call above):
+ * losses, seed fp32 [b] -> out fp32 [1], summed in a fixed order. */
+int mercury_reweighted_mean(const float* losses, const float* seed, int64_t b, float* out, void* stream);
+
 /* Sharded pools (one process per GPU, pytorch_collab.py:282-287 gives each worker its own
  * presample shard): `idx` are GLOBAL pool positions, this rank owns [shard_lo, shard_lo+shard_n).
  * Rows of owned draws are gathered from the local shard, all other output rows are zero-filled
@@ -199,14 +219,24 @@ int mercury_shard_select(const float* shard_totals, int nshards, int rank, const
  * Per step: mercury_sum_scores_exchange = mercury_sum_scores + all-gather (sums_all fp64 [nshards] is
  * filled for every rank); mercury_shard_select_exchange = all-gather of the chain totals (my_total: device
  * fp32, e.g. &stats[MERCURY_STAT_CHAIN_TOTAL]; totals_all fp32 [nshards] out) + mercury_shard_select.
- * The kernels store into the peers' boxes and wait, for at most 4 s (then MERCURY_ST_PEER_TIMEOUT), for
- * the peers' stores: every rank must make the same sequence of exchange calls, each on a GPU of its own. */
+ * The kernels store into the peers' boxes and wait for the peers' stores: every rank must make the same
+ * sequence of exchange calls, each on a GPU of its own, and reach each call within the bound of one wait
+ * (4 s, or MERCURY_PEER_WAIT_MS read by mercury_peer_create, or mercury_peer_set_wait) -- a loop in which one
+ * rank does minutes of extra work between steps (the reference's rank-0 evaluation, pytorch_collab.py:181)
+ * needs a barrier in front of the next step, a larger bound, or the collective exchange instead.
+ * A wait that runs out sets MERCURY_ST_PEER_TIMEOUT, marks the box dead (later waits give up at once) and
+ * POISONS the step: local_uniforms = NaN, and the draws of that rank get idx -1 and NaN nprob / seed, which
+ * survive a SUM all-reduce.  The host must treat the status as fatal for the step; after all ranks have
+ * synchronised (barrier), mercury_peer_reset on every rank's own box (then another barrier) returns the
+ * boxes to their initial state. */
 #define MERCURY_PEER_BOX_BYTES 4096
 #define MERCURY_PEER_HANDLE_BYTES 64
 int mercury_peer_create(void** box, unsigned char* handle);
 int mercury_peer_open(const unsigned char* handle, void** peer_box);
 int mercury_peer_close(void* peer_box);
 int mercury_peer_destroy(void* box);
+int mercury_peer_set_wait(void* box, int64_t wait_ms, void* stream);   /* own box; 0 < wait_ms <= 3 600 000 */
+int mercury_peer_reset(void* box, void* stream);                       /* own box; collective, see above     */
 int mercury_sum_scores_exchange(const float* scores, int64_t n, void* const* peer_boxes, int nshards, int rank,
                                 double* sums_all, int32_t* status, void* ws, size_t ws_bytes, void* stream);
 int mercury_shard_select_exchange(const float* my_total, void* const* peer_boxes, int nshards, int rank,

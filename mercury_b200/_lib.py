@@ -69,10 +69,13 @@ SIGNATURES = {
     "mercury_shard_select": (c_int, [c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp]),
     "mercury_score_head": (c_int, [c_vp, c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "mercury_score_head_wide": (c_int, [c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),
+    "mercury_reweighted_mean": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "mercury_peer_create": (c_int, [c_vp, c_vp]),
     "mercury_peer_open": (c_int, [c_vp, c_vp]),
     "mercury_peer_close": (c_int, [c_vp]),
     "mercury_peer_destroy": (c_int, [c_vp]),
+    "mercury_peer_set_wait": (c_int, [c_vp, c_i64, c_vp]),
+    "mercury_peer_reset": (c_int, [c_vp, c_vp]),
     "mercury_sum_scores_exchange": (c_int, [c_vp, c_i64, c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "mercury_shard_select_exchange": (c_int, [c_vp, c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "mercury_update_samples_workspace_bytes": (c_sz, [c_i64, c_i64]),

@@ -17,6 +17,8 @@
 //      boundary value.
 // A wrong guess costs time, never correctness.
 #include <cooperative_groups.h>
+
+#include <atomic>
 #include <math.h>
 
 #include <cstddef>
@@ -380,7 +382,7 @@ static_assert(sizeof(Pack) == 3072 && offsetof(Pack, raw) % 16 == 0 && offsetof(
 //   kEvSlow  : (chunk level) a chunk that needs the general code
 enum EvKind : uint32_t { kEvAdd = 0, kEvMap = 1, kEvSerial = 2, kEvPack = 3, kEvSlow = 4, kEvEnd = 5, kEvNone = 6 };  // (kEvEnd / kEvNone: step_fused.cuh)
 
-double g_guess_bias = 1.0;  // test hook (mercury_test_set_guess_bias): scales every guess
+std::atomic<double> g_guess_bias{1.0};  // test hook (mercury_test_set_guess_bias): scales every guess
 
 constexpr int kSumNT = 256, kSumIPT = kChunk / kSumNT;
 static_assert(kSumIPT * 8 == kSub, "a sub-chunk is 8 consecutive threads");
@@ -400,10 +402,14 @@ struct PeerBox {
     unsigned long long sum_lo[2][kMaxShards];
     unsigned long long total[2][kMaxShards];
     unsigned int seq_sum, seq_total;      // local step counters (peers never touch them)
-    unsigned int dead;                    // set by the first timed-out wait: later waits give up at once
+    unsigned int dead;                    // set by the first timed-out wait: later waits give up at once (mercury_peer_reset clears it)
+    unsigned long long wait_ns;           // bound of one wait (mercury_peer_create: MERCURY_PEER_WAIT_MS or 4 s; mercury_peer_set_wait)
 };
 static_assert(sizeof(PeerBox) <= MERCURY_PEER_BOX_BYTES, "PeerBox must fit the size the header promises");
-constexpr unsigned long long kPeerWaitNs = 4000000000ull;
+constexpr unsigned long long kPeerWaitNs = 4000000000ull;   // default bound
+// A step that saw a timeout must not look like a result: its draws get NaN probabilities and index -1, which survive the
+// SUM all-reduce that assembles a batch, and MERCURY_ST_PEER_TIMEOUT is set for the host to raise on.
+__device__ __forceinline__ double peer_poison() { return __longlong_as_double(0x7ff8000000000000ll); }
 
 __device__ __forceinline__ void peer_store(unsigned long long* p, unsigned long long v) {
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -419,18 +425,19 @@ __device__ __forceinline__ unsigned long long global_ns() {
     return t;
 }
 // polls *p until its low half equals seq; false on timeout
-__device__ __forceinline__ bool peer_wait(const unsigned long long* p, unsigned int seq, unsigned long long& word,
-                                          volatile unsigned int* dead) {
+__device__ __forceinline__ bool peer_wait(const unsigned long long* p, unsigned int seq, unsigned long long& word, PeerBox* box) {
+    volatile unsigned int* dead = &box->dead;
     word = peer_load(p);
     if ((unsigned int)word == seq) return true;
     if (*dead) return false;
+    const unsigned long long bound = box->wait_ns ? box->wait_ns : kPeerWaitNs;
     const unsigned long long t0 = global_ns();
     for (;;) {
         for (int i = 0; i < 64; ++i) {
             word = peer_load(p);
             if ((unsigned int)word == seq) return true;
         }
-        if (global_ns() - t0 > kPeerWaitNs) {
+        if (global_ns() - t0 > bound) {
             *dead = 1u;
             return false;
         }
@@ -529,8 +536,8 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
                     peer_store(&fs.peers[g]->sum_lo[par][fs.rank], (bits << 32) | sum_tag);
                 }
                 unsigned long long hi, lo;
-                const bool ok = peer_wait(&my_box->sum_hi[par][g], sum_tag, hi, &my_box->dead) &
-                                peer_wait(&my_box->sum_lo[par][g], sum_tag, lo, &my_box->dead);
+                const bool ok = peer_wait(&my_box->sum_hi[par][g], sum_tag, hi, my_box) &
+                                peer_wait(&my_box->sum_lo[par][g], sum_tag, lo, my_box);
                 if (!ok) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
                 gs[g] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
                 if (blockIdx.x == 0) fs.gsums_out[g] = gs[g];
@@ -1495,12 +1502,15 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
     if constexpr (PEER) {
         __shared__ float sh_tot[kMaxShards];
         __shared__ double sh_u;
+        __shared__ int sh_bad;
         PeerBox* mine = a.peers[a.rank];
         const unsigned int tag = mine->seq_total;   // (set by this step's spine)
         const int g = threadIdx.x;
+        if (g == 0) sh_bad = (*a.status & MERCURY_ST_PEER_TIMEOUT) ? 1 : 0;   // (the sums of this step may have timed out already)
+        __syncthreads();
         if (g < a.nshards) {
             unsigned long long w;
-            if (!peer_wait(&mine->total[tag & 1u][g], tag, w, &mine->dead)) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
+            if (!peer_wait(&mine->total[tag & 1u][g], tag, w, mine)) { atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT); sh_bad = 1; }
             sh_tot[g] = __uint_as_float((unsigned int)(w >> 32));
             if (j == 0) a.totals_all[g] = sh_tot[g];
         }
@@ -1523,6 +1533,7 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
                 if (out < 0.0) out = 0.0;
                 if (out >= 1.0) out = 0.99999999999999989;
             }
+            if (sh_bad) out = peer_poison();
             sh_u = out;
             a.local_u[j] = out;
         }
@@ -1540,9 +1551,11 @@ __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, doubl
     int64_t& chosen = ds.chosen;
     const float total = *a.total_ptr;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (uj < 0.0) {  // sharded pools: this draw belongs to another shard -> all-zero outputs (summed across ranks later)
-        if (threadIdx.x == 0) {
-            a.idx[j] = 0; a.nprob[j] = 0.f; a.seed[j] = 0.f;
+    if (!(uj >= 0.0)) {  // sharded pools: this draw belongs to another shard -> all-zero outputs (summed across ranks later);
+        if (threadIdx.x == 0) {   // NaN: a peer exchange of this step timed out -> poisoned outputs
+            const bool bad = uj != uj;
+            const float q = bad ? __int_as_float(0x7fc00000) : 0.f;
+            a.idx[j] = bad ? -1 : 0; a.nprob[j] = q; a.seed[j] = q;
             if (a.labels && a.out_labels) a.out_labels[j] = 0;
             if (a.index && a.out_index) a.out_index[j] = 0;
         }
@@ -1800,12 +1813,12 @@ int run_exact_boundaries(const WeightSrc& src, int64_t n, const CdfWs& w, int32_
     if (fused) {
         cudaError_t e = fused->peers
             ? launch_chain(true, summarize_kernel<true, true>, dim3(nchunks), dim3(kSumNT), 0, st, src, n, (const double*)w.approx,
-                           (const int*)w.slotid, g_guess_bias, w.summaries, w.subs, status, check, *fused)
+                           (const int*)w.slotid, g_guess_bias.load(), w.summaries, w.subs, status, check, *fused)
             : launch_chain(true, summarize_kernel<true, false>, dim3(nchunks), dim3(kSumNT), 0, st, src, n, (const double*)w.approx,
-                           (const int*)w.slotid, g_guess_bias, w.summaries, w.subs, status, check, *fused);
+                           (const int*)w.slotid, g_guess_bias.load(), w.summaries, w.subs, status, check, *fused);
         if (e != cudaSuccess) return cuda_fail(e, "summarize_kernel launch");
     } else {
-        summarize_kernel<false, false><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias, w.summaries, w.subs, status,
+        summarize_kernel<false, false><<<nchunks, kSumNT, 0, st>>>(src, n, w.approx, w.slotid, g_guess_bias.load(), w.summaries, w.subs, status,
                                                             check, FusedStats{});
     }
     MB_CHECK_LAUNCH("summarize_kernel");
@@ -1861,7 +1874,7 @@ int pool_stats_launch(const float* scores, int64_t n, const int64_t* h_bounds, i
     chunk_sums_kernel<<<nchunks, 256, 0, st>>>(scores, n, w.sums, nullptr, 0);
     MB_CHECK_LAUNCH("chunk_sums_kernel");
     stats_finalize_kernel<<<1, 1024, 0, st>>>(scores, n, w.sums, nchunks, bd, ema_state, ema_first, ema_alpha, smooth_alpha,
-                                              stats, w.approx, w.slotid, g_guess_bias, kSubSlots);
+                                              stats, w.approx, w.slotid, g_guess_bias.load(), kSubSlots);
     MB_CHECK_LAUNCH("stats_finalize_kernel");
     return MERCURY_OK;
 }
@@ -1940,7 +1953,7 @@ int update_tail_launch(const mercury_update_args& a, const float* scores, const 
 
 // ---- the whole step as one cooperative kernel (step_fused.cuh).  Returns 1 when the call does not fit that kernel (the
 // caller then runs the four-kernel chain), MERCURY_OK when it was launched, a negative error otherwise.
-int g_fused_mode = -1;  // test hook (mercury_test_set_fused): -1 = environment (MERCURY_FUSED, default on), 0 = off, 1 = on
+std::atomic<int> g_fused_mode{-1};  // test hook (mercury_test_set_fused): -1 = environment (MERCURY_FUSED, default on), 0 = off, 1 = on
 
 namespace {
 std::mutex g_fused_mu;
@@ -1986,19 +1999,20 @@ int fused_launch_typed(StepArgs& sa, int64_t want_ctas, cudaStream_t st) {
 
 int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     static const int env_on = env_knob("MERCURY_FUSED", 1, 0, 1);
-    if (!(g_fused_mode < 0 ? env_on : g_fused_mode)) return 1;
+    const int fused_mode = g_fused_mode.load();
+    if (!(fused_mode < 0 ? env_on : fused_mode)) return 1;
     if (a.scores_in || a.n_bounds != 0 || a.draw_only || a.global_sums) return 1;
     if (a.peer_boxes && a.cdf_mode != MERCURY_CDF_EXACT_SERIAL_F32) return 1;
     // sharded pools: the kernel chain is the faster one (measured at 2 and 8 GPUs: 54 us against 64 us per step -- two grid-wide
     // waits for the peers inside one resident grid cost more than inside two short kernels); the one-kernel sharded step stays
     // reachable through the test hook, which keeps it under test
-    if (a.peer_boxes && g_fused_mode != 1) return 1;
+    if (a.peer_boxes && fused_mode != 1) return 1;
 
     if (a.b > kStepMaxDraws || a.row_stride != a.c) return 1;
     const int64_t elt = a.dtype == MERCURY_F32 ? 4 : 2, row_bytes = a.c * elt;
     const int nchunks = (int)((a.n + kChunk - 1) / kChunk);
     if (row_bytes > 256 || nchunks > kStepMaxChunks) return 1;
-    if (g_fused_mode < 0 && nchunks > kStepBestChunks) return 1;   // (forced on by the test hook it takes all it can)
+    if (fused_mode < 0 && nchunks > kStepBestChunks) return 1;   // (forced on by the test hook it takes all it can)
     if ((reinterpret_cast<uintptr_t>(a.logits) & 15) || (reinterpret_cast<uintptr_t>(a.labels) & 15)) return 1;
     if (walk2_slots(nchunks) < 4) return 1;
     const CdfWs w = carve(ws, a.n, true);
@@ -2006,7 +2020,7 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     sa.logits = a.logits; sa.labels = a.labels; sa.n = a.n; sa.c = (int)a.c; sa.tile_rows = small_tile_rows(row_bytes);
     sa.ignore_index = a.ignore_index; sa.scores = a.scores; sa.part = w.sums;
     sa.ema_state = a.ema_state; sa.ema_first = a.ema_first; sa.ema_alpha = a.ema_alpha; sa.smooth_alpha = a.smooth_alpha; sa.stats = a.stats;
-    sa.nchunks = nchunks; sa.bias = g_guess_bias; sa.sums = w.summaries; sa.packs = reinterpret_cast<Pack2*>(w.subs);
+    sa.nchunks = nchunks; sa.bias = g_guess_bias.load(); sa.sums = w.summaries; sa.packs = reinterpret_cast<Pack2*>(w.subs);
     sa.start_bits = w.start_bits; sa.total = w.total; sa.ctrl = w.ctrl; sa.status = a.status;
     sa.cdf_mode = a.cdf_mode; sa.approx = w.approx;
     if (a.peer_boxes) {
@@ -2110,7 +2124,7 @@ int cdf_run(const char* who, const float* weights, int64_t n, int mode, float* c
     const int nchunks = (int)((n + kChunk - 1) / kChunk);
     chunk_sums_kernel<<<nchunks, 256, 0, st>>>(weights, n, w.sums, status, 1);
     MB_CHECK_LAUNCH("chunk_sums_kernel");
-    prefix_finalize_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, w.approx, w.slotid, g_guess_bias, slots);
+    prefix_finalize_kernel<<<1, 1024, 0, st>>>(w.sums, nchunks, w.approx, w.slotid, g_guess_bias.load(), slots);
     MB_CHECK_LAUNCH("prefix_finalize_kernel");
     if (mode == MERCURY_CDF_F64) {
         materialize_f64_kernel<<<nchunks, 256, 0, st>>>(weights, n, w.approx, nchunks, cdf, total, status);
@@ -2207,7 +2221,7 @@ __global__ void __launch_bounds__(1024) sum_exchange_kernel(const double* __rest
         peer_store(&peers[g]->sum_hi[par][rank], (bits >> 32 << 32) | seq);
         peer_store(&peers[g]->sum_lo[par][rank], (bits << 32) | seq);
         unsigned long long hi, lo;
-        const bool ok = peer_wait(&mine->sum_hi[par][g], seq, hi, &mine->dead) & peer_wait(&mine->sum_lo[par][g], seq, lo, &mine->dead);
+        const bool ok = peer_wait(&mine->sum_hi[par][g], seq, hi, mine) & peer_wait(&mine->sum_lo[par][g], seq, lo, mine);
         if (!ok) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
         sums_all[g] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
     }
@@ -2230,11 +2244,12 @@ __global__ void __launch_bounds__(256) select_exchange_kernel(const float* __res
     if (g < nshards) {
         peer_store(&peers[g]->total[par][rank], ((unsigned long long)__float_as_uint(*my_total) << 32) | seq);
         unsigned long long w;
-        if (!peer_wait(&mine->total[par][g], seq, w, &mine->dead)) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
+        if (!peer_wait(&mine->total[par][g], seq, w, mine)) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
         tot[g] = __uint_as_float((unsigned int)(w >> 32));
         totals_all[g] = tot[g];
     }
     __syncthreads();
+    const bool bad = (*reinterpret_cast<volatile int32_t*>(status) & MERCURY_ST_PEER_TIMEOUT) != 0;
     if (threadIdx.x == 0) {
         float s = 0.f;
         for (int k = 0; k < nshards; ++k) { s = __fadd_rn(s, tot[k]); cdf[k] = s; }
@@ -2252,11 +2267,40 @@ __global__ void __launch_bounds__(256) select_exchange_kernel(const float* __res
             if (out < 0.0) out = 0.0;
             if (out >= 1.0) out = 0.99999999999999989;
         }
-        local_u[j] = out;
+        local_u[j] = bad ? peer_poison() : out;
     }
 }
 }  // namespace
 }  // namespace mercury
+
+namespace mercury {
+namespace {
+// wait_ns > 0: set the bound; reset: back to the state mercury_peer_create leaves (words, step counters and `dead` cleared)
+__global__ void peer_config_kernel(PeerBox* box, unsigned long long wait_ns, int reset) {
+    if (reset) {
+        unsigned long long* w = reinterpret_cast<unsigned long long*>(box);
+        for (int i = threadIdx.x; i < (int)(offsetof(PeerBox, wait_ns) / 8); i += blockDim.x) w[i] = 0ull;
+    }
+    if (threadIdx.x == 0 && wait_ns) box->wait_ns = wait_ns;
+}
+static_assert(offsetof(PeerBox, wait_ns) % 8 == 0, "the words in front of wait_ns are cleared 8 bytes at a time");
+}  // namespace
+}  // namespace mercury
+
+extern "C" int mercury_peer_set_wait(void* box, int64_t wait_ms, void* stream) {
+    MB_CHECK_ARG(box && wait_ms > 0 && wait_ms <= 3600000, "mercury_peer_set_wait: box must be set and 0 < wait_ms <= 3 600 000");
+    mercury::peer_config_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(static_cast<mercury::PeerBox*>(box),
+                                                                    (unsigned long long)wait_ms * 1000000ull, 0);
+    MB_CHECK_LAUNCH("peer_config_kernel");
+    return MERCURY_OK;
+}
+
+extern "C" int mercury_peer_reset(void* box, void* stream) {
+    MB_CHECK_ARG(box, "mercury_peer_reset: null pointer");
+    mercury::peer_config_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(static_cast<mercury::PeerBox*>(box), 0ull, 1);
+    MB_CHECK_LAUNCH("peer_config_kernel");
+    return MERCURY_OK;
+}
 
 namespace mercury {
 // the whole sharded step behind mercury_update_samples (args.peer_boxes set): one PDL chain

@@ -69,10 +69,32 @@ __global__ void __launch_bounds__(kGatherNT) gather_owned_kernel(const int64_t* 
     }
 }
 
+// mean_j(loss_j / (N p_j)) = sum_j loss_j * seed_j: one CTA, pairwise tree in a fixed order (same bits run to run)
+__global__ void __launch_bounds__(256) reweighted_mean_kernel(const float* __restrict__ losses, const float* __restrict__ seed, int64_t b,
+                                                              float* __restrict__ out) {
+    __shared__ float red[256];
+    float acc = 0.f;
+    for (int64_t j = threadIdx.x; j < b; j += 256) acc = __fmaf_rn(losses[j], seed[j], acc);
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) red[threadIdx.x] = __fadd_rn(red[threadIdx.x], red[threadIdx.x + s]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = red[0];
+}
+
 }  // namespace
 }  // namespace mercury
 
 using namespace mercury;
+
+extern "C" int mercury_reweighted_mean(const float* losses, const float* seed, int64_t b, float* out, void* stream) {
+    MB_CHECK_ARG(b >= 0 && out && (b == 0 || (losses && seed)), "mercury_reweighted_mean: null pointer or negative b");
+    reweighted_mean_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(losses, seed, b, out);
+    MB_CHECK_LAUNCH("reweighted_mean_kernel");
+    return MERCURY_OK;
+}
 
 extern "C" int mercury_gather_owned(const int64_t* idx, int64_t b, int64_t shard_lo, int64_t shard_n, const void* data,
                                     int64_t row_bytes, const int64_t* labels, const int64_t* index, void* out_data,

@@ -19,6 +19,8 @@ extern "C" int mercury_peer_create(void** box, unsigned char* handle) {
     void* p = nullptr;
     MB_CHECK_CUDA(cudaMalloc(&p, MERCURY_PEER_BOX_BYTES));
     cudaError_t e = cudaMemset(p, 0, MERCURY_PEER_BOX_BYTES);
+    if (e == cudaSuccess && mercury_peer_set_wait(p, ::mercury::env_knob("MERCURY_PEER_WAIT_MS", 4000, 1, 3600000), nullptr) != MERCURY_OK)
+        e = cudaErrorUnknown;
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     cudaIpcMemHandle_t h;
     if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);

@@ -1040,7 +1040,7 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
         if (tid < a.nshards) {
             peer_store(&a.peers[tid]->total[tag & 1u][a.rank], ((unsigned long long)sb[nchunks] << 32) | tag);
             unsigned long long w;
-            if (!peer_wait(&mine->total[tag & 1u][tid], tag, w, &mine->dead)) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
+            if (!peer_wait(&mine->total[tag & 1u][tid], tag, w, mine)) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
             sh_cdf[tid] = __uint_as_float((unsigned int)(w >> 32));
             a.totals_all[tid] = sh_cdf[tid];
         }
@@ -1056,6 +1056,7 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
     }
     // ---- the chunk of every draw: first chunk whose last cdf value is not below u (ATen's lower bound), then publish
     const float total = b2f(sb[nchunks]);
+    const bool poisoned = a.peers && (*reinterpret_cast<volatile int32_t*>(a.status) & MERCURY_ST_PEER_TIMEOUT) != 0;
     for (int64_t j = tid; j < a.d.b; j += kStepNT) {
         double uj = a.d.u[j];
         if (a.peers) {   // which shard the uniform falls in, and where inside that shard's own CDF (-1: another rank's draw)
@@ -1068,6 +1069,13 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
                 lu = hi_c > lo_c ? (uj - lo_c) / (hi_c - lo_c) : 0.0;
                 if (lu < 0.0) lu = 0.0;
                 if (lu >= 1.0) lu = 0.99999999999999989;
+            }
+            if (poisoned) {   // a peer exchange of this step timed out (see peer_poison)
+                a.local_u[j] = peer_poison();
+                __threadfence();
+                st_relaxed_u64(&a.ctrl->dinfo[j], 1ull << 63);
+                st_relaxed_u64(&a.ctrl->dinfo2[j], (1ull << 63) | f2b(total));
+                continue;
             }
             a.local_u[j] = lu;
             if (lu < 0.0) {
@@ -1225,8 +1233,8 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
                 peer_store(&a.peers[tid]->sum_lo[par][a.rank], (bits << 32) | sum_tag);
             }
             unsigned long long hi, lo;
-            const bool ok = peer_wait(&my_box->sum_hi[par][tid], sum_tag, hi, &my_box->dead) &
-                            peer_wait(&my_box->sum_lo[par][tid], sum_tag, lo, &my_box->dead);
+            const bool ok = peer_wait(&my_box->sum_hi[par][tid], sum_tag, hi, my_box) &
+                            peer_wait(&my_box->sum_lo[par][tid], sum_tag, lo, my_box);
             if (!ok) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
             gs[tid] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
             if (blockIdx.x == 0) a.sums_all[tid] = gs[tid];

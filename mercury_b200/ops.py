@@ -70,7 +70,7 @@ def check_status(status: torch.Tensor) -> None:
     if bits & _lib.ST_ZERO_SUM:
         raise RuntimeError("invalid multinomial distribution (sum of probabilities <= 0)")
     if bits & _lib.ST_PEER_TIMEOUT:
-        raise RuntimeError("mercury_b200: a peer's exchange word did not arrive within 4 s (ranks out of step?)")
+        raise RuntimeError("mercury_b200: a peer's exchange word did not arrive within the bound (ranks out of step? the step's outputs are poisoned)")
     if bits & _lib.ST_INTERNAL:
         raise RuntimeError("mercury_b200: a wait inside the one-kernel step hit its 2 s bound (internal error)")
     if bits & _lib.ST_GROUP_COUNT:
@@ -344,6 +344,18 @@ def gather_reweight(p: torch.Tensor, idx: torch.Tensor, data: Optional[torch.Ten
                                                    _ptr(index), _ptr(out_data), _ptr(out_labels), _ptr(out_index),
                                                    nprob.data_ptr(), seed.data_ptr(), _stream()))
     return nprob, seed, out_data, out_labels, out_index
+
+
+def reweighted_mean(losses: torch.Tensor, seed: torch.Tensor) -> torch.Tensor:
+    """sum_j losses_j * seed_j = mean(losses / (N p)) (pytorch_collab.py:137,145), 0-dim fp32."""
+    _cuda(losses, "losses", torch.float32)
+    _cuda(seed, "seed", torch.float32)
+    if losses.numel() != seed.numel():
+        raise ValueError("losses and seed must have the same number of elements")
+    out = torch.empty(1, dtype=torch.float32, device=losses.device)
+    _lib.check(_lib.load().mercury_reweighted_mean(losses.contiguous().data_ptr(), seed.contiguous().data_ptr(), losses.numel(),
+                                                   out.data_ptr(), _stream()))
+    return out[0]
 
 
 def gather_owned(idx: torch.Tensor, shard_lo: int, shard_n: int, data: Optional[torch.Tensor] = None,

@@ -139,6 +139,21 @@ class PeerExchange:
                 raise err
         self.boxes = torch.tensor(ptrs, dtype=torch.int64, device=device)
 
+    def set_wait(self, wait_ms: int):
+        """Bound of one wait for a peer's word (default 4 s, or MERCURY_PEER_WAIT_MS at creation)."""
+        _lib.check(self._lib.mercury_peer_set_wait(self._box, int(wait_ms), torch.cuda.current_stream().cuda_stream))
+
+    def reset(self, group=None):
+        """Collective: after a MERCURY_ST_PEER_TIMEOUT, bring every rank's box back to its initial state (all ranks call
+        this; barrier - clear - barrier, so no rank's new words meet a peer's clearing)."""
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier(group=group)
+        _lib.check(self._lib.mercury_peer_reset(self._box, torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier(group=group)
+
     def close(self):
         for p in self._opened:
             self._lib.mercury_peer_close(p)
@@ -196,6 +211,10 @@ class ShardedPool:
             self.peer = PeerExchange(self.device, group) if exchange == "peer" else None
             self._xstatus = torch.zeros(1, dtype=torch.int32, device=self.device) if self.peer else None
         self.exchange = exchange if mode == "totals" else "nccl"
+        # exchange="peer": the status word of every step is copied to pinned host memory behind the step; the NEXT call (or
+        # check()) raises if a peer's word timed out -- a timed-out step is poisoned on the device (NaN nprob / seed, idx -1)
+        self._host_status = torch.zeros(1, dtype=torch.int32).pin_memory() if self.peer is not None and self.device.type == "cuda" else None
+        self._status_event = None
         self.fused = fused     # exchange="peer": the whole step as one C call / PDL chain (False: one call per stage)
 
     @property
@@ -260,6 +279,22 @@ class ShardedPool:
         return dict(idx=r.idx, nprob=r.nprob, seed=r.seed, stats=r.stats, status=r.status, data=r.data, labels=r.labels,
                     index=r.index, owned=self.local_u >= 0, scores=self.local_scores, xstatus=r.status)
 
+    def check(self, wait: bool = True):
+        """exchange="peer": raises if the last step's exchange timed out (``wait=False``: only if that step has finished --
+        what update_samples does on entry, so a poisoned run stops at the next step instead of training on).  After the
+        ranks have synchronised, ``pool.peer.reset()`` on every rank makes the exchange usable again."""
+        ev = self._status_event
+        if ev is None:
+            return
+        if wait:
+            ev.synchronize()
+        elif not ev.query():
+            return
+        self._status_event = None
+        if int(self._host_status[0]) & _lib.ST_PEER_TIMEOUT:
+            raise RuntimeError("mercury_b200: a peer's exchange word did not arrive within the bound (ranks more than the "
+                               "wait apart? PeerExchange.set_wait / MERCURY_PEER_WAIT_MS; recover with peer.reset() on all ranks)")
+
     def _all_gather_scores(self):
         if self.world == 1:
             return
@@ -275,7 +310,13 @@ class ShardedPool:
         positions), ``nprob``, ``seed``, ``stats``, ``status`` and this rank's ``data`` / ``labels`` /
         ``index`` rows (zero where another rank owns the draw) plus the ``owned`` mask."""
         if self.mode == "totals":
-            return self._update_totals(logits_local, labels_local, uniforms, data, index, assemble)
+            self.check(wait=False)
+            r = self._update_totals(logits_local, labels_local, uniforms, data, index, assemble)
+            if self._host_status is not None and r["xstatus"] is not None:
+                self._host_status.copy_(r["xstatus"], non_blocking=True)
+                self._status_event = torch.cuda.Event()
+                self._status_event.record()
+            return r
         b = self.backend
         b.score(logits_local, labels_local, self.local_scores)
         self._all_gather_scores()

@@ -179,3 +179,39 @@ def test_gradient_bucket_average_over_nccl_matches_the_reference_procedure():
     ret = mp.Manager().dict()
     mp.spawn(_grad_worker, args=(2, _free_port(), ret), nprocs=2, join=True)
     assert all(ret[0]) and all(ret[1])
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_one_process_two_devices_cdf_and_static_cdf():
+    """One process, cuda:0 then cuda:1: the >48 KB shared-memory opt-in of the spine and the static scratch address are
+    per-device state -- mercury_cdf, mercury_cdf_static and the whole step must work on the second device as on the first."""
+    from mercury_b200 import _lib, ops
+
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(9)
+    w_cpu = torch.rand(300_000, generator=g) + 0.01
+    chain = np.cumsum(w_cpu.numpy(), dtype=np.float32)
+    want = (chain / chain[-1]).astype(np.float32)
+    logits = torch.randn(100_000, 10, generator=g) * 2
+    labels = torch.randint(0, 10, (100_000,), generator=g)
+    u = torch.rand(64, dtype=torch.float64, generator=g)
+    results = []
+    for d in (0, 1):
+        dev = torch.device("cuda", d)
+        with torch.cuda.device(dev):
+            w = w_cpu.to(dev)
+            cdf, total = ops.cdf(w, "exact")
+            assert np.array_equal(cdf.cpu().numpy().view(np.uint32), want.view(np.uint32)), d
+            out, tot, status = torch.empty_like(w), torch.empty(1, device=dev), torch.zeros(1, dtype=torch.int32, device=dev)
+            rc = lib.mercury_cdf_static(w.data_ptr(), w.numel(), 0, out.data_ptr(), tot.data_ptr(), status.data_ptr(),
+                                        torch.cuda.current_stream().cuda_stream)
+            assert rc == 0, lib.mercury_last_error()
+            torch.cuda.synchronize()
+            assert np.array_equal(out.cpu().numpy().view(np.uint32), want.view(np.uint32)), d
+            for fused in (-1, 1):
+                ops.set_fused(fused)
+                r = ops.update_samples(logits.to(dev), labels.to(dev), u.to(dev), torch.zeros(1, device=dev), True)
+                ops.check_status(r.status)
+                results.append(r.idx.cpu())
+            ops.set_fused(-1)
+    assert all(torch.equal(results[0], x) for x in results[1:])

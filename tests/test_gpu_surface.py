@@ -299,6 +299,51 @@ def test_peer_exchange_world1_equals_collective_path(fused):
         p.peer.close()
 
 
+@pytest.mark.parametrize("path", ["staged", "chain", "one_kernel"])
+def test_peer_timeout_poisons_the_step_and_raises_then_reset_recovers(path):
+    """A peer that never shows up (a second, silent box on the same GPU stands in for rank 1 of 2): the wait gives up after
+    the configured bound, the step's outputs are poisoned (idx -1, NaN nprob/seed -- they would survive the assembling SUM
+    all-reduce), the next call raises, and after peer.reset() the exchange works again."""
+    from mercury_b200 import _lib, ops
+    from mercury_b200.sharded import PeerExchange, ShardedPool
+
+    gen = torch.Generator().manual_seed(34)
+    n, c, b = 30000, 10, 64
+    u = torch.rand(b, dtype=torch.float64, generator=gen).to(DEV)
+    logits = (torch.randn(n, c, generator=gen) * 2).to(DEV)
+    labels = torch.randint(0, c, (n,), generator=gen).to(DEV)
+    a = ShardedPool(n, DEV, mode="totals", exchange="nccl")
+    p = ShardedPool(n, DEV, mode="totals", exchange="peer", fused=path != "staged")
+    silent = PeerExchange(DEV)
+    ops.set_fused(1 if path == "one_kernel" else -1)
+    try:
+        good = (p.peer.boxes, p.sums_all, p.totals_all)
+        p.peer.set_wait(40)
+        p.peer.boxes = torch.tensor([p.peer._box, silent._box], dtype=torch.int64, device=DEV)
+        p.sums_all, p.totals_all = torch.zeros(2, dtype=torch.float64, device=DEV), torch.zeros(2, device=DEV)
+        r = p.update_samples(logits, labels, u)
+        torch.cuda.synchronize()
+        assert int(r["xstatus"].item()) & _lib.ST_PEER_TIMEOUT
+        assert bool((r["idx"] == -1).all()) and bool(torch.isnan(r["nprob"]).all()) and bool(torch.isnan(r["seed"]).all())
+        with pytest.raises(RuntimeError, match="did not arrive"):
+            p.update_samples(logits, labels, u)          # (the check on entry sees the finished, timed-out step)
+        p.peer.boxes, p.sums_all, p.totals_all = good
+        p.peer.reset()
+        r["xstatus"].zero_()
+        r["status"].zero_()
+        p.ema_first = True
+        ra, rp = a.update_samples(logits, labels, u), p.update_samples(logits, labels, u)
+        p.check()
+        assert torch.equal(ra["idx"], rp["idx"])
+        if path != "one_kernel":
+            assert torch.equal(ra["nprob"], rp["nprob"])
+        ops.check_status(rp["status"])
+    finally:
+        ops.set_fused(-1)
+        silent.close()
+        p.peer.close()
+
+
 @pytest.mark.parametrize("n,groups", [(192, 3), (50000, 4), (1000000, 7)])
 def test_groupwise_draw_kernel_matches_the_restated_reference(n, groups):
     """mercury_groupwise_draw against the restatement of util.py:140-157 (oracle.groupwise_probabilities + the exponential
