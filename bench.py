@@ -30,6 +30,9 @@ WORKLOADS = {
                  note="BASELINE configs[4] row shape (32k-class bf16), 128k-candidate resident slice per GPU"),
     "cfg5shard": dict(n=1 << 21, c=32768, dtype="bf16", b=256, payload=None,
                       note="BASELINE configs[4] at full size: one GPU's shard of the 2^24 x 32768 bf16 pool split 8 ways (137 GB resident)"),
+    "cfg5full": dict(n=None, c=32768, dtype="bf16", b=256, payload=None,
+                     note="BASELINE configs[4] whole: the 2^24 x 32768 bf16 pool (1.1 TB) split over the ranks (--gpus >= 2); a shard "
+                          "that does not fit in HBM (2 / 4 GPUs: 550 / 275 GB) streams from pinned host memory through pool.ChunkRing"),
 }
 FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md
 
@@ -286,11 +289,11 @@ EXCHANGE_NOTE = {
 }
 
 
-def timed_steps(step, npools, steps, warmup, use_graph, barrier, dist=None, dev=None):
+def timed_steps(step, npools, steps, warmup, use_graph, barrier, dist=None, dev=None, min_warm=3):
     """W warm-up steps, then EXACTLY `steps` timed steps between two barriers, CUDA events on the launching stream, max
     over ranks.  With graphs: one graph holding one step per pool, replayed steps // npools times, plus a graph with the
     remaining steps % npools steps.  Returns (ms per step, replay callable for extra untimed steps)."""
-    for i in range(max(3, warmup)):
+    for i in range(max(min_warm, warmup)):
         step(i)
     barrier()
     full = rest = None
@@ -329,7 +332,8 @@ def timed_steps(step, npools, steps, warmup, use_graph, barrier, dist=None, dev=
                 for i in range(nsteps % npools):
                     step(i)
 
-    run(max(npools, (max(3, warmup) // npools + 1) * npools))   # warm-up through the same path as the timed steps
+    if min_warm >= 3:
+        run(max(npools, (max(3, warmup) // npools + 1) * npools))   # warm-up through the same path as the timed steps
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -551,7 +555,7 @@ def main_single(args, wl, dev):
     print(json.dumps(line))
 
 
-def parity_check(ops, sp, pools, payload, index, u, n, world, rank, dist, dev, mode):
+def parity_check(ops, sp, do_step, u, n, world, rank, dist, dev, mode):
     """Before the timed region: this step's draw against the oracle, on the job's own scores.  Every rank's shard of
     scores is gathered once; rank 0 recomputes the draw on the CPU (oracle.sharded_draw_two_level for the totals mode,
     the flat serial-fp32 draw for the scores mode) and compares the indices, which the ranks assemble by a SUM
@@ -560,9 +564,7 @@ def parity_check(ops, sp, pools, payload, index, u, n, world, rank, dist, dev, m
 
     from oracle import mercury_oracle as orc
 
-    lg, lb = pools[0]
-    out = {}
-    r = sp.update_samples(lg, lb, u, data=payload, index=index, out=out)
+    r = do_step(0)
     torch.cuda.synchronize()
     idx = r["idx"].clone()
     if mode == "totals":
@@ -579,7 +581,7 @@ def parity_check(ops, sp, pools, payload, index, u, n, world, rank, dist, dev, m
             want = orc.draw_with_replacement(np.concatenate(sh), u.cpu().numpy())
         ok = bool(np.array_equal(idx.cpu().numpy(), want))
     return {"mode": "two-level (oracle.sharded_draw_two_level)" if mode == "totals" else "flat (serial fp32 chain over the gathered scores)",
-            "idx_equal": ok, "ranks": world, "draws": int(u.numel())}
+            "idx_equal": ok, "ranks": world, "draws": int(u.numel())}, idx
 
 
 def main_multi(args, wl, dev, world, rank):
@@ -591,14 +593,15 @@ def main_multi(args, wl, dev, world, rank):
 
     n, c, b = wl["n"], wl["c"], wl["b"]
     s = 4 if wl["dtype"] == "f32" else 2
-    npools = auto_pools(wl, args.pools)
+    pool_bytes = n * (c * s + 8)
+    streamed = pool_bytes > (150 << 30)          # the shard does not fit beside its scores: stream it through the chunk ring
+    npools = 1 if streamed else auto_pools(wl, args.pools)
     row_bytes = 0
     payload = None
     if wl["payload"]:
         payload = torch.rand((n,) + wl["payload"], device=dev, generator=torch.Generator(device=dev).manual_seed(2))
         row_bytes = payload[0].numel() * 4
     index = torch.arange(n, device=dev) + rank * n
-    pools = [make_pool(wl, dev, seed=100 * rank + i) for i in range(npools)]
     u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(3)).to(dev)
     out = {}
     exchange = args.exchange if args.shard_mode == "totals" else "nccl"
@@ -621,29 +624,89 @@ def main_multi(args, wl, dev, world, rank):
         dist.barrier()
         torch.cuda.synchronize()
 
-    def step(i):
-        lg, lb = pools[i % npools]
-        return sp.update_samples(lg, lb, u, data=payload, index=index, out=out)
+    stream_note = None
+    if streamed:
+        from mercury_b200.pool import ChunkRing
 
-    pc = parity_check(ops, sp, pools, payload, index, u, n, world, rank, dist, dev, args.shard_mode)
-    use_graph = args.graph and os.environ.get("MERCURY_BENCH_GRAPH_NCCL", "1") == "1"
+        win = 1 << 14                                 # 1 GiB of bf16 logits per window
+        ring = ChunkRing(win, c, dtype=torch.bfloat16 if s == 2 else torch.float32, device=dev, depth=3)
+        wlg, wlb = make_pool(dict(wl, n=win), dev, seed=100 * rank)
+        h_logits, h_labels = torch.empty(wlg.shape, dtype=wlg.dtype).pin_memory(), torch.empty(wlb.shape, dtype=wlb.dtype).pin_memory()
+        h_logits.copy_(wlg)
+        h_labels.copy_(wlb)
+        del wlg, wlb
+        labels_dev = torch.empty(n, dtype=torch.int64, device=dev)
+        nwin = n // win
+        stream_note = (f"shard of {pool_bytes >> 30} GiB streamed every step from pinned host memory through a ring of 3 x {win}-row windows "
+                       f"({nwin} windows per step; the synthetic host window is reused, the copies are real): the step is bound by the "
+                       f"host link, not by HBM")
+
+        def step(i, assemble=False):
+            ring.score(((h_logits, h_labels) for _ in range(nwin)), sp.local_scores, labels_dev)
+            return sp.update_samples(None, labels_dev, u, data=None, index=index, assemble=assemble)
+    else:
+        pools = [make_pool(wl, dev, seed=100 * rank + i) for i in range(npools)]
+
+        def step(i, assemble=False):
+            lg, lb = pools[i % npools]
+            return sp.update_samples(lg, lb, u, data=payload, index=index, out=out, assemble=assemble)
+
+    pc, _ = parity_check(ops, sp, step, u, n, world, rank, dist, dev, args.shard_mode)
+    use_graph = args.graph and not streamed and os.environ.get("MERCURY_BENCH_GRAPH_NCCL", "1") == "1"
+    min_warm = 1 if streamed else 3
     with ClockSampler(dev.index or 0) as clocks:
-        ms, run = timed_steps(step, npools, args.steps, args.warmup, use_graph, barrier, dist, dev)
-        extra = max(npools, min(20000, int(600.0 / max(ms, 1e-3))))   # (the SAME number of steps on every rank)
-        run(extra)
+        ms, run = timed_steps(step, npools, args.steps, args.warmup, use_graph, barrier, dist, dev, min_warm=min_warm)
+        if not streamed:
+            extra = max(npools, min(20000, int(600.0 / max(ms, 1e-3))))   # (the SAME number of steps on every rank)
+            run(extra)
         torch.cuda.synchronize()
     r = step(0)
     torch.cuda.synchronize()
     ops.check_status(r["status"])
     if r.get("xstatus") is not None:
         ops.check_status(r["xstatus"])
+    # ---- the same step with the batch ASSEMBLED on every rank: one all-reduce over the step's output arena
+    assembled = None
+    if args.shard_mode == "totals":
+        ms_a, _ = timed_steps(lambda i: step(i, True), npools, args.steps, args.warmup, use_graph, barrier, dist, dev, min_warm=min_warm)
+        ra = step(0, True)
+        torch.cuda.synchronize()
+        hi_, lo_ = ra["idx"].clone(), ra["idx"].clone()
+        dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo_, op=dist.ReduceOp.MIN)
+        mine = (ra["idx"] >= sp.lo) & (ra["idx"] < sp.lo + n)
+        same = bool(torch.equal(hi_, lo_)) and bool(torch.equal(mine, ra["owned"]))   # one batch everywhere; each draw has one owner
+        rows_ok = bool(torch.equal(ra["index"][mine], index[ra["idx"][mine] - sp.lo]))
+        if payload is not None:
+            rows_ok = rows_ok and bool(torch.equal(ra["data"][mine], payload[ra["idx"][mine] - sp.lo]))
+        t = torch.tensor([int(same and rows_ok)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        assembled = {"ms_per_step": ms_a, "value": n * world / (ms_a * 1e-3), "unit": "candidates/s",
+                     "collective": "ONE all-reduce (SUM over the raw 32-bit words) of the step's output arena: idx, nprob, seed, labels, index "
+                                   "and the payload rows in one buffer -- every row is zero on all ranks but its owner",
+                     "arena_bytes_per_rank": int(sp._arena.numel()) if sp._arena is not None else None,
+                     "batch_equal_on_all_ranks_and_to_the_owners_rows": bool(int(t))}
     peak, peak_src = peak_hbm()
     step_bytes = algorithmic_bytes(n, c, s, b, row_bytes)
     # ---- end to end with host buffers: every rank copies its shard's logits, labels and the uniforms in, results out
-    pool_bytes = n * (c * s + 8)
     e2e_rows = n if pool_bytes <= (8 << 30) else 1 << 16
     e2e = None
-    if e2e_rows == n:
+    if streamed:
+        # the timed step above already starts from host memory; here the results are read back as well
+        h_idx, h_np = torch.empty(b, dtype=torch.int64).pin_memory(), torch.empty(b, dtype=torch.float32).pin_memory()
+        barrier()
+        t0 = time.perf_counter()
+        rr = step(0)
+        h_idx.copy_(rr["idx"], non_blocking=True)
+        h_np.copy_(rr["nprob"], non_blocking=True)
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([e2e_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t)
+        e2e = {"value": n * world / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": world * pool_bytes,
+               "d2h_bytes_per_step": world * b * 12, "ms_per_step": e2e_ms, "steps": 1, "rows_per_step": n * world}
+    elif e2e_rows == n:
         lg0, lb0 = pools[0]
         h_logits = torch.empty(lg0.shape, dtype=lg0.dtype).pin_memory()
         h_labels = torch.empty(lb0.shape, dtype=lb0.dtype).pin_memory()
@@ -696,8 +759,10 @@ def main_multi(args, wl, dev, world, rank):
                          "frac": step_bytes / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "ms_per_launch": ms,
                          "algorithmic_bytes_per_launch": step_bytes},
             "parity_check": pc,
+            "assembled": assembled,
+            "streamed": stream_note,
             "e2e": e2e,
-            "gpu_launches": step_launches(ops, wl, world, exchange, args.shard_mode) * world * args.steps,
+            "gpu_launches": (step_launches(ops, wl, world, exchange, args.shard_mode) + (n // (1 << 14) if streamed else 0)) * world * args.steps,
             "clocks": clocks.summary(),
         }
         print(json.dumps(line))
@@ -733,6 +798,11 @@ def main():
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="launch every step eagerly (no CUDA graph)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
+    if wl["n"] is None:      # cfg5full: the 2^24 pool divided over the ranks
+        w = int(os.environ.get("WORLD_SIZE", "1"))
+        if w < 2 or (1 << 24) % w:
+            raise SystemExit("cfg5full is the multi-GPU configuration: launch it under torchrun with 2, 4 or 8 ranks")
+        wl["n"] = (1 << 24) // w
 
     if args.impl == "reference":
         run_reference(args, wl)

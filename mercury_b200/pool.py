@@ -71,3 +71,64 @@ class ResidentPool:
         if not self.bounds or (len(self.bounds) > 1 and self.bounds[-1] == self.bounds[-2]):
             return None
         return list(self.bounds)
+
+
+class ChunkRing:
+    """Scores a shard whose logits do not fit in HBM (the 2^24 x 32768 bf16 pool is 1.1 TB; at 2 / 4 GPUs a shard
+    is 550 / 275 GB): the logits stream through a ring of ``depth`` resident windows -- host -> device copies on a copy
+    stream, K1 on the caller's stream, one window of copy always in flight behind the window being scored -- and only the
+    4-byte scores stay resident.  The step's CDF / draw / gather then run on the resident scores
+    (``ops.update_samples(None, labels, ..., scores_in=scores)``).
+
+    ``windows`` yields ``(logits_host, labels_host)`` pairs (pinned host tensors, at most ``window_rows`` rows each); labels
+    are kept resident as well (8 B per candidate) when ``labels_out`` is given."""
+
+    def __init__(self, window_rows: int, num_classes: int, dtype=torch.bfloat16, device="cuda", depth: int = 3, ops_module=None):
+        if depth < 2:
+            raise ValueError("ChunkRing: depth must be at least 2 (one window copying while one is scored)")
+        if ops_module is None:
+            from . import ops as ops_module
+        self.ops = ops_module
+        self.device = torch.device(device)
+        self.window_rows, self.depth = int(window_rows), int(depth)
+        self.logits = [torch.empty(window_rows, num_classes, dtype=dtype, device=self.device) for _ in range(depth)]
+        self.labels = [torch.empty(window_rows, dtype=torch.int64, device=self.device) for _ in range(depth)]
+        cuda = self.device.type == "cuda"
+        self._copy_stream = torch.cuda.Stream(device=self.device) if cuda else None
+        self._ready = [torch.cuda.Event() for _ in range(depth)] if cuda else None      # window copied in
+        self._free = [torch.cuda.Event() for _ in range(depth)] if cuda else None       # window scored: may be overwritten
+        self._used = [False] * depth
+        self.status = None
+
+    def score(self, windows, scores_out: torch.Tensor, labels_out: Optional[torch.Tensor] = None, status=None) -> int:
+        """Fills ``scores_out[0:rows]`` window by window; returns the number of rows scored."""
+        pos = 0
+        cuda = self._copy_stream is not None
+        main = torch.cuda.current_stream(self.device) if cuda else None
+        for w, (h_logits, h_labels) in enumerate(windows):
+            m = h_logits.shape[0]
+            if m > self.window_rows:
+                raise ValueError("ChunkRing: a window has more rows than the ring's windows")
+            if pos + m > scores_out.numel():
+                raise ValueError("ChunkRing: more rows than scores_out holds")
+            k = w % self.depth
+            lg, lb = self.logits[k][:m], self.labels[k][:m]
+            if cuda:
+                with torch.cuda.stream(self._copy_stream):
+                    if self._used[k]:
+                        self._copy_stream.wait_event(self._free[k])
+                    lg.copy_(h_logits, non_blocking=True)
+                    lb.copy_(h_labels, non_blocking=True)
+                    self._ready[k].record(self._copy_stream)
+                main.wait_event(self._ready[k])
+            else:
+                lg.copy_(h_logits)
+                lb.copy_(h_labels)
+            self.ops.score(lg, lb, status=status, out=scores_out[pos:pos + m])
+            if labels_out is not None:
+                labels_out[pos:pos + m].copy_(lb, non_blocking=True)
+            if cuda:
+                self._free[k].record(main)
+                self._used[k] = True
+            pos += m
+        return pos

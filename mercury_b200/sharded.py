@@ -197,6 +197,7 @@ class ShardedPool:
         self.ema_alpha, self.smooth_alpha = ema_alpha, smooth_alpha
         self._draw_out: dict = {}
         self._gather_out: dict = {}
+        self._arena = self._arena_key = None
         self.peer = None
         self._xstatus = None
         if mode == "totals":
@@ -221,6 +222,40 @@ class ShardedPool:
     def local_scores(self) -> torch.Tensor:
         return self.scores_all if self.mode == "totals" else self.scores_all[self.lo:self.lo + self.n_local]
 
+    def _use_arena(self, b, data, labels, index):
+        """mode="totals", assemble=True: the step's outputs (idx, labels, index, nprob, seed, data rows) live in ONE buffer, so
+        the batch is assembled by a single all-reduce instead of one per tensor.  Every row is zero on all ranks but its
+        owner, so the integer SUM of the raw 32-bit words reproduces the owner's bits for every dtype."""
+        key = (b, None if data is None else (tuple(data.shape[1:]), data.dtype), labels is not None, index is not None)
+        if self._arena_key == key:
+            return
+        parts = [("idx", torch.int64, (b,)), ("nprob", torch.float32, (b,)), ("seed", torch.float32, (b,))]
+        if labels is not None:
+            parts.append(("labels", torch.int64, (b,)))
+        if index is not None:
+            parts.append(("index", torch.int64, (b,)))
+        if data is not None:
+            parts.append(("data", data.dtype, (b,) + tuple(data.shape[1:])))
+        offs, total = [], 0
+        for _, dt, shape in parts:
+            offs.append(total)
+            nbytes = torch.empty(0, dtype=dt).element_size() * int(torch.Size(shape).numel())
+            total += (nbytes + 15) // 16 * 16
+        self._arena = torch.zeros(max(total, 16), dtype=torch.uint8, device=self.device)
+        for (name, dt, shape), off in zip(parts, offs):
+            nbytes = torch.empty(0, dtype=dt).element_size() * int(torch.Size(shape).numel())
+            self._draw_out[name] = self._arena[off:off + nbytes].view(dt).view(shape)
+        self._arena_key = key
+
+    def _assemble(self, tensors):
+        lo, hi = (self._arena.data_ptr(), self._arena.data_ptr() + self._arena.numel()) if self._arena is not None else (0, 0)
+        live = [t for t in tensors if t is not None]
+        if live and all(lo <= t.data_ptr() < hi for t in live):
+            dist.all_reduce(self._arena.view(torch.int32), op=dist.ReduceOp.SUM, group=self.group)   # one collective
+            return
+        for t in live:          # (a backend that allocates its own outputs)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+
     def _all_gather_small(self, full: torch.Tensor):
         if self.world == 1:
             return
@@ -233,9 +268,12 @@ class ShardedPool:
 
     def _update_totals(self, logits_local, labels_local, uniforms, data, index, assemble):
         b = self.backend
-        if self.peer is not None and self.fused and hasattr(b, "sharded_step"):
+        if assemble and self.world > 1 and self.device.type == "cuda":
+            self._use_arena(uniforms.numel(), data, labels_local, index)
+        if logits_local is not None and self.peer is not None and self.fused and hasattr(b, "sharded_step"):
             return self._update_totals_fused(logits_local, labels_local, uniforms, data, index, assemble)
-        b.score(logits_local, labels_local, self.local_scores)
+        if logits_local is not None:     # (None: ``local_scores`` is filled already, e.g. by pool.ChunkRing for a streamed shard)
+            b.score(logits_local, labels_local, self.local_scores)
         if self.peer is not None:
             b.sum_scores_exchange(self.local_scores, self.peer.boxes, self.rank, self.sums_all, self._xstatus)
         else:
@@ -258,9 +296,7 @@ class ShardedPool:
         self._draw_out.update({k: r[k] for k in ("idx", "nprob", "seed", "data", "labels", "index") if r[k] is not None})
         owned = self.local_u >= 0
         if assemble and self.world > 1:
-            for t in (r["idx"], r["nprob"], r["seed"], r["data"], r["labels"], r["index"]):
-                if t is not None:
-                    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            self._assemble((r["idx"], r["nprob"], r["seed"], r["data"], r["labels"], r["index"]))
         return dict(idx=r["idx"], nprob=r["nprob"], seed=r["seed"], stats=stats, status=status, data=r["data"], labels=r["labels"],
                     index=r["index"], owned=owned, scores=self.local_scores, xstatus=self._xstatus)
 
@@ -273,9 +309,7 @@ class ShardedPool:
         self.ema_first = False
         self._draw_out.update({k: r[k] for k in ("idx", "nprob", "seed", "data", "labels", "index", "stats") if r[k] is not None})
         if assemble and self.world > 1:
-            for t in (r.idx, r.nprob, r.seed, r.data, r.labels, r.index):
-                if t is not None:
-                    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            self._assemble((r.idx, r.nprob, r.seed, r.data, r.labels, r.index))
         return dict(idx=r.idx, nprob=r.nprob, seed=r.seed, stats=r.stats, status=r.status, data=r.data, labels=r.labels,
                     index=r.index, owned=self.local_u >= 0, scores=self.local_scores, xstatus=r.status)
 
@@ -306,7 +340,8 @@ class ShardedPool:
 
     def update_samples(self, logits_local, labels_local, uniforms, data=None, index=None, assemble: bool = False,
                        out: Optional[dict] = None):
-        """One global importance-sampling step.  Returns a dict with the replicated ``idx`` (global
+        """One global importance-sampling step (``logits_local=None``: the shard's scores are in ``local_scores``
+        already -- a shard streamed through pool.ChunkRing).  Returns a dict with the replicated ``idx`` (global
         positions), ``nprob``, ``seed``, ``stats``, ``status`` and this rank's ``data`` / ``labels`` /
         ``index`` rows (zero where another rank owns the draw) plus the ``owned`` mask."""
         if self.mode == "totals":
@@ -318,7 +353,8 @@ class ShardedPool:
                 self._status_event.record()
             return r
         b = self.backend
-        b.score(logits_local, labels_local, self.local_scores)
+        if logits_local is not None:
+            b.score(logits_local, labels_local, self.local_scores)
         self._all_gather_scores()
         idx, nprob, seed, stats, status = b.draw(self.scores_all, uniforms, self.ema_state, self.ema_first, self.ema_alpha,
                                                  self.smooth_alpha, self._draw_out)

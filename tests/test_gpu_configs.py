@@ -215,3 +215,28 @@ def test_one_process_two_devices_cdf_and_static_cdf():
                 results.append(r.idx.cpu())
             ops.set_fused(-1)
     assert all(torch.equal(results[0], x) for x in results[1:])
+
+
+def test_chunk_ring_streamed_shard_equals_resident_step():
+    """A shard streamed from pinned host memory through a 3-window ring (H2D on a copy stream behind K1): scores bit-equal to
+    the resident call, and the step on those scores draws what the whole-step call draws."""
+    from mercury_b200 import ops
+    from mercury_b200.pool import ChunkRing
+
+    g = torch.Generator().manual_seed(13)
+    n, c, b, win = 300_000, 1000, 128, 1 << 15
+    logits = (torch.randn(n, c, generator=g) * 2).to(torch.bfloat16).pin_memory()
+    labels = torch.randint(0, c, (n,), generator=g).pin_memory()
+    u = torch.rand(b, dtype=torch.float64, generator=g).to(DEV)
+    ring = ChunkRing(win, c, dtype=torch.bfloat16, device=DEV, depth=3)
+    scores = torch.empty(n, device=DEV)
+    labs = torch.empty(n, dtype=torch.int64, device=DEV)
+    for rep in range(2):          # (second pass: every window of the ring is reused behind its "free" event)
+        scores.zero_()
+        rows = ring.score(((logits[i:i + win], labels[i:i + win]) for i in range(0, n, win)), scores, labs)
+        assert rows == n
+        whole = ops.update_samples(logits.to(DEV), labels.to(DEV), u, torch.zeros(1, device=DEV), True)
+        assert torch.equal(scores, whole.scores) and torch.equal(labs.cpu(), labels)
+        r = ops.update_samples(None, labs, u, torch.zeros(1, device=DEV), True, scores_in=scores)
+        ops.check_status(r.status)
+        assert torch.equal(r.idx, whole.idx) and torch.equal(r.nprob, whole.nprob)

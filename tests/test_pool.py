@@ -36,3 +36,28 @@ def test_ring_keeps_the_most_recent_candidates():
     assert sorted(index.tolist()) == sorted(allidx[-10:].tolist())
     assert index[:6].tolist() == allidx[10:16].tolist() and index[6:].tolist() == allidx[6:10].tolist()
     assert pool.growing_bounds() is None
+
+
+def test_chunk_ring_scores_a_streamed_shard_like_one_resident_call():
+    """pool.ChunkRing on CPU tensors (host logic: window rotation, ragged last window, bounds); the oracle stands in for K1."""
+    import torch
+    from oracle import mercury_oracle as orc
+    from mercury_b200.pool import ChunkRing
+
+    class Ops:
+        def score(self, logits, labels, status=None, out=None):
+            out.copy_(orc.score(logits, labels))
+            return out
+
+    g = torch.Generator().manual_seed(1)
+    n, c, win = 1000, 7, 128
+    logits, labels = torch.randn(n, c, generator=g), torch.randint(0, c, (n,), generator=g)
+    ring = ChunkRing(win, c, dtype=torch.float32, device="cpu", depth=3, ops_module=Ops())
+    scores, labs = torch.zeros(n), torch.zeros(n, dtype=torch.int64)
+    rows = ring.score(((logits[i:i + win], labels[i:i + win]) for i in range(0, n, win)), scores, labs)
+    assert rows == n and torch.equal(scores, orc.score(logits, labels)) and torch.equal(labs, labels)
+    import pytest
+    with pytest.raises(ValueError):
+        ring.score([(logits[:win + 1], labels[:win + 1])], scores)
+    with pytest.raises(ValueError):
+        ring.score(((logits[i:i + win], labels[i:i + win]) for i in range(0, n, win)), scores[:500])
