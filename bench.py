@@ -637,6 +637,8 @@ def main_multi(args, wl, dev, world, rank):
         del wlg, wlb
         labels_dev = torch.empty(n, dtype=torch.int64, device=dev)
         nwin = n // win
+        if sp.peer is not None:
+            sp.peer.set_wait(300_000)   # (ranks that share a host link can be seconds apart after hundreds of GB of copies)
         stream_note = (f"shard of {pool_bytes >> 30} GiB streamed every step from pinned host memory through a ring of 3 x {win}-row windows "
                        f"({nwin} windows per step; the synthetic host window is reused, the copies are real): the step is bound by the "
                        f"host link, not by HBM")
@@ -751,9 +753,10 @@ def main_multi(args, wl, dev, world, rank):
         value = n * world / (ms * 1e-3)
         line = {
             "metric": "importance-scored+sampled candidates/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "steps": args.steps, "warmup": max(min_warm, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
-            "config": make_config(args, wl, world, exchange),
+            "config": dict(make_config(args, wl, world, exchange), **({"launch": "eager launches (copy stream + compute stream)",
+                                                                       "l2": "the shard streams through HBM once per step"} if streamed else {})),
             "roofline": {"kernel": "whole step per GPU: score -> summarize -> spine -> draw on the rank's shard, exchanges inside",
                          "bound": "hbm", "achieved": step_bytes / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": step_bytes / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "ms_per_launch": ms,

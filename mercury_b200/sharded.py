@@ -216,6 +216,7 @@ class ShardedPool:
         # check()) raises if a peer's word timed out -- a timed-out step is poisoned on the device (NaN nprob / seed, idx -1)
         self._host_status = torch.zeros(1, dtype=torch.int32).pin_memory() if self.peer is not None and self.device.type == "cuda" else None
         self._status_event = None
+        self._last_xstatus = None
         self.fused = fused     # exchange="peer": the whole step as one C call / PDL chain (False: one call per stage)
 
     @property
@@ -319,13 +320,16 @@ class ShardedPool:
         ranks have synchronised, ``pool.peer.reset()`` on every rank makes the exchange usable again."""
         ev = self._status_event
         if ev is None:
-            return
-        if wait:
-            ev.synchronize()
-        elif not ev.query():
-            return
-        self._status_event = None
-        if int(self._host_status[0]) & _lib.ST_PEER_TIMEOUT:
+            # (steps replayed from a CUDA graph record no event: an explicit check reads the device word)
+            bits = int(self._last_xstatus.item()) if wait and self._last_xstatus is not None and self.peer is not None else 0
+        else:
+            if wait:
+                ev.synchronize()
+            elif not ev.query():
+                return
+            self._status_event = None
+            bits = int(self._host_status[0])
+        if bits & _lib.ST_PEER_TIMEOUT:
             raise RuntimeError("mercury_b200: a peer's exchange word did not arrive within the bound (ranks more than the "
                                "wait apart? PeerExchange.set_wait / MERCURY_PEER_WAIT_MS; recover with peer.reset() on all ranks)")
 
@@ -345,9 +349,12 @@ class ShardedPool:
         positions), ``nprob``, ``seed``, ``stats``, ``status`` and this rank's ``data`` / ``labels`` /
         ``index`` rows (zero where another rank owns the draw) plus the ``owned`` mask."""
         if self.mode == "totals":
-            self.check(wait=False)
+            capturing = self.device.type == "cuda" and torch.cuda.is_current_stream_capturing()
+            if not capturing:
+                self.check(wait=False)
             r = self._update_totals(logits_local, labels_local, uniforms, data, index, assemble)
-            if self._host_status is not None and r["xstatus"] is not None:
+            self._last_xstatus = r["xstatus"]
+            if self._host_status is not None and r["xstatus"] is not None and not capturing:
                 self._host_status.copy_(r["xstatus"], non_blocking=True)
                 self._status_event = torch.cuda.Event()
                 self._status_event.record()
