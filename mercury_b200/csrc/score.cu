@@ -48,8 +48,40 @@ __global__ void __launch_bounds__(256) score_generic_kernel(const T* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------------
+// 2^t on the FMA pipe (t <= ~0): Cody-Waite split by the 1.5*2^23 trick, degree-5 polynomial on [-0.5, 0.5] (max relative
+// error 1.9e-7, the same as MUFU.EX2's), exponent added as an integer.  With one MUFU.EX2 per logit the special-function
+// unit is the co-limiter of the bf16 1000-class shape (ncu: XU 68 % beside DRAM 75 %); POLY of every 8 logits go this way.
+__device__ __forceinline__ float ex2_poly(float t) {
+    t = fmaxf(t, -125.f);
+    const float z = __fadd_rn(t, 12582912.f);
+    const float f = __fadd_rn(t, -__fadd_rn(z, -12582912.f));
+    float g = fmaf(f, 0.0013264815788716078f, 0.009671512059867382f);
+    g = fmaf(f, g, 0.05550733581185341f);
+    g = fmaf(f, g, 0.24022242426872253f);
+    g = fmaf(f, g, 0.6931470036506653f);
+    return __int_as_float(__float_as_int(fmaf(f, g, 1.f)) + (__float_as_int(z) << 23));
+}
+
 // medium rows: one warp per row, the row held in registers as VPL 128-bit vectors per lane
-template <typename T, int VPL>
+constexpr int kDefaultPoly = -1;
+// Two logits per instruction where the ISA has it (sm_100: fma.rn.f32x2 / add.f32x2 on register pairs): the bf16 1000-class
+// shape is limited by instruction issue beside DRAM (profiles/r2_k1_poly_ab.jsonl), so the scale-and-shift and the
+// accumulation of a bf16x2 word are one instruction each instead of two.
+__device__ __forceinline__ unsigned long long pack2(float a, float b) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void term2_acc(uint32_t w, unsigned long long kk, unsigned long long nh, unsigned long long& acc) {
+    const unsigned long long xx = pack2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+    unsigned long long t;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(t) : "l"(xx), "l"(kk), "l"(nh));
+    float t0, t1;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(t0), "=f"(t1) : "l"(t));
+    const unsigned long long ee = pack2(ex2_approx(t0), ex2_approx(t1));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(acc) : "l"(acc), "l"(ee));
+}
+template <typename T, int VPL, int POLY = 0>
 __global__ void __launch_bounds__(256) score_warp_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels,
                                                          int64_t n, int64_t c, int64_t row_stride, int64_t ignore_index,
                                                          float* __restrict__ scores, int32_t* status) {
@@ -100,6 +132,19 @@ __global__ void __launch_bounds__(256) score_warp_kernel(const T* __restrict__ l
         m = warp_max(m);
         const ExpScale es(m);
         float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;  // independent partial sums (ILP)
+        if constexpr (sizeof(T) == 2 && POLY < 0) {   // packed pairs
+            const unsigned long long kk = pack2(kLog2e, kLog2e), nh = pack2(-es.hi, -es.hi);
+            unsigned long long a0 = 0ull, a1 = 0ull, a2 = 0ull, a3 = 0ull;
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) {
+                term2_acc(v[i].x, kk, nh, a0); term2_acc(v[i].y, kk, nh, a1);
+                term2_acc(v[i].z, kk, nh, a2); term2_acc(v[i].w, kk, nh, a3);
+            }
+            asm("add.rn.f32x2 %0, %0, %1;" : "+l"(a0) : "l"(a1));
+            asm("add.rn.f32x2 %0, %0, %1;" : "+l"(a2) : "l"(a3));
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(l0), "=f"(l1) : "l"(a0));
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(l2), "=f"(l3) : "l"(a2));
+        } else
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
             if constexpr (sizeof(T) == 4) {
@@ -108,10 +153,11 @@ __global__ void __launch_bounds__(256) score_warp_kernel(const T* __restrict__ l
                 l2 += es.term(__uint_as_float(v[i].z));
                 l3 += es.term(__uint_as_float(v[i].w));
             } else {
-                l0 += es.term(bf16_lo(v[i].x)); l1 += es.term(bf16_hi(v[i].x));
-                l2 += es.term(bf16_lo(v[i].y)); l3 += es.term(bf16_hi(v[i].y));
-                l0 += es.term(bf16_lo(v[i].z)); l1 += es.term(bf16_hi(v[i].z));
-                l2 += es.term(bf16_lo(v[i].w)); l3 += es.term(bf16_hi(v[i].w));
+                auto term = [&](float x, int slot) { return slot < POLY ? ex2_poly(fmaf(x, kLog2e, -es.hi)) : es.term(x); };
+                l0 += term(bf16_lo(v[i].x), 0); l1 += term(bf16_hi(v[i].x), 4);
+                l2 += term(bf16_lo(v[i].y), 1); l3 += term(bf16_hi(v[i].y), 5);
+                l0 += term(bf16_lo(v[i].z), 2); l1 += term(bf16_hi(v[i].z), 6);
+                l2 += term(bf16_lo(v[i].w), 3); l3 += term(bf16_hi(v[i].w), 7);
             }
         }
         const float l = warp_sum((l0 + l1) + (l2 + l3));
@@ -296,11 +342,20 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
     if (base16 && stride16 && (row_bytes & 15) == 0 && row_bytes <= 8192) {
         const int nvec = (int)(row_bytes >> 4);
         const int64_t warps_needed = n;
-        const int grid = (int)min_i64((warps_needed + 7) / 8, (int64_t)kSMs * 8);
+        // Grid: 96 CTAs per SM, far more than the 6 that are resident.  With 8 per SM (1.33 waves of resident CTAs, long
+        // grid-stride loops) the last third of the rows ran at a third of the occupancy: 0.445 ms at 1.28 M x 1000 bf16; short
+        // CTAs that the hardware hands out as slots free up give 0.378-0.390 ms (profiles/r2_k1_grid_sweep.jsonl).
+        static const int ctas_per_sm = env_knob("MERCURY_K1_WARP_CTAS", 96, 1, 4096);
+        const int grid = (int)min_i64((warps_needed + 7) / 8, (int64_t)kSMs * ctas_per_sm);
 #define MB_LAUNCH_WARP(VPL)                                                                                         \
     score_warp_kernel<T, VPL><<<grid, 256, 0, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status)
+        static const int poly = env_knob("MERCURY_K1_POLY", kDefaultPoly, -1, 3);   // -1: packed f32x2 arithmetic   // exponentials per 8 logits on the FMA pipe
         if (nvec <= 32) MB_LAUNCH_WARP(1);
         else if (nvec <= 64) MB_LAUNCH_WARP(2);
+        else if (nvec <= 128 && sizeof(T) == 2 && poly == -1) score_warp_kernel<T, 4, -1><<<grid, 256, 0, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
+        else if (nvec <= 128 && sizeof(T) == 2 && poly == 1) score_warp_kernel<T, 4, 1><<<grid, 256, 0, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
+        else if (nvec <= 128 && sizeof(T) == 2 && poly == 2) score_warp_kernel<T, 4, 2><<<grid, 256, 0, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
+        else if (nvec <= 128 && sizeof(T) == 2 && poly == 3) score_warp_kernel<T, 4, 3><<<grid, 256, 0, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
         else if (nvec <= 128) MB_LAUNCH_WARP(4);
         else if (nvec <= 256) MB_LAUNCH_WARP(8);
         else MB_LAUNCH_WARP(16);
@@ -314,7 +369,8 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
         auto kern = score_wide_kernel<T, STAGES, CHUNK, CONSUMERS>;
         const int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem, "score_wide smem attribute");
         if (rc) return rc;
-        const int grid = (int)min_i64(n, (int64_t)kSMs * 3);
+        static const int wide_ctas = env_knob("MERCURY_K1_WIDE_CTAS", 64, 1, 4096);
+        const int grid = (int)min_i64(n, (int64_t)kSMs * wide_ctas);
         kern<<<grid, CONSUMERS + kProducerThreads, smem, st>>>(logits, labels, n, c, row_stride, ignore_index, scores, status);
         MB_CHECK_LAUNCH("score_wide_kernel");
         return MERCURY_OK;
