@@ -44,8 +44,9 @@ def algorithmic_bytes(n, c, s, b, row_bytes):
 
 
 def k1_traffic(workload):
-    """DRAM bytes (read + write) of one K1 launch from the committed `ncu --set full` capture."""
-    p = os.path.join(ROOT, "profiles", "r1_k1_traffic.json")
+    """DRAM bytes (read + write) of one launch from the committed `ncu --set full` captures (profiles/r2_traffic.json):
+    `<workload>` = one K1 launch, `<workload>_step` = one launch of the one-kernel step."""
+    p = os.path.join(ROOT, "profiles", "r2_traffic.json")
     try:
         t = json.load(open(p))[workload]
         return t["dram_bytes_read"] + t["dram_bytes_write"]
@@ -516,7 +517,7 @@ def main_single(args, wl, dev):
         "roofline": {"kernel": "whole step: " + ("fused_step_kernel (score + statistics + exact CDF + draws + gather, one cooperative launch)"
                                                  if one_kernel else "score -> summarize -> spine -> draw (4 launches; K1 dominates)"),
                      "bound": "hbm", "achieved": res["step_gbs"], "peak": res["peak"], "unit": "GB/s", "frac": res["step_frac"],
-                     "traffic": None if one_kernel else traffic, "peak_source": res["peak_src"], "ms_per_launch": res["ms_per_step"],
+                     "traffic": k1_traffic(args.workload + "_step") if one_kernel else traffic, "peak_source": res["peak_src"], "ms_per_launch": res["ms_per_step"],
                      "algorithmic_bytes_per_launch": res["step_bytes"]},
         "k1_roofline": {"kernel": "K1 score (mercury_score) timed alone", "bound": "hbm", "achieved": res["k1_gbs"], "peak": res["peak"],
                         "unit": "GB/s", "frac": res["k1_frac"], "traffic": traffic, "ms_per_launch": res["k1_ms"],
