@@ -7,6 +7,8 @@ loop, logging and TensorBoard output of the reference are out of scope, SURVEY s
 """
 from __future__ import annotations
 
+from typing import Optional
+
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
@@ -29,15 +31,26 @@ def split_head(net):
     return features, net.linear
 
 
+class _Last(dict):
+    __getattr__ = dict.__getitem__
+
+
 class Trainer(object):
     POOL_BATCHES = 10  # pytorch_collab.py:95
 
     def __init__(self, net, optimizer, train_loader, presam_loader, test_loader, device, score_from_features: bool = False,
-                 ops_module=None):
+                 ops_module=None, global_draw: bool = False, sharded_kwargs: Optional[dict] = None):
         # score_from_features: presample batches stop before the classifier head (``split_head``) and are scored by
         # ``ops.score_head`` -- the logits of the pool are never materialised; needs a ResNet-shaped net.
         # ops_module: the operator module (default: the CUDA ops; the CPU tests inject an oracle-backed stand-in).
+        # global_draw (world > 1): the workers' presample pools form ONE sharded pool (sharded.ShardedPool, mode "totals"); every
+        # step draws world * B candidates from it and worker r trains on rows [r*B, (r+1)*B) of the assembled batch.  The
+        # reference's workers each draw from their own shard only (pytorch_collab.py:282-287); this is the north star's
+        # "global draw" wired into the same loop (my_run / init_processes, :252-292).
         self.ops = ops_module if ops_module is not None else ops
+        self.global_draw = global_draw
+        self._sharded_kwargs = dict(sharded_kwargs or {})
+        self._sp = None
         self.score_from_features = score_from_features
         self._head = split_head(net) if score_from_features else None
         self.net = net
@@ -105,6 +118,8 @@ class Trainer(object):
                                                      payload_dtype=data.dtype)
                 pool.append(idx, data, label, output)
         logits, labels, datas, index = pool.tensors()
+        if self.global_draw and self.world_size > 1:
+            return self._update_samples_global(ema_loss, alpha, B, logits, labels, datas, index)
         bounds = pool.growing_bounds()
         u = torch.rand(len(bounds) * B, dtype=torch.float64)[(len(bounds) - 1) * B:]
         if self._u_dev is None or self._u_dev.numel() != u.numel():
@@ -155,6 +170,32 @@ class Trainer(object):
         ema_loss.first_update = False
         self.last = r
         return r.nprob, r.data, r.labels, r.index, r.stats[_lib.STAT_MEAN]
+
+    def _update_samples_global(self, ema_loss, alpha, B, logits, labels, datas, index):
+        """The global draw: one sharded step over all workers' pools (one EMA update per step on the whole pool's mean --
+        the reference's ten updates on growing prefixes have no meaning across shards), world * B draws from rank 0's
+        uniform stream, the batch assembled on every rank by one all-reduce, worker r keeps its B rows.  N in ``N * p`` is the
+        global pool size; the backward seed is rescaled from 1 / (world * B) to 1 / B."""
+        from .sharded import ShardedPool
+
+        G = self.world_size
+        if self._sp is None or self._sp.n_local != labels.numel():
+            self._sp = ShardedPool(labels.numel(), self.device, ema_alpha=ema_loss.alpha, smooth_alpha=alpha,
+                                   **dict({"mode": "totals"}, **self._sharded_kwargs))
+        sp = self._sp
+        sp.ema_state, sp.ema_first, sp.smooth_alpha = ema_loss.state, ema_loss.first_update, alpha
+        u = torch.rand(G * B, dtype=torch.float64).to(self.device)
+        dist.broadcast(u, src=0)
+        if self._head is not None:          # the pool holds scores already
+            sp.local_scores.copy_(logits)
+            r = sp.update_samples(None, labels, u, data=datas, index=index, assemble=True)
+        else:
+            r = sp.update_samples(logits, labels, u, data=datas, index=index, assemble=True)
+        ema_loss.first_update = False
+        mine = slice(self.rank * B, (self.rank + 1) * B)
+        self.last = _Last(scores=r["scores"], stats=r["stats"], idx=r["idx"][mine], nprob=r["nprob"][mine], seed=r["seed"][mine] * float(G),
+                          data=r["data"][mine], labels=r["labels"][mine], index=r["index"][mine], status=r["status"])
+        return self.last.nprob, self.last.data, self.last.labels, self.last.index, r["stats"][_lib.STAT_MEAN]
 
     def train(self, max_steps=None):
         """One epoch of pytorch_collab.py:119-199 (timers, printing and periodic evaluation dropped)."""

@@ -240,3 +240,63 @@ def test_chunk_ring_streamed_shard_equals_resident_step():
         r = ops.update_samples(None, labs, u, torch.zeros(1, device=DEV), True, scores_in=scores)
         ops.check_status(r.status)
         assert torch.equal(r.idx, whole.idx) and torch.equal(r.nprob, whole.nprob)
+
+
+def _global_trainer_worker(rank, world, port, ret):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from mercury_b200.collab import Trainer
+    from mercury_b200.sampler import EMAverage
+
+    torch.manual_seed(0)
+    net = nn.Sequential(nn.Flatten(), nn.Linear(3 * 32 * 32, 10)).to(dev)
+    g = torch.Generator().manual_seed(50 + rank)
+    batches = [(torch.arange(i * 625, (i + 1) * 625) + 100000 * rank, torch.rand(625, 3, 32, 32, generator=g),
+                torch.randint(0, 10, (625,), generator=g)) for i in range(10)]      # 6250 candidates per worker (cfg4's shard)
+    tr = Trainer(net, None, _Loader([], 16), _Loader(batches, 625), None, dev, global_draw=True, sharded_kwargs={"exchange": "peer"})
+    ema = EMAverage(device=dev)
+    torch.manual_seed(77)
+    outs = []
+    for step in range(2):
+        probs, data, label, index, avg = tr.update_samples(ema)
+        torch.cuda.synchronize()
+        tr._sp.check()
+        outs.append(dict(probs=probs.cpu(), data=data.cpu(), index=index.cpu(), idx=tr.last.idx.cpu(), scores=tr.last.scores.cpu(),
+                         stats=tr.last.stats.cpu(), pool_data=tr._pool.tensors()[2].cpu(), pool_index=tr._pool.tensors()[3].cpu()))
+    ret[rank] = outs
+    dist.barrier()
+    tr._sp.peer.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_trainer_global_draw_two_gpus_matches_the_two_level_oracle():
+    """BASELINE configs[3] shape per worker (6250 candidates, 10 classes) on two real GPUs: Trainer(global_draw=True) over the
+    sharded pool with the in-kernel peer exchange; each worker's B rows are its slice of the oracle's two-level draw."""
+    import torch.multiprocessing as mp
+
+    world, B, nl = 2, 16, 6250
+    ret = mp.Manager().dict()
+    mp.spawn(_global_trainer_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    torch.manual_seed(77)
+    for step in range(2):
+        u = torch.rand(world * B, dtype=torch.float64).numpy()
+        st = ret[0][step]["stats"].numpy()
+        shards = [((ret[r][step]["scores"].numpy() + np.float32(st[2])).astype(np.float32) / np.float32(st[3])).astype(np.float32)
+                  for r in range(world)]
+        want = orc.sharded_draw_two_level(shards, u)
+        p_all = np.concatenate(shards)
+        for r in range(world):
+            o = ret[r][step]
+            mine = want[r * B:(r + 1) * B]
+            assert np.array_equal(o["idx"].numpy(), mine)
+            np.testing.assert_array_equal(o["probs"].numpy(), p_all[mine] * np.float32(world * nl))
+            for j, gidx in enumerate(mine):
+                owner, local = divmod(int(gidx), nl)
+                assert torch.equal(o["data"][j], ret[owner][step]["pool_data"][local])
+                assert int(o["index"][j]) == int(ret[owner][step]["pool_index"][local])

@@ -168,6 +168,69 @@ def test_sharded_pool_totals_mode_world2_matches_two_level_oracle():
         np.testing.assert_allclose(float(st[0]), float(losses.mean()), rtol=1e-6)
 
 
+class _Loader:
+    def __init__(self, batches, batch_size):
+        self.batches, self.batch_size = batches, batch_size
+
+    def __iter__(self):
+        return iter(self.batches)
+
+
+def _worker_trainer_global(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mercury_b200.collab import Trainer
+        from mercury_b200.sampler import EMAverage
+
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(48, 10))     # same weights on every worker
+        g = torch.Generator().manual_seed(50 + rank)                                # each worker its own presample shard
+        batches = [(torch.arange(i * 16, (i + 1) * 16) + 1000 * rank, torch.rand(16, 3, 4, 4, generator=g),
+                    torch.randint(0, 10, (16,), generator=g)) for i in range(10)]
+        tr = Trainer(net, None, _Loader([], 8), _Loader(batches, 16), None, "cpu", global_draw=True,
+                     sharded_kwargs={"backend": OracleBackend()})
+        ema = EMAverage(device="cpu")
+        torch.manual_seed(77)        # (rank 0's stream supplies the uniforms)
+        outs = []
+        for step in range(2):
+            probs, data, label, index, avg = tr.update_samples(ema)
+            outs.append(dict(probs=probs.clone(), data=data.clone(), label=label.clone(), index=index.clone(), avg=float(avg),
+                             idx=tr.last.idx.clone(), seed=tr.last.seed.clone(), scores=tr.last.scores.clone(), stats=tr.last.stats.clone(),
+                             pool_data=tr._pool.tensors()[2].clone(), pool_index=tr._pool.tensors()[3].clone()))
+        ret[rank] = outs
+    finally:
+        dist.destroy_process_group()
+
+
+def test_trainer_global_draw_world2_draws_from_the_sharded_pool():
+    """Trainer(global_draw=True): the two workers' presample pools are one sharded pool; one two-level draw of world * B
+    candidates per step, worker r trains on rows [r*B, (r+1)*B) -- checked against the two-level oracle over both shards."""
+    world, B, nl = 2, 8, 160
+    ret = mp.Manager().dict()
+    mp.spawn(_worker_trainer_global, args=(world, _free_port(), ret), nprocs=world, join=True)
+    torch.manual_seed(77)
+    for step in range(2):
+        u = torch.rand(world * B, dtype=torch.float64).numpy()
+        st = ret[0][step]["stats"].numpy()
+        assert np.array_equal(st[:4], ret[1][step]["stats"].numpy()[:4])
+        shards = [((ret[r][step]["scores"].numpy() + np.float32(st[2])).astype(np.float32) / np.float32(st[3])).astype(np.float32)
+                  for r in range(world)]
+        want = orc.sharded_draw_two_level(shards, u)
+        p_all = np.concatenate(shards)
+        for r in range(world):
+            o = ret[r][step]
+            mine = want[r * B:(r + 1) * B]
+            assert np.array_equal(o["idx"].numpy(), mine)
+            np.testing.assert_array_equal(o["probs"].numpy(), p_all[mine] * np.float32(world * nl))
+            np.testing.assert_allclose(o["seed"].numpy(), (1.0 / B) / o["probs"].numpy(), rtol=1e-6)
+            for j, gidx in enumerate(mine):          # rows come from the owning worker's pool
+                owner, local = divmod(int(gidx), nl)
+                assert torch.equal(o["data"][j], ret[owner][step]["pool_data"][local])
+                assert int(o["index"][j]) == int(ret[owner][step]["pool_index"][local])
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
