@@ -21,15 +21,17 @@
 namespace mercury {
 namespace {
 
-constexpr int kBM = 128, kBN = 256, kBK = 64, kStages = 4, kUmmaK = 16;
-constexpr int kTmemCols = 512;                       // two accumulators of 256 columns
+// Two shapes of the same kernel: class tiles of 256 (4 stages; the 1000-class head, tensor-bound) and of 64 (8 stages; heads
+// of up to a few dozen classes, where the kernel is a stream of features bound by HBM and a 256-wide tile would spend 25 x
+// the useful MMA work and re-read a 32 KB weight tile per stage).
+constexpr int kBM = 128, kBK = 64, kUmmaK = 16, kMaxStages = 8;
 constexpr int kThreads = 192;                        // warp 0: TMA, warp 1: MMA + TMEM, warps 2..5: epilogue
-constexpr uint32_t kABytes = kBM * kBK * 2, kBBytes = kBN * kBK * 2, kStageBytes = kABytes + kBBytes;
+constexpr uint32_t kABytes = kBM * kBK * 2;
 constexpr int kMaxClasses = 4096;                    // bias staged in shared memory
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct __align__(8) Bars {
-    uint64_t full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+    uint64_t full[kMaxStages], empty[kMaxStages], tmem_full[2], tmem_empty[2];
     uint32_t tmem_base;
 };
 
@@ -60,14 +62,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
     return (uint64_t)((saddr >> 4) & 0x3fffu) | (1ull << 16) /* LBO (unused with this swizzle) */ | (64ull << 32) /* SBO = 1024 B */ |
            (1ull << 46) /* descriptor version */ | (2ull << 61) /* SWIZZLE_128B */;
 }
-// instruction descriptor: D fp32, A and B bf16, both K-major, M = 128, N = 256
-constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+// instruction descriptor: D fp32, A and B bf16, both K-major, M = 128, N = bn
+constexpr uint32_t idesc_for(int bn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+}
 
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate) : "memory");
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {   // arrives on `bar` when every MMA issued so far has finished
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -85,10 +89,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+template <int kBN, int kStages>
 __global__ void __launch_bounds__(kThreads, 1)
 head_wide_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, int64_t n, int d, int c,
                  const float* __restrict__ bias, const int64_t* __restrict__ labels, int64_t ignore_index,
                  float* __restrict__ scores, int32_t* status) {
+    constexpr uint32_t kBBytes = kBN * kBK * 2, kStageBytes = kABytes + kBBytes;
+    constexpr int kTmemCols = 2 * kBN;               // two accumulators (a power of two >= 32)
+    constexpr uint32_t kIdesc = idesc_for(kBN);
+    static_assert(kStages <= kMaxStages && (kTmemCols == 128 || kTmemCols == 512), "shapes");
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     // (1024-byte alignment for the 128-byte swizzle; the launch asks for 1 KB of slack)
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -149,7 +158,7 @@ head_wide_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                         const uint64_t bd = umma_desc_sw128(smem_u32(stage_b + (size_t)stage * kBBytes));
 #pragma unroll
                         for (int k = 0; k < kBK / kUmmaK; ++k)   // 16 bf16 = 32 bytes further along K: +2 in the address field
-                            umma_f16(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), (kb | k) ? 1u : 0u);
+                            umma_f16(tmem_d, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), kIdesc, (kb | k) ? 1u : 0u);
                         umma_commit(&bars->empty[stage]);          // the stage is free once these MMAs have read it
                         if (++stage == kStages) { stage = 0; phase ^= 1u; }
                     }
@@ -258,19 +267,21 @@ extern "C" int mercury_score_head_wide(const void* features, int64_t n, int64_t 
     MB_CHECK_ARG(((reinterpret_cast<uintptr_t>(features) | reinterpret_cast<uintptr_t>(weight)) & 15) == 0,
                  "mercury_score_head_wide: features and weight must be 16-byte aligned");
     MB_CHECK_ARG(n < ((int64_t)1 << 31) && d < ((int64_t)1 << 24), "mercury_score_head_wide: n or d too large for the tile coordinates");
+    const bool narrow = c <= 128;          // (up to two class tiles of 64)
+    const int bn = narrow ? 64 : 256, stages = narrow ? 8 : 4;
     CUtensorMap tm_a, tm_b;
     int rc = make_map(&tm_a, features, n, d, row_stride, kBM);
-    if (!rc) rc = make_map(&tm_b, weight, c, d, weight_stride, kBN);
+    if (!rc) rc = make_map(&tm_b, weight, c, d, weight_stride, bn);
     if (rc) return rc;
-    const int num_n_tiles = (int)((c + kBN - 1) / kBN);
-    const size_t smem = 1024 + (size_t)kStages * kStageBytes + (size_t)num_n_tiles * kBN * 4 + sizeof(Bars) + 64;
-    rc = ensure_dynamic_smem(reinterpret_cast<const void*>(head_wide_kernel), smem, "head_wide_kernel smem attribute");
+    const int num_n_tiles = (int)((c + bn - 1) / bn);
+    const size_t smem = 1024 + (size_t)stages * (kABytes + (size_t)bn * kBK * 2) + (size_t)num_n_tiles * bn * 4 + sizeof(Bars) + 64;
+    auto kern = narrow ? head_wide_kernel<64, 8> : head_wide_kernel<256, 4>;
+    rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem, "head_wide_kernel smem attribute");
     if (rc) return rc;
     const int sms = device_sm_count();
     const int64_t tiles = (n + kBM - 1) / kBM;
     const int grid = (int)min_i64(tiles, sms > 0 ? sms : kSMs);
-    head_wide_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tm_a, tm_b, n, (int)d, (int)c, bias, labels, ignore_index,
-                                                                                  scores, status);
+    kern<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tm_a, tm_b, n, (int)d, (int)c, bias, labels, ignore_index, scores, status);
     MB_CHECK_LAUNCH("head_wide_kernel");
     return MERCURY_OK;
 }

@@ -36,6 +36,10 @@ def _case(n, d, c, seed, scale=0.05):
     (5000, 2048, 1000, True),    # several row tiles per CTA is not reached at this size; many CTAs
     (40000, 1024, 1500, True),   # persistent loop: more row tiles than SMs, 6 class tiles
     (257, 72, 300, True),        # feature width not a multiple of the K block (zero-filled by TMA)
+    (70000, 512, 10, True),      # narrow shape (class tiles of 64, 8 stages): the reference's 512 -> 10 head with bf16 weights
+    (3000, 512, 100, True),      # narrow shape, two class tiles (the second one ragged)
+    (1500, 256, 128, False),     # narrow shape, exactly two full class tiles
+    (1500, 256, 129, False),     # one class more: back to the 256-wide shape
 ])
 def test_wide_head_matches_linear_then_cross_entropy(ops, n, d, c, bias):
     feats, w, b, y = _case(n, d, c, seed=n + c)
