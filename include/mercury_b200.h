@@ -22,7 +22,8 @@
  *      * process-wide knobs read ONCE from the environment at first use and then fixed: MERCURY_PDL
  *        (0 = no programmatic dependent launch), MERCURY_K1_TILE / MERCURY_K1_CTAS (tile rows / grid of
  *        the small-row scoring kernel; validated, bad values are ignored), MERCURY_FUSED (-1 never,
- *        0 automatic, 1 always: the one-kernel step), MERCURY_STEP_CTAS, MERCURY_STEP_DBG and
+ *        0 automatic, 1 always: the one-kernel step), MERCURY_STEP_PDL, MERCURY_STEP_CTAS, MERCURY_STEP_DBG,
+ *        MERCURY_K1_WARP_CTAS, MERCURY_K1_WIDE_CTAS, MERCURY_K1_POLY and
  *        MERCURY_SPINE_DEBUG (development), MERCURY_PEER_WAIT_MS (bound of one peer wait);
  *      * mercury_test_set_guess_bias / mercury_test_set_fused / mercury_debug_step_times are TEST HOOKS:
  *        process-global atomics read at launch time, there so the parity tests can force the rare paths

@@ -1987,10 +1987,15 @@ int fused_launch_typed(StepArgs& sa, int64_t want_ctas, cudaStream_t st) {
     const int grid = (int)min_i64(min_i64((int64_t)per_sm * sms, want_ctas), kStepMaxCtas);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kStepThreads); cfg.dynamicSmemBytes = kStepSmemBytes; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    // programmatic serialization behind the previous launch on the stream: the kernel's first instruction is the wait for
+    // that launch, so only its dispatch and per-CTA set-up overlap the predecessor's tail
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    static const int step_pdl = env_knob("MERCURY_STEP_PDL", 1, 0, 1);
+    cfg.attrs = attr; cfg.numAttrs = (step_pdl && pdl_enabled()) ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, sa);
     if (e != cudaSuccess) return cuda_fail(e, "fused_step_kernel launch");
     return MERCURY_OK;

@@ -1120,6 +1120,8 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     __shared__ unsigned long long dinfo_s;
     cg::grid_group grid = cg::this_grid();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_wait();                 // (no-ops unless launched with programmatic serialization: nothing of the previous launch on the
+    pdl_launch_dependents();    //  stream is touched before it has completed; the next launch may be dispatched into free slots)
     if (blockIdx.x == 0 && tid == 0) {
         const unsigned long long now = global_ns();
         a.ctrl->nflag = 0u; a.ctrl->packs_done = 0u;
