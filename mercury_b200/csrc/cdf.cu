@@ -1489,7 +1489,7 @@ struct DrawSmem {
 // shared memory.  `bits_known`: the exact running sum in front of `chunk` when the caller already has it.
 template <bool NAMED>
 __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, double uj, int chunk, uint32_t bits_known, bool have_bits,
-                                             DrawSmem& ds, float* cdf_s);
+                                             DrawSmem& ds, float* cdf_s, bool preloaded = false);
 
 template <bool PEER>
 __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
@@ -1545,7 +1545,7 @@ __global__ void __launch_bounds__(kDrawNT) draw_kernel(DrawArgs a) {
 
 template <bool NAMED>
 __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, double uj, int chunk, uint32_t bits_known, bool have_bits,
-                                             DrawSmem& ds, float* cdf_s) {
+                                             DrawSmem& ds, float* cdf_s, bool preloaded) {
     ResolveSmem& rs = ds.rs;
     int* wcnt = ds.wcnt;
     int64_t& chosen = ds.chosen;
@@ -1591,15 +1591,19 @@ __device__ __forceinline__ void draw_resolve(const DrawArgs& a, int64_t j, doubl
     const int64_t start = (int64_t)chunk * kChunk;
     const int len = (int)min((int64_t)kChunk, a.n - start);
     uint32_t pb[kDrawIPT];
-    load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
-    uint32_t bits = have_bits ? bits_known : a.start_bits[chunk];
     float* pv = cdf_s;                       // the chunk's probabilities, for the serial walks
-    Pair* subm = rs.tot;                     // [32] one map per sub-chunk
-    {
+    if (preloaded) {   // (block-uniform: the caller put this very chunk's probabilities into cdf_s ahead of time, same layout)
+        const int base = threadIdx.x * kDrawIPT;
+#pragma unroll
+        for (int k = 0; k < kDrawIPT; ++k) pb[k] = f2b(pv[base + k]);
+    } else {
+        load_chunk<kDrawNT, kDrawIPT>(a.src, start, len, pb);
         const int base = threadIdx.x * kDrawIPT;
 #pragma unroll
         for (int k = 0; k < kDrawIPT; ++k) pv[base + k] = b2f(pb[k]);
     }
+    uint32_t bits = have_bits ? bits_known : a.start_bits[chunk];
+    Pair* subm = rs.tot;                     // [32] one map per sub-chunk
     if (a.dbg && blockIdx.x == 0 && threadIdx.x == 64) a.dbg[0] = global_ns();
     int cur = 0;                             // the exact sum `bits` is the one before sub-chunk `cur`
     for (;;) {                               // (block-uniform control flow: decisions travel through rs)

@@ -1110,6 +1110,39 @@ __device__ __forceinline__ unsigned int tile_begin(unsigned int b, unsigned int 
     return (unsigned int)((unsigned long long)T * tile_weight_prefix(b, G) / tile_weight_prefix(G, G));
 }
 
+// The chunk a CTA's first draw will most likely land in, from the fp64 sums of the scores (the exact chain differs from them
+// by its rounding drift, ~1e-5 relative: the estimate names the right chunk unless u sits that close to a chunk boundary --
+// 99.4 % of the draws at cfg2), and that chunk's probabilities, fetched into cdf_s in draw_resolve's layout.  Runs while the
+// walk is under way and the CTA has nothing else to do; if the walker's word names the same chunk, the resolve starts from
+// shared memory, if not, nothing is lost.  Not inlined: its registers must not lengthen the live ranges of the phases
+// around it (the kernel sits at its register limit).
+__device__ __noinline__ int spec_chunk2(const double* __restrict__ approx, int nchunks, int64_t n, const float* __restrict__ scores,
+                                        double u0, float shift, float total, double* dred1, float* cdf_s) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // approx[c]: the fp64 sum of the scores in front of chunk c, left there by the worker that owns the chunk (phase B0).  No
+    // synchronisation with those writes is needed: a stale or missing value can only make the guess wrong, never the result.
+    // (An estimate: the boundary's running total is compared with u * total -- no division per boundary.)
+    const double thr = u0 * (double)total, sh_d = (double)shift * (double)kChunk;
+    int cnt = 0;
+    for (int c = tid + 1; c < nchunks; c += kStepNT)
+        if (__ldcg(approx + c) + (double)c * sh_d < thr) ++cnt;
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    wsync();   // (the reduction scratch is free: this CTA's summaries are out)
+    if (lane == 0) dred1[warp] = (double)cnt;
+    wsync();
+    int c_est = 0;
+#pragma unroll
+    for (int i = 0; i < kStepNT / 32; ++i) c_est += (int)dred1[i];
+    const int chat = min(c_est, nchunks - 1);
+    const int64_t start = (int64_t)chat * kChunk;
+    const int len = (int)min((int64_t)kChunk, n - start);
+    const int base = tid * kDrawIPT;
+#pragma unroll
+    for (int k = 0; k < kDrawIPT; ++k)   // p = (score + shift) / total, WeightSrc::get's arithmetic
+        cdf_s[base + k] = base + k < len ? __fdiv_rn(__fadd_rn(scores[start + base + k], shift), total) : 0.f;
+    return chat;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 template <typename T, int CT>
 __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a) {
@@ -1278,7 +1311,10 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         for (int i = 0; i < 8; ++i) cur[i] = raw[i];
         if (k + 1 < c_count) load_raw(c_first + k + 1);   // next chunk's scores travel while this one is reduced
         if (f64) sum_f64_chunk(a, c_first + k, cur, shift, total, s2, epoch, k == 0);
-        else summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2, epoch, k == 0);
+        else {
+            if (tid == 0 && !a.peers) a.approx[c_first + k] = pre;   // (for the draws' speculation, spec_chunk2: no ordering needed)
+            summarize2_chunk(a, c_first + k, cur, pre, own, shift, total, s2, epoch, k == 0);
+        }
         pre += own;
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[15] = global_ns();
@@ -1328,6 +1364,13 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     DrawArgs da = a.d;
     da.src.stats = dstats;
     da.total_ptr = &dtotal;
+    // Speculation while the walk is under way (this CTA has nothing else to do): spec_chunk2 below.
+    int chat = -1;
+    if (!f64 && !a.peers && !walker && (int64_t)blockIdx.x < a.d.b && gridDim.x > 1) {
+        if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 0) a.ctrl->evt[97] = global_ns();
+        chat = spec_chunk2(a.approx, nchunks, a.n, a.scores, a.d.u[blockIdx.x], shift, total, s2.dred[1], cdf_s);
+        if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 0) a.ctrl->evt[98] = global_ns();
+    }
     for (int64_t j = blockIdx.x; j < a.d.b; j += gridDim.x) {
         wsync();   // (the walker's shared memory, and the previous draw's, are free again)
         if (tid == 0) {
@@ -1352,7 +1395,12 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 64) a.ctrl->evt[106] = global_ns();
         if (!(v >> 63)) return;  // timed out (reported): leave the outputs alone rather than write garbage
         if (f64) draw_resolve_f64<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), drun0, dtot64, ds);
-        else draw_resolve<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), (uint32_t)v, true, ds, cdf_s);
+        else {
+            const int chunk = (int)((v >> 32) & 0x7fffffffu);
+            const bool hit = j == (int64_t)blockIdx.x && chunk == chat;
+            if ((a.dbg_flags & 4) && tid == 0 && j == (int64_t)blockIdx.x) atomicAdd(reinterpret_cast<unsigned long long*>(&a.ctrl->evt[99]), hit ? 0x100000001ull : 1ull);
+            draw_resolve<true>(da, j, uj, chunk, (uint32_t)v, true, ds, cdf_s, hit);
+        }
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[8] = global_ns();
 }

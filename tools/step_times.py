@@ -43,4 +43,6 @@ if int(os.environ.get("MERCURY_STEP_DBG", "0")) & 2:
 if int(os.environ.get("MERCURY_STEP_DBG", "0")) & 4:
     e = t[16 + 100:16 + 110]
     print("CTA 0, chunk 0 (us since start): p ready %.2f | thread maps %.2f | summary written %.2f | sub-chunk maps %.2f | pack written %.2f" % tuple((x - t[0]) / 1e3 for x in e[:5]))
+    print("CTA 0 speculation (us since start): %.2f -> %.2f" % ((t[16 + 97] - t[0]) / 1e3, (t[16 + 98] - t[0]) / 1e3))
+    print("speculative chunk preload of the draws: %d of %d hit (cumulative over the launches so far)" % (t[16 + 99] >> 32, t[16 + 99] & 0xffffffff))
     print("CTA 0 draw (us since start): word seen %.2f | chunk loaded %.2f | slot known %.2f | done %.2f" % tuple((x - t[0]) / 1e3 for x in (e[6], e[7], e[8], t[8])))
