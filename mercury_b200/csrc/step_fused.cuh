@@ -70,6 +70,11 @@ struct StepCtrl {
     double dapprox[kStepMaxDraws];            // fp64 mode, per draw: the running total of p in front of its chunk ...
     double dtotal[kStepMaxDraws];             // ... and the total (written before dinfo[j], a fence in between)
     unsigned int k1_end[kStepMaxCtas];        // developer aid (MERCURY_STEP_DBG & 4): ns from the start until each CTA had scored
+    // sharded pools: the whole pool's sum of scores, received from the peers by CTA 0 and handed to the other CTAs in two
+    // self-validating words (1 << 63 | half of the double's bits) -- 443 CTAs polling the peers' words themselves was a storm of
+    // system-scope loads on one cache line; and, per draw, 1 << 63 | bits of the uniform rescaled into this shard
+    unsigned long long gsum[2];
+    unsigned long long dinfo3[kStepMaxDraws];
 };
 constexpr unsigned long long kStepSpinNs = 2000000000ull;  // no wait may last this long: report instead of hanging the GPU
 
@@ -1070,22 +1075,22 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
                 if (lu < 0.0) lu = 0.0;
                 if (lu >= 1.0) lu = 0.99999999999999989;
             }
+            // (the draw's CTA takes the rescaled uniform from dinfo3: a word that is valid on its own, so no fence is needed)
             if (poisoned) {   // a peer exchange of this step timed out (see peer_poison)
                 a.local_u[j] = peer_poison();
-                __threadfence();
+                st_relaxed_u64(&a.ctrl->dinfo3[j], (1ull << 63) | (unsigned long long)__double_as_longlong(peer_poison()));
                 st_relaxed_u64(&a.ctrl->dinfo[j], 1ull << 63);
                 st_relaxed_u64(&a.ctrl->dinfo2[j], (1ull << 63) | f2b(total));
                 continue;
             }
             a.local_u[j] = lu;
             if (lu < 0.0) {
-                __threadfence();
                 st_relaxed_u64(&a.ctrl->dinfo[j], (1ull << 63) | (1ull << 62));
                 st_relaxed_u64(&a.ctrl->dinfo2[j], (1ull << 63) | f2b(total));
                 continue;
             }
             uj = lu;
-            __threadfence();   // (the draw's CTA reads local_u[j] behind its word)
+            st_relaxed_u64(&a.ctrl->dinfo3[j], (1ull << 63) | (unsigned long long)__double_as_longlong(lu));   // (lu >= 0: bit 63 is free)
         }
         int lo = 0, hi = nchunks - 1;          // answer in [lo, hi]
         while (lo < hi) {
@@ -1150,7 +1155,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     __shared__ Sum2Smem s2;
     __shared__ DrawSmem ds;
     __shared__ WalkStatic wst;
-    __shared__ unsigned long long dinfo_s;
+    __shared__ unsigned long long dinfo_s, dinfo3_s;
     cg::grid_group grid = cg::this_grid();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     pdl_wait();                 // (no-ops unless launched with programmatic serialization: nothing of the previous launch on the
@@ -1163,6 +1168,10 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         a.ctrl->times[0] = now;
     }
     if (blockIdx.x == 0) for (int64_t j = tid; j < a.d.b; j += kStepThreads) { a.ctrl->dinfo[j] = 0ull; a.ctrl->dinfo2[j] = 0ull; }
+    if (blockIdx.x == 0 && a.peers) {
+        for (int64_t j = tid; j < a.d.b; j += kStepThreads) a.ctrl->dinfo3[j] = 0ull;
+        if (tid < 2) a.ctrl->gsum[tid] = 0ull;
+    }
     // ---- A: scores + tile sums
     // (contiguous tiles per CTA, so that one partial sum per CTA gives the pool statistics and the running totals in front
     // of the chunks: 2 loads per thread behind the barrier instead of every CTA re-reading every tile's sum)
@@ -1256,27 +1265,46 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         for (int i = 0; i < kStepNT / 32; ++i) { tot += s2.dred[0][i]; pre += s2.dred[1][i]; }
     }
     double n_stat = (double)a.n;
-    if (a.peers) {   // sharded pool: the statistics are those of the WHOLE pool -- CTA 0 pushes this shard's sum, every CTA waits for all
+    if (a.peers) {   // sharded pool: the statistics are those of the WHOLE pool -- CTA 0 exchanges the sums, everybody else takes its word
         __shared__ double gs[kMaxShards];
-        PeerBox* const my_box = a.peers[a.rank];
-        const unsigned int sum_tag = my_box->seq_sum + 1u;   // (the walker advances seq_sum once the step's sums are in)
-        const int par = sum_tag & 1u;
-        if (tid < a.nshards) {
-            if (blockIdx.x == 0) {
+        if (blockIdx.x == 0) {
+            PeerBox* const my_box = a.peers[a.rank];
+            const unsigned int sum_tag = my_box->seq_sum + 1u;   // (the walker advances seq_sum once the step's sums are in)
+            const int par = sum_tag & 1u;
+            if (tid < a.nshards) {
                 const unsigned long long bits = (unsigned long long)__double_as_longlong(tot);
                 peer_store(&a.peers[tid]->sum_hi[par][a.rank], (bits >> 32 << 32) | sum_tag);
                 peer_store(&a.peers[tid]->sum_lo[par][a.rank], (bits << 32) | sum_tag);
+                unsigned long long hi, lo;
+                const bool ok = peer_wait(&my_box->sum_hi[par][tid], sum_tag, hi, my_box) &
+                                peer_wait(&my_box->sum_lo[par][tid], sum_tag, lo, my_box);
+                if (!ok) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
+                gs[tid] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
+                a.sums_all[tid] = gs[tid];
             }
-            unsigned long long hi, lo;
-            const bool ok = peer_wait(&my_box->sum_hi[par][tid], sum_tag, hi, my_box) &
-                            peer_wait(&my_box->sum_lo[par][tid], sum_tag, lo, my_box);
-            if (!ok) atomicOr(a.status, MERCURY_ST_PEER_TIMEOUT);
-            gs[tid] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
-            if (blockIdx.x == 0) a.sums_all[tid] = gs[tid];
+            wsync();
+            tot = 0.0;
+            for (int i = 0; i < a.nshards; ++i) tot += gs[i];   // (same order on every rank)
+            if (tid == 0) {
+                const unsigned long long bits = (unsigned long long)__double_as_longlong(tot);
+                st_relaxed_u64(&a.ctrl->gsum[0], (1ull << 63) | (bits >> 32));
+                st_relaxed_u64(&a.ctrl->gsum[1], (1ull << 63) | (bits & 0xffffffffull));
+            }
+        } else {
+            if (tid == 0) {
+                unsigned long long g0, g1;
+                const unsigned long long t0 = global_ns();
+                for (unsigned int it = 0;; ++it) {
+                    g0 = ld_relaxed_u64(&a.ctrl->gsum[0]);
+                    g1 = ld_relaxed_u64(&a.ctrl->gsum[1]);
+                    if ((g0 & g1) >> 63) break;
+                    if ((it & 63u) == 63u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); break; }
+                }
+                gs[0] = __longlong_as_double((long long)(((g0 & 0xffffffffull) << 32) | (g1 & 0xffffffffull)));
+            }
+            wsync();
+            tot = gs[0];
         }
-        wsync();
-        tot = 0.0;
-        for (int i = 0; i < a.nshards; ++i) tot += gs[i];   // (same order on every rank and in every CTA)
         n_stat = (double)a.n_global;
     }
     const float mean = (float)(tot / n_stat);
@@ -1379,10 +1407,13 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
             for (unsigned int it = 0;; ++it) {
                 v = ld_relaxed_u64(&a.ctrl->dinfo[j]);
                 w = ld_relaxed_u64(&a.ctrl->dinfo2[j]);
-                if ((v & w) >> 63) break;
+                if ((v & w) >> 63) {
+                    if (!a.peers || ((v >> 62) & 1ull)) break;             // (not a sharded pool, or another rank's draw)
+                    const unsigned long long x = ld_relaxed_u64(&a.ctrl->dinfo3[j]);
+                    if (x >> 63) { dinfo3_s = x & ~(1ull << 63); break; }
+                }
                 if ((it & 63u) == 63u && global_ns() - t0 > kStepSpinNs) { atomicOr(a.status, MERCURY_ST_INTERNAL); v = 0ull; break; }
             }
-            if (a.peers) __threadfence();
             dinfo_s = v;
             dtotal = b2f((uint32_t)w);
             if (f64 && (v >> 63)) { __threadfence(); drun0 = __ldcg(&a.ctrl->dapprox[j]); dtot64 = __ldcg(&a.ctrl->dtotal[j]); }
@@ -1391,7 +1422,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         double uj = a.d.u[j];
         wsync();
         const unsigned long long v = dinfo_s;
-        if (a.peers && (v >> 63)) uj = ((v >> 62) & 1ull) ? -1.0 : __ldcg(&a.local_u[j]);   // (written in front of the word, fenced)
+        if (a.peers && (v >> 63)) uj = ((v >> 62) & 1ull) ? -1.0 : __longlong_as_double((long long)dinfo3_s);
         if ((a.dbg_flags & 4) && blockIdx.x == 0 && tid == 64) a.ctrl->evt[106] = global_ns();
         if (!(v >> 63)) return;  // timed out (reported): leave the outputs alone rather than write garbage
         if (f64) draw_resolve_f64<true>(da, j, uj, (int)((v >> 32) & 0x7fffffffu), drun0, dtot64, ds);
