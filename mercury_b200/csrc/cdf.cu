@@ -1780,7 +1780,10 @@ inline CdfWs carve(void* ws, int64_t n, bool direct_subs = false, int compact_sl
     const size_t nchunks = (size_t)((n + kChunk - 1) / kChunk);
     const size_t nsubs = direct_subs && nchunks <= (size_t)kFusedMaxChunks ? (nchunks > (size_t)kSubSlots ? nchunks : (size_t)kSubSlots)
                                                                           : (size_t)compact_slots;
-    const size_t nsums = direct_subs ? (size_t)(n / 128 + 2) : nchunks;
+    // whole-step layout: one fp64 sum per K1 tile; the smallest tile is 64 rows (small_tile_rows: rows of 185..256 bytes).
+    // (Until round 2 this said n / 128 -- right when the smallest tile had 128 rows; with 64-row tiles the sums of a pool of
+    // wide rows overran into the approx / summaries regions, found by tools/fuzz_step.py as a spurious "negative" status.)
+    const size_t nsums = direct_subs ? (size_t)(n / 64 + 2) : nchunks;
     unsigned char* p = static_cast<unsigned char*>(ws);
     CdfWs w;
     size_t off = 0;

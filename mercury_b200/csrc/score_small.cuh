@@ -214,6 +214,7 @@ __device__ __forceinline__ void score_small_body(unsigned char* smem, const T* _
 
 // tile geometry shared by both users
 __host__ __device__ inline int small_tile_rows(int64_t row_bytes) { return row_bytes <= 88 ? 256 : row_bytes <= 184 ? 128 : 64; }
+constexpr int kSmallMinTileRows = 64;   // (the whole-step workspace holds one sum per tile: cdf.cu carve() sizes it by this)
 __host__ __device__ inline size_t small_smem_bytes(int stages, int tile_rows, int64_t row_bytes) {
     const size_t logit_slot = ((size_t)tile_rows * row_bytes + 127) & ~(size_t)127;
     return kSmallHeader + (size_t)stages * (logit_slot + (size_t)tile_rows * 8);

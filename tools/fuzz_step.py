@@ -1,0 +1,60 @@
+"""Randomised check of the one-kernel step (and the chain) against the serial fp32 chain on the device's own probabilities:
+random pool sizes, class counts, draw counts, score distributions (heavy tails, exact ties, zeros, constant pools), EMA on/off,
+repeated launches on one workspace.  python tools/fuzz_step.py [iterations] [seed]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from mercury_b200 import ops  # noqa: E402
+from oracle import mercury_oracle as orc  # noqa: E402
+
+dev = torch.device("cuda", 0)
+iters = int(sys.argv[1]) if len(sys.argv) > 1 else 200
+rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 0)
+bad = 0
+for it in range(iters):
+    n = int(rng.choice([rng.integers(1, 5000), rng.integers(5000, 200_000), rng.integers(200_000, 1_570_000)]))
+    c = int(rng.choice([2, 3, 10, 10, 10, 17, 32, 64]))
+    b = int(rng.choice([1, 7, 128, 128, 256, 1000]))
+    dt = torch.float32 if rng.random() < 0.7 or c % 8 else torch.bfloat16
+    kind = int(rng.integers(0, 5))
+    g = torch.Generator(device=dev).manual_seed(int(rng.integers(1 << 30)))
+    x = torch.randn(n, c, generator=g, device=dev) * float(rng.choice([0.5, 2.0, 6.0]))
+    if kind == 1:      # exact ties: few distinct rows
+        x = x[torch.randint(0, 4, (n,), generator=g, device=dev)]
+    elif kind == 2:    # constant pool
+        x = x[:1].expand(n, c).contiguous()
+    elif kind == 3:    # many (near) zero losses
+        y0 = torch.randint(0, c, (n,), generator=g, device=dev)
+        x[torch.arange(n, device=dev), y0] += 40.0
+    x = x.to(dt)
+    y = torch.randint(0, c, (n,), generator=g, device=dev) if kind != 3 else y0
+    if kind == 3:      # ... but not all of them
+        flip = torch.rand(n, generator=g, device=dev) < 0.1
+        y = torch.where(flip, (y + 1) % c, y)
+    u = torch.rand(b, dtype=torch.float64, generator=torch.Generator().manual_seed(int(rng.integers(1 << 30)))).to(dev)
+    if b > 2:
+        u[0], u[1] = 0.0, 1.0 - 2.0 ** -53
+    for mode in (1, 0):
+        ops.set_fused(mode)
+        ema = torch.full((1,), float(rng.random() * 3), device=dev)
+        first = bool(rng.random() < 0.5)
+        for rep in range(2):
+            r = ops.update_samples(x, y, u, ema, first and rep == 0)
+            st = int(r.status.item())
+            p = ops.normalize(r.scores, r.stats).cpu().numpy()
+            want = orc.draw_with_replacement(p, u.cpu().numpy()) if st == 0 else None
+            got = r.idx.cpu().numpy()
+            ok = st != 0 or np.array_equal(got, want)
+            if not ok or (st & ~8):
+                bad += 1
+                nb = int((got != want).sum()) if want is not None else -1
+                print(f"MISMATCH it={it} mode={mode} rep={rep} n={n} c={c} b={b} dt={dt} kind={kind} status={st} differing={nb}", flush=True)
+    if it % 20 == 19:
+        print(f"{it + 1} iterations, {bad} bad", flush=True)
+ops.set_fused(-1)
+print("done:", iters, "iterations,", bad, "bad")
+sys.exit(1 if bad else 0)
