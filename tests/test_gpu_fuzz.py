@@ -22,6 +22,12 @@ def test_fuzz_both_step_paths_against_the_serial_chain():
     assert "150 iterations, 0 bad" in r.stdout
 
 
+def test_fuzz_standalone_operators_against_the_oracle():
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_ops.py"), "60", "2"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "done: 60 iterations, 0 bad" in r.stdout
+
+
 @pytest.mark.parametrize("fused", [0, 1])
 @pytest.mark.parametrize("n,c", [(832_582, 64), (645_335, 64), (300_000, 48)])
 def test_wide_small_rows_large_pool(fused, n, c):

@@ -53,6 +53,27 @@ for it in range(iters):
                 bad += 1
                 nb = int((got != want).sum()) if want is not None else -1
                 print(f"MISMATCH it={it} mode={mode} rep={rep} n={n} c={c} b={b} dt={dt} kind={kind} status={st} differing={nb}", flush=True)
+    if it % 4 == 0 and n >= 10:   # growing pools (pytorch_collab.py:95-112: one EMA update per presample batch) and scores handed in
+        ops.set_fused(-1)
+        nb = sorted(set(int(v) for v in rng.integers(1, n, size=int(rng.integers(1, 9)))) | {n})
+        e0 = float(rng.random() * 3)
+        ema = torch.full((1,), e0, device=dev)
+        first = bool(rng.random() < 0.5)
+        r = ops.update_samples(x, y, u, ema, first, bounds=nb)
+        sc = r.scores.cpu()
+        o = orc.EMAverage()
+        o.first_update, o.value = first, torch.tensor(e0)
+        for v in nb:
+            mean, wsum, _ = orc.pool_stats(sc[:v], o, 0.5)
+        st = r.stats.cpu().numpy()
+        p = ops.normalize(r.scores, r.stats).cpu().numpy()
+        ok = int(r.status.item()) == 0 and np.allclose(st[1], float(o.value), rtol=2e-6) and np.allclose(st[0], float(mean), rtol=2e-6) \
+            and np.allclose(float(ema), float(o.value), rtol=2e-6) and np.array_equal(r.idx.cpu().numpy(), orc.draw_with_replacement(p, u.cpu().numpy()))
+        r2 = ops.update_samples(None, y, u, torch.full((1,), e0, device=dev), first, scores_in=r.scores, bounds=nb)
+        ok = ok and torch.equal(r2.idx, r.idx) and torch.equal(r2.nprob, r.nprob)
+        if not ok:
+            bad += 1
+            print(f"MISMATCH (growing pools) it={it} n={n} c={c} b={b} bounds={nb} status={int(r.status.item())} ema={st[1]} want={float(o.value)}", flush=True)
     if it % 20 == 19:
         print(f"{it + 1} iterations, {bad} bad", flush=True)
 ops.set_fused(-1)
