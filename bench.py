@@ -290,6 +290,46 @@ EXCHANGE_NOTE = {
 }
 
 
+def bind_host_memory_near(dev_index):
+    """Best effort, for the end-to-end leg at N > 1: prefer host memory (and cores) on the NUMA node the GPU hangs off, so that
+    the pinned buffers of eight ranks do not all sit behind one socket's memory controller and the inter-socket link.  Returns
+    a short description of what was done (goes into the JSON line)."""
+    try:
+        pr = torch.cuda.get_device_properties(dev_index)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return f"gpu {bdf}: no NUMA node reported"
+        allowed = open("/proc/self/status").read().split("Mems_allowed_list:")[1].split()[0]
+        nodes = set()
+        for part in allowed.split(","):
+            lo, _, hi = part.partition("-")
+            nodes.update(range(int(lo), int(hi or lo) + 1))
+        if node not in nodes:
+            return f"gpu {bdf} on node {node}: not in this process's allowed memory nodes ({allowed})"
+        import ctypes
+
+        libc = ctypes.CDLL(None, use_errno=True)
+        mask = (ctypes.c_ulong * 16)()
+        mask[node // 64] = 1 << (node % 64)
+        rc = libc.syscall(238, 1, ctypes.byref(mask), 16 * 64 + 1)          # set_mempolicy(MPOL_PREFERRED, node)  (x86_64)
+        what = f"gpu {bdf} on node {node}: memory policy preferred({node})" + ("" if rc == 0 else f" failed (errno {ctypes.get_errno()})")
+        try:
+            cpus = set()
+            for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+            cpus &= os.sched_getaffinity(0)
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+                what += f", {len(cpus)} cores of that node"
+        except Exception:  # noqa: BLE001
+            pass
+        return what
+    except Exception as e:  # noqa: BLE001
+        return f"unavailable ({type(e).__name__})"
+
+
 def timed_steps(step, npools, steps, warmup, use_graph, barrier, dist=None, dev=None, min_warm=3):
     """W warm-up steps, then EXACTLY `steps` timed steps between two barriers, CUDA events on the launching stream, max
     over ranks.  With graphs: one graph holding one step per pool, replayed steps // npools times, plus a graph with the
@@ -588,6 +628,7 @@ def parity_check(ops, sp, do_step, u, n, world, rank, dist, dev, mode):
 def main_multi(args, wl, dev, world, rank):
     import torch.distributed as dist
 
+    numa = bind_host_memory_near(dev.index or 0)
     dist.init_process_group("nccl", device_id=dev)
     from mercury_b200 import ops
     from mercury_b200.sharded import ShardedPool
@@ -746,7 +787,8 @@ def main_multi(args, wl, dev, world, rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t)
         e2e = {"value": n * world / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": world * (n * (c * s + 8) + b * 8),
-               "d2h_bytes_per_step": world * (b * (8 + 4 + 4) + 32), "ms_per_step": e2e_ms, "steps": e2e_steps, "rows_per_step": n * world}
+               "d2h_bytes_per_step": world * (b * (8 + 4 + 4) + 32), "ms_per_step": e2e_ms, "steps": e2e_steps, "rows_per_step": n * world,
+               "host_memory": numa}
     else:
         e2e = {"value": None, "unit": "candidates/s", "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
                "note": "pool above 8 GB per GPU: the host path of this shape is timed on one GPU (row slice); not repeated per rank"}
