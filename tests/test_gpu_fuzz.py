@@ -49,3 +49,19 @@ def test_wide_small_rows_large_pool(fused, n, c):
         ops.set_fused(-1)
     ref = orc.score(x[:4096].cpu(), y[:4096].cpu())
     np.testing.assert_allclose(r.scores[:4096].cpu().numpy(), ref.numpy(), rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_fuzz_sharded_step_on_two_gpus():
+    """tools/fuzz_sharded.py under torchrun: random shard sizes / class counts / draw counts, exchange over peer memory (kernel
+    chain and one-kernel step) and over NCCL, each against the two-level oracle, assembled batch compared across ranks."""
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(port), os.path.join(ROOT, "tools", "fuzz_sharded.py"), "12", "4"],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "done: 12 iterations, 0 bad" in r.stdout
