@@ -255,6 +255,8 @@ def sharded_draw_two_level(p_shards, u):
     double(cdf) >= u, the last shard catching the rest); second level: the uniform rescaled into
     the shard, u' = (u - lo) / (hi - lo), searched in the shard's own serial fp32 CDF.
     Returns global positions.  (Not index-identical to torch.multinomial on the flat vector.)
+    Parity of this function is UNPINNED by the reference: the reference has no global draw (each worker draws from its own
+    shard, pytorch_collab.py:282-287); the definition is this repository's, built from two pinned serial-fp32 draws.
     """
     totals = np.asarray([serial_chain_f32(p)[-1] for p in p_shards], dtype=np.float32)
     c = np.cumsum(totals, dtype=np.float32)
