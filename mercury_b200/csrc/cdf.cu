@@ -1987,6 +1987,15 @@ int fused_launch_typed(StepArgs& sa, int64_t want_ctas, cudaStream_t st) {
         }
         per_sm = it->second;
     }
+    {   // developer knob: tile weights of the scoring phase
+        static std::once_flag once;
+        std::call_once(once, [] {
+            const char* e = getenv("MERCURY_STEP_W");
+            unsigned int w[5];
+            if (e && sscanf(e, "%u,%u,%u,%u,%u", &w[0], &w[1], &w[2], &w[3], &w[4]) == 5 && w[0] && w[1] && w[2] && w[0] < 1000 && w[1] < 1000 && w[2] < 1000)
+                cudaMemcpyToSymbol(c_tile_w, w, sizeof(w));
+        });
+    }
     const int sms = device_sm_count();
     if (per_sm <= 0 || sms <= 0) return 1;
     static const int knob_per_sm = env_knob("MERCURY_STEP_CTAS", 3, 1, 3);   // developer knob: CTAs per SM

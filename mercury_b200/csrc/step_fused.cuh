@@ -1103,13 +1103,18 @@ __device__ __forceinline__ void walker_body(const StepArgs& a, unsigned char* sm
     if (tid == 0) a.ctrl->times[7] = global_ns();
 }
 
-// Tiles of scores per CTA: contiguous ranges, the CTAs of the first third of the grid a little longer ones than those of
-// the last third.  With three CTAs per SM the grid comes up in three waves; the last wave starts about a microsecond
-// later (measured), and an even split would leave everybody waiting for it at the grid barrier.  A static rule, so the
-// sums come out the same in every run.  first tile of CTA b = T * W(b) / W(G), W = cumulative weight.
+// Tiles of scores per CTA: contiguous ranges, weighted by thirds of the grid (with three CTAs per SM the grid comes up in
+// three waves).  A static rule, so the sums come out the same in every run.  first tile of CTA b = T * W(b) / W(G), W =
+// cumulative weight.
+// (the three weights and the two split points -- 0: thirds of the grid -- live in constant memory so that the developer knob
+// MERCURY_STEP_W="w1,w2,w3,g1,g2" can replace them without a rebuild)
+// Equal weights since the launch carries the programmatic-serialization attribute: in back-to-back steps the CTAs are
+// dispatched while the previous step drains and the waves no longer start a microsecond apart (53 : 50 : 47, tuned before
+// that, measures 46.9 us per step against 46.3 us for 50 : 50 : 50 on the same box; more skew is worse either way).
+__constant__ unsigned int c_tile_w[5] = {50u, 50u, 50u, 0u, 0u};
 __device__ __forceinline__ unsigned int tile_weight_prefix(unsigned int b, unsigned int G) {
-    const unsigned int g1 = G / 3u, g2 = 2u * G / 3u;   // weights 53 : 50 : 47
-    return 53u * min(b, g1) + 50u * (min(b, g2) - min(b, g1)) + 47u * (b - min(b, g2));
+    const unsigned int g1 = c_tile_w[3] ? min(c_tile_w[3], G) : G / 3u, g2 = c_tile_w[4] ? min(max(c_tile_w[4], g1), G) : 2u * G / 3u;
+    return c_tile_w[0] * min(b, g1) + c_tile_w[1] * (min(b, g2) - min(b, g1)) + c_tile_w[2] * (b - min(b, g2));
 }
 __device__ __forceinline__ unsigned int tile_begin(unsigned int b, unsigned int G, unsigned int T) {
     return (unsigned int)((unsigned long long)T * tile_weight_prefix(b, G) / tile_weight_prefix(G, G));
