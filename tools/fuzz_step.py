@@ -24,7 +24,7 @@ for it in range(iters):
     g = torch.Generator(device=dev).manual_seed(int(rng.integers(1 << 30)))
     x = torch.randn(n, c, generator=g, device=dev) * float(rng.choice([0.5, 2.0, 6.0]))
     if kind == 1:      # exact ties: few distinct rows
-        x = x[torch.randint(0, 4, (n,), generator=g, device=dev)]
+        x = x[torch.randint(0, min(4, n), (n,), generator=g, device=dev)]
     elif kind == 2:    # constant pool
         x = x[:1].expand(n, c).contiguous()
     elif kind == 3:    # many (near) zero losses
