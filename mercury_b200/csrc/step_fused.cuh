@@ -1177,6 +1177,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         for (int64_t j = tid; j < a.d.b; j += kStepThreads) a.ctrl->dinfo3[j] = 0ull;
         if (tid < 2) a.ctrl->gsum[tid] = 0ull;
     }
+    __shared__ unsigned int b0_s[2];
     // ---- A: scores + tile sums
     // (contiguous tiles per CTA, so that one partial sum per CTA gives the pool statistics and the running totals in front
     // of the chunks: 2 loads per thread behind the barrier instead of every CTA re-reading every tile's sum)
@@ -1186,6 +1187,25 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         score_small_body<T, CT, kStepStages, kStepNT, true, false>(smem, static_cast<const T*>(a.logits), a.labels, a.n, a.c, a.tile_rows,
                                                                    a.ignore_index, a.scores, a.status, a.part, tb, te, ts,
                                                                    &a.ctrl->cta_part[blockIdx.x]);
+    }
+    // Which CTA's tiles straddle the start of this CTA's first chunk, and where that CTA's tiles begin: two numbers the
+    // statistics behind the grid barrier need, found by a handful of 64-bit divisions -- done here by one thread of the
+    // producer warp, which has issued its last tile and would only wait, instead of by every thread on the critical path behind
+    // the barrier.  (Not in front of the scoring phase: the whole CTA would wait for it at the ring's initial barrier.)
+    if (tid == kStepNT) {
+        const bool wk = blockIdx.x != gridDim.x - 1 || gridDim.x == 1;
+        const int nw = gridDim.x > 1 ? (int)gridDim.x - 1 : 1;
+        const int q0 = a.nchunks / nw, big = nw - a.nchunks % nw;
+        const int cf = wk ? (int)blockIdx.x * q0 + max(0, (int)blockIdx.x - big) : 0;
+        const unsigned int G = gridDim.x, T = (unsigned int)a.ntiles;
+        const unsigned int t0 = min((unsigned int)(cf * (kChunk / a.tile_rows)), T);
+        unsigned int bstar = T > 0u ? t0 * G / T : 0u;   // (a first guess; the weights move it by a few CTAs at most)
+        bstar = min(bstar, G - 1u);
+        while (bstar + 1u < G && tile_begin(bstar + 1u, G, T) <= t0) ++bstar;
+        while (bstar > 0u && tile_begin(bstar, G, T) > t0) --bstar;
+        if (t0 >= T) bstar = G;   // (nothing in front of a chunk that starts behind the last tile -- cannot happen)
+        b0_s[0] = bstar;
+        b0_s[1] = bstar < G ? tile_begin(bstar, G, T) : T;
     }
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[1] = global_ns();
     if ((a.dbg_flags & 4) && tid == 0) {   // developer aid: when the LAST CTA had scored, and when each one had
@@ -1244,14 +1264,10 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
         // (32-bit arithmetic: at most 2^16 tiles and 2^10 CTAs; 64-bit divisions are long instruction sequences)
         const unsigned int G = gridDim.x, T = (unsigned int)npart;
         const unsigned int t0 = min((unsigned int)(c_first * parts_per_chunk), T);
-        unsigned int bstar = T > 0u ? t0 * G / T : 0u;   // (a first guess; the weights move it by a few CTAs at most)
-        bstar = min(bstar, G - 1u);
-        while (bstar + 1u < G && tile_begin(bstar + 1u, G, T) <= t0) ++bstar;
-        while (bstar > 0u && tile_begin(bstar, G, T) > t0) --bstar;
-        if (t0 >= T) bstar = G;   // (nothing in front of a chunk that starts behind the last tile -- cannot happen)
+        const unsigned int bstar = b0_s[0];   // (found in front of the scoring phase, see there)
         double straddle = 0.0;
         if (warp == kStepNT / 32 - 1 && c_count > 0 && bstar < G)
-            for (unsigned int i = tile_begin(bstar, G, T) + lane; i < t0; i += 32) straddle += __ldcg(a.part + i);
+            for (unsigned int i = b0_s[1] + lane; i < t0; i += 32) straddle += __ldcg(a.part + i);
         for (int b = tid; b < (int)G; b += kStepNT) {   // (fixed order: every CTA gets the same bits)
             const double v = __ldcg(&a.ctrl->cta_part[b]);
             tot += v;
