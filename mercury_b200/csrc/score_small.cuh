@@ -88,7 +88,8 @@ template <typename T, int CT, int STAGES, int CONSUMERS, bool PRODUCER_LAST, boo
 __device__ __forceinline__ void score_small_body(unsigned char* smem, const T* __restrict__ logits, const int64_t* __restrict__ labels,
                                                  int64_t n, int c_rt, int tile_rows, int64_t ignore_index, float* __restrict__ scores,
                                                  int32_t* status, double* __restrict__ tile_sums, int64_t tile_begin, int64_t tile_end,
-                                                 int64_t tile_step, double* __restrict__ cta_sum_out) {
+                                                 int64_t tile_step, double* __restrict__ cta_sum_out,
+                                                 const unsigned int* range_smem = nullptr) {
     const int c = CT > 0 ? CT : c_rt;
     Ring<STAGES>* ring = reinterpret_cast<Ring<STAGES>*>(smem);
     const uint32_t logit_bytes = (uint32_t)tile_rows * c * sizeof(T);
@@ -98,6 +99,7 @@ __device__ __forceinline__ void score_small_body(unsigned char* smem, const T* _
     unsigned char* stage0 = smem + kSmallHeader;
     static_assert(sizeof(Ring<STAGES>) <= 128 && 128 + 2 * (CONSUMERS / 32) * 8 <= kSmallHeader, "header layout");
     ring_init(ring, CONSUMERS / 32);
+    if (range_smem) { tile_begin = range_smem[0]; tile_end = range_smem[1]; }   // (written by one thread in front of ring_init's barrier)
     if constexpr (PDL) {
         pdl_wait();                // (the previous step's draw kernel may still be reading the scores we overwrite)
         pdl_launch_dependents();

@@ -1182,11 +1182,12 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     // (contiguous tiles per CTA, so that one partial sum per CTA gives the pool statistics and the running totals in front
     // of the chunks: 2 loads per thread behind the barrier instead of every CTA re-reading every tile's sum)
     {
-        const unsigned int ntiles = (unsigned int)a.ntiles;   // (<= 2^16)
-        int64_t tb = tile_begin(blockIdx.x, gridDim.x, ntiles), te = tile_begin(blockIdx.x + 1u, gridDim.x, ntiles), ts = 1;
+        // (the CTA's tile range: two 64-bit divisions, by two threads instead of by everybody in front of the first load)
+        __shared__ unsigned int range_s[2];
+        if (tid < 2) range_s[tid] = tile_begin(blockIdx.x + (unsigned int)tid, gridDim.x, (unsigned int)a.ntiles);
         score_small_body<T, CT, kStepStages, kStepNT, true, false>(smem, static_cast<const T*>(a.logits), a.labels, a.n, a.c, a.tile_rows,
-                                                                   a.ignore_index, a.scores, a.status, a.part, tb, te, ts,
-                                                                   &a.ctrl->cta_part[blockIdx.x]);
+                                                                   a.ignore_index, a.scores, a.status, a.part, 0, 0, 1,
+                                                                   &a.ctrl->cta_part[blockIdx.x], range_s);
     }
     // Which CTA's tiles straddle the start of this CTA's first chunk, and where that CTA's tiles begin: two numbers the
     // statistics behind the grid barrier need, found by a handful of 64-bit divisions -- done here by one thread of the
