@@ -503,7 +503,7 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         const float ema_prev = *fs.ema_in;  // (early: its latency hides behind the loads below)
         PeerBox* const my_box = PEER ? fs.peers[fs.rank] : nullptr;
         const unsigned int sum_tag = PEER ? my_box->seq_sum + 1u : 0u;  // (the spine advances seq_sum once the step's sums are in)
-        const int first_part = (int)(start / fs.per), parts_per_chunk = kChunk / fs.per;
+        const int parts_per_chunk = kChunk / fs.per, first_part = (int)blockIdx.x * parts_per_chunk;   // (start / per without the 64-bit division)
         double tot = 0.0, pre = 0.0, own = 0.0;
         constexpr int kInFlight = 16;
         for (int i0 = threadIdx.x; i0 < fs.npart; i0 += kInFlight * kSumNT) {  // 16 loads in flight per thread
@@ -561,8 +561,9 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
             fs.stats[MERCURY_STAT_SHIFT] = shift; fs.stats[MERCURY_STAT_TOTAL] = total;
             fs.stats[4] = fs.stats[5] = fs.stats[6] = fs.stats[7] = 0.f;
         }
-        a_lo = (pre + (double)start * (double)shift) / (double)total;
-        a_hi = a_lo + (own + (double)len * (double)shift) / (double)total;
+        const double inv_total = 1.0 / (double)total;   // (one division: the approximate running totals only feed the guesses)
+        a_lo = (pre + (double)start * (double)shift) * inv_total;
+        a_hi = a_lo + (own + (double)len * (double)shift) * inv_total;
         {
             const int base = threadIdx.x * kSumIPT;
 #pragma unroll

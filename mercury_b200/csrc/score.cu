@@ -174,10 +174,11 @@ __global__ void __launch_bounds__(256) score_warp_kernel(const T* __restrict__ l
 template <typename T, int CT, int STAGES, int CONSUMERS>
 __global__ void __launch_bounds__(CONSUMERS + kProducerThreads, 3)
 score_small_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels, int64_t n, int c_rt, int tile_rows,
-                   int64_t ignore_index, float* __restrict__ scores, int32_t* status, double* __restrict__ tile_sums) {
+                   int64_t ignore_index, float* __restrict__ scores, int32_t* status, double* __restrict__ tile_sums, int64_t ntiles) {
     extern __shared__ __align__(128) unsigned char smem[];
+    // (ntiles comes from the host: a 64-bit division by every thread in front of the first load costs the kernel a microsecond)
     score_small_body<T, CT, STAGES, CONSUMERS, false, true>(smem, logits, labels, n, c_rt, tile_rows, ignore_index, scores, status,
-                                                            tile_sums, blockIdx.x, (n + tile_rows - 1) / tile_rows, gridDim.x, nullptr);
+                                                            tile_sums, blockIdx.x, ntiles, gridDim.x, nullptr);
 }
 
 
@@ -331,7 +332,7 @@ int launch_score(const T* logits, const int64_t* labels, int64_t n, int64_t c, i
             int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), smem, "score_small smem attribute");
             if (rc) return rc;
             cudaError_t e = launch_chain(chained, kern, dim3(grid), dim3(CONSUMERS + kProducerThreads), smem, st, logits, labels, n, (int)c, tile_rows,
-                             ignore_index, scores, status, part_sums);
+                             ignore_index, scores, status, part_sums, ntiles);
             if (e != cudaSuccess) return cuda_fail(e, "score_small_kernel launch");
             if (per_out && part_sums) *per_out = tile_rows;
             return MERCURY_OK;
