@@ -1969,7 +1969,7 @@ std::map<std::pair<int, const void*>, int> g_fused_ctas;  // (device, kernel) ->
 
 template <typename T, int CT>
 int fused_launch_typed(StepArgs& sa, int64_t want_ctas, cudaStream_t st) {
-    auto kern = fused_step_kernel<T, CT>;
+    auto kern = sa.cdf_mode == MERCURY_CDF_F64 ? fused_step_kernel<T, CT, true> : fused_step_kernel<T, CT, false>;
     const void* fn = reinterpret_cast<const void*>(kern);
     int rc = ensure_dynamic_smem(fn, kStepSmemBytes, "fused_step_kernel smem attribute");
     if (rc) return rc;

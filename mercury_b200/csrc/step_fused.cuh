@@ -1154,7 +1154,11 @@ __device__ __noinline__ int spec_chunk2(const double* __restrict__ approx, int n
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-template <typename T, int CT>
+// F64 = true: the non-exact mode as a kernel of its own, without the exact mode's code (29.5 -> 27.7 us per step).  The
+// general kernel (F64 = false) still decides at run time and keeps both: taking the fp64 code OUT of it made the exact mode a
+// microsecond slower (45.8 against 44.8 us, same box) -- at 250 KB of code and the register limit, the compiler's choices
+// for the hot phases move with everything around them; measured, kept as it was.
+template <typename T, int CT, bool F64>
 __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ Sum2Smem s2;
@@ -1219,7 +1223,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     if (blockIdx.x == 0 && tid == 0) a.ctrl->times[2] = global_ns();
 
     const unsigned long long epoch = __ldcg(&a.ctrl->epoch);
-    const bool f64 = a.cdf_mode == MERCURY_CDF_F64;   // (no walk: fp64 chunk sums, their scan, one CTA per draw)
+    const bool f64 = F64 || a.cdf_mode == MERCURY_CDF_F64;   // (no walk: fp64 chunk sums, their scan, one CTA per draw)
     // ---- B: statistics (pytorch_collab.py:109-112), then: the last CTA is the walker and owns no chunks (with a single
     // CTA it is its own worker); the others each take a contiguous block of chunks
     const int nchunks = a.nchunks;
