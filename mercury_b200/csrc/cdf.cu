@@ -2002,6 +2002,10 @@ int fused_launch_typed(StepArgs& sa, int64_t want_ctas, cudaStream_t st) {
     static const int knob_per_sm = env_knob("MERCURY_STEP_CTAS", 3, 1, 3);   // developer knob: CTAs per SM
     if (knob_per_sm < per_sm) per_sm = knob_per_sm;
     const int grid = (int)min_i64(min_i64((int64_t)per_sm * sms, want_ctas), kStepMaxCtas);
+    {   // the split of the chunks over the worker CTAs (all but the last CTA), for the kernel's phase B
+        const int nworkers = grid > 1 ? grid - 1 : 1;
+        sa.chunks_q = sa.nchunks / nworkers; sa.chunks_r = sa.nchunks % nworkers; sa.parts_per_chunk = kChunk / sa.tile_rows;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kStepThreads); cfg.dynamicSmemBytes = kStepSmemBytes; cfg.stream = st;
     cudaLaunchAttribute attr[2];

@@ -80,7 +80,7 @@ constexpr unsigned long long kStepSpinNs = 2000000000ull;  // no wait may last t
 
 struct StepArgs {
     // K1
-    const void* logits; const int64_t* labels; int64_t n; int c; int tile_rows; int ntiles; int64_t ignore_index; float* scores;
+    const void* logits; const int64_t* labels; int64_t n; int c; int tile_rows; int ntiles; int chunks_q, chunks_r, parts_per_chunk; int64_t ignore_index; float* scores;
     double* part;                  // [ntiles] fp64 sums of the tiles' scores
     // statistics
     float* ema_state; int ema_first; double ema_alpha, smooth_alpha; float* stats;
@@ -1200,7 +1200,7 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     if (tid == kStepNT) {
         const bool wk = blockIdx.x != gridDim.x - 1 || gridDim.x == 1;
         const int nw = gridDim.x > 1 ? (int)gridDim.x - 1 : 1;
-        const int q0 = a.nchunks / nw, big = nw - a.nchunks % nw;
+        const int q0 = a.nchunks / nw, big = nw - a.nchunks % nw;   // (as in phase B; this thread has time for the divisions)
         const int cf = wk ? (int)blockIdx.x * q0 + max(0, (int)blockIdx.x - big) : 0;
         const unsigned int G = gridDim.x, T = (unsigned int)a.ntiles;
         const unsigned int t0 = min((unsigned int)(cf * (kChunk / a.tile_rows)), T);
@@ -1230,13 +1230,13 @@ __global__ void __launch_bounds__(kStepThreads, 3) fused_step_kernel(StepArgs a)
     const bool walker = blockIdx.x == gridDim.x - 1;
     const int nworkers = gridDim.x > 1 ? (int)gridDim.x - 1 : 1;
     const bool worker = !walker || gridDim.x == 1;
-    const int q = nchunks / nworkers, r = nchunks % nworkers;
+    const int q = a.chunks_q, r = a.chunks_r;   // (nchunks / nworkers and the remainder, from the host: no division behind the barrier)
     // (the r larger blocks at the END of the pool: the expensive chunks -- those in which the running sum changes binade,
     // crowded at the head of the pool -- then sit alone in their CTA)
     const int big0 = nworkers - r;
     const int c_first = worker ? (int)blockIdx.x * q + max(0, (int)blockIdx.x - big0) : 0;
     const int c_count = worker ? q + ((int)blockIdx.x >= big0 ? 1 : 0) : 0;
-    const int per = a.tile_rows, npart = a.ntiles, parts_per_chunk = kChunk / per;
+    const int per = a.tile_rows, npart = a.ntiles, parts_per_chunk = a.parts_per_chunk;
     float raw[8];
     auto load_raw = [&](int c) {
         const int64_t start = (int64_t)c * kChunk;
