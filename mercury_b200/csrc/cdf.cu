@@ -462,6 +462,10 @@ struct FusedStats {
     // CTA 0 pushes this shard's sum, every CTA waits for all G sums in its own box; gsums_out (fp64 [nshards]) is
     // filled by CTA 0 for the caller
     PeerBox* const* peers; int nshards, rank; double* gsums_out;
+    // ... where only CTA 0 waits for the peers: it hands the whole pool's sum to the other CTAs in two words of this GPU's
+    // memory, (half of the double's bits << 32 | the exchange's tag) -- every CTA polling the peers' words itself is a storm of
+    // system-scope loads on one cache line that grows with the number of shards
+    unsigned long long* gsum;
 };
 
 // PEER: sharded pool with the sums exchanged inside this kernel (a separate instantiation, so that the one-GPU kernel
@@ -526,25 +530,44 @@ __global__ void __launch_bounds__(kSumNT) summarize_kernel(WeightSrc src, int64_
         for (int i = 0; i < kSumNT / 32; ++i) { tot += dred[0][i]; pre += dred[1][i]; own += dred[2][i]; }
         // pytorch_collab.py:109-112 -- mean, EMA (util.py:207-213), shift = alpha*ema, total = sum(s + shift)
         double n_stat = (double)n;
-        if constexpr (PEER) {  // sharded pool, sums exchanged here: push (CTA 0), then every CTA waits for all G in its own box
+        if constexpr (PEER) {  // sharded pool, sums exchanged here by CTA 0; the other CTAs take the result from fs.gsum
             __shared__ double gs[kMaxShards];
             const int par = sum_tag & 1u, g = threadIdx.x;
-            if (g < fs.nshards) {
-                if (blockIdx.x == 0) {
+            if (blockIdx.x == 0) {
+                if (g < fs.nshards) {
                     const unsigned long long bits = (unsigned long long)__double_as_longlong(tot);
                     peer_store(&fs.peers[g]->sum_hi[par][fs.rank], (bits >> 32 << 32) | sum_tag);
                     peer_store(&fs.peers[g]->sum_lo[par][fs.rank], (bits << 32) | sum_tag);
+                    unsigned long long hi, lo;
+                    const bool ok = peer_wait(&my_box->sum_hi[par][g], sum_tag, hi, my_box) &
+                                    peer_wait(&my_box->sum_lo[par][g], sum_tag, lo, my_box);
+                    if (!ok) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
+                    gs[g] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
+                    fs.gsums_out[g] = gs[g];
                 }
-                unsigned long long hi, lo;
-                const bool ok = peer_wait(&my_box->sum_hi[par][g], sum_tag, hi, my_box) &
-                                peer_wait(&my_box->sum_lo[par][g], sum_tag, lo, my_box);
-                if (!ok) atomicOr(status, MERCURY_ST_PEER_TIMEOUT);
-                gs[g] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
-                if (blockIdx.x == 0) fs.gsums_out[g] = gs[g];
+                __syncthreads();
+                tot = 0.0;
+                for (int i = 0; i < fs.nshards; ++i) tot += gs[i];   // (same order on every rank)
+                if (threadIdx.x == 0) {
+                    const unsigned long long bits = (unsigned long long)__double_as_longlong(tot);
+                    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(fs.gsum), "l"((bits >> 32 << 32) | sum_tag) : "memory");
+                    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(fs.gsum + 1), "l"((bits << 32) | sum_tag) : "memory");
+                }
+            } else {
+                if (threadIdx.x == 0) {   // (bounded like a peer wait, twice as long: CTA 0 may itself be waiting for a peer)
+                    unsigned long long hi = 0ull, lo = 0ull;
+                    const unsigned long long bound = 2ull * (my_box->wait_ns ? my_box->wait_ns : kPeerWaitNs), t0 = global_ns();
+                    for (unsigned int it = 0;; ++it) {
+                        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(hi) : "l"(fs.gsum) : "memory");
+                        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(lo) : "l"(fs.gsum + 1) : "memory");
+                        if ((unsigned int)hi == sum_tag && (unsigned int)lo == sum_tag) break;
+                        if ((it & 63u) == 63u && global_ns() - t0 > bound) { atomicOr(status, MERCURY_ST_PEER_TIMEOUT); break; }
+                    }
+                    gs[0] = __longlong_as_double((long long)((hi >> 32 << 32) | (lo >> 32)));
+                }
+                __syncthreads();
+                tot = gs[0];
             }
-            __syncthreads();
-            tot = 0.0;
-            for (int i = 0; i < fs.nshards; ++i) tot += gs[i];   // (same order on every rank and in every CTA)
             n_stat = (double)fs.n_global;
         } else if (fs.gsums) {  // whole-pool statistics from the shard sums (same order on every rank)
             tot = 0.0;
@@ -2032,7 +2055,8 @@ int fused_step_launch(const mercury_update_args& a, void* ws, cudaStream_t st) {
     // sharded pools: the kernel chain is the faster one (measured at 2 and 8 GPUs: 54 us against 64 us per step -- two grid-wide
     // waits for the peers inside one resident grid cost more than inside two short kernels); the one-kernel sharded step stays
     // reachable through the test hook, which keeps it under test
-    if (a.peer_boxes && fused_mode != 1) return 1;
+    static const int peer_knob = env_knob("MERCURY_FUSED_PEER", 0, 0, 1);   // developer knob: the one-kernel step for sharded pools too
+    if (a.peer_boxes && fused_mode != 1 && !peer_knob) return 1;
 
     if (a.b > kStepMaxDraws || a.row_stride != a.c) return 1;
     const int64_t elt = a.dtype == MERCURY_F32 ? 4 : 2, row_bytes = a.c * elt;
@@ -2350,6 +2374,7 @@ int sharded_step_launch(const mercury_update_args& a, const float* scores, const
     fs.stats = a.stats;
     fs.n_global = a.n_global;
     fs.peers = peers; fs.nshards = a.n_shards; fs.rank = a.shard_rank; fs.gsums_out = a.sums_all;
+    fs.gsum = w.ctrl->gsum_chain;
     int rc = run_exact_boundaries(src, a.n, w, a.status, 1, st, &fs, a.ema_state);
     if (rc) return rc;
     if (a.b > 0) {

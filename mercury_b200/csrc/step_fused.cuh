@@ -74,6 +74,7 @@ struct StepCtrl {
     // self-validating words (1 << 63 | half of the double's bits) -- 443 CTAs polling the peers' words themselves was a storm of
     // system-scope loads on one cache line; and, per draw, 1 << 63 | bits of the uniform rescaled into this shard
     unsigned long long gsum[2];
+    unsigned long long gsum_chain[2];   // the same hand-over in the kernel chain's summarize_kernel (half of the bits << 32 | exchange tag)
     unsigned long long dinfo3[kStepMaxDraws];
 };
 constexpr unsigned long long kStepSpinNs = 2000000000ull;  // no wait may last this long: report instead of hanging the GPU
