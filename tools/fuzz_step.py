@@ -49,7 +49,9 @@ for it in range(iters):
             want = orc.draw_with_replacement(p, u.cpu().numpy()) if st == 0 else None
             got = r.idx.cpu().numpy()
             ok = st != 0 or np.array_equal(got, want)
-            if not ok or (st & ~8):
+            # (a pool whose losses and EMA are all zero has total 0: torch.multinomial raises there too; 8 = zero sum, and the
+            # 0/0 probabilities then also read as "not >= 0")
+            if not ok or (st and not (st & 8)):
                 bad += 1
                 nb = int((got != want).sum()) if want is not None else -1
                 print(f"MISMATCH it={it} mode={mode} rep={rep} n={n} c={c} b={b} dt={dt} kind={kind} status={st} differing={nb}", flush=True)
